@@ -1,0 +1,119 @@
+/*
+ * vst_b200.h — C ABI of libvst_b200.so: the sm_100a hot path of tanmud/video_style_transfer
+ * (AnimateDiff-XL motion module + UnZipLoRA content/style attention).
+ *
+ * Conventions:
+ *   - every pointer is a raw DEVICE pointer unless the name ends in _host;
+ *   - `stream` is a cudaStream_t passed as void*; no entry point synchronises it or allocates;
+ *   - return 0 on success, negative on error (VST_E_*); vst_last_error() gives the text;
+ *   - dtype tags: VST_F32 / VST_BF16.  bf16 storage, fp32 accumulation everywhere.
+ * Each entry point names the reference interface (file:line under the reference tree) whose
+ * arithmetic it replaces.
+ */
+#ifndef VST_B200_H
+#define VST_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VST_F32 0
+#define VST_BF16 1
+
+#define VST_OK 0
+#define VST_E_BADARG (-1)
+#define VST_E_UNSUPPORTED (-2)
+#define VST_E_CUDA (-3)
+
+/* library version (major*10000 + minor*100 + patch) and last error text (thread-local). */
+int vst_version(void);
+const char* vst_last_error(void);
+/* SM count / compute capability of the current device. */
+int vst_device_info(int* sm_count, int* cc_major, int* cc_minor);
+
+/* ---- a9: layout rearrange (+ sinusoidal position add) -------------------------------------
+ * animatediff/temporal_transformer.py:129-133: (B,C,F,H,W) -> (B*H*W, F, C), then x + pe[:, :F].
+ * x is addressed as x[b*sB + c*sC + f*sF + hw] (element strides), so both the contiguous
+ * (B,C,F,H,W) tensor of config 1 and the live (B*F,C,H,W) layout are accepted.
+ * pe: optional fp32 table, row stride C, at least F rows (PositionalEncoding.pe, :11-18).
+ * The add is done in fp32 and rounded once to out_dtype (bit-exact vs torch). */
+int vst_rearrange_fwd(const void* x, void* y, const float* pe, int B, int C, int F, int HW,
+                      int64_t sB, int64_t sC, int64_t sF, int in_dtype, int out_dtype,
+                      void* stream);
+/* animatediff/temporal_transformer.py:143-144: (B*H*W, F, C) -> out[b*sB + c*sC + f*sF + hw]
+ * (+ residual at the same addressing: the motion module's closing `+ residual`). */
+int vst_rearrange_bwd(const void* y, void* out, const void* residual, int B, int C, int F,
+                      int HW, int64_t sB, int64_t sC, int64_t sF, int in_dtype, int out_dtype,
+                      void* stream);
+
+/* ---- a10: GroupNorm over the (B,C,F,H,W) view, fused with the forward rearrange ------------
+ * diffusers TransformerTemporalModel.norm = GroupNorm(32, C, eps 1e-6) (un-vendored); in-tree
+ * analogue call animatediff/attention_processor.py:50-51.
+ * stats: per (b, group) partial (count, mean, M2) triples -> workspace `partials`
+ *        (fp32, vst_groupnorm5d_partials(...) triples per (b,group));
+ * finalize: Chan-combines the partials into mean / rstd ([B*groups] fp32 each);
+ * apply_rearrange: y[(b,hw), f, c] = (x - mean) * rstd * gamma[c] + beta[c]. */
+int vst_groupnorm5d_partials(int C, int F, int HW, int groups);
+int vst_groupnorm5d_stats(const void* x, float* partials, int B, int C, int F, int HW,
+                          int64_t sB, int64_t sC, int64_t sF, int groups, int dtype,
+                          void* stream);
+int vst_groupnorm5d_finalize(const float* partials, int nparts, int B, int groups, float eps,
+                             float* mean, float* rstd, void* stream);
+int vst_groupnorm5d_apply_rearrange(const void* x, void* y, const float* mean,
+                                    const float* rstd, const void* gamma, const void* beta,
+                                    int B, int C, int F, int HW, int64_t sB, int64_t sC,
+                                    int64_t sF, int groups, int in_dtype, int out_dtype,
+                                    int param_dtype, void* stream);
+
+/* ---- K9: LayerNorm over the last dim, optional fused `+ pe[row % F]` -----------------------
+ * animatediff/temporal_transformer.py:44,52,69,74,111,140 (LN) and :27 (position add, which
+ * diffusers' BasicTransformerBlock applies right after norm1/norm2). */
+int vst_layernorm(const void* x, void* y, const void* gamma, const void* beta, const float* pe,
+                  int64_t rows, int C, int F, float eps, int in_dtype, int out_dtype,
+                  int param_dtype, void* stream);
+
+/* ---- a8: frame-axis temporal self-attention ------------------------------------------------
+ * animatediff/temporal_transformer.py:45-50,69-71 / diffusers motion attn1, attn2.
+ * q,k,v,o: (N, F, heads*d) bf16 with row strides ldq/ldk/ldv/ldo (elements), F <= 32,
+ * softmax(q k^T / sqrt(d)) v per (sequence, head). */
+int vst_temporal_attn_fwd(const void* q, const void* k, const void* v, void* o, int64_t N,
+                          int F, int heads, int d, int64_t ldq, int64_t ldk, int64_t ldv,
+                          int64_t ldo, float scale, void* stream);
+
+/* ---- a3/a4/a5/a7: fused LoRA GEMM ----------------------------------------------------------
+ * D[M,N] = (A1[M,K1] * B1[N,K1]^T + A2[M,K2] * B2[N,K2]^T + bias[N] + residual[M,N]) * out_scale
+ * bf16 operands, fp32 accumulation in TMEM (tcgen05), bf16 or fp32 output.
+ * It is the single GEMM behind
+ *   unziplora_unet/lora_linear.py:74-81 + unziplora_linear_layer.py:298-346 (A1=x, B1=W,
+ *   A2=[u_c|u_s], B2=scale*[m_c.B_c | m_s.B_s]), lora_unzip.py:66-75 (u from other streams),
+ *   animatediff/temporal_lora.py:29-32 (A2=u, B2=(alpha/r) B), and the u = x A^T pre-pass
+ *   (K2 = 0).  K1, K2 multiples of 8; N multiple of 8; lda/ldb/ldd in elements.
+ * bias is bias_dtype (VST_F32 / VST_BF16); residual has the output dtype.
+ * residual/out_scale fuse attention_processor.py:91-94. */
+int vst_lora_gemm(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1,
+                  const void* A2, int64_t lda2, const void* B2, int64_t ldb2, int K2,
+                  const void* bias, int bias_dtype, const void* residual, int64_t ldr,
+                  float out_scale, void* D, int64_t ldd, int64_t M, int N, int out_dtype,
+                  void* stream);
+/* B2'[n, j] = scale * m[n] * mask[n] * B[n, j] for up to two branches packed side by side
+ * (columns [0,r) content, [r,2r) style); m/mask may be NULL (=1).  unziplora_linear_layer.py
+ * :313,:321 (merger), :236-237 (hard mask), lora_linear.py:81 (scale). */
+int vst_lora_pack_up(const void* Bc, const void* mc, const uint8_t* maskc, const void* Bs,
+                     const void* ms, const uint8_t* masks, float scale, void* out, int N, int r,
+                     int param_dtype, void* stream);
+
+/* ---- a2: spatial self / text cross attention (flash, tcgen05) -------------------------------
+ * animatediff/attention_processor.py:74-83 (head split, SDPA, head merge) in one kernel.
+ * q,o: (Bt, Sq, heads*64) bf16; k,v: (Bk, Sk, heads*64) bf16 where batch b reads k/v batch
+ * b / kv_group (kv_group = Bt/Bk implements the text repeat_interleave of :62-66 without
+ * materialising it).  lse (optional, fp32 (Bt,heads,Sq)) is saved for the backward. */
+int vst_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int Bt,
+                 int heads, int Sq, int Sk, int d, int64_t ldq, int64_t ldk, int64_t ldv,
+                 int64_t ldo, int kv_group, float scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VST_B200_H */

@@ -1,0 +1,286 @@
+"""Generate tests/golden/*.npz by running the REFERENCE's own modules (imported from
+/root/reference in the build container) on seeded inputs, and check the oracle restatement
+(oracle/hotpath.py, oracle/processor.py) against them while doing so.
+
+Run here only:  python -m oracle.make_golden
+The GPU box has no /root/reference; tests read only the committed .npz files.
+"""
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+REF = os.environ.get("VST_REFERENCE", "/root/reference")
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+
+
+def _np(d):
+    return {k: (v.detach().cpu().numpy() if isinstance(v, torch.Tensor) else np.asarray(v))
+            for k, v in d.items()}
+
+
+def _close(a, b, tol, what):
+    err = (a - b).abs().max().item() / max(b.abs().max().item(), 1e-30)
+    assert err <= tol, f"oracle != reference for {what}: rel err {err:.3e} > {tol}"
+    return err
+
+
+def main():
+    sys.path.insert(0, REF)
+    from animatediff.temporal_transformer import TemporalTransformer, PositionalEncoding
+    from animatediff.attention_processor import AnimateDiffAttnProcessor2_0
+    from animatediff.temporal_lora import TemporalLoRALinear
+    from unziplora_unet.unziplora_linear_layer import (UnZipLoRALinearLayer,
+                                                       UnZipLoRALinearLayerInfer)
+    from unziplora_unet.lora_linear import LoRACompatibleLinear
+    import unziplora_unet.lora_unzip as lora_unzip
+    from oracle import hotpath as hp
+    from oracle import processor as op
+
+    os.makedirs(OUT, exist_ok=True)
+    report = {}
+
+    # ---- a9: positional table + rearranges -------------------------------------------
+    g = {}
+    for c in (40, 64, 320):
+        pe = PositionalEncoding(c, 32).pe
+        assert torch.equal(pe, hp.positional_table(c, 32))
+        if c != 320:
+            g[f"pe_{c}"] = pe
+    torch.manual_seed(0)
+    x = torch.randn(2, 24, 8, 3, 5)
+    y_ref = x.permute(0, 3, 4, 2, 1).reshape(-1, 8, 24) + PositionalEncoding(24, 32).pe[:, :8]
+    assert torch.equal(y_ref, hp.rearrange_fwd(x, hp.positional_table(24)))
+    back_ref = y_ref.view(2, 3, 5, 8, 24).permute(0, 4, 3, 1, 2).contiguous()
+    assert torch.equal(back_ref, hp.rearrange_bwd(y_ref, 2, 3, 5))
+    g.update(rearr_x=x, rearr_y=y_ref, rearr_back=back_ref)
+    np.savez_compressed(os.path.join(OUT, "layout.npz"), **_np(g))
+
+    # ---- a11: TemporalTransformer (config-1 family) -----------------------------------
+    g = {}
+    for tag, (b, c, f, h, w, layers, heads) in {
+        "tiny": (2, 64, 8, 3, 4, 2, 8),
+        "d40": (1, 160, 16, 4, 4, 1, 4),
+    }.items():
+        torch.manual_seed(1)
+        m = TemporalTransformer(c, layers, heads).eval()
+        # default LN/bias init is trivial (1/0): randomise so the affine terms are exercised
+        with torch.no_grad():
+            for n_, p_ in m.named_parameters():
+                if "norm" in n_ or n_.endswith("bias"):
+                    p_.add_(0.1 * torch.randn_like(p_))
+        x = torch.randn(b, c, f, h, w)
+        with torch.no_grad():
+            y = m(x, num_frames=f)
+        sd = {k: v for k, v in m.state_dict().items()}
+        yo = hp.temporal_transformer(x, sd, layers, heads)
+        report[f"tt_{tag}"] = _close(yo, y, 2e-5, f"TemporalTransformer {tag}")
+        g[f"{tag}/x"] = x
+        g[f"{tag}/y"] = y
+        g[f"{tag}/meta"] = np.array([b, c, f, h, w, layers, heads])
+        for k, v in sd.items():
+            g[f"{tag}/sd/{k}"] = v
+    np.savez_compressed(os.path.join(OUT, "temporal_transformer.npz"), **_np(g))
+    # config 1 at full size: checked here, not stored (21 MB)
+    torch.manual_seed(0)
+    m = TemporalTransformer(320, 2, 8).eval()
+    x = torch.randn(1, 320, 16, 32, 32)
+    with torch.no_grad():
+        y = m(x, 16)
+    report["tt_config1"] = _close(hp.temporal_transformer(x, dict(m.state_dict()), 2, 8), y, 2e-5,
+                                  "TemporalTransformer config1")
+
+    # ---- a3/a4: UnZipLoRA layers -------------------------------------------------------
+    g = {}
+    fin, fout, r = 48, 40, 8
+    torch.manual_seed(2)
+    lay = UnZipLoRALinearLayerInfer(fin, fout, r, ["content", "style"])
+    with torch.no_grad():
+        lay.merge_content.uniform_(0, 1)
+        lay.merge_style.uniform_(0, 1)
+    W = {k: lay.lora_matrix_dic[k].weight.detach() for k in
+         ("content_down", "content_up", "style_down", "style_up")}
+    x = torch.randn(3, 7, fin)
+    x2 = torch.randn(3, 7, fin)
+    g.update({"infer/" + k: v for k, v in W.items()})
+    g.update({"infer/merge_content": lay.merge_content, "infer/merge_style": lay.merge_style,
+              "infer/x": x, "infer/x2": x2})
+    for ft in ("both", "content", "style"):
+        for mc in (False, True):
+            for ms in (False, True):
+                lay.set_forward(ft)
+                lay.set_layer_mask("content", mc)
+                lay.set_layer_mask("style", ms)
+                for two in (False, True):
+                    with torch.no_grad():
+                        y = lay(x, x2 if two else None)
+                    yo = hp.unziplora_delta(x, x2 if two else None, W["content_down"],
+                                            W["content_up"], W["style_down"], W["style_up"],
+                                            lay.merge_content.detach(), lay.merge_style.detach(),
+                                            ft, mc, ms, infer=True)
+                    _close(yo, y, 1e-6, f"infer {ft} {mc} {ms} {two}")
+                    g[f"infer/y_{ft}_{int(mc)}{int(ms)}_{int(two)}"] = y
+    # training layer: hard masks multiply; grads through A, B, mergers, x
+    torch.manual_seed(3)
+    tl = UnZipLoRALinearLayer(fin, fout, r, ["content", "style"], lora_matrix_num=2)
+    with torch.no_grad():
+        tl.merge_content.uniform_(0, 1)
+        tl.merge_style.uniform_(0, 1)
+    tl.mask_content = torch.rand(fout) > 0.5
+    tl.mask_style = torch.rand(fout) > 0.5
+    g.update({"train/" + k: tl.lora_matrix_dic[k].weight.detach().clone() for k in W})
+    g.update({"train/merge_content": tl.merge_content.detach().clone(),
+              "train/merge_style": tl.merge_style.detach().clone(),
+              "train/mask_content": tl.mask_content, "train/mask_style": tl.mask_style})
+    dy = torch.randn(3, 7, fout)
+    g["train/dy"] = dy
+    for ft in ("both", "content", "style"):
+        for masked in (False, True):
+            tl.set_forward(ft)
+            tl.set_layer_mask("content", masked)
+            tl.set_layer_mask("style", masked)
+            xa = x.clone().requires_grad_(True)
+            xb = x2.clone().requires_grad_(True)
+            tl.zero_grad()
+            y = tl(xa, xb)
+            y.backward(dy)
+            args = [tl.lora_matrix_dic[k].weight.detach().clone().requires_grad_(True) for k in
+                    ("content_down", "content_up", "style_down", "style_up")]
+            mco = tl.merge_content.detach().clone().requires_grad_(True)
+            mso = tl.merge_style.detach().clone().requires_grad_(True)
+            xo, xo2 = x.clone().requires_grad_(True), x2.clone().requires_grad_(True)
+            yo = hp.unziplora_delta(xo, xo2, *args, mco, mso, ft, masked, masked, infer=False,
+                                    mask_c=tl.mask_content, mask_s=tl.mask_style)
+            _close(yo, y, 1e-6, f"train {ft} {masked}")
+            yo.backward(dy)
+            tag = f"train/{ft}_{int(masked)}"
+            g[tag + "/y"] = y
+            pairs = {"dx": (xa.grad, xo.grad), "dx2": (xb.grad, xo2.grad),
+                     "dmc": (tl.merge_content.grad, mco.grad),
+                     "dms": (tl.merge_style.grad, mso.grad)}
+            for k, a in zip(("content_down", "content_up", "style_down", "style_up"), args):
+                pairs["d_" + k] = (tl.lora_matrix_dic[k].weight.grad, a.grad)
+            for k, (gr, go) in pairs.items():
+                if gr is None:
+                    assert go is None or go.abs().max() == 0, k
+                    continue
+                _close(go, gr, 1e-5, tag + k)
+                g[f"{tag}/{k}"] = gr.clone()
+    np.savez_compressed(os.path.join(OUT, "unziplora.npz"), **_np(g))
+
+    # ---- a3/a5: LoRACompatibleLinear (both variants) + a7 TemporalLoRALinear ----------
+    g = {}
+    torch.manual_seed(4)
+    lin = LoRACompatibleLinear(fin, fout)
+    lay.set_forward("both"); lay.set_layer_mask("content", False); lay.set_layer_mask("style", False)
+    lin.set_lora_layer(lay)
+    with torch.no_grad():
+        y = lin(x, 0.7)
+    yo = hp.lora_compatible_linear(x, lin.weight.detach(), lin.bias.detach(),
+                                   hp.unziplora_delta(x, None, W["content_down"], W["content_up"],
+                                                      W["style_down"], W["style_up"],
+                                                      lay.merge_content.detach(),
+                                                      lay.merge_style.detach()), 0.7)
+    _close(yo, y, 1e-6, "LoRACompatibleLinear")
+    lin3 = lora_unzip.LoRACompatibleLinear(fin, fout)
+    with torch.no_grad():
+        lin3.weight.copy_(lin.weight)
+        lin3.bias.copy_(lin.bias)
+    lin3.set_lora_layer(lay)
+    x1 = torch.randn(3, 7, fin)
+    with torch.no_grad():
+        y3 = lin3(x, 0.7, x1, x2)
+    yo3 = hp.lora_compatible_linear(x, lin.weight.detach(), lin.bias.detach(),
+                                    hp.unziplora_delta(x1, x2, W["content_down"], W["content_up"],
+                                                       W["style_down"], W["style_up"],
+                                                       lay.merge_content.detach(),
+                                                       lay.merge_style.detach()), 0.7)
+    _close(yo3, y3, 1e-6, "lora_unzip.LoRACompatibleLinear")
+    g.update(weight=lin.weight, bias=lin.bias, x=x, x1=x1, x2=x2, y=y, y3=y3, scale=0.7)
+    torch.manual_seed(5)
+    base = torch.nn.Linear(fin, fout)
+    tlo = TemporalLoRALinear(base, rank=4, alpha=2.0)
+    with torch.no_grad():
+        tlo.lora_B.normal_(0, 0.25)
+    xt = torch.randn(5, 6, fin, requires_grad=True)
+    yt = tlo(xt)
+    dyt = torch.randn_like(yt)
+    yt.backward(dyt)
+    yo = hp.temporal_lora_linear(xt.detach(), base.weight.detach(), base.bias.detach(),
+                                 tlo.lora_A.detach(), tlo.lora_B.detach(), tlo.scale)
+    _close(yo, yt.detach(), 1e-6, "TemporalLoRALinear")
+    g.update(t_weight=base.weight, t_bias=base.bias, t_A=tlo.lora_A, t_B=tlo.lora_B,
+             t_scale=tlo.scale, t_x=xt, t_y=yt, t_dy=dyt, t_dx=xt.grad, t_dA=tlo.lora_A.grad,
+             t_dB=tlo.lora_B.grad, t_delta=tlo.get_delta(), t_merged=tlo.merged_weight())
+    np.savez_compressed(os.path.join(OUT, "lora_linear.npz"), **_np(g))
+
+    # ---- a1: AnimateDiffAttnProcessor2_0 on a duck-typed attn ---------------------------
+    g = {}
+    C, heads, ctx, rr = 64, 4, 24, 8
+    torch.manual_seed(6)
+
+    def mk(i, o, bias):
+        l = LoRACompatibleLinear(i, o, bias=bias)
+        ll = UnZipLoRALinearLayerInfer(i, o, rr, ["content", "style"])
+        with torch.no_grad():
+            ll.merge_content.uniform_(0, 1)
+            ll.merge_style.uniform_(0, 1)
+        l.set_lora_layer(ll)
+        return l
+
+    def oproj(l):
+        ll = l.lora_layer
+        d = ll.lora_matrix_dic
+        return op.UnzipProj(l.weight.detach(), None if l.bias is None else l.bias.detach(),
+                            d["content_down"].weight.detach(), d["content_up"].weight.detach(),
+                            d["style_down"].weight.detach(), d["style_up"].weight.detach(),
+                            ll.merge_content.detach(), ll.merge_style.detach(), ll.forward_type,
+                            ll.masked_matrix["content"], ll.masked_matrix["style"])
+
+    proc = AnimateDiffAttnProcessor2_0()
+    for kind in ("self", "cross"):
+        kv_in = C if kind == "self" else ctx
+        attn = types.SimpleNamespace(
+            spatial_norm=None, group_norm=None, norm_cross=False, heads=heads,
+            to_q=mk(C, C, False), to_k=mk(kv_in, C, False), to_v=mk(kv_in, C, False),
+            to_out=torch.nn.ModuleList([mk(C, C, True), torch.nn.Dropout(0.0)]),
+            residual_connection=(kind == "self"), rescale_output_factor=1.5 if kind == "self" else 1.0)
+        hs = torch.randn(6, 20, C)                         # B*F = 6 (B=2, F=3)
+        ehs = None if kind == "self" else torch.randn(2, 11, ctx)
+        with torch.no_grad():
+            y = proc(attn, hs, ehs, scale=0.9)
+        P = op.SpatialAttnParams(heads, oproj(attn.to_q), oproj(attn.to_k), oproj(attn.to_v),
+                                 oproj(attn.to_out[0]), attn.residual_connection,
+                                 attn.rescale_output_factor)
+        report[f"proc_{kind}"] = _close(op.animatediff_attn_processor(P, hs, ehs, scale=0.9), y,
+                                        2e-5, f"processor {kind}")
+        g[f"{kind}/hs"] = hs
+        g[f"{kind}/y"] = y
+        if ehs is not None:
+            g[f"{kind}/ehs"] = ehs
+        g[f"{kind}/meta"] = np.array([heads, int(attn.residual_connection)])
+        g[f"{kind}/rescale"] = attn.rescale_output_factor
+        for nm, l in (("to_q", attn.to_q), ("to_k", attn.to_k), ("to_v", attn.to_v),
+                      ("to_out", attn.to_out[0])):
+            pr = oproj(l)
+            for fld in ("weight", "bias", "a_c", "b_c", "a_s", "b_s", "m_c", "m_s"):
+                v = getattr(pr, fld)
+                if v is not None:
+                    g[f"{kind}/{nm}/{fld}"] = v
+        if kind == "self":                                  # 4-D input branch :33-36,88-89
+            hs4 = torch.randn(6, C, 4, 5)
+            with torch.no_grad():
+                y4 = proc(attn, hs4, None, scale=0.9)
+            _close(op.animatediff_attn_processor(P, hs4, None, scale=0.9), y4, 2e-5, "4-D")
+            g["self/hs4"], g["self/y4"] = hs4, y4
+    np.savez_compressed(os.path.join(OUT, "attn_processor.npz"), **_np(g))
+
+    for k, v in report.items():
+        print(f"{k}: oracle-vs-reference rel err {v:.2e}")
+    print("golden written to", OUT)
+
+
+if __name__ == "__main__":
+    main()

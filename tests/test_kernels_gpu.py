@@ -1,0 +1,207 @@
+"""-m gpu parity tests of the individual CUDA kernels, called through the C ABI
+(video_style_transfer_b200.ops -> ctypes -> libvst_b200.so) and checked against the CPU oracle
+(oracle/hotpath.py) on the same seeded inputs.
+
+Tolerances (BASELINE.json north_star): layout kernels bit-exact; bf16 attention / GEMM outputs
+within 1e-2 max relative error vs the fp32 oracle, defined per tensor as max|a-b| / max|b|.
+"""
+import math
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+REL_TOL = 1e-2
+
+
+def rel_err(a, b):
+    a, b = a.float().cpu(), b.float().cpu()
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1e-30)).item()
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from video_style_transfer_b200 import ops as o
+    return o
+
+
+@pytest.fixture(scope="module")
+def hp():
+    from oracle import hotpath
+    return hotpath
+
+
+# ---- a9: layout (bit-exact) ----------------------------------------------------------------------
+def test_rearrange_golden_fp32(ops):
+    g = np.load(os.path.join(GOLD, "layout.npz"))
+    x = torch.from_numpy(g["rearr_x"]).cuda()
+    from oracle.hotpath import positional_table
+    pe = positional_table(24).cuda()
+    y = ops.rearrange_fwd(x, pe)
+    assert torch.equal(y.cpu(), torch.from_numpy(g["rearr_y"]))
+    back = ops.rearrange_bwd(y, 2, 3, 5)
+    assert torch.equal(back.cpu(), torch.from_numpy(g["rearr_back"]))
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("shape", [(1, 320, 16, 32, 32), (2, 64, 8, 8, 8), (1, 72, 5, 6, 4),
+                                   (1, 640, 16, 16, 16), (1, 8, 1, 1, 8)])
+@pytest.mark.parametrize("frames_major", [False, True])
+def test_rearrange_bit_exact(ops, hp, dtype, shape, frames_major):
+    torch.manual_seed(0)
+    b, c, f, h, w = shape
+    if frames_major:   # live layout: (B*F,C,H,W) storage viewed as (B,C,F,H,W)
+        x = torch.randn(b, f, c, h, w).to(dtype).cuda().permute(0, 2, 1, 3, 4)
+    else:
+        x = torch.randn(b, c, f, h, w).to(dtype).cuda()
+    pe = hp.positional_table(c).cuda()
+    y = ops.rearrange_fwd(x, None)
+    assert torch.equal(y.cpu(), hp.rearrange_fwd(x.cpu()))
+    y_pe = ops.rearrange_fwd(x, pe)
+    want = (hp.rearrange_fwd(x.cpu().float()) + pe.cpu()[:, :f]).to(dtype)   # one fp32 add, one rounding
+    assert torch.equal(y_pe.cpu(), want)
+    back = ops.rearrange_bwd(y, b, h, w, frames_major=frames_major)
+    assert torch.equal(back.cpu(), x.cpu())                                  # round trip
+    res = torch.randn(x.shape).to(dtype).cuda()
+    if frames_major:
+        res = torch.randn(b, f, c, h, w).to(dtype).cuda().permute(0, 2, 1, 3, 4)
+    back_r = ops.rearrange_bwd(y, b, h, w, residual5=res, frames_major=frames_major)
+    assert torch.equal(back_r.cpu(), (x.cpu().float() + res.cpu().float()).to(dtype))
+
+
+def test_rearrange_empty(ops):
+    x = torch.empty(0, 64, 16, 8, 8, dtype=torch.bfloat16, device="cuda")
+    assert ops.rearrange_fwd(x).shape == (0, 16, 64)
+
+
+# ---- a10 / K9: norms ---------------------------------------------------------------------------------
+@pytest.mark.parametrize("shape", [(1, 320, 16, 32, 32), (2, 64, 4, 8, 8), (1, 96, 3, 5, 3)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_groupnorm5d_rearrange(ops, hp, shape, dtype):
+    torch.manual_seed(1)
+    b, c, f, h, w = shape
+    x = (torch.randn(b, f, c, h, w) * 2 + 0.5).to(dtype).cuda().permute(0, 2, 1, 3, 4)
+    gamma, beta = torch.randn(c).cuda(), torch.randn(c).cuda()
+    y, mean, rstd = ops.groupnorm5d_rearrange(x, gamma, beta, 32, 1e-6)
+    xr = x.cpu().float()
+    want = hp.rearrange_fwd(hp.groupnorm5d(xr, gamma.cpu(), beta.cpu(), 32, 1e-6))
+    mu = xr.reshape(b, 32, -1).mean(-1).reshape(-1)
+    assert torch.allclose(mean.cpu(), mu, atol=1e-5, rtol=1e-5)
+    tol = 1e-2 if dtype == torch.bfloat16 else 1e-5
+    assert rel_err(y, want) < tol
+
+
+@pytest.mark.parametrize("c", [320, 640, 1280, 64])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_layernorm(ops, hp, c, dtype):
+    torch.manual_seed(2)
+    f = 16
+    x = (torch.randn(37 * f, c) * 1.5 + 0.3).to(dtype).cuda()
+    g, b = torch.randn(c).cuda(), torch.randn(c).cuda()
+    y = ops.layernorm(x, g, b, 1e-5)
+    want = hp.layernorm(x.cpu().float(), g.cpu(), b.cpu(), 1e-5)
+    tol = 1e-2 if dtype == torch.bfloat16 else 1e-5
+    assert rel_err(y, want) < tol
+    pe = hp.positional_table(c).cuda()
+    y2 = ops.layernorm(x, g, b, 1e-5, pe=pe, frames=f)
+    want2 = want.reshape(37, f, c) + pe.cpu()[:, :f]
+    assert rel_err(y2, want2.reshape(-1, c)) < tol
+
+
+# ---- a8: temporal attention ------------------------------------------------------------------------
+@pytest.mark.parametrize("f,heads,d", [(16, 8, 40), (16, 8, 80), (16, 8, 160), (32, 8, 40),
+                                       (32, 8, 160), (8, 8, 8), (5, 4, 40), (24, 2, 64)])
+def test_temporal_attn(ops, hp, f, heads, d):
+    torch.manual_seed(3)
+    n, c = 67, heads * d
+    qkv = torch.randn(n, f, 3 * c).to(torch.bfloat16).cuda()       # packed projection output
+    q, k, v = qkv[..., :c], qkv[..., c:2 * c], qkv[..., 2 * c:]
+    o = ops.temporal_attn(q, k, v, heads)
+
+    def sp(t):
+        return t.cpu().float().reshape(n, f, heads, d).transpose(1, 2)
+
+    want = hp.sdpa(sp(q), sp(k), sp(v)).transpose(1, 2).reshape(n, f, c)
+    assert rel_err(o, want) < REL_TOL
+
+
+# ---- a3/a7: fused LoRA GEMM --------------------------------------------------------------------------
+@pytest.mark.parametrize("m,n,k1,k2", [(128, 128, 64, 0), (128, 64, 128, 0), (256, 256, 256, 64),
+                                       (1000, 640, 640, 128), (300, 320, 320, 32),
+                                       (77, 1280, 2048, 128), (21, 40, 48, 16), (513, 960, 320, 96)])
+@pytest.mark.parametrize("out_dtype", [torch.bfloat16, torch.float32])
+def test_lora_gemm(ops, m, n, k1, k2, out_dtype):
+    torch.manual_seed(4)
+    a1 = torch.randn(m, k1).to(torch.bfloat16).cuda()
+    b1 = (torch.randn(n, k1) / math.sqrt(k1)).to(torch.bfloat16).cuda()
+    a2 = b2 = None
+    if k2:
+        a2 = torch.randn(m, k2).to(torch.bfloat16).cuda()
+        b2 = (torch.randn(n, k2) / math.sqrt(k2)).to(torch.bfloat16).cuda()
+    bias = torch.randn(n).cuda()
+    res = torch.randn(m, n).to(out_dtype).cuda()
+    out = ops.lora_gemm(a1, b1, a2, b2, bias=bias, residual=res, out_scale=0.5, out_dtype=out_dtype)
+    want = a1.cpu().float() @ b1.cpu().float().t() + bias.cpu() + res.cpu().float()
+    if k2:
+        want = want + a2.cpu().float() @ b2.cpu().float().t()
+    want = want * 0.5
+    assert rel_err(out, want) < (REL_TOL if out_dtype == torch.bfloat16 else 1e-4)
+    plain = ops.lora_gemm(a1, b1, out_dtype=out_dtype)
+    assert rel_err(plain, a1.cpu().float() @ b1.cpu().float().t()) < (
+        REL_TOL if out_dtype == torch.bfloat16 else 1e-4)
+
+
+def test_lora_gemm_linearity(ops):
+    """Size-independent property at a full config-3 shape (M=16384, C=1280): exact identity
+    columns of B pick out columns of A, and doubling A doubles D (power-of-two scaling is exact)."""
+    torch.manual_seed(5)
+    m, k = 16384, 1280
+    a = torch.randn(m, k).to(torch.bfloat16).cuda()
+    eye = torch.eye(k).to(torch.bfloat16).cuda()
+    d = ops.lora_gemm(a, eye)
+    assert torch.equal(d, a)
+    w = (torch.randn(k, k) / 36).to(torch.bfloat16).cuda()
+    d1, d2 = ops.lora_gemm(a, w), ops.lora_gemm(a * 2, w)
+    assert torch.equal(d1 * 2, d2)
+
+
+def test_lora_pack_up(ops):
+    torch.manual_seed(6)
+    n, r = 40, 8
+    bc, bs = torch.randn(n, r).cuda(), torch.randn(n, r).cuda()
+    mc, ms = torch.rand(n).cuda(), torch.rand(n).cuda()
+    mk = (torch.rand(n) > 0.5).cuda()
+    out = ops.lora_pack_up(bc, mc, mk, bs, ms, None, 0.7)
+    want = torch.cat([bc * (0.7 * mc * mk)[:, None], bs * (0.7 * ms)[:, None]], 1)
+    assert rel_err(out, want) < 5e-3
+    only_s = ops.lora_pack_up(None, None, None, bs, None, None, 1.0)
+    assert torch.equal(only_s.cpu(), bs.cpu().to(torch.bfloat16))
+
+
+# ---- a2: spatial / cross attention ------------------------------------------------------------------
+@pytest.mark.parametrize("bt,bk,heads,sq,sk", [(2, 2, 2, 128, 128), (2, 2, 3, 256, 384),
+                                               (4, 2, 2, 200, 77), (1, 1, 10, 1024, 1024),
+                                               (3, 1, 1, 100, 300), (1, 1, 2, 64, 1)])
+def test_attn_fwd(ops, hp, bt, bk, heads, sq, sk):
+    torch.manual_seed(7)
+    c = heads * 64
+    q = torch.randn(bt, sq, c).to(torch.bfloat16).cuda()
+    k = torch.randn(bk, sk, c).to(torch.bfloat16).cuda()
+    v = torch.randn(bk, sk, c).to(torch.bfloat16).cuda()
+    o, lse = ops.attn_fwd(q, k, v, heads, return_lse=True)
+    g = bt // bk
+
+    def sp(t, b, s):
+        return t.cpu().float().reshape(b, s, heads, 64).transpose(1, 2)
+
+    kk = sp(k, bk, sk).repeat_interleave(g, dim=0)
+    vv = sp(v, bk, sk).repeat_interleave(g, dim=0)
+    qq = sp(q, bt, sq)
+    want = hp.sdpa(qq, kk, vv).transpose(1, 2).reshape(bt, sq, c)
+    assert rel_err(o, want) < REL_TOL
+    want_lse = torch.logsumexp(qq @ kk.transpose(-1, -2) / 8.0, dim=-1)
+    assert torch.allclose(lse.cpu(), want_lse, atol=2e-2, rtol=1e-3)

@@ -1,0 +1,60 @@
+"""ctypes binding of libvst_b200.so (the C ABI declared in include/vst_b200.h).
+
+There is no CPU or eager-PyTorch fallback: if the shared library is missing or a symbol cannot
+be resolved, importing this module raises.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libvst_b200.so")
+
+VST_F32, VST_BF16 = 0, 1
+
+_p, _i, _l, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float
+
+# name -> (restype, argtypes); mirrors include/vst_b200.h one to one
+SIGNATURES = {
+    "vst_version": (_i, []),
+    "vst_last_error": (C.c_char_p, []),
+    "vst_device_info": (_i, [C.POINTER(_i)] * 3),
+    "vst_rearrange_fwd": (_i, [_p, _p, _p, _i, _i, _i, _i, _l, _l, _l, _i, _i, _p]),
+    "vst_rearrange_bwd": (_i, [_p, _p, _p, _i, _i, _i, _i, _l, _l, _l, _i, _i, _p]),
+    "vst_groupnorm5d_partials": (_i, [_i, _i, _i, _i]),
+    "vst_groupnorm5d_stats": (_i, [_p, _p, _i, _i, _i, _i, _l, _l, _l, _i, _i, _p]),
+    "vst_groupnorm5d_finalize": (_i, [_p, _i, _i, _i, _f, _p, _p, _p]),
+    "vst_groupnorm5d_apply_rearrange": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _l, _l, _l,
+                                             _i, _i, _i, _i, _p]),
+    "vst_layernorm": (_i, [_p, _p, _p, _p, _p, _l, _i, _i, _f, _i, _i, _i, _p]),
+    "vst_temporal_attn_fwd": (_i, [_p, _p, _p, _p, _l, _i, _i, _i, _l, _l, _l, _l, _f, _p]),
+    "vst_lora_gemm": (_i, [_p, _l, _p, _l, _i, _p, _l, _p, _l, _i, _p, _i, _p, _l, _f, _p, _l, _l,
+                           _i, _i, _p]),
+    "vst_lora_pack_up": (_i, [_p, _p, _p, _p, _p, _p, _f, _p, _i, _i, _i, _p]),
+    "vst_attn_fwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _l, _l, _l, _l, _i, _f, _p]),
+}
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} not found: build it with `make` (or __graft_entry__.build()). "
+            "video_style_transfer_b200 has no CPU / eager fallback.")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is missing: fail loudly
+        fn.restype = res
+        fn.argtypes = args
+    return lib
+
+
+lib = _load()
+
+
+class VstError(RuntimeError):
+    pass
+
+
+def check(rc: int, what: str):
+    if rc != 0:
+        msg = lib.vst_last_error()
+        raise VstError(f"{what} failed (rc={rc}): {msg.decode() if msg else ''}")

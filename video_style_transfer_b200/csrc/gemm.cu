@@ -1,0 +1,357 @@
+// a3/a4/a5/a7: the fused LoRA GEMM on tcgen05.
+//
+//   D[M,N] = (A1[M,K1] B1[N,K1]^T + A2[M,K2] B2[N,K2]^T + bias[N] + residual[M,N]) * out_scale
+//
+// The low-rank update rides in the same TMEM accumulator as extra K-blocks (A2 = u = x A^T,
+// B2 = scale * m (.) B packed by vst_lora_pack_up), so W x + m_c(.)(B_c A_c x) + m_s(.)(B_s A_s x)
+// is ONE pass over x and one write of y.  Reference arithmetic: unziplora_unet/lora_linear.py
+// :74-81, unziplora_linear_layer.py:298-346 (which does 3 dense GEMMs + 2 in x out
+// materialisations per call), lora_unzip.py:66-75, animatediff/temporal_lora.py:29-32.
+//
+// Kernel shape (sm_100a): persistent, one CTA per SM, 192 threads:
+//   warp 0      TMA producer  (A/B k-blocks -> 128B-swizzled smem ring, mbarrier full/empty)
+//   warp 1      MMA issuer    (one elected lane: tcgen05.mma 128 x BN x 16, accumulators in TMEM,
+//                              two accumulator stages so the epilogue overlaps the next tile)
+//   warps 2..5  epilogue      (tcgen05.ld -> +bias, +residual, *scale -> bf16/fp32 -> global)
+// Roofline: tensor pipe; algorithmic FLOPs = 2*M*N*(K1+K2).
+#include "common.cuh"
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;  // one 128-byte swizzle atom of bf16
+constexpr int kThreads = 192;
+constexpr int kSmemBudget = 200 * 1024;
+
+template <int BN>
+struct Cfg {
+  static constexpr int kStageBytes = (BM + BN) * BK * 2;
+  static constexpr int kStages = (kSmemBudget / kStageBytes) > 8 ? 8 : (kSmemBudget / kStageBytes);
+  static constexpr int kAccStride = BN <= 64 ? 64 : (BN <= 128 ? 128 : 256);
+  static constexpr int kTmemCols = 2 * kAccStride;  // power of two >= 32
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+};
+
+struct EpiArgs {
+  const void* bias;
+  const void* residual;
+  void* D;
+  int64_t ldr, ldd, M;
+  int N;
+  float out_scale;
+  int bias_bf16, out_f32;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(kThreads, 1)
+lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
+                 const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
+                 int nk1, int nk2, int m_tiles, int n_tiles, EpiArgs ep) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint64_t* empty = full + C::kStages;
+  uint64_t* acc_full = empty + C::kStages;
+  uint64_t* acc_empty = acc_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nk = nk1 + nk2;
+  const int total_tiles = m_tiles * n_tiles;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA1);
+    tma_prefetch_desc(&tmB1);
+    if (nk2 > 0) {
+      tma_prefetch_desc(&tmA2);
+      tma_prefetch_desc(&tmB2);
+    }
+    for (int i = 0; i < C::kStages; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_empty[i], 4);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, C::kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================= TMA producer =================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
+        for (int kb = 0; kb < nk; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1, 1);
+          uint8_t* sa = smem + stage * C::kStageBytes;
+          uint8_t* sb = sa + BM * BK * 2;
+          mbar_arrive_expect_tx(&full[stage], C::kStageBytes);
+          if (kb < nk1) {
+            tma_load_2d(sa, &tmA1, &full[stage], kb * BK, m0);
+            tma_load_2d(sb, &tmB1, &full[stage], kb * BK, n0);
+          } else {
+            tma_load_2d(sa, &tmA2, &full[stage], (kb - nk1) * BK, m0);
+            tma_load_2d(sb, &tmB2, &full[stage], (kb - nk1) * BK, n0);
+          }
+          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        mbar_wait(&acc_empty[acc], acc_phase ^ 1, 2);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * C::kAccStride;
+        for (int kb = 0; kb < nk; ++kb) {
+          mbar_wait(&full[stage], phase, 3);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * C::kStageBytes);
+          const uint32_t sb = sa + BM * BK * 2;
+          const uint64_t da = umma_desc_sw128(sa, 1024);
+          const uint64_t db = umma_desc_sw128(sb, 1024);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k)
+            umma_bf16_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+          umma_commit(&empty[stage]);  // frees the smem slot once these MMAs have read it
+          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&acc_full[acc]);   // accumulator complete -> epilogue
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else {
+    // ================= epilogue (warps 2..5; TMEM lane quarter = warp % 4) =================
+    const int quarter = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
+      mbar_wait(&acc_full[acc], acc_phase, 4);
+      tc_fence_after();
+      const int64_t row = (int64_t)m0 + quarter * 32 + lane;
+      const bool row_ok = row < ep.M;
+      const uint32_t taddr = tmem_base + acc * C::kAccStride + (uint32_t(quarter * 32) << 16);
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld32(taddr + c0, r);
+        tmem_ld_wait();
+        if (row_ok) {
+#pragma unroll
+          for (int v8 = 0; v8 < 4; ++v8) {
+            const int col = n0 + c0 + v8 * 8;
+            if (col >= ep.N) break;
+            float o[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = __uint_as_float(r[v8 * 8 + j]);
+            if (ep.bias != nullptr) {
+              if (ep.bias_bf16) {
+                const uint4 bv = __ldg(reinterpret_cast<const uint4*>(
+                    reinterpret_cast<const __nv_bfloat16*>(ep.bias) + col));
+                const uint32_t bw[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  const float2 e = unpack_bf16(bw[j]);
+                  o[2 * j] += e.x;
+                  o[2 * j + 1] += e.y;
+                }
+              } else {
+                const float4 b0 = __ldg(reinterpret_cast<const float4*>(
+                    reinterpret_cast<const float*>(ep.bias) + col));
+                const float4 b1 = __ldg(reinterpret_cast<const float4*>(
+                    reinterpret_cast<const float*>(ep.bias) + col + 4));
+                o[0] += b0.x; o[1] += b0.y; o[2] += b0.z; o[3] += b0.w;
+                o[4] += b1.x; o[5] += b1.y; o[6] += b1.z; o[7] += b1.w;
+              }
+            }
+            if (ep.out_f32) {
+              float* dp = reinterpret_cast<float*>(ep.D) + row * ep.ldd + col;
+              if (ep.residual != nullptr) {
+                const float* rp = reinterpret_cast<const float*>(ep.residual) + row * ep.ldr + col;
+                const float4 r0 = *reinterpret_cast<const float4*>(rp);
+                const float4 r1 = *reinterpret_cast<const float4*>(rp + 4);
+                o[0] += r0.x; o[1] += r0.y; o[2] += r0.z; o[3] += r0.w;
+                o[4] += r1.x; o[5] += r1.y; o[6] += r1.z; o[7] += r1.w;
+              }
+#pragma unroll
+              for (int j = 0; j < 8; ++j) o[j] *= ep.out_scale;
+              *reinterpret_cast<float4*>(dp) = make_float4(o[0], o[1], o[2], o[3]);
+              *reinterpret_cast<float4*>(dp + 4) = make_float4(o[4], o[5], o[6], o[7]);
+            } else {
+              __nv_bfloat16* dp = reinterpret_cast<__nv_bfloat16*>(ep.D) + row * ep.ldd + col;
+              if (ep.residual != nullptr) {
+                const uint4 rv = *reinterpret_cast<const uint4*>(
+                    reinterpret_cast<const __nv_bfloat16*>(ep.residual) + row * ep.ldr + col);
+                const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  const float2 e = unpack_bf16(rw[j]);
+                  o[2 * j] += e.x;
+                  o[2 * j + 1] += e.y;
+                }
+              }
+#pragma unroll
+              for (int j = 0; j < 8; ++j) o[j] *= ep.out_scale;
+              uint4 w;
+              w.x = pack_bf16(o[0], o[1]); w.y = pack_bf16(o[2], o[3]);
+              w.z = pack_bf16(o[4], o[5]); w.w = pack_bf16(o[6], o[7]);
+              *reinterpret_cast<uint4*>(dp) = w;
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, C::kTmemCols);
+  }
+}
+
+int make_operand_map(CUtensorMap* m, const void* p, int64_t rows, int K, int64_t ld, int box_rows) {
+  const uint64_t dims[2] = {(uint64_t)K, (uint64_t)rows};
+  const uint64_t strides[2] = {2, (uint64_t)ld * 2};
+  const uint32_t box[2] = {BK, (uint32_t)box_rows};
+  return vst_make_tmap(m, p, 2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+template <int BN>
+int launch(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, const void* A2,
+           int64_t lda2, const void* B2, int64_t ldb2, int K2, const EpiArgs& ep,
+           cudaStream_t st) {
+  using C = Cfg<BN>;
+  CUtensorMap tA1, tB1, tA2, tB2;
+  int rc;
+  if ((rc = make_operand_map(&tA1, A1, ep.M, K1, lda1, BM))) return rc;
+  if ((rc = make_operand_map(&tB1, B1, ep.N, K1, ldb1, BN))) return rc;
+  if (K2 > 0) {
+    if ((rc = make_operand_map(&tA2, A2, ep.M, K2, lda2, BM))) return rc;
+    if ((rc = make_operand_map(&tB2, B2, ep.N, K2, ldb2, BN))) return rc;
+  } else {
+    tA2 = tA1;
+    tB2 = tB1;
+  }
+  auto kern = lora_gemm_kernel<BN>;
+  static bool configured = false;
+  if (!configured) {
+    VST_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     C::kSmemBytes));
+    configured = true;
+  }
+  const int m_tiles = (int)((ep.M + BM - 1) / BM), n_tiles = (ep.N + BN - 1) / BN;
+  const int64_t tiles = (int64_t)m_tiles * n_tiles;
+  VST_REQUIRE(tiles < (1ll << 31), VST_E_UNSUPPORTED, "lora_gemm: too many tiles");
+  const int grid = (int)(tiles < vst_sm_count() ? tiles : vst_sm_count());
+  kern<<<grid, kThreads, C::kSmemBytes, st>>>(tA1, tB1, tA2, tB2, (K1 + BK - 1) / BK,
+                                               (K2 + BK - 1) / BK, m_tiles, n_tiles, ep);
+  VST_LAUNCH_OK();
+  return VST_OK;
+}
+
+// ---- vst_lora_pack_up: B2'[n, br*r + j] = scale * m_br[n] * mask_br[n] * B_br[n, j] ------------
+template <typename T>
+__global__ void pack_up_kernel(const T* __restrict__ Bc, const T* __restrict__ mc,
+                               const uint8_t* __restrict__ maskc, const T* __restrict__ Bs,
+                               const T* __restrict__ ms, const uint8_t* __restrict__ masks,
+                               float scale, __nv_bfloat16* __restrict__ out, int N, int r,
+                               int nbr) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int width = nbr * r;
+  if (idx >= (int64_t)N * width) return;
+  const int n = (int)(idx / width), j = (int)(idx % width);
+  const bool second = (Bc != nullptr) && j >= r;
+  const T* Bm = (Bc == nullptr || second) ? Bs : Bc;
+  const T* m = (Bc == nullptr || second) ? ms : mc;
+  const uint8_t* mk = (Bc == nullptr || second) ? masks : maskc;
+  const int jj = second ? j - r : j;
+  float val = (float)Bm[(int64_t)n * r + jj] * scale;
+  if (m != nullptr) val *= (float)m[n];
+  if (mk != nullptr && mk[n] == 0) val = 0.f;
+  out[idx] = __float2bfloat16_rn(val);
+}
+
+}  // namespace
+
+extern "C" int vst_lora_gemm(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1,
+                             const void* A2, int64_t lda2, const void* B2, int64_t ldb2, int K2,
+                             const void* bias, int bias_dtype, const void* residual, int64_t ldr,
+                             float out_scale, void* D, int64_t ldd, int64_t M, int N,
+                             int out_dtype, void* stream) {
+  VST_REQUIRE(M >= 0 && N > 0 && K1 > 0 && K2 >= 0, VST_E_BADARG, "lora_gemm: bad shape");
+  if (M == 0) return VST_OK;
+  VST_REQUIRE(A1 && B1 && D && (K2 == 0 || (A2 && B2)), VST_E_BADARG, "lora_gemm: null pointer");
+  VST_REQUIRE(K1 % 8 == 0 && K2 % 8 == 0 && N % 8 == 0, VST_E_UNSUPPORTED,
+              "lora_gemm: K1=%d, K2=%d, N=%d must be multiples of 8", K1, K2, N);
+  VST_REQUIRE(lda1 % 8 == 0 && ldb1 % 8 == 0 && (K2 == 0 || (lda2 % 8 == 0 && ldb2 % 8 == 0)),
+              VST_E_UNSUPPORTED, "lora_gemm: operand row strides must be multiples of 8 elements");
+  VST_REQUIRE(out_dtype == VST_F32 || out_dtype == VST_BF16, VST_E_BADARG, "lora_gemm: out dtype");
+  const int oa = out_dtype == VST_F32 ? 4 : 8;
+  VST_REQUIRE(ldd % oa == 0 && (residual == nullptr || ldr % oa == 0), VST_E_UNSUPPORTED,
+              "lora_gemm: output/residual row strides must keep 16-byte alignment");
+  VST_REQUIRE((reinterpret_cast<uintptr_t>(D) & 15) == 0 &&
+                  (reinterpret_cast<uintptr_t>(residual) & 15) == 0 &&
+                  (reinterpret_cast<uintptr_t>(bias) & 15) == 0,
+              VST_E_UNSUPPORTED, "lora_gemm: D/residual/bias must be 16-byte aligned");
+  EpiArgs ep{bias, residual, D, ldr, ldd, M, N, out_scale, bias_dtype == VST_BF16,
+             out_dtype == VST_F32};
+  cudaStream_t st = (cudaStream_t)stream;
+#define GO(BNV) return launch<BNV>(A1, lda1, B1, ldb1, K1, A2, lda2, B2, ldb2, K2, ep, st)
+  if (N % 256 == 0) GO(256);
+  if (N % 160 == 0) GO(160);
+  if (N % 192 == 0) GO(192);
+  if (N % 128 == 0) GO(128);
+  if (N <= 64) GO(64);
+  if (N <= 128) GO(128);
+  if (N <= 160) GO(160);
+  GO(256);
+#undef GO
+}
+
+extern "C" int vst_lora_pack_up(const void* Bc, const void* mc, const uint8_t* maskc,
+                                const void* Bs, const void* ms, const uint8_t* masks, float scale,
+                                void* out, int N, int r, int param_dtype, void* stream) {
+  VST_REQUIRE(N > 0 && r > 0 && out && (Bc || Bs), VST_E_BADARG, "lora_pack_up: bad argument");
+  const int nbr = (Bc ? 1 : 0) + (Bs ? 1 : 0);
+  const int64_t total = (int64_t)N * nbr * r;
+  const int threads = 256;
+  const unsigned grid = (unsigned)((total + threads - 1) / threads);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (param_dtype == VST_BF16)
+    pack_up_kernel<__nv_bfloat16><<<grid, threads, 0, st>>>(
+        (const __nv_bfloat16*)Bc, (const __nv_bfloat16*)mc, maskc, (const __nv_bfloat16*)Bs,
+        (const __nv_bfloat16*)ms, masks, scale, (__nv_bfloat16*)out, N, r, nbr);
+  else if (param_dtype == VST_F32)
+    pack_up_kernel<float><<<grid, threads, 0, st>>>((const float*)Bc, (const float*)mc, maskc,
+                                                    (const float*)Bs, (const float*)ms, masks,
+                                                    scale, (__nv_bfloat16*)out, N, r, nbr);
+  else {
+    vst_set_error("lora_pack_up: bad param dtype %d", param_dtype);
+    return VST_E_BADARG;
+  }
+  VST_LAUNCH_OK();
+  return VST_OK;
+}

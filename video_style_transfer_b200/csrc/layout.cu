@@ -1,0 +1,311 @@
+// a9: (B,C,F,H,W) <-> (B*H*W, F, C) rearranges with the sinusoidal position add / residual add
+// fused into the store.  Reference: animatediff/temporal_transformer.py:129-133,143-144 and
+// PositionalEncoding.forward :27.  Pure data movement => bit-exact (the optional add is one
+// fp32 add rounded once, exactly what torch does for same-dtype operands).
+//
+// HBM-bound: one read + one write per element.  Tile = 64 positions x 32 words staged in shared
+// memory; 16-byte global loads along hw, 16-byte global stores along c; the shared tile is
+// XOR-swizzled at 16-byte-chunk granularity so both phases are bank-conflict free for bf16.
+#include "common.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kTileHW = 64;
+constexpr int kTileWords = 32;  // 64 bf16 channels or 32 fp32 channels
+
+__device__ __forceinline__ int swz(int row, int word) {
+  return row * kTileWords + ((((word >> 2) ^ (row >> 3)) & 7) << 2) + (word & 3);
+}
+
+// a10 apply fused into the forward rearrange (MODE 2): y = x * a_c + b_c with
+// a_c = rstd[b,g] * gamma[c], b_c = beta[c] - mean[b,g] * a_c   (fp32, rounded once).
+struct NormArgs {
+  const float* mean;
+  const float* rstd;
+  const void* gamma;
+  const void* beta;
+  int groups;
+  int param_bf16;
+};
+__device__ __forceinline__ float2 norm_coeffs(const NormArgs& na, int b, int c, int C) {
+  const int g = c / (C / na.groups);
+  const float mu = __ldg(na.mean + b * na.groups + g), rs = __ldg(na.rstd + b * na.groups + g);
+  float ga, be;
+  if (na.param_bf16) {
+    ga = __bfloat162float(((const __nv_bfloat16*)na.gamma)[c]);
+    be = __bfloat162float(((const __nv_bfloat16*)na.beta)[c]);
+  } else {
+    ga = __ldg((const float*)na.gamma + c);
+    be = __ldg((const float*)na.beta + c);
+  }
+  const float a = rs * ga;
+  return make_float2(a, be - mu * a);
+}
+__device__ __forceinline__ uint32_t norm_word(uint32_t w, float2 ab) {
+  const float2 e = unpack_bf16(w);
+  return pack_bf16(fmaf(e.x, ab.x, ab.y), fmaf(e.y, ab.x, ab.y));
+}
+
+// ---- bf16: two channel rows per thread, 2x2 transposes with byte permutes -------------------
+// MODE 0: forward (x[b,c,f,hw] -> y[(b,hw),f,c] + pe[f,c])
+// MODE 1: backward (y[(b,hw),f,c] -> out[b,c,f,hw] + residual[b,c,f,hw])
+// MODE 2: forward with the GroupNorm affine applied on the way in
+template <int MODE>
+__global__ void __launch_bounds__(kThreads)
+rearrange_bf16_kernel(const __nv_bfloat16* __restrict__ src, __nv_bfloat16* __restrict__ dst,
+                      const float* __restrict__ pe, const __nv_bfloat16* __restrict__ residual,
+                      int C, int F, int HW, int64_t sB, int64_t sC, int64_t sF, int tilesHW,
+                      int tilesC, NormArgs na) {
+  __shared__ __align__(16) uint32_t tile[kTileHW * kTileWords];
+  int t = blockIdx.x;
+  const int thw = t % tilesHW;
+  t /= tilesHW;
+  const int tc = t % tilesC;
+  t /= tilesC;
+  const int f = t % F;
+  const int b = t / F;
+  const int hw0 = thw * kTileHW, c0 = tc * 64;
+  const int tid = threadIdx.x;
+
+  // "planar" tensor P[b,c,f,hw] (strided) and "token" tensor T[(b,hw),f,c]
+  const int64_t pbase = (int64_t)b * sB + (int64_t)f * sF;
+  const int64_t tbase = ((int64_t)b * HW * F + f) * C;  // + hw*F*C + c
+
+  if (MODE == 0 || MODE == 2) {
+    // load: thread = (channel pair cp, hw chunk hc); 16 B along hw from rows c, c+1
+    const int hc = tid & 7, cp = tid >> 3;
+    const int c = c0 + 2 * cp, hw = hw0 + 8 * hc;
+    uint4 r0 = make_uint4(0, 0, 0, 0), r1 = r0;
+    if (hw < HW && c < C) {
+      r0 = ld_stream16(src + pbase + (int64_t)c * sC + hw);
+      if (c + 1 < C) r1 = ld_stream16(src + pbase + (int64_t)(c + 1) * sC + hw);
+    }
+    uint32_t a[4] = {r0.x, r0.y, r0.z, r0.w}, bb[4] = {r1.x, r1.y, r1.z, r1.w};
+    if (MODE == 2 && hw < HW && c < C) {
+      const float2 k0 = norm_coeffs(na, b, c, C);
+      const float2 k1 = c + 1 < C ? norm_coeffs(na, b, c + 1, C) : k0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        a[j] = norm_word(a[j], k0);
+        bb[j] = norm_word(bb[j], k1);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      tile[swz(8 * hc + 2 * j, cp)] = __byte_perm(a[j], bb[j], 0x5410);      // (c,hw) (c+1,hw)
+      tile[swz(8 * hc + 2 * j + 1, cp)] = __byte_perm(a[j], bb[j], 0x7632);  // hw+1
+    }
+    __syncthreads();
+    // store: item = (hw row, 16-B chunk of 8 channels)
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+      const int item = tid + it * kThreads;
+      const int row = item >> 3, ch = item & 7;
+      const int hwr = hw0 + row, cc = c0 + 8 * ch;
+      if (hwr < HW && cc < C) {
+        uint4 v = *reinterpret_cast<const uint4*>(&tile[swz(row, 4 * ch)]);
+        if (pe != nullptr) {
+          const float4 p0 = __ldg(reinterpret_cast<const float4*>(pe + (int64_t)f * C + cc));
+          const float4 p1 = __ldg(reinterpret_cast<const float4*>(pe + (int64_t)f * C + cc + 4));
+          float2 e;
+          e = unpack_bf16(v.x); v.x = pack_bf16(e.x + p0.x, e.y + p0.y);
+          e = unpack_bf16(v.y); v.y = pack_bf16(e.x + p0.z, e.y + p0.w);
+          e = unpack_bf16(v.z); v.z = pack_bf16(e.x + p1.x, e.y + p1.y);
+          e = unpack_bf16(v.w); v.w = pack_bf16(e.x + p1.z, e.y + p1.w);
+        }
+        st_stream16(dst + tbase + (int64_t)hwr * F * C + cc, v);
+      }
+    }
+  } else {
+    // load: item = (hw row, 16-B chunk of 8 channels) from the token tensor
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+      const int item = tid + it * kThreads;
+      const int row = item >> 3, ch = item & 7;
+      const int hwr = hw0 + row, cc = c0 + 8 * ch;
+      uint4 v = make_uint4(0, 0, 0, 0);
+      if (hwr < HW && cc < C) v = ld_stream16(src + tbase + (int64_t)hwr * F * C + cc);
+      *reinterpret_cast<uint4*>(&tile[swz(row, 4 * ch)]) = v;
+    }
+    __syncthreads();
+    const int hc = tid & 7, cp = tid >> 3;
+    const int c = c0 + 2 * cp, hw = hw0 + 8 * hc;
+    if (hw < HW && c < C) {
+      uint32_t lo[4], hi[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const uint32_t w0 = tile[swz(8 * hc + 2 * j, cp)];      // (c,hw)   (c+1,hw)
+        const uint32_t w1 = tile[swz(8 * hc + 2 * j + 1, cp)];  // (c,hw+1) (c+1,hw+1)
+        lo[j] = __byte_perm(w0, w1, 0x5410);                    // row c  : hw, hw+1
+        hi[j] = __byte_perm(w0, w1, 0x7632);                    // row c+1
+      }
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        if (c + r >= C) break;
+        uint32_t* w = r == 0 ? lo : hi;
+        const int64_t off = pbase + (int64_t)(c + r) * sC + hw;
+        if (residual != nullptr) {
+          const uint4 rr = ld_stream16(residual + off);
+          const uint32_t rv[4] = {rr.x, rr.y, rr.z, rr.w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float2 e = unpack_bf16(w[j]), q = unpack_bf16(rv[j]);
+            w[j] = pack_bf16(e.x + q.x, e.y + q.y);
+          }
+        }
+        st_stream16(dst + off, make_uint4(w[0], w[1], w[2], w[3]));
+      }
+    }
+  }
+}
+
+// ---- generic fallback (fp32, or shapes/pointers that are not 16-byte friendly) ---------------
+template <typename T>
+__device__ __forceinline__ float to_f(T v);
+template <>
+__device__ __forceinline__ float to_f<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ float to_f<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <typename T>
+__device__ __forceinline__ T from_f(float v);
+template <>
+__device__ __forceinline__ float from_f<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ __nv_bfloat16 from_f<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+
+template <typename T, int MODE>
+__global__ void __launch_bounds__(kThreads)
+rearrange_generic_kernel(const T* __restrict__ src, T* __restrict__ dst,
+                         const float* __restrict__ pe, const T* __restrict__ residual, int C,
+                         int F, int HW, int64_t sB, int64_t sC, int64_t sF, int tilesHW,
+                         int tilesC, NormArgs na) {
+  __shared__ T tile[32][33];
+  int t = blockIdx.x;
+  const int thw = t % tilesHW;
+  t /= tilesHW;
+  const int tc = t % tilesC;
+  t /= tilesC;
+  const int f = t % F;
+  const int b = t / F;
+  const int hw0 = thw * 32, c0 = tc * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  const int64_t pbase = (int64_t)b * sB + (int64_t)f * sF;
+  const int64_t tbase = ((int64_t)b * HW * F + f) * C;
+  if (MODE == 0 || MODE == 2) {
+    for (int i = ty; i < 32; i += 8) {
+      const int c = c0 + i, hw = hw0 + tx;
+      if (c < C && hw < HW) {
+        T v = src[pbase + (int64_t)c * sC + hw];
+        if (MODE == 2) {
+          const float2 k = norm_coeffs(na, b, c, C);
+          v = from_f<T>(fmaf(to_f<T>(v), k.x, k.y));
+        }
+        tile[i][tx] = v;
+      }
+    }
+    __syncthreads();
+    for (int i = ty; i < 32; i += 8) {
+      const int hw = hw0 + i, c = c0 + tx;
+      if (c < C && hw < HW) {
+        T v = tile[tx][i];
+        if (pe != nullptr) v = from_f<T>(to_f<T>(v) + pe[(int64_t)f * C + c]);
+        dst[tbase + (int64_t)hw * F * C + c] = v;
+      }
+    }
+  } else {
+    for (int i = ty; i < 32; i += 8) {
+      const int hw = hw0 + i, c = c0 + tx;
+      if (c < C && hw < HW) tile[i][tx] = src[tbase + (int64_t)hw * F * C + c];
+    }
+    __syncthreads();
+    for (int i = ty; i < 32; i += 8) {
+      const int c = c0 + i, hw = hw0 + tx;
+      if (c < C && hw < HW) {
+        const int64_t off = pbase + (int64_t)c * sC + hw;
+        T v = tile[tx][i];
+        if (residual != nullptr) v = from_f<T>(to_f<T>(v) + to_f<T>(residual[off]));
+        dst[off] = v;
+      }
+    }
+  }
+}
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+template <int MODE>
+int launch(const void* src, void* dst, const float* pe, const void* residual, int B, int C,
+           int F, int HW, int64_t sB, int64_t sC, int64_t sF, int dtype, cudaStream_t st,
+           NormArgs na = NormArgs{nullptr, nullptr, nullptr, nullptr, 1, 0}) {
+  if ((int64_t)B * C * F * HW == 0) return VST_OK;
+  const bool fast = dtype == VST_BF16 && C % 8 == 0 && HW % 8 == 0 && sB % 8 == 0 &&
+                    sC % 8 == 0 && sF % 8 == 0 && aligned16(src) && aligned16(dst) &&
+                    (residual == nullptr || aligned16(residual)) &&
+                    (pe == nullptr || aligned16(pe));
+  if (fast) {
+    const int tilesHW = (HW + kTileHW - 1) / kTileHW, tilesC = (C + 63) / 64;
+    const int64_t grid = (int64_t)B * F * tilesHW * tilesC;
+    VST_REQUIRE(grid < (1ll << 31), VST_E_UNSUPPORTED, "rearrange: grid too large");
+    rearrange_bf16_kernel<MODE><<<(unsigned)grid, kThreads, 0, st>>>(
+        (const __nv_bfloat16*)src, (__nv_bfloat16*)dst, pe, (const __nv_bfloat16*)residual, C, F,
+        HW, sB, sC, sF, tilesHW, tilesC, na);
+  } else {
+    const int tilesHW = (HW + 31) / 32, tilesC = (C + 31) / 32;
+    const int64_t grid = (int64_t)B * F * tilesHW * tilesC;
+    VST_REQUIRE(grid < (1ll << 31), VST_E_UNSUPPORTED, "rearrange: grid too large");
+    if (dtype == VST_BF16)
+      rearrange_generic_kernel<__nv_bfloat16, MODE><<<(unsigned)grid, kThreads, 0, st>>>(
+          (const __nv_bfloat16*)src, (__nv_bfloat16*)dst, pe, (const __nv_bfloat16*)residual, C,
+          F, HW, sB, sC, sF, tilesHW, tilesC, na);
+    else
+      rearrange_generic_kernel<float, MODE><<<(unsigned)grid, kThreads, 0, st>>>(
+          (const float*)src, (float*)dst, pe, (const float*)residual, C, F, HW, sB, sC, sF,
+          tilesHW, tilesC, na);
+  }
+  VST_LAUNCH_OK();
+  return VST_OK;
+}
+
+int check(const void* a, const void* b, int B, int C, int F, int HW, int in_dtype,
+          int out_dtype) {
+  VST_REQUIRE(B >= 0 && C >= 0 && F >= 0 && HW >= 0, VST_E_BADARG, "rearrange: negative dim");
+  VST_REQUIRE(in_dtype == out_dtype && (in_dtype == VST_F32 || in_dtype == VST_BF16),
+              VST_E_UNSUPPORTED, "rearrange: in/out dtype must match and be f32 or bf16");
+  VST_REQUIRE((a && b) || (int64_t)B * C * F * HW == 0, VST_E_BADARG, "rearrange: null pointer");
+  return VST_OK;
+}
+
+}  // namespace
+
+extern "C" int vst_rearrange_fwd(const void* x, void* y, const float* pe, int B, int C, int F,
+                                 int HW, int64_t sB, int64_t sC, int64_t sF, int in_dtype,
+                                 int out_dtype, void* stream) {
+  int rc = check(x, y, B, C, F, HW, in_dtype, out_dtype);
+  if (rc) return rc;
+  return launch<0>(x, y, pe, nullptr, B, C, F, HW, sB, sC, sF, in_dtype, (cudaStream_t)stream);
+}
+
+extern "C" int vst_rearrange_bwd(const void* y, void* out, const void* residual, int B, int C,
+                                 int F, int HW, int64_t sB, int64_t sC, int64_t sF, int in_dtype,
+                                 int out_dtype, void* stream) {
+  int rc = check(y, out, B, C, F, HW, in_dtype, out_dtype);
+  if (rc) return rc;
+  return launch<1>(y, out, nullptr, residual, B, C, F, HW, sB, sC, sF, in_dtype,
+                   (cudaStream_t)stream);
+}
+
+extern "C" int vst_groupnorm5d_apply_rearrange(const void* x, void* y, const float* mean,
+                                               const float* rstd, const void* gamma,
+                                               const void* beta, int B, int C, int F, int HW,
+                                               int64_t sB, int64_t sC, int64_t sF, int groups,
+                                               int in_dtype, int out_dtype, int param_dtype,
+                                               void* stream) {
+  int rc = check(x, y, B, C, F, HW, in_dtype, out_dtype);
+  if (rc) return rc;
+  VST_REQUIRE(groups > 0 && C % groups == 0, VST_E_BADARG, "groupnorm: C %% groups != 0");
+  VST_REQUIRE(mean && rstd && gamma && beta, VST_E_BADARG, "groupnorm: null stats/affine");
+  VST_REQUIRE(param_dtype == VST_F32 || param_dtype == VST_BF16, VST_E_BADARG, "bad param dtype");
+  NormArgs na{mean, rstd, gamma, beta, groups, param_dtype == VST_BF16};
+  return launch<2>(x, y, nullptr, nullptr, B, C, F, HW, sB, sC, sF, in_dtype,
+                   (cudaStream_t)stream, na);
+}

@@ -1,0 +1,293 @@
+// a10 statistics (GroupNorm over the (B,C,F,H,W) view) and K9 LayerNorm (+ fused position add).
+// Both are HBM-bound: one 16-byte-vectorised pass, warp-shuffle reductions, fp32 statistics.
+//
+// GroupNorm statistics are computed as (count, mean, M2) partials over slabs that a block holds
+// entirely in registers (exact two-pass inside the slab) and merged with Chan's formula, so
+// there is no E[x^2]-E[x]^2 cancellation and the result is deterministic (no atomics).  Under
+// sequence parallelism the partials are what crosses the NVLink all-reduce.
+#include "common.cuh"
+
+namespace {
+
+constexpr int kSlabThreads = 256;
+constexpr int kVecPerThread = 4;                                      // 4 x 8 bf16
+constexpr int kSlabElems = kSlabThreads * kVecPerThread * 8;          // 8192
+
+__device__ __forceinline__ float block_sum(float v, float* red) {
+  v = warp_sum(v);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = blockDim.x >> 5;
+  __syncthreads();
+  if (l == 0) red[w] = v;
+  __syncthreads();
+  float t = l < nw ? red[l] : 0.f;
+  return warp_sum(t);
+}
+
+template <typename T>
+__device__ __forceinline__ void load8(const T* p, float* v);
+template <>
+__device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bfloat16* p, float* v) {
+  const uint4 r = ld_stream16(p);
+  float2 e;
+  e = unpack_bf16(r.x); v[0] = e.x; v[1] = e.y;
+  e = unpack_bf16(r.y); v[2] = e.x; v[3] = e.y;
+  e = unpack_bf16(r.z); v[4] = e.x; v[5] = e.y;
+  e = unpack_bf16(r.w); v[6] = e.x; v[7] = e.y;
+}
+template <>
+__device__ __forceinline__ void load8<float>(const float* p, float* v) {
+  const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+
+// grid = B*groups*F*slabs; block (b,g,f,s) reduces elements [s*8192, ...) of the cg*HW chunk.
+template <typename T, bool VEC>
+__global__ void __launch_bounds__(kSlabThreads)
+gn_stats_kernel(const T* __restrict__ x, float* __restrict__ partials, int C, int F, int HW,
+                int64_t sB, int64_t sC, int64_t sF, int groups, int slabs) {
+  __shared__ float red[32];
+  int t = blockIdx.x;
+  const int s = t % slabs; t /= slabs;
+  const int f = t % F; t /= F;
+  const int g = t % groups;
+  const int b = t / groups;
+  const int cg = C / groups;
+  const int64_t chunk = (int64_t)cg * HW;
+  const int64_t e0 = (int64_t)s * kSlabElems;
+  const T* base = x + (int64_t)b * sB + (int64_t)f * sF + (int64_t)g * cg * sC;
+
+  float v[kVecPerThread][8];
+  float sum = 0.f;
+  int cnt = 0;
+#pragma unroll
+  for (int i = 0; i < kVecPerThread; ++i) {
+    const int64_t e = e0 + ((int64_t)i * kSlabThreads + threadIdx.x) * 8;
+    if (VEC) {
+      if (e < chunk) {
+        const int c = (int)(e / HW), hw = (int)(e % HW);
+        load8<T>(base + (int64_t)c * sC + hw, v[i]);
+        cnt += 8;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[i][j] = 0.f;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int64_t ej = e + j;
+        if (ej < chunk) {
+          const int c = (int)(ej / HW), hw = (int)(ej % HW);
+          v[i][j] = (float)base[(int64_t)c * sC + hw];
+          ++cnt;
+        } else {
+          v[i][j] = 0.f;
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sum += v[i][j];
+  }
+  const int64_t rem = chunk - e0;
+  const float n = (float)(rem < kSlabElems ? rem : kSlabElems);
+  const float mean = block_sum(sum, red) / n;
+  float m2 = 0.f;
+#pragma unroll
+  for (int i = 0; i < kVecPerThread; ++i) {
+    const int64_t e = e0 + ((int64_t)i * kSlabThreads + threadIdx.x) * 8;
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if (e + j < chunk) {
+        const float d = v[i][j] - mean;
+        m2 = fmaf(d, d, m2);
+      }
+  }
+  m2 = block_sum(m2, red);
+  if (threadIdx.x == 0) {
+    float* out = partials + ((int64_t)(b * groups + g) * (F * slabs) + (f * slabs + s)) * 3;
+    out[0] = n; out[1] = mean; out[2] = m2;
+  }
+  (void)cnt;
+}
+
+__device__ __forceinline__ void chan(float& n, float& mu, float& m2, float nb, float mub,
+                                     float m2b) {
+  if (nb == 0.f) return;
+  const float nn = n + nb, d = mub - mu;
+  mu = mu + d * (nb / nn);
+  m2 = m2 + m2b + d * d * (n * nb / nn);
+  n = nn;
+}
+
+// one warp per (b, group): fixed-order combine => deterministic
+__global__ void gn_finalize_kernel(const float* __restrict__ partials, int nparts, float eps,
+                                   float* __restrict__ mean, float* __restrict__ rstd) {
+  const int bg = blockIdx.x, l = threadIdx.x;
+  const float* p = partials + (int64_t)bg * nparts * 3;
+  float n = 0.f, mu = 0.f, m2 = 0.f;
+  for (int i = l; i < nparts; i += 32) chan(n, mu, m2, p[3 * i], p[3 * i + 1], p[3 * i + 2]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float nb = __shfl_xor_sync(0xffffffffu, n, o);
+    const float mub = __shfl_xor_sync(0xffffffffu, mu, o);
+    const float m2b = __shfl_xor_sync(0xffffffffu, m2, o);
+    // combine in a lane-symmetric order so every lane ends with the same value
+    float na = n, mua = mu, m2a = m2;
+    if (l & o) { na = nb; mua = mub; m2a = m2b; chan(na, mua, m2a, n, mu, m2); }
+    else chan(na, mua, m2a, nb, mub, m2b);
+    n = na; mu = mua; m2 = m2a;
+  }
+  if (l == 0) {
+    mean[bg] = mu;
+    rstd[bg] = rsqrtf(m2 / n + eps);
+  }
+}
+
+// ---- LayerNorm: one warp per row, row cached in registers ---------------------------------------
+template <typename TI, typename TO, typename TP, int MAXV>
+__global__ void __launch_bounds__(256)
+layernorm_kernel(const TI* __restrict__ x, TO* __restrict__ y, const TP* __restrict__ gamma,
+                 const TP* __restrict__ beta, const float* __restrict__ pe, int64_t rows, int C,
+                 int F, float eps) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const TI* xr = x + row * C;
+  const int nvec = C >> 3;
+  float v[MAXV][8];
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int vi = lane + 32 * i;
+    if (vi < nvec) {
+      load8<TI>(xr + vi * 8, v[i]);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) sum += v[i][j];
+    }
+  }
+  const float mean = warp_sum(sum) / (float)C;
+  float m2 = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int vi = lane + 32 * i;
+    if (vi < nvec) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float d = v[i][j] - mean;
+        m2 = fmaf(d, d, m2);
+      }
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(m2) / (float)C + eps);
+  const float* per = pe ? pe + (int64_t)(row % F) * C : nullptr;
+  TO* yr = y + row * C;
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int vi = lane + 32 * i;
+    if (vi < nvec) {
+      float o[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int c = vi * 8 + j;
+        float r = (v[i][j] - mean) * rstd;
+        if (gamma) r = r * (float)gamma[c];
+        if (beta) r = r + (float)beta[c];
+        o[j] = r;
+      }
+      if (per) {
+        // LN output is first rounded to the activation dtype, then the position row is added
+        // (diffusers: norm_hidden_states = pos_embed(norm1(x))) -- two roundings, as in torch.
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = (float)(TO)o[j] + per[vi * 8 + j];
+      }
+      if (sizeof(TO) == 2) {
+        uint4 w;
+        w.x = pack_bf16(o[0], o[1]); w.y = pack_bf16(o[2], o[3]);
+        w.z = pack_bf16(o[4], o[5]); w.w = pack_bf16(o[6], o[7]);
+        *reinterpret_cast<uint4*>(yr + vi * 8) = w;
+      } else {
+        float4* d = reinterpret_cast<float4*>(yr + vi * 8);
+        d[0] = make_float4(o[0], o[1], o[2], o[3]);
+        d[1] = make_float4(o[4], o[5], o[6], o[7]);
+      }
+    }
+  }
+}
+
+template <typename TI, typename TO, typename TP>
+int launch_ln(const void* x, void* y, const void* g, const void* b, const float* pe, int64_t rows,
+              int C, int F, float eps, cudaStream_t st) {
+  const int wpb = 8;
+  const int64_t grid = (rows + wpb - 1) / wpb;
+  VST_REQUIRE(grid < (1ll << 31), VST_E_UNSUPPORTED, "layernorm: too many rows");
+  const int nvec = C / 8;
+  if (nvec <= 64)
+    layernorm_kernel<TI, TO, TP, 2><<<(unsigned)grid, wpb * 32, 0, st>>>(
+        (const TI*)x, (TO*)y, (const TP*)g, (const TP*)b, pe, rows, C, F, eps);
+  else
+    layernorm_kernel<TI, TO, TP, 8><<<(unsigned)grid, wpb * 32, 0, st>>>(
+        (const TI*)x, (TO*)y, (const TP*)g, (const TP*)b, pe, rows, C, F, eps);
+  VST_LAUNCH_OK();
+  return VST_OK;
+}
+
+}  // namespace
+
+extern "C" int vst_groupnorm5d_partials(int C, int F, int HW, int groups) {
+  if (groups <= 0 || C % groups != 0) return VST_E_BADARG;
+  const int64_t chunk = (int64_t)(C / groups) * HW;
+  return (int)(F * ((chunk + kSlabElems - 1) / kSlabElems));
+}
+
+extern "C" int vst_groupnorm5d_stats(const void* x, float* partials, int B, int C, int F, int HW,
+                                     int64_t sB, int64_t sC, int64_t sF, int groups, int dtype,
+                                     void* stream) {
+  VST_REQUIRE(groups > 0 && C % groups == 0, VST_E_BADARG, "groupnorm: C %% groups != 0");
+  VST_REQUIRE(x && partials, VST_E_BADARG, "groupnorm: null pointer");
+  VST_REQUIRE(dtype == VST_F32 || dtype == VST_BF16, VST_E_BADARG, "groupnorm: bad dtype");
+  const int slabs = vst_groupnorm5d_partials(C, F, HW, groups) / F;
+  const int64_t grid = (int64_t)B * groups * F * slabs;
+  VST_REQUIRE(grid > 0 && grid < (1ll << 31), VST_E_UNSUPPORTED, "groupnorm: bad grid");
+  const bool vec = HW % 8 == 0 && sB % 8 == 0 && sC % 8 == 0 && sF % 8 == 0 &&
+                   (reinterpret_cast<uintptr_t>(x) & 31) == 0;
+  cudaStream_t st = (cudaStream_t)stream;
+#define GN_LAUNCH(T, V)                                                                         \
+  gn_stats_kernel<T, V><<<(unsigned)grid, kSlabThreads, 0, st>>>((const T*)x, partials, C, F, HW, \
+                                                                 sB, sC, sF, groups, slabs)
+  if (dtype == VST_BF16) { if (vec) GN_LAUNCH(__nv_bfloat16, true); else GN_LAUNCH(__nv_bfloat16, false); }
+  else { if (vec) GN_LAUNCH(float, true); else GN_LAUNCH(float, false); }
+#undef GN_LAUNCH
+  VST_LAUNCH_OK();
+  return VST_OK;
+}
+
+extern "C" int vst_groupnorm5d_finalize(const float* partials, int nparts, int B, int groups,
+                                        float eps, float* mean, float* rstd, void* stream) {
+  VST_REQUIRE(partials && mean && rstd && nparts > 0 && B > 0 && groups > 0, VST_E_BADARG,
+              "groupnorm finalize: bad argument");
+  gn_finalize_kernel<<<B * groups, 32, 0, (cudaStream_t)stream>>>(partials, nparts, eps, mean, rstd);
+  VST_LAUNCH_OK();
+  return VST_OK;
+}
+
+extern "C" int vst_layernorm(const void* x, void* y, const void* gamma, const void* beta,
+                             const float* pe, int64_t rows, int C, int F, float eps, int in_dtype,
+                             int out_dtype, int param_dtype, void* stream) {
+  VST_REQUIRE(rows >= 0 && C > 0, VST_E_BADARG, "layernorm: bad shape");
+  if (rows == 0) return VST_OK;
+  VST_REQUIRE(x && y, VST_E_BADARG, "layernorm: null pointer");
+  VST_REQUIRE(C % 8 == 0 && C <= 2048, VST_E_UNSUPPORTED, "layernorm: C must be a multiple of 8, <= 2048");
+  VST_REQUIRE(pe == nullptr || F > 0, VST_E_BADARG, "layernorm: F must be > 0 with pe");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int key = in_dtype * 4 + out_dtype * 2 + param_dtype;
+  switch (key) {
+    case 0: return launch_ln<float, float, float>(x, y, gamma, beta, pe, rows, C, F, eps, st);
+    case 2: return launch_ln<float, __nv_bfloat16, float>(x, y, gamma, beta, pe, rows, C, F, eps, st);
+    case 3: return launch_ln<float, __nv_bfloat16, __nv_bfloat16>(x, y, gamma, beta, pe, rows, C, F, eps, st);
+    case 6: return launch_ln<__nv_bfloat16, __nv_bfloat16, float>(x, y, gamma, beta, pe, rows, C, F, eps, st);
+    case 7: return launch_ln<__nv_bfloat16, __nv_bfloat16, __nv_bfloat16>(x, y, gamma, beta, pe, rows, C, F, eps, st);
+    default:
+      vst_set_error("layernorm: unsupported dtype combination in=%d out=%d param=%d", in_dtype,
+                    out_dtype, param_dtype);
+      return VST_E_UNSUPPORTED;
+  }
+}

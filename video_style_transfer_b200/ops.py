@@ -1,0 +1,232 @@
+"""Tensor-level entry points over the C ABI (include/vst_b200.h).  torch is plumbing here:
+device memory, the current stream and dtype checks.  All arithmetic happens in libvst_b200.so.
+"""
+import math
+from typing import Optional, Tuple
+
+import torch
+
+from ._lib import VST_BF16, VST_F32, check, lib
+
+_DT = {torch.float32: VST_F32, torch.bfloat16: VST_BF16}
+
+
+def _dt(t: torch.Tensor) -> int:
+    try:
+        return _DT[t.dtype]
+    except KeyError:
+        raise TypeError(f"unsupported dtype {t.dtype}: the sm_100a path takes float32 / bfloat16")
+
+
+def _cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("video_style_transfer_b200 ops need CUDA tensors (no CPU fallback)")
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _planar_strides(x5: torch.Tensor) -> Tuple[int, int, int]:
+    """(sB, sC, sF) of a (B,C,F,H,W) view whose (H,W) block is contiguous."""
+    b, c, f, h, w = x5.shape
+    if h * w > 1 and not (x5.stride(4) == 1 and (h == 1 or x5.stride(3) == w)):
+        raise ValueError("the (H,W) plane of the (B,C,F,H,W) view must be contiguous")
+    return x5.stride(0), x5.stride(1), x5.stride(2)
+
+
+# ---- a9 -------------------------------------------------------------------------------------------
+def rearrange_fwd(x5: torch.Tensor, pe: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """(B,C,F,H,W) view -> (B*H*W, F, C) [+ pe[:F]]; temporal_transformer.py:129-133."""
+    _cuda(x5, pe)
+    b, c, f, h, w = x5.shape
+    sB, sC, sF = _planar_strides(x5)
+    y = torch.empty((b * h * w, f, c), dtype=x5.dtype, device=x5.device)
+    if pe is not None:
+        pe = pe.reshape(-1, pe.shape[-1])
+        if pe.dtype != torch.float32 or not pe.is_contiguous() or pe.shape[0] < f or pe.shape[1] != c:
+            raise ValueError("pe must be a contiguous fp32 (>=F, C) table")
+    check(lib.vst_rearrange_fwd(x5.data_ptr(), y.data_ptr(), _ptr(pe), b, c, f, h * w, sB, sC, sF,
+                                _dt(x5), _dt(y), _stream()), "vst_rearrange_fwd")
+    return y
+
+
+def rearrange_bwd(y: torch.Tensor, b: int, h: int, w: int, residual5: Optional[torch.Tensor] = None,
+                  frames_major: bool = False) -> torch.Tensor:
+    """(B*H*W, F, C) -> (B,C,F,H,W) contiguous (temporal_transformer.py:143-144), or, with
+    frames_major, the (B,C,F,H,W) view of a fresh (B*F,C,H,W) tensor.  residual5 (same view
+    geometry as the output) is added in the store."""
+    _cuda(y, residual5)
+    n, f, c = y.shape
+    assert n == b * h * w and y.is_contiguous()
+    if frames_major:
+        out = torch.empty((b, f, c, h, w), dtype=y.dtype, device=y.device).permute(0, 2, 1, 3, 4)
+    else:
+        out = torch.empty((b, c, f, h, w), dtype=y.dtype, device=y.device)
+    sB, sC, sF = _planar_strides(out)
+    if residual5 is not None:
+        if residual5.shape != out.shape or residual5.stride() != out.stride() or residual5.dtype != y.dtype:
+            raise ValueError("residual must have the output's shape, strides and dtype")
+    check(lib.vst_rearrange_bwd(y.data_ptr(), out.data_ptr(), _ptr(residual5), b, c, f, h * w, sB,
+                                sC, sF, _dt(y), _dt(out), _stream()), "vst_rearrange_bwd")
+    return out
+
+
+# ---- a10 ------------------------------------------------------------------------------------------
+def groupnorm5d_stats(x5: torch.Tensor, groups: int = 32, eps: float = 1e-6):
+    _cuda(x5)
+    b, c, f, h, w = x5.shape
+    sB, sC, sF = _planar_strides(x5)
+    nparts = lib.vst_groupnorm5d_partials(c, f, h * w, groups)
+    if nparts <= 0:
+        raise ValueError("groupnorm5d: C must be divisible by groups")
+    partials = torch.empty((b * groups, nparts, 3), dtype=torch.float32, device=x5.device)
+    mean = torch.empty(b * groups, dtype=torch.float32, device=x5.device)
+    rstd = torch.empty_like(mean)
+    check(lib.vst_groupnorm5d_stats(x5.data_ptr(), partials.data_ptr(), b, c, f, h * w, sB, sC, sF,
+                                    groups, _dt(x5), _stream()), "vst_groupnorm5d_stats")
+    check(lib.vst_groupnorm5d_finalize(partials.data_ptr(), nparts, b, groups, eps, mean.data_ptr(),
+                                       rstd.data_ptr(), _stream()), "vst_groupnorm5d_finalize")
+    return mean, rstd
+
+
+def groupnorm5d_rearrange(x5: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor,
+                          groups: int = 32, eps: float = 1e-6):
+    """GroupNorm over (C/groups, F, H, W) of the (B,C,F,H,W) view, written straight into the
+    (B*H*W, F, C) token layout.  Returns (tokens, mean, rstd)."""
+    _cuda(x5, gamma, beta)
+    b, c, f, h, w = x5.shape
+    mean, rstd = groupnorm5d_stats(x5, groups, eps)
+    sB, sC, sF = _planar_strides(x5)
+    if gamma.dtype != beta.dtype:
+        raise TypeError("gamma/beta dtype mismatch")
+    y = torch.empty((b * h * w, f, c), dtype=x5.dtype, device=x5.device)
+    check(lib.vst_groupnorm5d_apply_rearrange(
+        x5.data_ptr(), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gamma.data_ptr(),
+        beta.data_ptr(), b, c, f, h * w, sB, sC, sF, groups, _dt(x5), _dt(y), _dt(gamma),
+        _stream()), "vst_groupnorm5d_apply_rearrange")
+    return y, mean, rstd
+
+
+# ---- K9 -------------------------------------------------------------------------------------------
+def layernorm(x: torch.Tensor, gamma: Optional[torch.Tensor], beta: Optional[torch.Tensor],
+              eps: float = 1e-5, pe: Optional[torch.Tensor] = None, frames: int = 1,
+              out_dtype: Optional[torch.dtype] = None) -> torch.Tensor:
+    _cuda(x, gamma, beta, pe)
+    c = x.shape[-1]
+    x2 = x.reshape(-1, c)
+    if not x2.is_contiguous():
+        x2 = x2.contiguous()
+    y = torch.empty(x2.shape, dtype=out_dtype or x.dtype, device=x.device)
+    pdt = _dt(gamma) if gamma is not None else (_dt(beta) if beta is not None else VST_F32)
+    if pe is not None:
+        pe = pe.reshape(-1, pe.shape[-1])
+        assert pe.dtype == torch.float32 and pe.is_contiguous() and pe.shape[0] >= frames
+    check(lib.vst_layernorm(x2.data_ptr(), y.data_ptr(), _ptr(gamma), _ptr(beta), _ptr(pe),
+                            x2.shape[0], c, frames, eps, _dt(x2), _dt(y), pdt, _stream()),
+          "vst_layernorm")
+    return y.reshape(x.shape)
+
+
+# ---- a8 -------------------------------------------------------------------------------------------
+def temporal_attn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int,
+                  scale: Optional[float] = None) -> torch.Tensor:
+    """q,k,v (N, F, heads*d) bf16 (last dim contiguous; row stride free) -> o (N, F, heads*d)."""
+    _cuda(q, k, v)
+    n, f, c = q.shape
+    d = c // heads
+    for t in (q, k, v):
+        if t.dtype != torch.bfloat16 or t.stride(2) != 1 or t.stride(0) != f * t.stride(1):
+            raise ValueError("temporal_attn: bf16 (N,F,C) tensors with contiguous C and dense (N,F)")
+    o = torch.empty((n, f, c), dtype=torch.bfloat16, device=q.device)
+    check(lib.vst_temporal_attn_fwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), n, f,
+                                    heads, d, q.stride(1), k.stride(1), v.stride(1), o.stride(1),
+                                    scale if scale is not None else 1.0 / math.sqrt(d), _stream()),
+          "vst_temporal_attn_fwd")
+    return o
+
+
+# ---- a3/a4/a5/a7 ----------------------------------------------------------------------------------
+def _mat(t: torch.Tensor, name: str):
+    if t.dtype != torch.bfloat16 or t.dim() != 2 or t.stride(1) != 1:
+        raise ValueError(f"lora_gemm: {name} must be a 2-D bf16 matrix with contiguous rows")
+    return t
+
+
+def lora_gemm(a1: torch.Tensor, b1: torch.Tensor, a2: Optional[torch.Tensor] = None,
+              b2: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None,
+              residual: Optional[torch.Tensor] = None, out_scale: float = 1.0,
+              out: Optional[torch.Tensor] = None,
+              out_dtype: torch.dtype = torch.bfloat16) -> torch.Tensor:
+    """out[M,N] = (a1 b1^T + a2 b2^T + bias + residual) * out_scale."""
+    _cuda(a1, b1, a2, b2, bias, residual, out)
+    _mat(a1, "a1"), _mat(b1, "b1")
+    m, k1 = a1.shape
+    n = b1.shape[0]
+    assert b1.shape[1] == k1
+    k2 = 0
+    if a2 is not None:
+        _mat(a2, "a2"), _mat(b2, "b2")
+        k2 = a2.shape[1]
+        assert a2.shape[0] == m and b2.shape == (n, k2)
+    if out is None:
+        out = torch.empty((m, n), dtype=out_dtype, device=a1.device)
+    assert out.shape == (m, n) and out.stride(1) == 1
+    if residual is not None:
+        assert residual.shape == (m, n) and residual.stride(1) == 1 and residual.dtype == out.dtype
+    check(lib.vst_lora_gemm(
+        a1.data_ptr(), a1.stride(0), b1.data_ptr(), b1.stride(0), k1,
+        _ptr(a2), a2.stride(0) if a2 is not None else 0, _ptr(b2),
+        b2.stride(0) if b2 is not None else 0, k2,
+        _ptr(bias), _dt(bias) if bias is not None else VST_F32,
+        _ptr(residual), residual.stride(0) if residual is not None else 0, out_scale,
+        out.data_ptr(), out.stride(0), m, n, _dt(out), _stream()), "vst_lora_gemm")
+    return out
+
+
+def lora_pack_up(b_c: Optional[torch.Tensor], m_c: Optional[torch.Tensor],
+                 mask_c: Optional[torch.Tensor], b_s: Optional[torch.Tensor],
+                 m_s: Optional[torch.Tensor], mask_s: Optional[torch.Tensor],
+                 scale: float) -> torch.Tensor:
+    """[scale*m_c*mask_c (.) B_c | scale*m_s*mask_s (.) B_s] as one bf16 (N, nbr*r) matrix."""
+    ref = b_c if b_c is not None else b_s
+    _cuda(b_c, m_c, mask_c, b_s, m_s, mask_s)
+    n, r = ref.shape
+    nbr = (b_c is not None) + (b_s is not None)
+    for t in (b_c, m_c, b_s, m_s):
+        if t is not None and (t.dtype != ref.dtype or not t.is_contiguous()):
+            raise ValueError("lora_pack_up: parameters must share a dtype and be contiguous")
+    masks = []
+    for mk in (mask_c, mask_s):
+        masks.append(None if mk is None else mk.to(torch.uint8).contiguous())
+    out = torch.empty((n, nbr * r), dtype=torch.bfloat16, device=ref.device)
+    check(lib.vst_lora_pack_up(_ptr(b_c), _ptr(m_c), _ptr(masks[0]), _ptr(b_s), _ptr(m_s),
+                               _ptr(masks[1]), scale, out.data_ptr(), n, r, _dt(ref), _stream()),
+          "vst_lora_pack_up")
+    return out
+
+
+# ---- a2 -------------------------------------------------------------------------------------------
+def attn_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int,
+             scale: Optional[float] = None, return_lse: bool = False):
+    """q (Bt,Sq,h*64), k/v (Bk,Sk,h*64) bf16, Bt % Bk == 0 (batch b reads kv batch b//(Bt/Bk))."""
+    _cuda(q, k, v)
+    bt, sq, c = q.shape
+    bk, sk, _ = k.shape
+    d = c // heads
+    for t in (q, k, v):
+        if t.dtype != torch.bfloat16 or t.stride(2) != 1 or t.stride(0) != t.shape[1] * t.stride(1):
+            raise ValueError("attn_fwd: bf16 (B,S,C) tensors with contiguous C and dense (B,S)")
+    assert v.shape == k.shape and bt % bk == 0
+    o = torch.empty((bt, sq, c), dtype=torch.bfloat16, device=q.device)
+    lse = torch.empty((bt, heads, sq), dtype=torch.float32, device=q.device) if return_lse else None
+    check(lib.vst_attn_fwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), _ptr(lse), bt,
+                           heads, sq, sk, d, q.stride(1), k.stride(1), v.stride(1), o.stride(1),
+                           bt // bk, scale if scale is not None else 1.0 / math.sqrt(d), _stream()),
+          "vst_attn_fwd")
+    return (o, lse) if return_lse else o
