@@ -22,6 +22,9 @@ extern "C" {
 #define VST_F32 0
 #define VST_BF16 1
 
+#define VST_ACT_NONE 0
+#define VST_ACT_GELU 1
+
 #define VST_OK 0
 #define VST_E_BADARG (-1)
 #define VST_E_UNSUPPORTED (-2)
@@ -83,7 +86,8 @@ int vst_temporal_attn_fwd(const void* q, const void* k, const void* v, void* o, 
                           int64_t ldo, float scale, void* stream);
 
 /* ---- a3/a4/a5/a7: fused LoRA GEMM ----------------------------------------------------------
- * D[M,N] = (A1[M,K1] * B1[N,K1]^T + A2[M,K2] * B2[N,K2]^T + bias[N] + residual[M,N]) * out_scale
+ * D[M,N] = (act(A1[M,K1] * B1[N,K1]^T + A2[M,K2] * B2[N,K2]^T + bias[N]) + residual[M,N]) * out_scale
+ * act: VST_ACT_NONE, or VST_ACT_GELU (exact erf GELU: temporal_transformer.py:53-55).
  * bf16 operands, fp32 accumulation in TMEM (tcgen05), bf16 or fp32 output.
  * It is the single GEMM behind
  *   unziplora_unet/lora_linear.py:74-81 + unziplora_linear_layer.py:298-346 (A1=x, B1=W,
@@ -95,14 +99,20 @@ int vst_temporal_attn_fwd(const void* q, const void* k, const void* v, void* o, 
 int vst_lora_gemm(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1,
                   const void* A2, int64_t lda2, const void* B2, int64_t ldb2, int K2,
                   const void* bias, int bias_dtype, const void* residual, int64_t ldr,
-                  float out_scale, void* D, int64_t ldd, int64_t M, int N, int out_dtype,
-                  void* stream);
+                  float out_scale, int act, void* D, int64_t ldd, int64_t M, int N,
+                  int out_dtype, void* stream);
 /* B2'[n, j] = scale * m[n] * mask[n] * B[n, j] for up to two branches packed side by side
  * (columns [0,r) content, [r,2r) style); m/mask may be NULL (=1).  unziplora_linear_layer.py
  * :313,:321 (merger), :236-237 (hard mask), lora_linear.py:81 (scale). */
 int vst_lora_pack_up(const void* Bc, const void* mc, const uint8_t* maskc, const void* Bs,
                      const void* ms, const uint8_t* masks, float scale, void* out, int N, int r,
                      int param_dtype, void* stream);
+
+/* ---- §8f-1 (next): GEGLU gate of the motion feed-forward ------------------------------------
+ * out[r, j] = hg[r, j] * gelu(hg[r, inner + j]); diffusers FeedForward("geglu") (un-vendored),
+ * exact GELU as animatediff/temporal_transformer.py:55.  bf16. */
+int vst_geglu(const void* hg, void* out, int64_t rows, int inner, int64_t ld_in, int64_t ld_out,
+              void* stream);
 
 /* ---- a2: spatial self / text cross attention (flash, tcgen05) -------------------------------
  * animatediff/attention_processor.py:74-83 (head split, SDPA, head merge) in one kernel.

@@ -168,6 +168,39 @@ def main():
                     continue
                 _close(go, gr, 1e-5, tag + k)
                 g[f"{tag}/{k}"] = gr.clone()
+    # host-side bookkeeping of the training layer (reference :53-220), pinned for the drop-in
+    tl.set_forward("both"); tl.set_layer_mask("content", False); tl.set_layer_mask("style", False)
+    tl.zero_grad()
+    tl(x.clone(), x2.clone()).backward(dy)
+    for k in W:
+        g[f"book/grad_{k}"] = tl.lora_matrix_dic[k].weight.grad.clone()
+    g["book/grad_merge_content"] = tl.merge_content.grad.clone()
+    g["book/grad_merge_style"] = tl.merge_style.grad.clone()
+    g["book/similarity_unmasked"] = tl.compute_mergers_similarity()
+    for key in ("content", "style"):
+        g[f"book/norm_L2_{key}"] = tl.get_unziplora_norm(key, "L2")
+        g[f"book/norm_L1_{key}"] = tl.get_unziplora_norm(key, "L1", multiple=False)
+        d_, u_ = tl.get_unziplora_weight(key)
+        g[f"book/weight_up_{key}"] = u_.clone()
+        tl.set_cone_score(key)
+        tl.get_unziplora_cone(key, accumulate=True)
+        g[f"book/cone_acc_{key}"] = getattr(tl, f"column_score_{key}").clone()
+        tl.get_unziplora_cone(key, accumulate=False)
+        g[f"book/cone_sparsity_{key}"] = getattr(tl, f"column_score_{key}").clone()
+    tl.column_score_content = torch.rand(fout)
+    tl.column_score_style = torch.rand(fout)
+    g["book/score_content"], g["book/score_style"] = tl.column_score_content.clone(), tl.column_score_style.clone()
+    tl.mask_content = torch.zeros(fout, dtype=torch.bool)
+    tl.mask_style = torch.zeros(fout, dtype=torch.bool)
+    tl.mask_updated_elements(None, step_ratio=0.25, avoid=True)
+    g["book/mask_content_after"], g["book/mask_style_after"] = tl.mask_content.clone(), tl.mask_style.clone()
+    tl.set_layer_mask("content", True); tl.set_layer_mask("style", True)
+    g["book/similarity_masked"] = tl.compute_mergers_similarity()
+    tl.set_gradient_mask(False)
+    g["book/grad_merge_content_overlap"] = tl.merge_content.grad.clone()
+    tl.mask_updated_elements("style", step_ratio=0.5)
+    g["book/mask_content_keyed"], g["book/mask_style_keyed"] = tl.mask_content.clone(), tl.mask_style.clone()
+    g["book/log_selected_style"] = tl.log_selected_mask("style")
     np.savez_compressed(os.path.join(OUT, "unziplora.npz"), **_np(g))
 
     # ---- a3/a5: LoRACompatibleLinear (both variants) + a7 TemporalLoRALinear ----------
@@ -214,11 +247,55 @@ def main():
     g.update(t_weight=base.weight, t_bias=base.bias, t_A=tlo.lora_A, t_B=tlo.lora_B,
              t_scale=tlo.scale, t_x=xt, t_y=yt, t_dy=dyt, t_dx=xt.grad, t_dA=tlo.lora_A.grad,
              t_dB=tlo.lora_B.grad, t_delta=tlo.get_delta(), t_merged=tlo.merged_weight())
+    # compute_orth_loss / merged checkpoint on a two-module toy "unet" (temporal_lora.py:126-192)
+    from animatediff.temporal_lora import (compute_orth_loss, build_spatial_lora_index,
+                                           inject_temporal_lora, get_merged_motion_state_dict)
+    torch.manual_seed(7)
+
+    class Attn(torch.nn.Module):
+        def __init__(self, dim, spatial):
+            super().__init__()
+            mk_ = (lambda: LoRACompatibleLinear(dim, dim)) if spatial else (lambda: torch.nn.Linear(dim, dim))
+            self.to_q, self.to_k, self.to_v = mk_(), mk_(), mk_()
+            self.to_out = torch.nn.ModuleList([mk_(), torch.nn.Dropout(0.0)])
+
+    def toy(dim=16, r=4):
+        unet = torch.nn.Module()
+        blk = torch.nn.Module()
+        sp = torch.nn.Module(); sp.transformer_blocks = torch.nn.ModuleList([torch.nn.Module()])
+        sp.transformer_blocks[0].attn1 = Attn(dim, True)
+        mm = torch.nn.Module(); mm.temporal_transformer = torch.nn.Module()
+        mm.temporal_transformer.transformer_blocks = torch.nn.ModuleList([torch.nn.Module()])
+        mm.temporal_transformer.transformer_blocks[0].attn1 = Attn(dim, False)
+        blk.attentions = torch.nn.ModuleList([sp]); blk.motion_modules = torch.nn.ModuleList([mm])
+        unet.down_blocks = torch.nn.ModuleList([blk])
+        for lin in (sp.transformer_blocks[0].attn1.to_q, sp.transformer_blocks[0].attn1.to_k,
+                    sp.transformer_blocks[0].attn1.to_v, sp.transformer_blocks[0].attn1.to_out[0]):
+            lin.set_lora_layer(UnZipLoRALinearLayerInfer(dim, dim, r, ["content", "style"]))
+        return unet
+
+    unet = toy()
+    g["toy/state"] = np.array(0)
+    for k, v in unet.state_dict().items():
+        g[f"toy/sd/{k}"] = v.clone()
+    n_wrapped = inject_temporal_lora(unet, rank=4, alpha=2.0)
+    with torch.no_grad():
+        for n_, m_ in unet.named_modules():
+            if isinstance(m_, TemporalLoRALinear):
+                m_.lora_B.normal_(0, 0.3)
+                g[f"toy/lora/{n_}.lora_A"] = m_.lora_A.clone()
+                g[f"toy/lora/{n_}.lora_B"] = m_.lora_B.clone()
+    idx = build_spatial_lora_index(unet)
+    g["toy/n_wrapped"] = n_wrapped
+    g["toy/index_keys"] = np.array(sorted(idx.keys()))
+    g["toy/orth_loss"] = compute_orth_loss(unet, idx, 1e-2).detach()
+    for k, v in get_merged_motion_state_dict(unet).items():
+        g[f"toy/merged/{k}"] = v
     np.savez_compressed(os.path.join(OUT, "lora_linear.npz"), **_np(g))
 
     # ---- a1: AnimateDiffAttnProcessor2_0 on a duck-typed attn ---------------------------
     g = {}
-    C, heads, ctx, rr = 64, 4, 24, 8
+    C, heads, ctx, rr = 128, 2, 24, 8
     torch.manual_seed(6)
 
     def mk(i, o, bias):

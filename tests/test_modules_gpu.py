@@ -1,0 +1,262 @@
+"""-m gpu parity tests of the drop-in modules (the reference's plugin surface) against the golden
+vectors produced by the reference's own modules and against the CPU oracle on seeded inputs.
+bf16 tolerance: max|a-b| / max|b| <= 1e-2 per tensor (north_star)."""
+import os
+import types
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+TOL = 1e-2
+
+
+def T(a):
+    return torch.from_numpy(np.asarray(a))
+
+
+def sub(g, prefix):
+    return {k[len(prefix):]: T(g[k]) for k in g.files if k.startswith(prefix)}
+
+
+def rel(a, b):
+    a, b = a.detach().float().cpu(), b.detach().float().cpu()
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1e-30)).item()
+
+
+# ---- a11 / config 1 -------------------------------------------------------------------------------------
+@pytest.mark.parametrize("tag", ["tiny", "d40"])
+def test_temporal_transformer_golden(tag):
+    from video_style_transfer_b200.animatediff.temporal_transformer import TemporalTransformer
+    g = np.load(os.path.join(GOLD, "temporal_transformer.npz"))
+    b, c, f, h, w, layers, heads = [int(v) for v in g[f"{tag}/meta"]]
+    m = TemporalTransformer(c, layers, heads)
+    m.load_state_dict(sub(g, f"{tag}/sd/"))
+    m = m.cuda()
+    y = m(T(g[f"{tag}/x"]).cuda(), num_frames=f)
+    assert y.dtype == torch.float32 and y.shape == (b, c, f, h, w)
+    assert rel(y, T(g[f"{tag}/y"])) < TOL
+
+
+def test_temporal_transformer_config1_vs_oracle():
+    """BASELINE config 1 at full size: 1x320x16x32x32 fp32, TemporalTransformer(320, 2, 8)."""
+    from oracle import hotpath as hp
+    from video_style_transfer_b200.animatediff.temporal_transformer import TemporalTransformer
+    torch.manual_seed(0)
+    m = TemporalTransformer(320, 2, 8)
+    x = torch.randn(1, 320, 16, 32, 32)
+    want = hp.temporal_transformer(x, {k: v.float() for k, v in m.state_dict().items()}, 2, 8)
+    y = m.cuda()(x.cuda(), num_frames=16)
+    assert rel(y, want) < TOL
+    cos = torch.nn.functional.cosine_similarity(y.cpu().flatten(), want.flatten(), dim=0)
+    assert cos > 0.999
+
+
+# ---- a3/a4: UnZipLoRA layers --------------------------------------------------------------------------
+def _load_layer(cls, p, **kw):
+    lay = cls(48, 40, 8, ["content", "style"], **kw)
+    with torch.no_grad():
+        for k in ("content_down", "content_up", "style_down", "style_up"):
+            lay.lora_matrix_dic[k].weight.copy_(p[k])
+        lay.merge_content.copy_(p["merge_content"])
+        lay.merge_style.copy_(p["merge_style"])
+    return lay.cuda()
+
+
+def test_unziplora_infer_golden():
+    from video_style_transfer_b200.unziplora_unet.unziplora_linear_layer import UnZipLoRALinearLayerInfer
+    g = np.load(os.path.join(GOLD, "unziplora.npz"))
+    p = sub(g, "infer/")
+    lay = _load_layer(UnZipLoRALinearLayerInfer, p)
+    x, x2 = p["x"].cuda(), p["x2"].cuda()
+    scale = p["y_both_00_1"].abs().max()
+    for ft in ("both", "content", "style"):
+        for mc in (0, 1):
+            for ms in (0, 1):
+                lay.set_forward(ft)
+                lay.set_layer_mask("content", bool(mc))
+                lay.set_layer_mask("style", bool(ms))
+                for two in (0, 1):
+                    y = lay(x, x2 if two else None)
+                    want = p[f"y_{ft}_{mc}{ms}_{two}"]
+                    assert y.shape == want.shape and y.dtype == torch.float32
+                    assert ((y.cpu() - want).abs().max() / scale).item() < TOL, (ft, mc, ms, two)
+
+
+def test_unziplora_train_forward_golden():
+    from video_style_transfer_b200.unziplora_unet.unziplora_linear_layer import UnZipLoRALinearLayer
+    g = np.load(os.path.join(GOLD, "unziplora.npz"))
+    p, t = sub(g, "infer/"), sub(g, "train/")
+    lay = _load_layer(UnZipLoRALinearLayer, t, lora_matrix_num=2)
+    lay.mask_content, lay.mask_style = t["mask_content"].cuda(), t["mask_style"].cuda()
+    x, x2 = p["x"].cuda(), p["x2"].cuda()
+    scale = t["both_0/y"].abs().max()
+    for ft in ("both", "content", "style"):
+        for masked in (0, 1):
+            lay.set_forward(ft)
+            lay.set_layer_mask("content", bool(masked))
+            lay.set_layer_mask("style", bool(masked))
+            y = lay(x, x2)
+            assert ((y.cpu() - t[f"{ft}_{masked}/y"]).abs().max() / scale).item() < TOL, (ft, masked)
+
+
+def test_lora_compatible_linear_golden():
+    from video_style_transfer_b200.unziplora_unet import lora_linear, lora_unzip
+    from video_style_transfer_b200.unziplora_unet.unziplora_linear_layer import UnZipLoRALinearLayerInfer
+    g = np.load(os.path.join(GOLD, "lora_linear.npz"))
+    u = sub(np.load(os.path.join(GOLD, "unziplora.npz")), "infer/")
+    lay = _load_layer(UnZipLoRALinearLayerInfer, u)
+    for cls, args, key in ((lora_linear.LoRACompatibleLinear, (), "y"),
+                           (lora_unzip.LoRACompatibleLinear, ("x1", "x2"), "y3")):
+        lin = cls(48, 40)
+        with torch.no_grad():
+            lin.weight.copy_(T(g["weight"]))
+            lin.bias.copy_(T(g["bias"]))
+        lin = lin.cuda()
+        lin.set_lora_layer(lay)
+        assert hasattr(lin, "set_lora_layer") and lin.lora_layer is lay
+        y = lin(T(g["x"]).cuda(), float(g["scale"]), *[T(g[a]).cuda() for a in args])
+        assert rel(y, T(g[key])) < TOL
+        lin.set_lora_layer(None)
+        y0 = lin(T(g["x"]).cuda())
+        assert rel(y0, torch.nn.functional.linear(T(g["x"]), T(g["weight"]), T(g["bias"]))) < TOL
+
+
+def test_temporal_lora_linear_golden():
+    from video_style_transfer_b200.animatediff.temporal_lora import TemporalLoRALinear
+    g = np.load(os.path.join(GOLD, "lora_linear.npz"))
+    base = torch.nn.Linear(48, 40)
+    with torch.no_grad():
+        base.weight.copy_(T(g["t_weight"]))
+        base.bias.copy_(T(g["t_bias"]))
+    m = TemporalLoRALinear(base, rank=4, alpha=2.0)
+    with torch.no_grad():
+        m.lora_A.copy_(T(g["t_A"]))
+        m.lora_B.copy_(T(g["t_B"]))
+    y = m.cuda()(T(g["t_x"]).cuda())
+    assert rel(y, T(g["t_y"])) < TOL
+
+
+# ---- a1: the attention processor ------------------------------------------------------------------------
+def _build_attn(g, kind, dtype=torch.float32):
+    from video_style_transfer_b200.unziplora_unet.lora_linear import LoRACompatibleLinear
+    from video_style_transfer_b200.unziplora_unet.unziplora_linear_layer import UnZipLoRALinearLayerInfer
+
+    def mk(nm):
+        f = sub(g, f"{kind}/{nm}/")
+        out_f, in_f = f["weight"].shape
+        r = f["a_c"].shape[0]
+        lin = LoRACompatibleLinear(in_f, out_f, bias="bias" in f)
+        lay = UnZipLoRALinearLayerInfer(in_f, out_f, r, ["content", "style"])
+        with torch.no_grad():
+            lin.weight.copy_(f["weight"])
+            if "bias" in f:
+                lin.bias.copy_(f["bias"])
+            d = lay.lora_matrix_dic
+            d["content_down"].weight.copy_(f["a_c"]); d["content_up"].weight.copy_(f["b_c"])
+            d["style_down"].weight.copy_(f["a_s"]); d["style_up"].weight.copy_(f["b_s"])
+            lay.merge_content.copy_(f["m_c"]); lay.merge_style.copy_(f["m_s"])
+        lin.set_lora_layer(lay)
+        return lin.cuda().to(dtype)
+
+    heads, res = [int(v) for v in g[f"{kind}/meta"]]
+    return types.SimpleNamespace(
+        spatial_norm=None, group_norm=None, norm_cross=False, heads=heads, to_q=mk("to_q"),
+        to_k=mk("to_k"), to_v=mk("to_v"),
+        to_out=torch.nn.ModuleList([mk("to_out"), torch.nn.Dropout(0.0)]),
+        residual_connection=bool(res), rescale_output_factor=float(g[f"{kind}/rescale"]))
+
+
+@pytest.mark.parametrize("kind", ["self", "cross"])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_attn_processor_golden(kind, dtype):
+    from video_style_transfer_b200.animatediff.attention_processor import AnimateDiffAttnProcessor2_0
+    g = np.load(os.path.join(GOLD, "attn_processor.npz"))
+    attn = _build_attn(g, kind, dtype)
+    proc = AnimateDiffAttnProcessor2_0()
+    ehs = T(g["cross/ehs"]).cuda().to(dtype) if kind == "cross" else None
+    y = proc(attn, T(g[f"{kind}/hs"]).cuda().to(dtype), ehs, scale=0.9, some_unknown_kwarg=1)
+    assert y.dtype == dtype
+    assert rel(y, T(g[f"{kind}/y"])) < (TOL if dtype == torch.float32 else 2 * TOL)
+    if kind == "self":
+        y4 = proc(attn, T(g["self/hs4"]).cuda().to(dtype), None, scale=0.9)
+        assert y4.shape == tuple(g["self/hs4"].shape)
+        assert rel(y4, T(g["self/y4"])) < (TOL if dtype == torch.float32 else 2 * TOL)
+
+
+def test_attn_processor_sdxl_midblock_vs_oracle():
+    """Config-2 geometry (SDXL mid-block: C=1280, 20 heads, ctx 2048, rank 64) at a reduced
+    token count the CPU oracle finishes in seconds."""
+    from oracle import processor as op
+    from video_style_transfer_b200.animatediff.attention_processor import AnimateDiffAttnProcessor2_0
+    from video_style_transfer_b200.unziplora_unet.lora_linear import LoRACompatibleLinear
+    from video_style_transfer_b200.unziplora_unet.unziplora_linear_layer import UnZipLoRALinearLayerInfer
+    torch.manual_seed(0)
+    C, heads, ctx, r = 1280, 20, 2048, 64
+
+    def mk(i, o, bias):
+        lin = LoRACompatibleLinear(i, o, bias=bias)
+        lay = UnZipLoRALinearLayerInfer(i, o, r, ["content", "style"])
+        with torch.no_grad():
+            lay.merge_content.uniform_(0, 1)
+            lay.merge_style.uniform_(0, 1)
+        lin.set_lora_layer(lay)
+        return lin
+
+    def oproj(l):
+        ll, d = l.lora_layer, l.lora_layer.lora_matrix_dic
+        f = lambda t: None if t is None else t.detach().float().cpu()
+        return op.UnzipProj(f(l.weight), f(l.bias), f(d["content_down"].weight), f(d["content_up"].weight),
+                            f(d["style_down"].weight), f(d["style_up"].weight), f(ll.merge_content),
+                            f(ll.merge_style))
+
+    proc = AnimateDiffAttnProcessor2_0()
+    for kind in ("self", "cross"):
+        kv = C if kind == "self" else ctx
+        attn = types.SimpleNamespace(
+            spatial_norm=None, group_norm=None, norm_cross=False, heads=heads,
+            to_q=mk(C, C, False), to_k=mk(kv, C, False), to_v=mk(kv, C, False),
+            to_out=torch.nn.ModuleList([mk(C, C, True), torch.nn.Dropout(0.0)]),
+            residual_connection=False, rescale_output_factor=1.0)
+        P = op.SpatialAttnParams(heads, oproj(attn.to_q), oproj(attn.to_k), oproj(attn.to_v),
+                                 oproj(attn.to_out[0]))
+        hs = torch.randn(4, 256, C)
+        ehs = None if kind == "self" else torch.randn(1, 77, ctx)
+        want = op.animatediff_attn_processor(P, hs, ehs, scale=1.0)
+        for m in (attn.to_q, attn.to_k, attn.to_v, attn.to_out):
+            m.cuda().to(torch.bfloat16)
+        y = proc(attn, hs.cuda().to(torch.bfloat16), None if ehs is None else ehs.cuda().to(torch.bfloat16))
+        assert rel(y, want) < 2 * TOL, kind
+
+
+# ---- motion module vs the (unpinned) oracle restatement ----------------------------------------------------
+@pytest.mark.parametrize("c,hw,f,lora", [(320, 8, 16, False), (640, 4, 16, True), (64, 3, 5, False)])
+def test_motion_module_vs_oracle(c, hw, f, lora):
+    from oracle import processor as op
+    from video_style_transfer_b200.motion_module import MotionModule
+    from video_style_transfer_b200.animatediff.temporal_lora import inject_temporal_lora, TemporalLoRALinear
+    torch.manual_seed(0)
+    holder = torch.nn.Module()
+    holder.motion_modules = torch.nn.ModuleList([MotionModule(c, 8)])
+    with torch.no_grad():
+        for n, p in holder.named_parameters():
+            if "norm" in n or n.endswith("bias"):
+                p.add_(0.1 * torch.randn_like(p))
+    cfg = None
+    if lora:
+        assert inject_temporal_lora(holder, rank=32, alpha=1.0) == 8
+        cfg = {"rank": 32, "scale": 1.0 / 32}
+        with torch.no_grad():
+            for m in holder.modules():
+                if isinstance(m, TemporalLoRALinear):
+                    m.lora_B.normal_(0, 0.2)
+    mm = holder.motion_modules[0]
+    w = {k: v.float() for k, v in mm.temporal_transformer.state_dict().items()}
+    w["pos_embed.pe"] = w["transformer_blocks.0.pos_embed.pe"]
+    x = torch.randn(2 * f, c, hw, hw)
+    want = op.motion_module(x, w, f, 8, 32, cfg)
+    y = mm.cuda()(x.cuda().to(torch.bfloat16), num_frames=f)
+    assert y.shape == x.shape and y.dtype == torch.bfloat16
+    assert rel(y, want) < 2 * TOL

@@ -1,0 +1,78 @@
+"""Host-side glue shared by the drop-in modules: cached bf16 operand copies and the one fused
+projection call every linear on the hot path goes through."""
+import weakref
+from typing import Dict, Optional, Sequence, Tuple
+
+import torch
+
+from . import ops
+
+_cache: Dict[Tuple, Tuple] = {}
+
+
+def _alive(refs):
+    return all(r() is not None for r in refs)
+
+
+def pad8(n: int) -> int:
+    return (n + 7) // 8 * 8
+
+
+def pad_branch_cols(bp: torch.Tensor, nbr: int, r: int) -> torch.Tensor:
+    """(N, nbr*r) packed up-projections -> (N, nbr*pad8(r)), zero columns appended per branch
+    (ranks that are not multiples of 8, e.g. the rank-4 default of LoRALinearLayer)."""
+    if r % 8 == 0:
+        return bp
+    n = bp.shape[0]
+    return torch.nn.functional.pad(bp.view(n, nbr, r), (0, pad8(r) - r)).reshape(n, nbr * pad8(r))
+
+
+def bf16_cached(*tensors: torch.Tensor, pad_rows: bool = False) -> torch.Tensor:
+    """bf16, contiguous copy of a parameter (or the row-wise concatenation of several), cached
+    until any of them is modified in place (tensor._version) or re-allocated (data_ptr).
+    pad_rows: zero-pad each tensor's row count to a multiple of 8 first (LoRA down matrices)."""
+    pad_rows = pad_rows and any(t.shape[0] % 8 for t in tensors)
+    if len(tensors) == 1 and not pad_rows:
+        t = tensors[0]
+        if t.dtype == torch.bfloat16 and t.is_contiguous():
+            return t.detach()
+    key = tuple(id(t) for t in tensors) + (pad_rows,)
+    stamp = tuple((t._version, t.data_ptr()) for t in tensors)
+    hit = _cache.get(key)
+    if hit is not None and hit[1] == stamp and _alive(hit[0]):
+        return hit[2]
+    with torch.no_grad():
+        parts = [t.detach().to(torch.bfloat16) for t in tensors]
+        if pad_rows:
+            parts = [torch.nn.functional.pad(q, (0, 0, 0, pad8(q.shape[0]) - q.shape[0])) for q in parts]
+        val = parts[0].contiguous() if len(parts) == 1 else torch.cat(parts, dim=0).contiguous()
+    if len(_cache) > 4096:
+        for k in [k for k, v in _cache.items() if not _alive(v[0])]:
+            del _cache[k]
+    _cache[key] = (tuple(weakref.ref(t) for t in tensors), stamp, val)
+    return val
+
+
+def as_rows_bf16(x: torch.Tensor) -> torch.Tensor:
+    """(..., K) activation -> contiguous 2-D bf16 (rows, K)."""
+    x2 = x.reshape(-1, x.shape[-1])
+    if x2.dtype != torch.bfloat16:
+        x2 = x2.to(torch.bfloat16)
+    if x2.stride(1) != 1 or (x2.stride(0) % 8) != 0:
+        x2 = x2.contiguous()
+    return x2
+
+
+def fused_linear(x2: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor],
+                 low_rank: Optional[Tuple[torch.Tensor, torch.Tensor]] = None,
+                 residual: Optional[torch.Tensor] = None, out_scale: float = 1.0,
+                 act: str = "none", out_dtype: torch.dtype = torch.bfloat16) -> torch.Tensor:
+    """y = (act(x W^T + u B'^T + bias) + residual) * out_scale on the tcgen05 GEMM.
+    low_rank = (u (M,R) bf16, B' (N,R) bf16) or None."""
+    w = bf16_cached(weight)
+    b = None if bias is None else bias.detach()
+    if b is not None and b.dtype not in (torch.float32, torch.bfloat16):
+        b = b.float()
+    u, bp = low_rank if low_rank is not None else (None, None)
+    return ops.lora_gemm(x2, w, u, bp, bias=b, residual=residual, out_scale=out_scale, act=act,
+                         out_dtype=out_dtype)

@@ -27,9 +27,10 @@ SIGNATURES = {
                                              _i, _i, _i, _i, _p]),
     "vst_layernorm": (_i, [_p, _p, _p, _p, _p, _l, _i, _i, _f, _i, _i, _i, _p]),
     "vst_temporal_attn_fwd": (_i, [_p, _p, _p, _p, _l, _i, _i, _i, _l, _l, _l, _l, _f, _p]),
-    "vst_lora_gemm": (_i, [_p, _l, _p, _l, _i, _p, _l, _p, _l, _i, _p, _i, _p, _l, _f, _p, _l, _l,
-                           _i, _i, _p]),
+    "vst_lora_gemm": (_i, [_p, _l, _p, _l, _i, _p, _l, _p, _l, _i, _p, _i, _p, _l, _f, _i, _p, _l,
+                           _l, _i, _i, _p]),
     "vst_lora_pack_up": (_i, [_p, _p, _p, _p, _p, _p, _f, _p, _i, _i, _i, _p]),
+    "vst_geglu": (_i, [_p, _p, _l, _i, _l, _l, _p]),
     "vst_attn_fwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _l, _l, _l, _l, _i, _f, _p]),
 }
 
@@ -54,7 +55,12 @@ class VstError(RuntimeError):
     pass
 
 
+launch_count = 0   # kernels launched through the C ABI (each compute entry point launches one)
+
+
 def check(rc: int, what: str):
+    global launch_count
+    launch_count += 1
     if rc != 0:
         msg = lib.vst_last_error()
         raise VstError(f"{what} failed (rc={rc}): {msg.decode() if msg else ''}")

@@ -39,7 +39,7 @@ struct EpiArgs {
   int64_t ldr, ldd, M;
   int N;
   float out_scale;
-  int bias_bf16, out_f32;
+  int bias_bf16, out_f32, act;
 };
 
 template <int BN>
@@ -181,6 +181,11 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
                 o[4] += b1.x; o[5] += b1.y; o[6] += b1.z; o[7] += b1.w;
               }
             }
+            if (ep.act == 1) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                o[j] = 0.5f * o[j] * (1.f + erff(o[j] * 0.70710678118654752f));  // exact GELU
+            }
             if (ep.out_f32) {
               float* dp = reinterpret_cast<float*>(ep.D) + row * ep.ldd + col;
               if (ep.residual != nullptr) {
@@ -299,7 +304,7 @@ __global__ void pack_up_kernel(const T* __restrict__ Bc, const T* __restrict__ m
 extern "C" int vst_lora_gemm(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1,
                              const void* A2, int64_t lda2, const void* B2, int64_t ldb2, int K2,
                              const void* bias, int bias_dtype, const void* residual, int64_t ldr,
-                             float out_scale, void* D, int64_t ldd, int64_t M, int N,
+                             float out_scale, int act, void* D, int64_t ldd, int64_t M, int N,
                              int out_dtype, void* stream) {
   VST_REQUIRE(M >= 0 && N > 0 && K1 > 0 && K2 >= 0, VST_E_BADARG, "lora_gemm: bad shape");
   if (M == 0) return VST_OK;
@@ -309,6 +314,7 @@ extern "C" int vst_lora_gemm(const void* A1, int64_t lda1, const void* B1, int64
   VST_REQUIRE(lda1 % 8 == 0 && ldb1 % 8 == 0 && (K2 == 0 || (lda2 % 8 == 0 && ldb2 % 8 == 0)),
               VST_E_UNSUPPORTED, "lora_gemm: operand row strides must be multiples of 8 elements");
   VST_REQUIRE(out_dtype == VST_F32 || out_dtype == VST_BF16, VST_E_BADARG, "lora_gemm: out dtype");
+  VST_REQUIRE(act == VST_ACT_NONE || act == VST_ACT_GELU, VST_E_BADARG, "lora_gemm: bad act %d", act);
   const int oa = out_dtype == VST_F32 ? 4 : 8;
   VST_REQUIRE(ldd % oa == 0 && (residual == nullptr || ldr % oa == 0), VST_E_UNSUPPORTED,
               "lora_gemm: output/residual row strides must keep 16-byte alignment");
@@ -317,7 +323,7 @@ extern "C" int vst_lora_gemm(const void* A1, int64_t lda1, const void* B1, int64
                   (reinterpret_cast<uintptr_t>(bias) & 15) == 0,
               VST_E_UNSUPPORTED, "lora_gemm: D/residual/bias must be 16-byte aligned");
   EpiArgs ep{bias, residual, D, ldr, ldd, M, N, out_scale, bias_dtype == VST_BF16,
-             out_dtype == VST_F32};
+             out_dtype == VST_F32, act};
   cudaStream_t st = (cudaStream_t)stream;
 #define GO(BNV) return launch<BNV>(A1, lda1, B1, ldb1, K1, A2, lda2, B2, ldb2, K2, ep, st)
   if (N % 256 == 0) GO(256);

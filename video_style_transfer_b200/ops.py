@@ -161,9 +161,9 @@ def _mat(t: torch.Tensor, name: str):
 def lora_gemm(a1: torch.Tensor, b1: torch.Tensor, a2: Optional[torch.Tensor] = None,
               b2: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None,
               residual: Optional[torch.Tensor] = None, out_scale: float = 1.0,
-              out: Optional[torch.Tensor] = None,
+              act: str = "none", out: Optional[torch.Tensor] = None,
               out_dtype: torch.dtype = torch.bfloat16) -> torch.Tensor:
-    """out[M,N] = (a1 b1^T + a2 b2^T + bias + residual) * out_scale."""
+    """out[M,N] = (act(a1 b1^T + a2 b2^T + bias) + residual) * out_scale; act in {none, gelu}."""
     _cuda(a1, b1, a2, b2, bias, residual, out)
     _mat(a1, "a1"), _mat(b1, "b1")
     m, k1 = a1.shape
@@ -185,7 +185,7 @@ def lora_gemm(a1: torch.Tensor, b1: torch.Tensor, a2: Optional[torch.Tensor] = N
         b2.stride(0) if b2 is not None else 0, k2,
         _ptr(bias), _dt(bias) if bias is not None else VST_F32,
         _ptr(residual), residual.stride(0) if residual is not None else 0, out_scale,
-        out.data_ptr(), out.stride(0), m, n, _dt(out), _stream()), "vst_lora_gemm")
+        {"none": 0, "gelu": 1}[act], out.data_ptr(), out.stride(0), m, n, _dt(out), _stream()), "vst_lora_gemm")
     return out
 
 
@@ -230,3 +230,16 @@ def attn_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int,
                            bt // bk, scale if scale is not None else 1.0 / math.sqrt(d), _stream()),
           "vst_attn_fwd")
     return (o, lse) if return_lse else o
+
+
+# ---- §8f-1 ----------------------------------------------------------------------------------------
+def geglu(hg: torch.Tensor) -> torch.Tensor:
+    """hg (rows, 2*inner) bf16 -> hg[:, :inner] * gelu(hg[:, inner:])."""
+    _cuda(hg)
+    assert hg.dtype == torch.bfloat16 and hg.dim() == 2 and hg.stride(1) == 1
+    rows, two = hg.shape
+    inner = two // 2
+    out = torch.empty((rows, inner), dtype=torch.bfloat16, device=hg.device)
+    check(lib.vst_geglu(hg.data_ptr(), out.data_ptr(), rows, inner, hg.stride(0), out.stride(0),
+                        _stream()), "vst_geglu")
+    return out

@@ -1,0 +1,173 @@
+"""The SDXL-AnimateDiff hot-path stack: every spatial attention (UnZipLoRA, rank 64 content+style)
+and every motion module (temporal LoRA, rank 32) of one ``UNetMotionModel`` forward, under the
+module names diffusers gives them, random-initialised.  It is the workload of BASELINE config 3
+restricted to SURVEY.md §8's hot path -- the ResNet / conv / spatial feed-forward layers between
+these modules belong to the un-vendored diffusers UNet and are out of scope.
+
+SDXL geometry (unziplora_unet/utils.py:35-47,88-104): latent side S = 128 at 1024^2;
+  L0  C=320   S^2        no spatial attention          motion modules: down 2 + up 3
+  L1  C=640   (S/2)^2    2 blocks/attn, 10 heads       attn: down 2 + up 3   motion: 2 + 3
+  L2  C=1280  (S/4)^2    10 blocks/attn, 20 heads      attn: down 2 + mid 1 + up 3   motion: 2 + 3
+=> 70 self + 70 cross attention calls and 15 motion modules per UNet forward.
+"""
+from typing import List, Tuple
+
+import torch
+import torch.nn as nn
+
+from .animatediff.attention_processor import AnimateDiffAttnProcessor2_0
+from .animatediff.temporal_lora import inject_temporal_lora
+from .motion_module import MotionModule
+from .unziplora_unet.lora_linear import LoRACompatibleLinear
+from .unziplora_unet.unziplora_linear_layer import UnZipLoRALinearLayerInfer
+
+TEXT_DIM = 2048
+TEXT_LEN = 77
+
+
+class SpatialAttention(nn.Module):
+    """The slice of diffusers' ``Attention`` that the processor protocol reads
+    (animatediff/attention_processor.py:30-94; SURVEY.md §8b duck-type)."""
+
+    def __init__(self, query_dim: int, heads: int, cross_dim: int = None, rank: int = 64):
+        super().__init__()
+        kv = cross_dim or query_dim
+        self.heads = heads
+        self.spatial_norm = None
+        self.group_norm = None
+        self.norm_cross = None
+        self.residual_connection = False
+        self.rescale_output_factor = 1.0
+        self.to_q = LoRACompatibleLinear(query_dim, query_dim, bias=False)
+        self.to_k = LoRACompatibleLinear(kv, query_dim, bias=False)
+        self.to_v = LoRACompatibleLinear(kv, query_dim, bias=False)
+        self.to_out = nn.ModuleList([LoRACompatibleLinear(query_dim, query_dim, bias=True),
+                                     nn.Dropout(0.0)])
+        for lin in (self.to_q, self.to_k, self.to_v, self.to_out[0]):
+            lay = UnZipLoRALinearLayerInfer(lin.in_features, lin.out_features, rank,
+                                            ["content", "style"])
+            with torch.no_grad():
+                lay.merge_content.uniform_(0, 1)
+                lay.merge_style.uniform_(0, 1)
+            lin.set_lora_layer(lay)
+        self.processor = None       # created on first use (needs a CUDA device)
+
+    def set_processor(self, processor):
+        self.processor = processor
+
+    def forward(self, hidden_states, encoder_hidden_states=None, **kw):
+        if self.processor is None:
+            self.processor = AnimateDiffAttnProcessor2_0()
+        return self.processor(self, hidden_states, encoder_hidden_states=encoder_hidden_states, **kw)
+
+
+class _Block(nn.Module):
+    def __init__(self, dim, heads):
+        super().__init__()
+        self.attn1 = SpatialAttention(dim, heads)
+        self.attn2 = SpatialAttention(dim, heads, TEXT_DIM)
+
+
+class _Transformer2D(nn.Module):
+    def __init__(self, dim, heads, depth):
+        super().__init__()
+        self.transformer_blocks = nn.ModuleList([_Block(dim, heads) for _ in range(depth)])
+
+
+class _UNetBlock(nn.Module):
+    def __init__(self, dim, n_attn, depth, n_motion):
+        super().__init__()
+        self.dim = dim
+        if n_attn:
+            self.attentions = nn.ModuleList([_Transformer2D(dim, dim // 64, depth)
+                                             for _ in range(n_attn)])
+        if n_motion:
+            self.motion_modules = nn.ModuleList([MotionModule(dim, 8) for _ in range(n_motion)])
+
+
+class SDXLHotPath(nn.Module):
+    """levels: (C, latent-side divisor).  ``forward_plan()`` lists the modules in UNet order."""
+
+    def __init__(self, temporal_rank: int = 32, depth_scale: float = 1.0):
+        super().__init__()
+        d2, d10 = max(1, round(2 * depth_scale)), max(1, round(10 * depth_scale))
+        self.down_blocks = nn.ModuleList([_UNetBlock(320, 0, 0, 2), _UNetBlock(640, 2, d2, 2),
+                                          _UNetBlock(1280, 2, d10, 2)])
+        self.mid_block = _UNetBlock(1280, 1, d10, 0)
+        self.up_blocks = nn.ModuleList([_UNetBlock(1280, 3, d10, 3), _UNetBlock(640, 3, d2, 3),
+                                        _UNetBlock(320, 0, 0, 3)])
+        self.n_temporal_lora = inject_temporal_lora(self, rank=temporal_rank, alpha=1.0)
+        with torch.no_grad():      # B = 0 at init would make the low-rank update a no-op
+            for n, p in self.named_parameters():
+                if n.endswith("lora_B"):
+                    p.normal_(0, 1.0 / temporal_rank)
+
+    @staticmethod
+    def level_of(dim: int) -> int:
+        return {320: 0, 640: 1, 1280: 2}[dim]
+
+    def forward_plan(self) -> List[Tuple[str, int, nn.Module]]:
+        """[(kind, level, module)] with kind in {self, cross, motion}, in UNet execution order
+        (per UNet block: attention i then motion module i, as UNetMotionModel interleaves them)."""
+        plan = []
+        for blk in list(self.down_blocks) + [self.mid_block] + list(self.up_blocks):
+            lvl = self.level_of(blk.dim)
+            attns = list(getattr(blk, "attentions", []))
+            motions = list(getattr(blk, "motion_modules", []))
+            for i in range(max(len(attns), len(motions))):
+                if i < len(attns):
+                    for tb in attns[i].transformer_blocks:
+                        plan.append(("self", lvl, tb.attn1))
+                        plan.append(("cross", lvl, tb.attn2))
+                if i < len(motions):
+                    plan.append(("motion", lvl, motions[i]))
+        return plan
+
+
+def level_shapes(frames: int, latent: int = 128, batch: int = 1):
+    """Per level: (B*F, C, H, W) hidden-state shape."""
+    return [(batch * frames, 320, latent, latent), (batch * frames, 640, latent // 2, latent // 2),
+            (batch * frames, 1280, latent // 4, latent // 4)]
+
+
+@torch.no_grad()
+def run_unet_hotpath(plan, xs4, xs3, text, frames: int):
+    """One UNet forward's worth of hot-path calls.  xs4[l]: (B*F,C,H,W) motion-module input,
+    xs3[l]: (B*F,HW,C) spatial token input, text: (B,77,2048).  Every module reads its level's
+    input (the conv/FF layers that would sit between them are out of scope) and the last output
+    per level is returned."""
+    outs = [None, None, None]
+    for kind, lvl, mod in plan:
+        if kind == "self":
+            outs[lvl] = mod(xs3[lvl])
+        elif kind == "cross":
+            outs[lvl] = mod(xs3[lvl], encoder_hidden_states=text)
+        else:
+            outs[lvl] = mod(xs4[lvl], num_frames=frames)
+    return outs
+
+
+def hotpath_flops(plan, frames: int, latent: int = 128, batch: int = 1):
+    """Algorithmic FLOPs of one UNet forward of the plan (SURVEY.md §8d formulas), by kernel family."""
+    fl = {"attn_self": 0.0, "attn_cross": 0.0, "proj": 0.0, "temporal_attn": 0.0, "motion_gemm": 0.0}
+    side = [latent, latent // 2, latent // 4]
+    dims = [320, 640, 1280]
+    for kind, lvl, _ in plan:
+        c, hw = dims[lvl], side[lvl] ** 2
+        m = batch * frames * hw
+        r2 = 128
+        if kind == "self":
+            fl["attn_self"] += 4.0 * batch * frames * hw * hw * c
+            fl["proj"] += 4 * (2.0 * m * c * c + 2.0 * m * r2 * (c + c))
+        elif kind == "cross":
+            fl["attn_cross"] += 4.0 * batch * frames * hw * TEXT_LEN * c
+            mt = batch * TEXT_LEN
+            fl["proj"] += 2 * (2.0 * m * c * c + 2.0 * m * r2 * 2 * c)
+            fl["proj"] += 2 * (2.0 * mt * TEXT_DIM * c + 2.0 * mt * r2 * (TEXT_DIM + c))
+        else:
+            n = batch * hw
+            fl["temporal_attn"] += 2 * 4.0 * n * frames * frames * c
+            fl["motion_gemm"] += 2.0 * m * c * c * 2                       # proj_in, proj_out
+            fl["motion_gemm"] += 8 * (2.0 * m * c * c + 2.0 * m * 32 * 2 * c)   # 2 x (q,k,v,out) + LoRA
+            fl["motion_gemm"] += 2.0 * m * c * 8 * c + 2.0 * m * 4 * c * c   # GEGLU FF
+    return fl
