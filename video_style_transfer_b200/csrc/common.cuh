@@ -122,28 +122,28 @@ __device__ __forceinline__ uint64_t globaltimer_ns() {
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
+// try_wait suspends the thread in hardware until the phase completes or the hint (ns) expires, so
+// a waiting role does not burn issue slots the math warps need.
+__device__ __forceinline__ uint32_t mbar_try_wait(uint32_t addr, uint32_t parity) {
+  uint32_t done;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(done)
+      : "r"(addr), "r"(parity), "r"(1000000u)
+      : "memory");
+  return done;
+}
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int tag = 0) {
   const uint32_t addr = smem_u32(bar);
-  uint32_t done;
-  uint64_t t0 = 0;
-  uint32_t spins = 0;
-  for (;;) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done)
-        : "r"(addr), "r"(parity)
-        : "memory");
-    if (done) break;
-    if ((++spins & 1023u) == 0) {
-      const uint64_t now = globaltimer_ns();
-      if (t0 == 0) t0 = now;
-      if (now - t0 > VST_WATCHDOG_NS) {
-        printf("vst watchdog: mbarrier wait timed out (tag %d, block %d,%d,%d thread %d)\n", tag,
-               blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x);
-        __trap();
-      }
+  if (mbar_try_wait(addr, parity)) return;
+  const uint64_t t0 = globaltimer_ns();
+  while (!mbar_try_wait(addr, parity)) {
+    if (globaltimer_ns() - t0 > VST_WATCHDOG_NS) {
+      printf("vst watchdog: mbarrier wait timed out (tag %d, block %d,%d,%d thread %d)\n", tag,
+             blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x);
+      __trap();
     }
   }
 }
