@@ -94,11 +94,14 @@ int vst_temporal_attn_fwd(const void* q, const void* k, const void* v, void* o, 
  *   A2=[u_c|u_s], B2=scale*[m_c.B_c | m_s.B_s]), lora_unzip.py:66-75 (u from other streams),
  *   animatediff/temporal_lora.py:29-32 (A2=u, B2=(alpha/r) B), and the u = x A^T pre-pass
  *   (K2 = 0).  K1, K2 multiples of 8; N multiple of 8; lda/ldb/ldd in elements.
+ * k2_group_n > 0 groups the low-rank term for projections fused along N (q|k|v in one GEMM):
+ * output columns [g*k2_group_n, (g+1)*k2_group_n) read A2 columns [g*K2, (g+1)*K2) and their own
+ * rows of B2[N,K2]; A2 is then [M, G*K2].  k2_group_n must be a multiple of 64 that tiles N.
  * bias is bias_dtype (VST_F32 / VST_BF16); residual has the output dtype.
  * residual/out_scale fuse attention_processor.py:91-94. */
 int vst_lora_gemm(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1,
                   const void* A2, int64_t lda2, const void* B2, int64_t ldb2, int K2,
-                  const void* bias, int bias_dtype, const void* residual, int64_t ldr,
+                  int k2_group_n, const void* bias, int bias_dtype, const void* residual, int64_t ldr,
                   float out_scale, int act, void* D, int64_t ldd, int64_t M, int N,
                   int out_dtype, void* stream);
 /* B2'[n, j] = scale * m[n] * mask[n] * B[n, j] for up to two branches packed side by side

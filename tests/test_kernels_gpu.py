@@ -205,3 +205,21 @@ def test_attn_fwd(ops, hp, bt, bk, heads, sq, sk):
     assert rel_err(o, want) < REL_TOL
     want_lse = torch.logsumexp(qq @ kk.transpose(-1, -2) / 8.0, dim=-1)
     assert torch.allclose(lse.cpu(), want_lse, atol=2e-2, rtol=1e-3)
+
+
+@pytest.mark.parametrize("m,c,k1,k2,groups", [(300, 128, 64, 16, 3), (1000, 640, 640, 128, 3),
+                                              (77, 1280, 2048, 128, 2), (513, 320, 320, 32, 3)])
+def test_lora_gemm_grouped_low_rank(ops, m, c, k1, k2, groups):
+    """q|k|v fused along N: output columns of group g read only their own K2 columns of A2."""
+    torch.manual_seed(8)
+    n = groups * c
+    a1 = torch.randn(m, k1).to(torch.bfloat16).cuda()
+    b1 = (torch.randn(n, k1) / math.sqrt(k1)).to(torch.bfloat16).cuda()
+    a2 = torch.randn(m, groups * k2).to(torch.bfloat16).cuda()
+    b2 = (torch.randn(n, k2) / math.sqrt(k2)).to(torch.bfloat16).cuda()
+    out = ops.lora_gemm(a1, b1, a2, b2, k2_group_n=c)
+    want = a1.cpu().float() @ b1.cpu().float().t()
+    for g in range(groups):
+        want[:, g * c:(g + 1) * c] += (a2.cpu().float()[:, g * k2:(g + 1) * k2]
+                                       @ b2.cpu().float()[g * c:(g + 1) * c].t())
+    assert rel_err(out, want) < REL_TOL

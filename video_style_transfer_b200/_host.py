@@ -76,3 +76,17 @@ def fused_linear(x2: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Te
     u, bp = low_rank if low_rank is not None else (None, None)
     return ops.lora_gemm(x2, w, u, bp, bias=b, residual=residual, out_scale=out_scale, act=act,
                          out_dtype=out_dtype)
+
+
+def cached_build(tensors: Sequence[torch.Tensor], extra, builder):
+    """Memoise ``builder()`` (a derived operand such as the packed, merger-scaled up-projection)
+    on the identity + in-place version of ``tensors`` and on ``extra`` (scale, forward type ...)."""
+    key = ("build",) + tuple(id(t) for t in tensors) + (extra,)
+    stamp = tuple((t._version, t.data_ptr()) for t in tensors)
+    hit = _cache.get(key)
+    if hit is not None and hit[1] == stamp and _alive(hit[0]):
+        return hit[2]
+    with torch.no_grad():
+        val = builder()
+    _cache[key] = (tuple(weakref.ref(t) for t in tensors), stamp, val)
+    return val

@@ -27,7 +27,7 @@ SIGNATURES = {
                                              _i, _i, _i, _i, _p]),
     "vst_layernorm": (_i, [_p, _p, _p, _p, _p, _l, _i, _i, _f, _i, _i, _i, _p]),
     "vst_temporal_attn_fwd": (_i, [_p, _p, _p, _p, _l, _i, _i, _i, _l, _l, _l, _l, _f, _p]),
-    "vst_lora_gemm": (_i, [_p, _l, _p, _l, _i, _p, _l, _p, _l, _i, _p, _i, _p, _l, _f, _i, _p, _l,
+    "vst_lora_gemm": (_i, [_p, _l, _p, _l, _i, _p, _l, _p, _l, _i, _i, _p, _i, _p, _l, _f, _i, _p, _l,
                            _l, _i, _i, _p]),
     "vst_lora_pack_up": (_i, [_p, _p, _p, _p, _p, _p, _f, _p, _i, _i, _i, _p]),
     "vst_geglu": (_i, [_p, _p, _l, _i, _l, _l, _p]),

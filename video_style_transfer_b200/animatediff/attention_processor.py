@@ -15,6 +15,7 @@ import torch
 
 from .. import ops
 from .._host import as_rows_bf16
+from ..fused import project_fused
 
 
 class AnimateDiffAttnProcessor2_0:
@@ -51,21 +52,26 @@ class AnimateDiffAttnProcessor2_0:
         lora_scale = scale if hasattr(attn.to_q, "lora_layer") else 1.0
 
         x2 = as_rows_bf16(hidden_states)
-        q = self._proj(attn.to_q, x2, lora_scale)
         if encoder_hidden_states is None:
-            e2, kv_batch, seq_k = x2, batch_size, seq_q
+            # self-attention: q | k | v read the same tokens -> one GEMM, N = 3C
+            q, k, v = project_fused((attn.to_q, attn.to_k, attn.to_v), x2, lora_scale)
+            kv_batch, seq_k = batch_size, seq_q
         else:
+            q = self._proj(attn.to_q, x2, lora_scale)
             if attn.norm_cross:
                 encoder_hidden_states = attn.norm_encoder_hidden_states(encoder_hidden_states)
             kv_batch, seq_k = encoder_hidden_states.shape[:2]
             if batch_size % kv_batch != 0:
                 raise ValueError("text batch must divide the B*F batch")
             e2 = as_rows_bf16(encoder_hidden_states)       # NOT repeated: kv_group handles :62-66
-        k = self._proj(attn.to_k, e2, lora_scale)
-        v = self._proj(attn.to_v, e2, lora_scale)
+            k, v = project_fused((attn.to_k, attn.to_v), e2, lora_scale)   # one GEMM, N = 2C
         inner = k.shape[-1]
-        o = ops.attn_fwd(q.view(batch_size, seq_q, inner), k.view(kv_batch, seq_k, inner),
-                         v.view(kv_batch, seq_k, inner), attn.heads)
+
+        def rows3(t, b_, s_):      # (b*s, inner) column view -> (b, s, inner) with the same row stride
+            return t.as_strided((b_, s_, inner), (s_ * t.stride(0), t.stride(0), 1), t.storage_offset())
+
+        o = ops.attn_fwd(rows3(q, batch_size, seq_q), rows3(k, kv_batch, seq_k),
+                         rows3(v, kv_batch, seq_k), attn.heads)
         o2 = o.view(batch_size * seq_q, inner)
 
         fuse_res = (attn.residual_connection and input_ndim == 3 and residual.dtype == torch.bfloat16

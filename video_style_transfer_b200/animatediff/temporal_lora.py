@@ -11,7 +11,7 @@ import torch
 import torch.nn as nn
 
 from .. import ops
-from .._host import as_rows_bf16, bf16_cached, fused_linear, pad_branch_cols
+from .._host import as_rows_bf16, bf16_cached, cached_build, fused_linear, pad_branch_cols
 
 
 class TemporalLoRALinear(nn.Module):
@@ -31,15 +31,30 @@ class TemporalLoRALinear(nn.Module):
         self.lora_B = nn.Parameter(torch.zeros(base.out_features, rank, device=w.device,
                                                dtype=w.dtype))
 
+    # "LoRA site" protocol shared with LoRACompatibleLinear (see fused.py)
+    def site_weight(self):
+        return self.base.weight
+
+    def site_bias(self):
+        return self.base.bias
+
+    def site_downs(self):
+        return [self.lora_A]
+
+    def site_up(self, scale: float = 1.0):
+        """(alpha/r) * B as bf16 (out, pad8(r)), cached on lora_B's version."""
+        def build():
+            bp = ops.lora_pack_up(None, None, None, self.lora_B.detach().contiguous(), None, None,
+                                  float(self.scale))
+            return pad_branch_cols(bp, 1, self.rank)
+        return cached_build([self.lora_B], float(self.scale), build)
+
     def fused_forward(self, x2: torch.Tensor, scale: float = 1.0, residual=None,
                       out_scale: float = 1.0, act: str = "none",
                       out_dtype: torch.dtype = torch.bfloat16) -> torch.Tensor:
         u = ops.lora_gemm(x2, bf16_cached(self.lora_A, pad_rows=True))
-        bp = ops.lora_pack_up(None, None, None, self.lora_B.detach().contiguous(), None, None,
-                              float(self.scale))
-        bp = pad_branch_cols(bp, 1, self.rank)
-        return fused_linear(x2, self.base.weight, self.base.bias, (u, bp), residual, out_scale, act,
-                            out_dtype)
+        return fused_linear(x2, self.base.weight, self.base.bias, (u, self.site_up()), residual,
+                            out_scale, act, out_dtype)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         y = self.fused_forward(as_rows_bf16(x))

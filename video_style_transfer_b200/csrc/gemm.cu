@@ -46,7 +46,8 @@ template <int BN>
 __global__ void __launch_bounds__(kThreads, 1)
 lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
                  const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
-                 int nk1, int nk2, int m_tiles, int n_tiles, EpiArgs ep) {
+                 int nk1, int nk2, int m_tiles, int n_tiles, int k2_group_n, int k2_cols,
+                 EpiArgs ep) {
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -100,7 +101,9 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
             tma_load_2d(sa, &tmA1, &full[stage], kb * BK, m0);
             tma_load_2d(sb, &tmB1, &full[stage], kb * BK, n0);
           } else {
-            tma_load_2d(sa, &tmA2, &full[stage], (kb - nk1) * BK, m0);
+            // grouped low-rank operand: output columns of group g read A2 columns [g*K2, ...)
+            const int a2_off = k2_group_n > 0 ? (n0 / k2_group_n) * k2_cols : 0;
+            tma_load_2d(sa, &tmA2, &full[stage], a2_off + (kb - nk1) * BK, m0);
             tma_load_2d(sb, &tmB2, &full[stage], (kb - nk1) * BK, n0);
           }
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
@@ -246,7 +249,7 @@ int make_operand_map(CUtensorMap* m, const void* p, int64_t rows, int K, int64_t
 
 template <int BN>
 int launch(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, const void* A2,
-           int64_t lda2, const void* B2, int64_t ldb2, int K2, const EpiArgs& ep,
+           int64_t lda2, const void* B2, int64_t ldb2, int K2, int k2_group_n, const EpiArgs& ep,
            cudaStream_t st) {
   using C = Cfg<BN>;
   CUtensorMap tA1, tB1, tA2, tB2;
@@ -254,7 +257,8 @@ int launch(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, c
   if ((rc = make_operand_map(&tA1, A1, ep.M, K1, lda1, BM))) return rc;
   if ((rc = make_operand_map(&tB1, B1, ep.N, K1, ldb1, BN))) return rc;
   if (K2 > 0) {
-    if ((rc = make_operand_map(&tA2, A2, ep.M, K2, lda2, BM))) return rc;
+    const int groups = k2_group_n > 0 ? (ep.N + k2_group_n - 1) / k2_group_n : 1;
+    if ((rc = make_operand_map(&tA2, A2, ep.M, K2 * groups, lda2, BM))) return rc;
     if ((rc = make_operand_map(&tB2, B2, ep.N, K2, ldb2, BN))) return rc;
   } else {
     tA2 = tA1;
@@ -272,7 +276,8 @@ int launch(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, c
   VST_REQUIRE(tiles < (1ll << 31), VST_E_UNSUPPORTED, "lora_gemm: too many tiles");
   const int grid = (int)(tiles < vst_sm_count() ? tiles : vst_sm_count());
   kern<<<grid, kThreads, C::kSmemBytes, st>>>(tA1, tB1, tA2, tB2, (K1 + BK - 1) / BK,
-                                               (K2 + BK - 1) / BK, m_tiles, n_tiles, ep);
+                                               (K2 + BK - 1) / BK, m_tiles, n_tiles, k2_group_n, K2,
+                                               ep);
   VST_LAUNCH_OK();
   return VST_OK;
 }
@@ -303,7 +308,7 @@ __global__ void pack_up_kernel(const T* __restrict__ Bc, const T* __restrict__ m
 
 extern "C" int vst_lora_gemm(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1,
                              const void* A2, int64_t lda2, const void* B2, int64_t ldb2, int K2,
-                             const void* bias, int bias_dtype, const void* residual, int64_t ldr,
+                             int k2_group_n, const void* bias, int bias_dtype, const void* residual, int64_t ldr,
                              float out_scale, int act, void* D, int64_t ldd, int64_t M, int N,
                              int out_dtype, void* stream) {
   VST_REQUIRE(M >= 0 && N > 0 && K1 > 0 && K2 >= 0, VST_E_BADARG, "lora_gemm: bad shape");
@@ -325,15 +330,22 @@ extern "C" int vst_lora_gemm(const void* A1, int64_t lda1, const void* B1, int64
   EpiArgs ep{bias, residual, D, ldr, ldd, M, N, out_scale, bias_dtype == VST_BF16,
              out_dtype == VST_F32, act};
   cudaStream_t st = (cudaStream_t)stream;
-#define GO(BNV) return launch<BNV>(A1, lda1, B1, ldb1, K1, A2, lda2, B2, ldb2, K2, ep, st)
-  if (N % 256 == 0) GO(256);
-  if (N % 160 == 0) GO(160);
-  if (N % 192 == 0) GO(192);
-  if (N % 128 == 0) GO(128);
+  VST_REQUIRE(k2_group_n >= 0 && (k2_group_n == 0 || K2 > 0), VST_E_BADARG, "lora_gemm: bad k2_group_n");
+  const int gn = (K2 > 0 && k2_group_n > 0) ? k2_group_n : 0;
+#define GO(BNV) return launch<BNV>(A1, lda1, B1, ldb1, K1, A2, lda2, B2, ldb2, K2, gn, ep, st)
+#define FITS(BNV) (N % BNV == 0 && (gn == 0 || gn % BNV == 0))
+  if (FITS(256)) GO(256);
+  if (FITS(160)) GO(160);
+  if (FITS(192)) GO(192);
+  if (FITS(128)) GO(128);
+  if (FITS(64)) GO(64);
+  VST_REQUIRE(gn == 0, VST_E_UNSUPPORTED,
+              "lora_gemm: k2_group_n=%d must be a multiple of 64 that tiles N=%d", gn, N);
   if (N <= 64) GO(64);
   if (N <= 128) GO(128);
   if (N <= 160) GO(160);
   GO(256);
+#undef FITS
 #undef GO
 }
 

@@ -1,0 +1,92 @@
+"""Projections that read the same activation, fused along N into one tcgen05 GEMM.
+
+to_q | to_k | to_v of a self-attention (or to_k | to_v of a cross-attention, or the q/k/v
+TemporalLoRALinear of a motion-module attention) share their input, so
+    [q | k | v] = x [W_q; W_k; W_v]^T + u B'^T,   u = x [A_q; A_k; A_v]^T
+is two launches instead of nine, x is read twice instead of six times, and the 3C-wide output
+tiles the 148 SMs with far less wave-quantisation loss than three C-wide GEMMs.  The low-rank
+term is *grouped* (vst_lora_gemm k2_group_n): output columns of projection g only read their own
+K2 columns of u, so no block-diagonal zero padding is multiplied.
+
+Every linear taking part implements the "LoRA site" protocol: site_weight(), site_bias(),
+site_downs() -> [A_i (r, in)], site_up(scale) -> B' (out, K2) or None.  Concatenated / packed
+operands are cached on the parameters' in-place versions (``_host.bf16_cached/cached_build``), so
+an optimiser step or a merger clamp invalidates them.
+"""
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import ops
+from ._host import bf16_cached, cached_build, fused_linear, pad8
+
+
+def _site(layer):
+    if hasattr(layer, "site_weight"):
+        return layer
+    if isinstance(layer, torch.nn.Linear):
+        return _PlainSite(layer)
+    raise TypeError(f"{type(layer).__name__} is not a linear the sm_100a path knows how to run")
+
+
+class _PlainSite:
+    """nn.Linear without an adapter."""
+
+    def __init__(self, lin):
+        self.lin = lin
+        self.out_features = lin.out_features
+
+    def site_weight(self):
+        return self.lin.weight
+
+    def site_bias(self):
+        return self.lin.bias
+
+    def site_downs(self):
+        return []
+
+    def site_up(self, scale=1.0):
+        return None
+
+
+def project_one(layer, x2: torch.Tensor, scale: float = 1.0, residual=None, out_scale: float = 1.0,
+                act: str = "none", out_dtype=torch.bfloat16) -> torch.Tensor:
+    s = _site(layer)
+    downs = s.site_downs()
+    low = None
+    if downs:
+        bp = s.site_up(scale)
+        if bp is not None:
+            low = (ops.lora_gemm(x2, bf16_cached(*downs, pad_rows=True)), bp)
+    return fused_linear(x2, s.site_weight(), s.site_bias(), low, residual, out_scale, act, out_dtype)
+
+
+def project_fused(layers: Sequence, x2: torch.Tensor, scale: float = 1.0) -> List[torch.Tensor]:
+    """[layer(x) for layer in layers] as column views of one (M, sum out) GEMM result when the
+    layers are compatible; otherwise one fused GEMM per layer."""
+    sites = [_site(l) for l in layers]
+    ws = [s.site_weight() for s in sites]
+    n0 = ws[0].shape[0]
+    biases = [s.site_bias() for s in sites]
+    downs = [s.site_downs() for s in sites]
+    ups = [s.site_up(scale) if d else None for s, d in zip(sites, downs)]
+    k2s = {None if u is None else u.shape[1] for u in ups}
+    same = (len(sites) > 1 and all(w.shape == ws[0].shape for w in ws) and n0 % 64 == 0
+            and len(k2s) == 1 and (all(b is None for b in biases) or all(b is not None for b in biases)))
+    if not same:
+        return [project_one(l, x2, scale) for l in layers]
+    w = bf16_cached(*ws)
+    bias = None
+    if biases[0] is not None:
+        bias = cached_build(list(biases), "catbias", lambda: torch.cat([b.detach().float() for b in biases]))
+    k2 = k2s.pop()
+    if k2 is None:
+        y = ops.lora_gemm(x2, w, bias=bias)
+    else:
+        flat = [a for d in downs for a in d]
+        a_cat = bf16_cached(*flat, pad_rows=True)                       # (G*K2, in)
+        assert a_cat.shape[0] == len(sites) * k2
+        bp = cached_build(list(ups), "catup", lambda: torch.cat(list(ups), dim=0).contiguous())
+        u = ops.lora_gemm(x2, a_cat)                                    # (M, G*K2)
+        y = ops.lora_gemm(x2, w, u, bp, bias=bias, k2_group_n=n0)
+    return [y[:, i * n0:(i + 1) * n0] for i in range(len(sites))]

@@ -22,14 +22,13 @@ import torch.nn as nn
 
 from . import ops
 from ._host import fused_linear
+from .fused import project_fused, project_one
 from .animatediff.temporal_lora import TemporalLoRALinear
 from .animatediff.temporal_transformer import PositionalEncoding
 
 
 def _project(layer, x2, residual=None):
-    if isinstance(layer, TemporalLoRALinear):
-        return layer.fused_forward(x2, residual=residual)
-    return fused_linear(x2, layer.weight, layer.bias, residual=residual)
+    return project_one(layer, x2, residual=residual)
 
 
 class TemporalAttention(nn.Module):
@@ -46,10 +45,12 @@ class TemporalAttention(nn.Module):
     def forward_tokens(self, xn: torch.Tensor, n: int, f: int, residual: torch.Tensor):
         """xn, residual: (N*F, C) bf16 -> residual + to_out(attn(q,k,v))."""
         c = xn.shape[1]
-        q = _project(self.to_q, xn).view(n, f, c)
-        k = _project(self.to_k, xn).view(n, f, c)
-        v = _project(self.to_v, xn).view(n, f, c)
-        o = ops.temporal_attn(q, k, v, self.heads)
+        q, k, v = project_fused((self.to_q, self.to_k, self.to_v), xn)     # one GEMM, N = 3C
+
+        def seq(t):   # (N*F, C) column view of the packed result -> (N, F, C), same row stride
+            return t.as_strided((n, f, c), (f * t.stride(0), t.stride(0), 1), t.storage_offset())
+
+        o = ops.temporal_attn(seq(q), seq(k), seq(v), self.heads)
         return _project(self.to_out[0], o.view(n * f, c), residual=residual)
 
 

@@ -161,7 +161,7 @@ def _mat(t: torch.Tensor, name: str):
 def lora_gemm(a1: torch.Tensor, b1: torch.Tensor, a2: Optional[torch.Tensor] = None,
               b2: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None,
               residual: Optional[torch.Tensor] = None, out_scale: float = 1.0,
-              act: str = "none", out: Optional[torch.Tensor] = None,
+              act: str = "none", k2_group_n: int = 0, out: Optional[torch.Tensor] = None,
               out_dtype: torch.dtype = torch.bfloat16) -> torch.Tensor:
     """out[M,N] = (act(a1 b1^T + a2 b2^T + bias) + residual) * out_scale; act in {none, gelu}."""
     _cuda(a1, b1, a2, b2, bias, residual, out)
@@ -172,8 +172,9 @@ def lora_gemm(a1: torch.Tensor, b1: torch.Tensor, a2: Optional[torch.Tensor] = N
     k2 = 0
     if a2 is not None:
         _mat(a2, "a2"), _mat(b2, "b2")
-        k2 = a2.shape[1]
-        assert a2.shape[0] == m and b2.shape == (n, k2)
+        k2 = b2.shape[1]
+        groups = (n // k2_group_n) if k2_group_n else 1
+        assert a2.shape == (m, k2 * groups) and b2.shape[0] == n
     if out is None:
         out = torch.empty((m, n), dtype=out_dtype, device=a1.device)
     assert out.shape == (m, n) and out.stride(1) == 1
@@ -182,7 +183,7 @@ def lora_gemm(a1: torch.Tensor, b1: torch.Tensor, a2: Optional[torch.Tensor] = N
     check(lib.vst_lora_gemm(
         a1.data_ptr(), a1.stride(0), b1.data_ptr(), b1.stride(0), k1,
         _ptr(a2), a2.stride(0) if a2 is not None else 0, _ptr(b2),
-        b2.stride(0) if b2 is not None else 0, k2,
+        b2.stride(0) if b2 is not None else 0, k2, k2_group_n if a2 is not None else 0,
         _ptr(bias), _dt(bias) if bias is not None else VST_F32,
         _ptr(residual), residual.stride(0) if residual is not None else 0, out_scale,
         {"none": 0, "gelu": 1}[act], out.data_ptr(), out.stride(0), m, n, _dt(out), _stream()), "vst_lora_gemm")

@@ -11,7 +11,7 @@ import torch
 from torch import nn
 
 from .. import ops
-from .._host import as_rows_bf16, bf16_cached, fused_linear, pad_branch_cols
+from .._host import as_rows_bf16, bf16_cached, cached_build, fused_linear, pad_branch_cols
 
 
 class LoRALinearLayer(nn.Module):
@@ -31,12 +31,21 @@ class LoRALinearLayer(nn.Module):
         nn.init.normal_(self.down.weight, std=1 / rank)
         nn.init.zeros_(self.up.weight)
 
-    def fused_operands(self, x_content, x_style=None, scale: float = 1.0):
+    def site_downs(self):
+        return [self.down.weight]
+
+    def site_up(self, scale: float = 1.0):
         s = scale if self.network_alpha is None else scale * self.network_alpha / self.rank
+
+        def build():
+            bp = ops.lora_pack_up(None, None, None, self.up.weight.detach().contiguous(), None,
+                                  None, float(s))
+            return pad_branch_cols(bp, 1, self.rank)
+        return cached_build([self.up.weight], float(s), build)
+
+    def fused_operands(self, x_content, x_style=None, scale: float = 1.0):
         u = ops.lora_gemm(x_content, bf16_cached(self.down.weight, pad_rows=True))
-        bp = ops.lora_pack_up(None, None, None, self.up.weight.detach().contiguous(), None, None,
-                              float(s))
-        return u, pad_branch_cols(bp, 1, self.rank)
+        return u, self.site_up(scale)
 
     def forward(self, hidden_states: torch.Tensor) -> torch.Tensor:
         u, bp = self.fused_operands(as_rows_bf16(hidden_states), None, 1.0)
@@ -53,6 +62,19 @@ class LoRACompatibleLinear(nn.Linear):
 
     def set_lora_layer(self, lora_layer: Optional[nn.Module]):
         self.lora_layer = lora_layer
+
+    # "LoRA site" protocol (see fused.py): what a projection fused along N needs from each linear
+    def site_weight(self):
+        return self.weight
+
+    def site_bias(self):
+        return self.bias
+
+    def site_downs(self):
+        return [] if self.lora_layer is None else self.lora_layer.site_downs()
+
+    def site_up(self, scale: float = 1.0):
+        return None if self.lora_layer is None else self.lora_layer.site_up(scale)
 
     def fused_forward(self, x2: torch.Tensor, scale: float = 1.0,
                       x_content: Optional[torch.Tensor] = None,

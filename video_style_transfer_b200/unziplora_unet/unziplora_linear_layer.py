@@ -15,7 +15,7 @@ import torch
 from torch import nn
 
 from .. import ops
-from .._host import as_rows_bf16, bf16_cached, pad8, pad_branch_cols
+from .._host import as_rows_bf16, bf16_cached, cached_build, pad8, pad_branch_cols
 
 _KEYS = ("content", "style")
 
@@ -69,6 +69,38 @@ class _UnZipBase(nn.Module):
             out.append((key, use_merger, mask))
         return out
 
+    def site_downs(self):
+        """Down-projection weights of the active branches, in branch order."""
+        return [self.lora_matrix_dic[f"{k}_down"].weight for k, _, _ in self._active()]
+
+    def site_up(self, scale: float = 1.0) -> Optional[torch.Tensor]:
+        """B' (out, nact*pad8(r)) = scale * [m_c (.) mask_c (.) B_c | m_s (.) mask_s (.) B_s], bf16,
+        cached until a parameter, mask, the scale or the forward type changes."""
+        act = self._active()
+        if not act:
+            return None
+        d = self.lora_matrix_dic
+        ups, mrg, msk, deps = {}, {}, {}, []
+        for k, use_merger, mask in act:
+            ups[k] = d[f"{k}_up"].weight
+            mrg[k] = getattr(self, f"merge_{k}") if use_merger else None
+            msk[k] = mask
+            deps += [t for t in (ups[k], mrg[k], mask) if t is not None]
+        sig = (float(scale), tuple((k, um, mk is not None) for k, um, mk in act))
+
+        def build():
+            g = lambda t, like: None if t is None else t.detach().to(device=like.device, dtype=like.dtype).contiguous()
+            uc, us = ups.get("content"), ups.get("style")
+            like = uc if uc is not None else us
+            bp = ops.lora_pack_up(
+                None if uc is None else uc.detach().contiguous(), g(mrg.get("content"), like),
+                None if msk.get("content") is None else msk["content"].to(like.device),
+                None if us is None else us.detach().contiguous(), g(mrg.get("style"), like),
+                None if msk.get("style") is None else msk["style"].to(like.device), float(scale))
+            return pad_branch_cols(bp, len(act), self.rank)
+
+        return cached_build(deps, sig, build)
+
     def fused_operands(self, x_content: torch.Tensor, x_style: Optional[torch.Tensor],
                        scale: float = 1.0) -> Optional[Tuple[torch.Tensor, torch.Tensor]]:
         """(u (M,R), B' (out,R)) such that scale * self(x_content, x_style) == u B'^T, with
@@ -78,9 +110,8 @@ class _UnZipBase(nn.Module):
             return None
         if x_style is None:
             x_style = x_content
-        d = self.lora_matrix_dic
         xs = {"content": x_content, "style": x_style}
-        downs = [d[f"{k}_down"].weight for k, _, _ in act]
+        downs = self.site_downs()
         if len(act) == 2 and x_style is x_content:
             u = ops.lora_gemm(x_content, bf16_cached(*downs, pad_rows=True))   # one GEMM, N = 2r
         else:
@@ -88,14 +119,7 @@ class _UnZipBase(nn.Module):
             u = torch.empty((m, len(act) * r8), dtype=torch.bfloat16, device=x_content.device)
             for i, (k, _, _) in enumerate(act):
                 ops.lora_gemm(xs[k], bf16_cached(downs[i], pad_rows=True), out=u[:, i * r8:(i + 1) * r8])
-        ups, mrg, msk = {}, {}, {}
-        for k, use_merger, mask in act:
-            ups[k] = d[f"{k}_up"].weight.detach().contiguous()
-            mrg[k] = getattr(self, f"merge_{k}").detach().to(ups[k].dtype) if use_merger else None
-            msk[k] = None if mask is None else mask.to(ups[k].device)
-        bp = ops.lora_pack_up(ups.get("content"), mrg.get("content"), msk.get("content"),
-                              ups.get("style"), mrg.get("style"), msk.get("style"), float(scale))
-        return u, pad_branch_cols(bp, len(act), self.rank)
+        return u, self.site_up(scale)
 
     def forward(self, hidden_states_content: torch.Tensor,
                 hidden_states_style: torch.Tensor = None) -> torch.Tensor:
