@@ -132,7 +132,10 @@ def test_temporal_attn(ops, hp, f, heads, d):
 # ---- a3/a7: fused LoRA GEMM --------------------------------------------------------------------------
 @pytest.mark.parametrize("m,n,k1,k2", [(128, 128, 64, 0), (128, 64, 128, 0), (256, 256, 256, 64),
                                        (1000, 640, 640, 128), (300, 320, 320, 32),
-                                       (77, 1280, 2048, 128), (21, 40, 48, 16), (513, 960, 320, 96)])
+                                       (77, 1280, 2048, 128), (21, 40, 48, 16), (513, 960, 320, 96),
+                                       # large enough for the CTA-pair (cta_group::2) kernel
+                                       (19200, 1280, 1280, 128), (19000, 640, 640, 128),
+                                       (37888, 384, 320, 32)])
 @pytest.mark.parametrize("out_dtype", [torch.bfloat16, torch.float32])
 def test_lora_gemm(ops, m, n, k1, k2, out_dtype):
     torch.manual_seed(4)
@@ -208,6 +211,7 @@ def test_attn_fwd(ops, hp, bt, bk, heads, sq, sk):
 
 
 @pytest.mark.parametrize("m,c,k1,k2,groups", [(300, 128, 64, 16, 3), (1000, 640, 640, 128, 3),
+                                              (6400, 1280, 1280, 128, 3), (16384, 640, 640, 128, 3),
                                               (77, 1280, 2048, 128, 2), (513, 320, 320, 32, 3)])
 def test_lora_gemm_grouped_low_rank(ops, m, c, k1, k2, groups):
     """q|k|v fused along N: output columns of group g read only their own K2 columns of A2."""
@@ -223,3 +227,14 @@ def test_lora_gemm_grouped_low_rank(ops, m, c, k1, k2, groups):
         want[:, g * c:(g + 1) * c] += (a2.cpu().float()[:, g * k2:(g + 1) * k2]
                                        @ b2.cpu().float()[g * c:(g + 1) * c].t())
     assert rel_err(out, want) < REL_TOL
+
+
+@pytest.mark.parametrize("m,n", [(128, 128), (300, 192), (4096, 256)])
+def test_lora_gemm_identity_row_col_mapping(ops, m, n):
+    """D = A I must reproduce A bit for bit: pins the TMEM-lane -> row and chunk -> column mapping
+    of the TMA-store epilogue (values <= 256 are exact in bf16)."""
+    eye = torch.eye(n).to(torch.bfloat16).cuda()
+    rows = (torch.arange(m) % 251).float()[:, None].expand(m, n).to(torch.bfloat16).cuda().contiguous()
+    cols = torch.arange(n).float()[None, :].expand(m, n).to(torch.bfloat16).cuda().contiguous()
+    assert torch.equal(ops.lora_gemm(rows, eye), rows)
+    assert torch.equal(ops.lora_gemm(cols, eye), cols)

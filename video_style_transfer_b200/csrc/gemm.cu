@@ -14,14 +14,26 @@
 //                              two accumulator stages so the epilogue overlaps the next tile)
 //   warps 2..5  epilogue      (tcgen05.ld -> +bias, +residual, *scale -> bf16/fp32 -> global)
 // Roofline: tensor pipe; algorithmic FLOPs = 2*M*N*(K1+K2).
+#include <stdlib.h>
+#include <string.h>
+
 #include "common.cuh"
+
+static bool vst_force_single_cta() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("VST_GEMM_SINGLE_CTA"); v = (e && e[0] == '1') ? 1 : 0; }
+  return v == 1;
+}
 
 namespace {
 
 constexpr int BM = 128;
 constexpr int BK = 64;  // one 128-byte swizzle atom of bf16
-constexpr int kThreads = 192;
-constexpr int kSmemBudget = 200 * 1024;
+constexpr int kEpiWarps = 8;                 // 2 per TMEM lane quarter, interleaved over column chunks
+constexpr int kThreads = 64 + 32 * kEpiWarps;
+constexpr int kStageOutBytes = 32 * 32 * 2;  // one 32-row x 32-col bf16 chunk per TMA store
+constexpr int kOutBytes = kEpiWarps * 2 * kStageOutBytes;
+constexpr int kSmemBudget = 198400;          // operand ring; + kOutBytes staging + barriers <= 227 KB
 
 template <int BN>
 struct Cfg {
@@ -29,7 +41,7 @@ struct Cfg {
   static constexpr int kStages = (kSmemBudget / kStageBytes) > 8 ? 8 : (kSmemBudget / kStageBytes);
   static constexpr int kAccStride = BN <= 64 ? 64 : (BN <= 128 ? 128 : 256);
   static constexpr int kTmemCols = 2 * kAccStride;  // power of two >= 32
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kOutBytes + 1024 /*align*/ + 256;
 };
 
 struct EpiArgs {
@@ -42,17 +54,175 @@ struct EpiArgs {
   int bias_bf16, out_f32, act;
 };
 
+// One 32-column chunk of one accumulator row: +bias, act, +residual, *scale, store.
+__device__ __forceinline__ void epilogue_chunk(const EpiArgs& ep, const uint32_t* r, int64_t row,
+                                               bool row_ok, int n0, int c0) {
+  if (row_ok) {
+#pragma unroll
+    for (int v8 = 0; v8 < 4; ++v8) {
+      const int col = n0 + c0 + v8 * 8;
+      if (col >= ep.N) break;
+      float o[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = __uint_as_float(r[v8 * 8 + j]);
+      if (ep.bias != nullptr) {
+        if (ep.bias_bf16) {
+          const uint4 bv = __ldg(reinterpret_cast<const uint4*>(
+              reinterpret_cast<const __nv_bfloat16*>(ep.bias) + col));
+          const uint32_t bw[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float2 e = unpack_bf16(bw[j]);
+            o[2 * j] += e.x;
+            o[2 * j + 1] += e.y;
+          }
+        } else {
+          const float4 b0 = __ldg(reinterpret_cast<const float4*>(
+              reinterpret_cast<const float*>(ep.bias) + col));
+          const float4 b1 = __ldg(reinterpret_cast<const float4*>(
+              reinterpret_cast<const float*>(ep.bias) + col + 4));
+          o[0] += b0.x; o[1] += b0.y; o[2] += b0.z; o[3] += b0.w;
+          o[4] += b1.x; o[5] += b1.y; o[6] += b1.z; o[7] += b1.w;
+        }
+      }
+      if (ep.act == 1) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          o[j] = 0.5f * o[j] * (1.f + erff(o[j] * 0.70710678118654752f));  // exact GELU
+      }
+      if (ep.out_f32) {
+        float* dp = reinterpret_cast<float*>(ep.D) + row * ep.ldd + col;
+        if (ep.residual != nullptr) {
+          const float* rp = reinterpret_cast<const float*>(ep.residual) + row * ep.ldr + col;
+          const float4 r0 = *reinterpret_cast<const float4*>(rp);
+          const float4 r1 = *reinterpret_cast<const float4*>(rp + 4);
+          o[0] += r0.x; o[1] += r0.y; o[2] += r0.z; o[3] += r0.w;
+          o[4] += r1.x; o[5] += r1.y; o[6] += r1.z; o[7] += r1.w;
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] *= ep.out_scale;
+        *reinterpret_cast<float4*>(dp) = make_float4(o[0], o[1], o[2], o[3]);
+        *reinterpret_cast<float4*>(dp + 4) = make_float4(o[4], o[5], o[6], o[7]);
+      } else {
+        __nv_bfloat16* dp = reinterpret_cast<__nv_bfloat16*>(ep.D) + row * ep.ldd + col;
+        if (ep.residual != nullptr) {
+          const uint4 rv = *reinterpret_cast<const uint4*>(
+              reinterpret_cast<const __nv_bfloat16*>(ep.residual) + row * ep.ldr + col);
+          const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float2 e = unpack_bf16(rw[j]);
+            o[2 * j] += e.x;
+            o[2 * j + 1] += e.y;
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] *= ep.out_scale;
+        uint4 w;
+        w.x = pack_bf16(o[0], o[1]); w.y = pack_bf16(o[2], o[3]);
+        w.z = pack_bf16(o[4], o[5]); w.w = pack_bf16(o[6], o[7]);
+        *reinterpret_cast<uint4*>(dp) = w;
+      }
+    }
+  }
+}
+
+// bias / activation / scale of one 32-column chunk, packed to bf16 (TMA-store path: no residual)
+__device__ __forceinline__ void epilogue_pack(const EpiArgs& ep, const uint32_t* r, int col0,
+                                              uint32_t* w) {
+#pragma unroll
+  for (int v8 = 0; v8 < 4; ++v8) {
+    const int col = col0 + v8 * 8;
+    float o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = __uint_as_float(r[v8 * 8 + j]);
+    if (ep.bias != nullptr && col < ep.N) {
+      if (ep.bias_bf16) {
+        const uint4 bv = __ldg(reinterpret_cast<const uint4*>(
+            reinterpret_cast<const __nv_bfloat16*>(ep.bias) + col));
+        const uint32_t bw[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 e = unpack_bf16(bw[j]);
+          o[2 * j] += e.x;
+          o[2 * j + 1] += e.y;
+        }
+      } else {
+        const float4 b0 = __ldg(reinterpret_cast<const float4*>(
+            reinterpret_cast<const float*>(ep.bias) + col));
+        const float4 b1 = __ldg(reinterpret_cast<const float4*>(
+            reinterpret_cast<const float*>(ep.bias) + col + 4));
+        o[0] += b0.x; o[1] += b0.y; o[2] += b0.z; o[3] += b0.w;
+        o[4] += b1.x; o[5] += b1.y; o[6] += b1.z; o[7] += b1.w;
+      }
+    }
+    if (ep.act == 1) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = 0.5f * o[j] * (1.f + erff(o[j] * 0.70710678118654752f));
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      w[v8 * 4 + j] = pack_bf16(o[2 * j] * ep.out_scale, o[2 * j + 1] * ep.out_scale);
+  }
+}
+
+// Epilogue of one 128-row x BN accumulator by the 8 epilogue warps of a CTA.  Warp e owns TMEM
+// lane quarter e % 4 and every second 32-column chunk.  bf16 output without residual goes
+// TMEM -> registers -> 64B-swizzled smem chunk -> TMA store (full-line, asynchronous writes; the
+// store clips rows >= M and columns >= N); otherwise rows are written directly.
+template <int BN>
+__device__ __forceinline__ void epilogue_tile(const EpiArgs& ep, const CUtensorMap* tmD,
+                                              uint32_t tacc, int m0, int n0, int ewarp, int lane,
+                                              uint8_t* stage_out, int& buf) {
+  // a warp can only read the TMEM lane quarter given by its hardware warp id % 4 (warps 2..9)
+  const int quarter = (ewarp + 2) & 3, half = ewarp >> 2;
+  const int64_t row = (int64_t)m0 + quarter * 32 + lane;
+  const bool row_ok = row < ep.M;
+  const uint32_t taddr = tacc + (uint32_t(quarter * 32) << 16);
+  const bool via_tma = ep.residual == nullptr && !ep.out_f32;
+#pragma unroll 1
+  for (int c0 = half * 32; c0 < BN; c0 += 64) {
+    uint32_t r[32];
+    tmem_ld32(taddr + c0, r);
+    tmem_ld_wait();
+    if (n0 + c0 >= ep.N) continue;
+    if (via_tma) {
+      uint32_t w[16];
+      epilogue_pack(ep, r, n0 + c0, w);
+      uint8_t* sbuf = stage_out + buf * kStageOutBytes;
+      if (lane == 0) tma_store_wait_read<1>();      // the store that last used this buffer is done
+      __syncwarp();
+      uint8_t* srow = sbuf + lane * 64;
+      const int sx = (lane >> 1) & 3;                // SWIZZLE_64B: 16-B chunk ^= (row >> 1) & 3
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        *reinterpret_cast<uint4*>(srow + ((q ^ sx) * 16)) =
+            make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        tma_store_2d(tmD, sbuf, n0 + c0, m0 + quarter * 32);
+        tma_store_commit();
+      }
+      buf ^= 1;
+    } else {
+      epilogue_chunk(ep, r, row, row_ok, n0, c0);
+    }
+  }
+}
+
 template <int BN>
 __global__ void __launch_bounds__(kThreads, 1)
 lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
                  const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
-                 int nk1, int nk2, int m_tiles, int n_tiles, int k2_group_n, int k2_cols,
+                 const __grid_constant__ CUtensorMap tmD, int nk1, int nk2, int m_tiles, int n_tiles, int k2_group_n, int k2_cols,
                  EpiArgs ep) {
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint8_t* stage_out = smem + C::kStages * C::kStageBytes;   // 1024-aligned: stage sizes are k*1024
+  uint64_t* full = reinterpret_cast<uint64_t*>(stage_out + kOutBytes);
   uint64_t* empty = full + C::kStages;
   uint64_t* acc_full = empty + C::kStages;
   uint64_t* acc_empty = acc_full + 2;
@@ -75,7 +245,7 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], 4);
+      mbar_init(&acc_empty[i], kEpiWarps);
     }
     fence_mbar_init();
   }
@@ -140,96 +310,24 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
       }
     }
   } else {
-    // ================= epilogue (warps 2..5; TMEM lane quarter = warp % 4) =================
-    const int quarter = warp & 3;
+    // ================= epilogue (warps 2..9) =================
+    const int ewarp = warp - 2;
+    uint8_t* my_out = stage_out + ewarp * 2 * kStageOutBytes;
+    int buf = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
+    if (lane == 0) tma_prefetch_desc(&tmD);
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
       mbar_wait(&acc_full[acc], acc_phase, 4);
       tc_fence_after();
-      const int64_t row = (int64_t)m0 + quarter * 32 + lane;
-      const bool row_ok = row < ep.M;
-      const uint32_t taddr = tmem_base + acc * C::kAccStride + (uint32_t(quarter * 32) << 16);
-#pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
-        uint32_t r[32];
-        tmem_ld32(taddr + c0, r);
-        tmem_ld_wait();
-        if (row_ok) {
-#pragma unroll
-          for (int v8 = 0; v8 < 4; ++v8) {
-            const int col = n0 + c0 + v8 * 8;
-            if (col >= ep.N) break;
-            float o[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) o[j] = __uint_as_float(r[v8 * 8 + j]);
-            if (ep.bias != nullptr) {
-              if (ep.bias_bf16) {
-                const uint4 bv = __ldg(reinterpret_cast<const uint4*>(
-                    reinterpret_cast<const __nv_bfloat16*>(ep.bias) + col));
-                const uint32_t bw[4] = {bv.x, bv.y, bv.z, bv.w};
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                  const float2 e = unpack_bf16(bw[j]);
-                  o[2 * j] += e.x;
-                  o[2 * j + 1] += e.y;
-                }
-              } else {
-                const float4 b0 = __ldg(reinterpret_cast<const float4*>(
-                    reinterpret_cast<const float*>(ep.bias) + col));
-                const float4 b1 = __ldg(reinterpret_cast<const float4*>(
-                    reinterpret_cast<const float*>(ep.bias) + col + 4));
-                o[0] += b0.x; o[1] += b0.y; o[2] += b0.z; o[3] += b0.w;
-                o[4] += b1.x; o[5] += b1.y; o[6] += b1.z; o[7] += b1.w;
-              }
-            }
-            if (ep.act == 1) {
-#pragma unroll
-              for (int j = 0; j < 8; ++j)
-                o[j] = 0.5f * o[j] * (1.f + erff(o[j] * 0.70710678118654752f));  // exact GELU
-            }
-            if (ep.out_f32) {
-              float* dp = reinterpret_cast<float*>(ep.D) + row * ep.ldd + col;
-              if (ep.residual != nullptr) {
-                const float* rp = reinterpret_cast<const float*>(ep.residual) + row * ep.ldr + col;
-                const float4 r0 = *reinterpret_cast<const float4*>(rp);
-                const float4 r1 = *reinterpret_cast<const float4*>(rp + 4);
-                o[0] += r0.x; o[1] += r0.y; o[2] += r0.z; o[3] += r0.w;
-                o[4] += r1.x; o[5] += r1.y; o[6] += r1.z; o[7] += r1.w;
-              }
-#pragma unroll
-              for (int j = 0; j < 8; ++j) o[j] *= ep.out_scale;
-              *reinterpret_cast<float4*>(dp) = make_float4(o[0], o[1], o[2], o[3]);
-              *reinterpret_cast<float4*>(dp + 4) = make_float4(o[4], o[5], o[6], o[7]);
-            } else {
-              __nv_bfloat16* dp = reinterpret_cast<__nv_bfloat16*>(ep.D) + row * ep.ldd + col;
-              if (ep.residual != nullptr) {
-                const uint4 rv = *reinterpret_cast<const uint4*>(
-                    reinterpret_cast<const __nv_bfloat16*>(ep.residual) + row * ep.ldr + col);
-                const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                  const float2 e = unpack_bf16(rw[j]);
-                  o[2 * j] += e.x;
-                  o[2 * j + 1] += e.y;
-                }
-              }
-#pragma unroll
-              for (int j = 0; j < 8; ++j) o[j] *= ep.out_scale;
-              uint4 w;
-              w.x = pack_bf16(o[0], o[1]); w.y = pack_bf16(o[2], o[3]);
-              w.z = pack_bf16(o[4], o[5]); w.w = pack_bf16(o[6], o[7]);
-              *reinterpret_cast<uint4*>(dp) = w;
-            }
-          }
-        }
-      }
+      epilogue_tile<BN>(ep, &tmD, tmem_base + acc * C::kAccStride, m0, n0, ewarp, lane, my_out, buf);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[acc]);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+    if (lane == 0) tma_store_wait<0>();
   }
 
   tc_fence_before();
@@ -240,11 +338,174 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
   }
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// CTA-pair variant (cta_group::2): a cluster of two CTAs (the two SMs of a TPC) owns a 256 x BN
+// tile.  Each CTA stages its own 128 rows of A and HALF of the B tile (BN/2 rows), and the leader
+// issues one tcgen05.mma M=256 that reads both halves: per SM the shared-memory traffic per MAC
+// (TMA writes + MMA reads) drops by a third against the 128 x BN single-CTA tile, which is what
+// bounds the single-CTA kernel at ~56 % of tensor peak.
+//   full[s]      lives in the leader; both CTAs' TMA loads complete_tx on it
+//   empty[s]     in both CTAs, released by a multicast tcgen05.commit
+//   acc_full[a]  in both CTAs (multicast commit); acc_empty[a] in the leader, 8 warp arrivals
+// ------------------------------------------------------------------------------------------------
+template <int BN>
+struct Cfg2 {
+  static constexpr int kBRows = BN / 2;
+  static constexpr int kStageBytes = (BM + kBRows) * BK * 2;
+  static constexpr int kStages = (kSmemBudget / kStageBytes) > 8 ? 8 : (kSmemBudget / kStageBytes);
+  static constexpr int kAccStride = BN <= 64 ? 64 : (BN <= 128 ? 128 : 256);
+  static constexpr int kTmemCols = 2 * kAccStride;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kOutBytes + 1024 + 256;
+};
+
+template <int BN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+lora_gemm2_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
+                  const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
+                  const __grid_constant__ CUtensorMap tmD, int nk1, int nk2, int m_tiles, int n_tiles, int k2_group_n, int k2_cols,
+                  EpiArgs ep) {
+  using C = Cfg2<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  uint8_t* stage_out = smem + C::kStages * C::kStageBytes;   // 1024-aligned: stage sizes are k*1024
+  uint64_t* full = reinterpret_cast<uint64_t*>(stage_out + kOutBytes);
+  uint64_t* empty = full + C::kStages;
+  uint64_t* acc_full = empty + C::kStages;
+  uint64_t* acc_empty = acc_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int nk = nk1 + nk2;
+  const int total_tiles = m_tiles * n_tiles;          // m_tiles counts 256-row tiles
+  const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA1);
+    tma_prefetch_desc(&tmB1);
+    if (nk2 > 0) {
+      tma_prefetch_desc(&tmA2);
+      tma_prefetch_desc(&tmB2);
+    }
+    for (int i = 0; i < C::kStages; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_empty[i], 2 * kEpiWarps);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc_2sm(tmem_slot, C::kTmemCols);
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================= TMA producer (both CTAs) =================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = cluster_id; tile < total_tiles; tile += n_clusters) {
+        const int m0 = (tile / n_tiles) * (2 * BM) + rank * BM;
+        const int n0 = (tile % n_tiles) * BN;
+        const int nb = n0 + rank * C::kBRows;          // this CTA's half of the B tile
+        for (int kb = 0; kb < nk; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1, 1);
+          uint8_t* sa = smem + stage * C::kStageBytes;
+          uint8_t* sb = sa + BM * BK * 2;
+          if (leader) mbar_arrive_expect_tx(&full[stage], 2 * C::kStageBytes);
+          if (kb < nk1) {
+            tma_load_2d_2sm(sa, &tmA1, &full[stage], kb * BK, m0);
+            tma_load_2d_2sm(sb, &tmB1, &full[stage], kb * BK, nb);
+          } else {
+            const int a2_off = k2_group_n > 0 ? (n0 / k2_group_n) * k2_cols : 0;
+            tma_load_2d_2sm(sa, &tmA2, &full[stage], a2_off + (kb - nk1) * BK, m0);
+            tma_load_2d_2sm(sb, &tmB2, &full[stage], (kb - nk1) * BK, nb);
+          }
+          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer (leader CTA only) =================
+    if (leader && lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(2 * BM, BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = cluster_id; tile < total_tiles; tile += n_clusters) {
+        mbar_wait(&acc_empty[acc], acc_phase ^ 1, 2);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * C::kAccStride;
+        for (int kb = 0; kb < nk; ++kb) {
+          mbar_wait(&full[stage], phase, 3);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * C::kStageBytes);
+          const uint32_t sb = sa + BM * BK * 2;
+          const uint64_t da = umma_desc_sw128(sa, 1024);
+          const uint64_t db = umma_desc_sw128(sb, 1024);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k)
+            umma_bf16_ss_2sm(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+          umma_commit_2sm(&empty[stage]);
+          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit_2sm(&acc_full[acc]);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else {
+    // ================= epilogue (warps 2..9 of both CTAs; own 128 rows) =================
+    const int ewarp = warp - 2;
+    uint8_t* my_out = stage_out + ewarp * 2 * kStageOutBytes;
+    int buf = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    if (lane == 0) tma_prefetch_desc(&tmD);
+    for (int tile = cluster_id; tile < total_tiles; tile += n_clusters) {
+      const int m0 = (tile / n_tiles) * (2 * BM) + rank * BM, n0 = (tile % n_tiles) * BN;
+      mbar_wait(&acc_full[acc], acc_phase, 4);
+      tc_fence_after();
+      epilogue_tile<BN>(ep, &tmD, tmem_base + acc * C::kAccStride, m0, n0, ewarp, lane, my_out, buf);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(&acc_empty[acc], 0);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+    if (lane == 0) tma_store_wait<0>();
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_2sm(tmem_base, C::kTmemCols);
+  }
+}
+
 int make_operand_map(CUtensorMap* m, const void* p, int64_t rows, int K, int64_t ld, int box_rows) {
   const uint64_t dims[2] = {(uint64_t)K, (uint64_t)rows};
   const uint64_t strides[2] = {2, (uint64_t)ld * 2};
   const uint32_t box[2] = {BK, (uint32_t)box_rows};
   return vst_make_tmap(m, p, 2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+int make_out_map(CUtensorMap* m, const EpiArgs& ep) {
+  if (ep.out_f32 || ep.residual != nullptr) {      // direct-store path: the map is never used
+    memset(m, 0, sizeof(*m));
+    return VST_OK;
+  }
+  const uint64_t dims[2] = {(uint64_t)ep.N, (uint64_t)ep.M};
+  const uint64_t strides[2] = {2, (uint64_t)ep.ldd * 2};
+  const uint32_t box[2] = {32, 32};
+  return vst_make_tmap(m, ep.D, 2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_64B);
 }
 
 template <int BN>
@@ -264,6 +525,8 @@ int launch(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, c
     tA2 = tA1;
     tB2 = tB1;
   }
+  CUtensorMap tD;
+  if ((rc = make_out_map(&tD, ep))) return rc;
   auto kern = lora_gemm_kernel<BN>;
   static bool configured = false;
   if (!configured) {
@@ -275,7 +538,45 @@ int launch(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, c
   const int64_t tiles = (int64_t)m_tiles * n_tiles;
   VST_REQUIRE(tiles < (1ll << 31), VST_E_UNSUPPORTED, "lora_gemm: too many tiles");
   const int grid = (int)(tiles < vst_sm_count() ? tiles : vst_sm_count());
-  kern<<<grid, kThreads, C::kSmemBytes, st>>>(tA1, tB1, tA2, tB2, (K1 + BK - 1) / BK,
+  kern<<<grid, kThreads, C::kSmemBytes, st>>>(tA1, tB1, tA2, tB2, tD, (K1 + BK - 1) / BK,
+                                               (K2 + BK - 1) / BK, m_tiles, n_tiles, k2_group_n, K2,
+                                               ep);
+  VST_LAUNCH_OK();
+  return VST_OK;
+}
+
+
+template <int BN>
+int launch2(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, const void* A2,
+            int64_t lda2, const void* B2, int64_t ldb2, int K2, int k2_group_n, const EpiArgs& ep,
+            cudaStream_t st) {
+  using C = Cfg2<BN>;
+  CUtensorMap tA1, tB1, tA2, tB2;
+  int rc;
+  if ((rc = make_operand_map(&tA1, A1, ep.M, K1, lda1, BM))) return rc;
+  if ((rc = make_operand_map(&tB1, B1, ep.N, K1, ldb1, C::kBRows))) return rc;
+  if (K2 > 0) {
+    const int groups = k2_group_n > 0 ? (ep.N + k2_group_n - 1) / k2_group_n : 1;
+    if ((rc = make_operand_map(&tA2, A2, ep.M, K2 * groups, lda2, BM))) return rc;
+    if ((rc = make_operand_map(&tB2, B2, ep.N, K2, ldb2, C::kBRows))) return rc;
+  } else {
+    tA2 = tA1;
+    tB2 = tB1;
+  }
+  CUtensorMap tD;
+  if ((rc = make_out_map(&tD, ep))) return rc;
+  auto kern = lora_gemm2_kernel<BN>;
+  static bool configured = false;
+  if (!configured) {
+    VST_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     C::kSmemBytes));
+    configured = true;
+  }
+  const int m_tiles = (int)((ep.M + 2 * BM - 1) / (2 * BM)), n_tiles = ep.N / BN;
+  const int64_t tiles = (int64_t)m_tiles * n_tiles;
+  const int pairs = vst_sm_count() / 2;
+  const int grid = 2 * (int)(tiles < pairs ? tiles : pairs);
+  kern<<<grid, kThreads, C::kSmemBytes, st>>>(tA1, tB1, tA2, tB2, tD, (K1 + BK - 1) / BK,
                                                (K2 + BK - 1) / BK, m_tiles, n_tiles, k2_group_n, K2,
                                                ep);
   VST_LAUNCH_OK();
@@ -334,6 +635,12 @@ extern "C" int vst_lora_gemm(const void* A1, int64_t lda1, const void* B1, int64
   const int gn = (K2 > 0 && k2_group_n > 0) ? k2_group_n : 0;
 #define GO(BNV) return launch<BNV>(A1, lda1, B1, ldb1, K1, A2, lda2, B2, ldb2, K2, gn, ep, st)
 #define FITS(BNV) (N % BNV == 0 && (gn == 0 || gn % BNV == 0))
+#define GO2(BNV) return launch2<BNV>(A1, lda1, B1, ldb1, K1, A2, lda2, B2, ldb2, K2, gn, ep, st)
+  // CTA pairs (256-row tiles) once there is at least one tile per SM pair to keep busy
+  const bool big = M >= 2048 && !vst_force_single_cta();
+  if (big && FITS(256) && (M / 256) * (N / 256) >= vst_sm_count() / 2) GO2(256);
+  if (big && FITS(160) && (M / 256) * (N / 160) >= vst_sm_count() / 2) GO2(160);
+  if (big && FITS(128) && (M / 256) * (N / 128) >= vst_sm_count() / 2) GO2(128);
   if (FITS(256)) GO(256);
   if (FITS(160)) GO(160);
   if (FITS(192)) GO(192);
