@@ -3,18 +3,26 @@
 // head merge) -- the head split/merge transposes disappear into the TMA tensor maps, and the
 // text repeat_interleave of :62-66 into the kv batch index (b / kv_group).
 //
-// One CTA = 128 query rows of one (batch, head); two CTAs are resident per SM (256 TMEM columns
-// each: S [0,128) fp32, O [128,192) fp32, P [192,256) bf16 pairs).  192 threads:
-//   warps 0..3  softmax: thread t owns query row t (TMEM lane t).  Per 128-key block ONE pass:
+// One CTA = NT x 128 query rows of one (batch, head); NT = 1 ships, with two CTAs resident per SM
+// (256 TMEM columns each: S [0,128) fp32, O [128,192) fp32, P [192,256) bf16 pairs).  Warps:
+//   0..3        softmax: thread t owns query row t (TMEM lane t).  Per 128-key block ONE pass:
 //               S row -> registers (S is released at once, so the next S = Q K^T overlaps this
-//               block's softmax), row max, P = exp2(s*scale - m) with packed f32x2 math, bf16 P
-//               written back to TMEM.  O accumulates in TMEM across blocks; it is rescaled only
-//               when the running max moves by more than 2^8 (lazy rescale), by the same warps.
-//   warp 4      TMA producer: Q once, K / V tiles [128 x 64] (2 stages each).
-//   warp 5      MMA issuer: S = Q K^T (4 x tcgen05.mma 128x128x16, both operands K-major smem)
-//               and O += P V (8 x 128x64x16, A = P from TMEM, B = V MN-major straight from its
-//               row-major tile), so P never touches shared memory.
+//               block's softmax), row max (4 independent chains), P = exp2(s*scale - m) with packed
+//               f32x2 math, kPoly of every 8 pairs on the FMA pipe (ex2_poly2), bf16 P written back
+//               to TMEM.  O accumulates in TMEM across blocks; it is rescaled only when the running
+//               max moves by more than 2^8 (lazy rescale), by the same warps.
+//   4           TMA producer: Q once, K / V tiles [128 x 64] (2 stages each).
+//   5           MMA issuer (whole warp in the loop, one elected lane issues): S = Q K^T
+//               (4 x tcgen05.mma 128x128x16, both operands K-major smem) and O += P V
+//               (8 x 128x64x16, A = P from TMEM, B = V MN-major straight from its row-major tile),
+//               so P never touches shared memory.
+// What bounds it (r01 measurements, scripts/ubench/*.cu, profiles/attn_r01_notes.md): at head dim 64
+// a 128x128 score block is ~530 clk of tensor work but 1024 clk of MUFU.EX2 (16/clk/SM, and
+// ex2.f16x2 is two MUFU ops, no packed rate), so the kernel is XU-bound; NT = 2 (K/V shared by two
+// tiles in one CTA), 8 half-row softmax warps, a per-SM CTA stagger and an exp-phase mutex between
+// tiles were all measured and were slower or equal.
 // Roofline: tensor pipe for self-attention (S/2 FLOP/B); FLOPs = 4*Bt*h*Sq*Sk*d.
+#include <stdlib.h>
 #include <type_traits>
 
 #include "common.cuh"
@@ -24,10 +32,13 @@ namespace {
 constexpr int BQ = 128;   // query rows per CTA
 constexpr int BKV = 128;  // keys per block
 constexpr int HD = 64;    // head dim
-constexpr int kThreads = 192;
-constexpr int KST = 2;    // K and V stages
+constexpr int NT = 1;     // query tiles per CTA (they share every K / V tile: halves the L2 traffic)
+constexpr int kTmaWarp = 4 * NT;             // warps [0, 4 NT): softmax; then TMA; then NT MMA warps
+constexpr int kThreads = 32 * (4 * NT + 1 + NT);
+constexpr int KST = NT == 1 ? 2 : 3;    // K and V stages
 constexpr int kTile = 128 * HD * 2;  // 16 KB
-constexpr int kSmemBytes = kTile * (1 + 2 * KST) + 1024 + 128;
+constexpr int kSmemBytes = kTile * (NT + 2 * KST) + 1024 + 256;
+constexpr int kDefaultPoly = 2;
 constexpr float kRescaleThreshold = 8.f;  // log2 units: P stays below 2^8, safe in bf16 / fp32
 
 __device__ __forceinline__ float ex2(float x) {
@@ -36,71 +47,104 @@ __device__ __forceinline__ float ex2(float x) {
   return y;
 }
 
+// exp2 on the FMA pipe (Cody-Waite split + degree-3 minimax polynomial, |rel err| < 7.6e-5, far
+// below the bf16 rounding of P).  The MUFU unit retires 16 ex2/clk/SM: at head dim 64 that is
+// 1024 clk per 128x128 score block against 512 clk of tensor work, so the kernel was XU-bound
+// (ncu r01: xu pipe 72 %, tensor 36 %).  kPoly of every 8 packed pairs take this path instead.
+// x is clamped to >= -126 so the exponent add cannot wrap; x <= 2^8 by the lazy-rescale bound.
+__device__ __forceinline__ float2 ex2_poly2(float2 x) {
+  const float2 magic = make_float2(12582912.f, 12582912.f);      // 1.5 * 2^23
+  const float2 nmagic = make_float2(-12582912.f, -12582912.f);
+  x.x = fmaxf(x.x, -126.f);
+  x.y = fmaxf(x.y, -126.f);
+  const float2 xf = __fadd2_rn(x, magic);        // low mantissa bits = round(x)
+  const float2 xi = __fadd2_rn(xf, nmagic);      // round(x) as a float
+  const float2 f = __fadd2_rn(x, make_float2(-xi.x, -xi.y));   // in [-0.5, 0.5]
+  const float2 c3 = make_float2(0.05520550534129143f, 0.05520550534129143f);
+  const float2 c2 = make_float2(0.24261397123336792f, 0.24261397123336792f);
+  const float2 c1 = make_float2(0.6932547688484192f, 0.6932547688484192f);
+  const float2 c0 = make_float2(0.9999276995658875f, 0.9999276995658875f);
+  float2 p = __ffma2_rn(c3, f, c2);
+  p = __ffma2_rn(p, f, c1);
+  p = __ffma2_rn(p, f, c0);
+  p.x = __int_as_float(__float_as_int(p.x) + (__float_as_int(xf.x) << 23));
+  p.y = __int_as_float(__float_as_int(p.y) + (__float_as_int(xf.y) << 23));
+  return p;
+}
+
 struct AttnArgs {
   float* lse;
   int Sq, Sk, heads, kv_group;
   float scale_log2;
 };
 
-__global__ void __launch_bounds__(kThreads, 2)
+template <int kPoly>
+__global__ void __launch_bounds__(kThreads, 2 / NT)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
                 AttnArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
-  uint8_t* sQ = smem;
-  uint8_t* sK = sQ + kTile;
-  uint8_t* sV = sK + KST * kTile;
+  uint8_t* sQ = smem;                       // [NT] query tiles (reused to stage O)
+  uint8_t* sK = sQ + NT * kTile;            // [KST]
+  uint8_t* sV = sK + KST * kTile;           // [KST]
   uint64_t* bars = reinterpret_cast<uint64_t*>(sV + KST * kTile);
-  uint64_t* q_full = bars;
-  uint64_t* k_full = bars + 1;          // [KST]
-  uint64_t* k_empty = k_full + KST;     // [KST]
-  uint64_t* v_full = k_empty + KST;     // [KST]
-  uint64_t* v_empty = v_full + KST;     // [KST]
-  uint64_t* s_full = v_empty + KST;     // S_j complete in TMEM
-  uint64_t* s_free = s_full + 1;        // S_j copied to registers by all 128 rows
-  uint64_t* p_full = s_free + 1;        // P_j in TMEM (and O rescaled if needed)
-  uint64_t* o_full = p_full + 1;        // O += P_j V_j complete
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 1);
+  uint64_t* q_full = bars;                  // [NT]
+  uint64_t* k_full = q_full + NT;           // [KST]
+  uint64_t* k_empty = k_full + KST;         // [KST]  both tiles' S MMAs have read K_j
+  uint64_t* v_full = k_empty + KST;         // [KST]
+  uint64_t* v_empty = v_full + KST;         // [KST]  both tiles' PV MMAs have read V_j
+  uint64_t* s_full = v_empty + KST;         // [NT] S_j complete in TMEM
+  uint64_t* s_free = s_full + NT;           // [NT] S_j copied to registers by all 128 rows
+  uint64_t* p_full = s_free + NT;           // [NT] P_j in TMEM (and O rescaled if needed)
+  uint64_t* o_full = p_full + NT;           // [NT] O += P_j V_j complete
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + NT);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int q0 = blockIdx.x * BQ, head = blockIdx.y, b = blockIdx.z;
+  const int q0 = blockIdx.x * (NT * BQ), head = blockIdx.y, b = blockIdx.z;
   const int nblk = (a.Sk + BKV - 1) / BKV;
 
   if (threadIdx.x == 0) {
-    mbar_init(q_full, 1);
+    for (int t = 0; t < NT; ++t) {
+      mbar_init(&q_full[t], 1);
+      mbar_init(&s_full[t], 1);
+      mbar_init(&s_free[t], 128);
+      mbar_init(&p_full[t], 128);
+      mbar_init(&o_full[t], 1);
+    }
     for (int i = 0; i < KST; ++i) {
       mbar_init(&k_full[i], 1);
-      mbar_init(&k_empty[i], 1);
+      mbar_init(&k_empty[i], NT);
       mbar_init(&v_full[i], 1);
-      mbar_init(&v_empty[i], 1);
+      mbar_init(&v_empty[i], NT);
     }
-    mbar_init(s_full, 1);
-    mbar_init(s_free, 128);
-    mbar_init(p_full, 128);
-    mbar_init(o_full, 1);
     fence_mbar_init();
   }
-  if (warp == 5) tmem_alloc(tmem_slot, 256);
+  if (warp == kTmaWarp) tmem_alloc(tmem_slot, 256 * NT);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tS = tmem_base;        // columns [0,128): S (fp32)
-  const uint32_t tO = tmem_base + 128;  // columns [128,192): O accumulator (fp32)
-  const uint32_t tP = tmem_base + 192;  // columns [192,256): P (bf16 pairs, 2 keys per column)
 
-  if (warp == 4) {
+  if (warp == kTmaWarp) {
     // ================= TMA producer =================
     if (lane == 0) {
       tma_prefetch_desc(&tmQ);
       tma_prefetch_desc(&tmK);
       tma_prefetch_desc(&tmV);
-      mbar_arrive_expect_tx(q_full, kTile);
-      tma_load_3d(sQ, &tmQ, q_full, head * HD, q0, b);
       const int bk = b / a.kv_group;
-      for (int j = 0; j < nblk; ++j) {
+      mbar_arrive_expect_tx(&q_full[0], kTile);
+      tma_load_3d(sQ, &tmQ, &q_full[0], head * HD, q0, b);
+      mbar_arrive_expect_tx(&k_full[0], kTile);
+      tma_load_3d(sK, &tmK, &k_full[0], head * HD, 0, bk);
+      if (NT > 1) {
+        mbar_arrive_expect_tx(&q_full[NT - 1], kTile);
+        tma_load_3d(sQ + kTile, &tmQ, &q_full[NT - 1], head * HD, q0 + BQ, b);
+      }
+      mbar_arrive_expect_tx(&v_full[0], kTile);
+      tma_load_3d(sV, &tmV, &v_full[0], head * HD, 0, bk);
+      for (int j = 1; j < nblk; ++j) {
         const int st = j % KST;
         const uint32_t ph = ((j / KST) & 1) ^ 1;
         mbar_wait(&k_empty[st], ph, 10);
@@ -111,49 +155,65 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         tma_load_3d(sV + st * kTile, &tmV, &v_full[st], head * HD, j * BKV, bk);
       }
     }
-  } else if (warp == 5) {
-    // ================= MMA issuer =================
-    if (lane == 0) {
-      constexpr uint32_t idesc_s = umma_idesc_bf16(BQ, BKV, 0, 0);
-      constexpr uint32_t idesc_o = umma_idesc_bf16(BQ, HD, 0, 1);  // B (= V) is MN-major
-      const uint64_t dq = umma_desc_sw128(smem_u32(sQ), 1024);
-      mbar_wait(q_full, 0, 20);
-      auto issue_s = [&](int j) {
-        const int st = j % KST;
-        mbar_wait(&k_full[st], (j / KST) & 1, 21);
-        tc_fence_after();
-        const uint64_t dk = umma_desc_sw128(smem_u32(sK + st * kTile), 1024);
+  } else if (warp > kTmaWarp) {
+    // ================= MMA issuers: one warp per query tile, sharing the K / V stages ==========
+    // The whole warp runs the loop and one elected lane issues (warp-uniform control flow keeps the
+    // descriptors in uniform registers; see scripts/ubench/mma_rate.cu).
+    const bool issuer = elect_one();
+    const int t = warp - kTmaWarp - 1;
+    const uint32_t tS = tmem_base + t * 256;   // S (fp32) columns [0,128) of this tile's half
+    const uint32_t tO = tS + 128;              // O accumulator (fp32), 64 columns
+    const uint32_t tP = tS + 192;              // P (bf16 pairs, 2 keys per column), 64 columns
+    constexpr uint32_t idesc_s = umma_idesc_bf16(BQ, BKV, 0, 0);
+    constexpr uint32_t idesc_o = umma_idesc_bf16(BQ, HD, 0, 1);  // B (= V) is MN-major
+    const uint64_t dq = umma_desc_sw128(smem_u32(sQ + t * kTile), 1024);
+    mbar_wait(&q_full[t], 0, 20);
+    auto issue_s = [&](int j) {
+      const int st = j % KST;
+      mbar_wait(&k_full[st], (j / KST) & 1, 21);
+      tc_fence_after();
+      const uint64_t dk = umma_desc_sw128(smem_u32(sK + st * kTile), 1024);
+      if (issuer) {
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k) umma_bf16_ss(tS, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
         umma_commit(&k_empty[st]);
-        umma_commit(s_full);
-      };
-      issue_s(0);
-      for (int j = 0; j < nblk; ++j) {
-        if (j + 1 < nblk) {
-          mbar_wait(s_free, j & 1, 24);  // S_j is in registers: S_{j+1} overlaps softmax j
-          issue_s(j + 1);
-        }
-        const int st = j % KST;
-        mbar_wait(p_full, j & 1, 22);
-        mbar_wait(&v_full[st], (j / KST) & 1, 23);
-        tc_fence_after();
-        const uint64_t dv = umma_desc_sw128(smem_u32(sV + st * kTile), 1024, 8192);
+        umma_commit(&s_full[t]);
+      }
+      __syncwarp();
+    };
+    issue_s(0);
+    for (int j = 0; j < nblk; ++j) {
+      if (j + 1 < nblk) {
+        mbar_wait(&s_free[t], j & 1, 24);  // S_j is in registers: S_{j+1} overlaps softmax j
+        issue_s(j + 1);
+      }
+      const int st = j % KST;
+      mbar_wait(&p_full[t], j & 1, 22);
+      mbar_wait(&v_full[st], (j / KST) & 1, 23);
+      tc_fence_after();
+      const uint64_t dv = umma_desc_sw128(smem_u32(sV + st * kTile), 1024, 8192);
+      if (issuer) {
 #pragma unroll
         for (int k = 0; k < BKV / 16; ++k) {
           // A: 16 keys of P = 8 TMEM columns; B: 16 key rows of V = 16 x 128 B further on
           umma_bf16_ts(tO, tP + 8 * k, dv + uint64_t((k * 2048) >> 4), idesc_o, (j | k) != 0);
         }
         umma_commit(&v_empty[st]);
-        umma_commit(o_full);
+        umma_commit(&o_full[t]);
       }
+      __syncwarp();
     }
   } else {
-    // ================= softmax + output (warps 0..3) =================
+    // ================= softmax + output: warps 0..3 tile 0, warps 4..7 tile 1 =================
     // Instruction budget per score (the SM issues 128 lanes/clk; the MMAs need ~512 clk per
     // 128x128 block): 0.5 FMNMX3 + 0.5 FFMA2 + 1 MUFU.EX2 + 0.5 FADD2 + 0.5 F2FP.
-    const int row = warp * 32 + lane;  // query row within the tile == TMEM lane
-    const uint32_t lane_off = uint32_t(warp * 32) << 16;
+    const int t = warp >> 2;
+    const int row = (warp & 3) * 32 + lane;  // query row within the tile == TMEM lane
+    const uint32_t lane_off = uint32_t((warp & 3) * 32) << 16;
+    const uint32_t tS = tmem_base + t * 256 + lane_off;
+    const uint32_t tO = tS + 128;
+    const uint32_t tP = tS + 192;
+    const int qt = q0 + t * BQ;
     float m = -INFINITY;               // running (possibly stale) row max, log2 domain
     float2 l2 = make_float2(0.f, 0.f);
     const float2 sc2 = make_float2(a.scale_log2, a.scale_log2);
@@ -161,23 +221,28 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     for (int j = 0; j < nblk; ++j) {
       const int kv0 = j * BKV;
       const bool tail = kv0 + BKV > a.Sk;
-      mbar_wait(s_full, j & 1, 30);
+      mbar_wait(&s_full[t], j & 1, 30);
       tc_fence_after();
       uint32_t r[BKV];
 #pragma unroll
-      for (int c = 0; c < BKV / 32; ++c) tmem_ld32(tS + lane_off + c * 32, r + c * 32);
+      for (int c = 0; c < BKV / 32; ++c) tmem_ld32(tS + c * 32, r + c * 32);
       tmem_ld_wait();
       tc_fence_before();
-      mbar_arrive(s_free);             // the tensor pipe may overwrite S now
+      mbar_arrive(&s_free[t]);         // the tensor pipe may overwrite S now
       if (tail) {
 #pragma unroll
         for (int i = 0; i < BKV; ++i)
           if (kv0 + i >= a.Sk) r[i] = 0xff800000u;  // -inf: excluded from max, exp2 -> 0
       }
-      float mx = -INFINITY;
+      // four independent chains: the 3-input max has 4-cycle latency, one chain would serialise
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-      for (int i = 0; i < BKV; i += 2)
-        mx = fmaxf(mx, fmaxf(__uint_as_float(r[i]), __uint_as_float(r[i + 1])));
+      for (int i = 0; i < BKV; i += 8) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          mx4[c] = fmaxf(mx4[c], fmaxf(__uint_as_float(r[i + 2 * c]), __uint_as_float(r[i + 2 * c + 1])));
+      }
+      const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       // lazy rescale: keep the stale max unless the new one is > 2^8 larger
       const float m_cand = fmaxf(m, mx * a.scale_log2);
       const bool grow = m_cand - m > kRescaleThreshold;   // true on the first block (m = -inf)
@@ -190,13 +255,15 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       for (int i = 0; i < BKV / 2; ++i) {
         const float2 sv = __ffma2_rn(
             make_float2(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1])), sc2, nm2);
-        const float2 pv = make_float2(ex2(sv.x), ex2(sv.y));
+        // pairs are spread Bresenham-style so MUFU and FMA work interleave in the schedule
+        const bool poly = ((i * kPoly) & 7) + kPoly > 7 && kPoly > 0;
+        const float2 pv = poly ? ex2_poly2(sv) : make_float2(ex2(sv.x), ex2(sv.y));
         l2 = __fadd2_rn(l2, pv);
         r[i] = pack_bf16(pv.x, pv.y);   // in place: word i <- keys 2i, 2i+1 (already consumed)
       }
       if (j > 0) {
         // P V of the previous block must have finished reading P (and writing O)
-        mbar_wait(o_full, (j - 1) & 1, 31);
+        mbar_wait(&o_full[t], (j - 1) & 1, 31);
         tc_fence_after();
         if (__any_sync(0xffffffffu, grow)) {
           // O *= alpha for this warp's 32 rows (alpha = 1 for rows that did not grow)
@@ -204,36 +271,37 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #pragma unroll
           for (int c = 0; c < HD / 32; ++c) {
             uint32_t o[32];
-            tmem_ld32(tO + lane_off + c * 32, o);
+            tmem_ld32(tO + c * 32, o);
             tmem_ld_wait();
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
-              const float2 t = __fmul2_rn(
+              const float2 tt = __fmul2_rn(
                   make_float2(__uint_as_float(o[2 * i]), __uint_as_float(o[2 * i + 1])), al2);
-              o[2 * i] = __float_as_uint(t.x);
-              o[2 * i + 1] = __float_as_uint(t.y);
+              o[2 * i] = __float_as_uint(tt.x);
+              o[2 * i + 1] = __float_as_uint(tt.y);
             }
-            tmem_st32(tO + lane_off + c * 32, o);
+            tmem_st32(tO + c * 32, o);
           }
         }
       }
-      tmem_st32(tP + lane_off, r);
-      tmem_st32(tP + lane_off + 32, r + 32);
+      tmem_st32(tP, r);
+      tmem_st32(tP + 32, r + 32);
       tmem_st_wait();
       tc_fence_before();
-      mbar_arrive(p_full);
+      mbar_arrive(&p_full[t]);
     }
-    // ---- normalise, stage O through smem (the Q tile is dead), TMA store ----
-    mbar_wait(o_full, (nblk - 1) & 1, 32);
+    // ---- normalise, stage O through smem (this tile's Q is dead), TMA store ----
+    mbar_wait(&o_full[t], (nblk - 1) & 1, 32);
     tc_fence_after();
     const float l = l2.x + l2.y;
     const float inv = 1.f / l;
-    uint8_t* orow = sQ + row * 128;
+    uint8_t* otile = sQ + t * kTile;
+    uint8_t* orow = otile + row * 128;
     const int rx = row & 7;
 #pragma unroll
     for (int c = 0; c < HD / 32; ++c) {
       uint32_t o[32];
-      tmem_ld32(tO + lane_off + c * 32, o);
+      tmem_ld32(tO + c * 32, o);
       tmem_ld_wait();
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
@@ -245,13 +313,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         *reinterpret_cast<uint4*>(orow + (((c * 4 + q) ^ rx) * 16)) = w;
       }
     }
-    if (a.lse != nullptr && q0 + row < a.Sq)
-      a.lse[((int64_t)b * a.heads + head) * a.Sq + q0 + row] =
+    if (a.lse != nullptr && qt + row < a.Sq)
+      a.lse[((int64_t)b * a.heads + head) * a.Sq + qt + row] =
           (m + log2f(l)) * 0.6931471805599453f;
     fence_proxy_async_smem();
-    asm volatile("bar.sync 1, 128;" ::: "memory");
-    if (threadIdx.x == 0) {
-      tma_store_4d(&tmO, sQ, head * HD, q0, b, 0);
+    if (t == 0) asm volatile("bar.sync 1, 128;" ::: "memory");
+    else asm volatile("bar.sync 2, 128;" ::: "memory");
+    if ((threadIdx.x & 127) == 0 && qt < a.Sq) {
+      tma_store_4d(&tmO, otile, head * HD, qt, b, 0);
       tma_store_commit();
       tma_store_wait<0>();
     }
@@ -259,9 +328,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 5) {
+  if (warp == kTmaWarp) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 256);
+    tmem_dealloc(tmem_base, 256 * NT);
   }
 }
 
@@ -294,15 +363,26 @@ extern "C" int vst_attn_fwd(const void* q, const void* k, const void* v, void* o
   if ((rc = make_qkv_map(&tK, k, Bt / kv_group, Sk, width, ldk, 0))) return rc;
   if ((rc = make_qkv_map(&tV, v, Bt / kv_group, Sk, width, ldv, 0))) return rc;
   if ((rc = make_qkv_map(&tO, o, Bt, Sq, width, ldo, 1))) return rc;
-  static bool configured = false;
-  if (!configured) {
-    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     kSmemBytes));
-    configured = true;
+  // kPoly: how many of every 8 exp2 pairs run on the FMA pipe.  VST_ATTN_POLY overrides the
+  // default (tuning only).
+  static int poly = -1;
+  if (poly < 0) {
+    const char* e = getenv("VST_ATTN_POLY");
+    poly = e ? atoi(e) : kDefaultPoly;
+    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
   }
   AttnArgs a{lse, Sq, Sk, heads, kv_group, scale * 1.4426950408889634f};
-  dim3 grid((Sq + BQ - 1) / BQ, heads, Bt);
-  attn_fwd_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(tQ, tK, tV, tO, a);
+  dim3 grid((Sq + NT * BQ - 1) / (NT * BQ), heads, Bt);
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (poly) {
+    case 0: attn_fwd_kernel<0><<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tO, a); break;
+    case 3: attn_fwd_kernel<3><<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tO, a); break;
+    case 4: attn_fwd_kernel<4><<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tO, a); break;
+    default: attn_fwd_kernel<2><<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tO, a); break;
+  }
   VST_LAUNCH_OK();
   return VST_OK;
 }
