@@ -111,6 +111,24 @@ int vst_lora_pack_up(const void* Bc, const void* mc, const uint8_t* maskc, const
                      const void* ms, const uint8_t* masks, float scale, void* out, int N, int r,
                      int param_dtype, void* stream);
 
+/* ---- a3/a4/a5/a7 backward: GEMM with transposed operands, deterministic split-K ----------------
+ * D[M,N] (+)= alpha * ( opA(A1) opB(B1)^T + opA(A2) opB(B2)^T )
+ *   opA(A) is [M,K]: transA = 0 -> A stored [M,K] (row stride lda), 1 -> stored [K,M];
+ *   opB(B) is [N,K]: transB = 0 -> B stored [N,K] (row stride ldb), 1 -> stored [K,N].
+ * bf16 operands, fp32 accumulation (tcgen05), bf16 or fp32 output; accumulate != 0 adds into D.
+ * It is the arithmetic autograd derives for unziplora_linear_layer.py:221-263,
+ * temporal_lora.py:29-32 and lora_linear.py:74-81:
+ *   dx = dy W + du [A_c; A_s] (transB=1, two pairs), du = dy B' (transB=1),
+ *   dB' = dy^T u, dA = du^T x, dW = dy^T x (transA = transB = 1, contraction over tokens).
+ * Small outputs with a long contraction are split over k; the fp32 partials go to `workspace`
+ * (vst_gemm_workspace_bytes; 0 = no split needed) and are summed in a fixed order.  With a NULL or
+ * short workspace the call still succeeds, unsplit. */
+int64_t vst_gemm_workspace_bytes(int64_t M, int N, int64_t K1, int64_t K2);
+int vst_gemm(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int64_t K1,
+             const void* A2, int64_t lda2, const void* B2, int64_t ldb2, int64_t K2, int transA,
+             int transB, void* D, int64_t ldd, int64_t M, int N, float alpha, int accumulate,
+             int out_dtype, void* workspace, int64_t workspace_bytes, void* stream);
+
 /* ---- §8f-1 (next): GEGLU gate of the motion feed-forward ------------------------------------
  * out[r, j] = hg[r, j] * gelu(hg[r, inner + j]); diffusers FeedForward("geglu") (un-vendored),
  * exact GELU as animatediff/temporal_transformer.py:55.  bf16. */

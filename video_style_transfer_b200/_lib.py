@@ -30,6 +30,9 @@ SIGNATURES = {
     "vst_lora_gemm": (_i, [_p, _l, _p, _l, _i, _p, _l, _p, _l, _i, _i, _p, _i, _p, _l, _f, _i, _p, _l,
                            _l, _i, _i, _p]),
     "vst_lora_pack_up": (_i, [_p, _p, _p, _p, _p, _p, _f, _p, _i, _i, _i, _p]),
+    "vst_gemm_workspace_bytes": (_l, [_l, _i, _l, _l]),
+    "vst_gemm": (_i, [_p, _l, _p, _l, _l, _p, _l, _p, _l, _l, _i, _i, _p, _l, _l, _i, _f, _i, _i, _p,
+                      _l, _p]),
     "vst_geglu": (_i, [_p, _p, _l, _i, _l, _l, _p]),
     "vst_attn_fwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _l, _l, _l, _l, _i, _f, _p]),
 }

@@ -212,6 +212,37 @@ def lora_pack_up(b_c: Optional[torch.Tensor], m_c: Optional[torch.Tensor],
     return out
 
 
+def gemm(a1: torch.Tensor, b1: torch.Tensor, a2: Optional[torch.Tensor] = None,
+         b2: Optional[torch.Tensor] = None, trans_a: bool = False, trans_b: bool = False,
+         alpha: float = 1.0, out: Optional[torch.Tensor] = None, accumulate: bool = False,
+         out_dtype: torch.dtype = torch.bfloat16) -> torch.Tensor:
+    """out[M,N] (+)= alpha * (opA(a1) opB(b1)^T + opA(a2) opB(b2)^T).  opA(a) is [M,K] (a stored
+    [K,M] when trans_a); opB(b) is [N,K] (b stored [K,N] when trans_b).  The backward-pass GEMM."""
+    _cuda(a1, b1, a2, b2, out)
+    _mat(a1, "a1"), _mat(b1, "b1")
+    m, k1 = (a1.shape[1], a1.shape[0]) if trans_a else a1.shape
+    n = b1.shape[1] if trans_b else b1.shape[0]
+    assert (b1.shape[0] if trans_b else b1.shape[1]) == k1, "gemm: contraction extents differ"
+    k2 = 0
+    if a2 is not None:
+        _mat(a2, "a2"), _mat(b2, "b2")
+        m2, k2 = (a2.shape[1], a2.shape[0]) if trans_a else a2.shape
+        assert m2 == m and (b2.shape[1] if trans_b else b2.shape[0]) == n
+        assert (b2.shape[0] if trans_b else b2.shape[1]) == k2
+    if out is None:
+        assert not accumulate
+        out = torch.empty((m, n), dtype=out_dtype, device=a1.device)
+    assert out.shape == (m, n) and out.stride(1) == 1
+    wsb = lib.vst_gemm_workspace_bytes(m, n, k1, k2)
+    ws = torch.empty(wsb, dtype=torch.uint8, device=a1.device) if wsb else None
+    check(lib.vst_gemm(a1.data_ptr(), a1.stride(0), b1.data_ptr(), b1.stride(0), k1, _ptr(a2),
+                       a2.stride(0) if a2 is not None else 0, _ptr(b2),
+                       b2.stride(0) if b2 is not None else 0, k2, int(trans_a), int(trans_b),
+                       out.data_ptr(), out.stride(0), m, n, alpha, int(accumulate), _dt(out),
+                       _ptr(ws), wsb, _stream()), "vst_gemm")
+    return out
+
+
 # ---- a2 -------------------------------------------------------------------------------------------
 def attn_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int,
              scale: Optional[float] = None, return_lse: bool = False):
