@@ -129,6 +129,19 @@ int vst_gemm(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int64_t
              int transB, void* D, int64_t ldd, int64_t M, int N, float alpha, int accumulate,
              int out_dtype, void* workspace, int64_t workspace_bytes, void* stream);
 
+/* Adjoint of vst_lora_pack_up.  dBp: fp32 gradient of the packed operand, row stride ld, branch br
+ * occupying columns [br*rp, br*rp + r) (rp = rank padded to 8).  Outputs (fp32, any may be NULL):
+ *   dB_br[n,j] = scale m_br[n] mask_br[n] dBp[n, br*rp+j],  dm_br[n] = scale mask_br[n] sum_j dBp B_br. */
+int vst_lora_pack_up_bwd(const float* dBp, int64_t ld, int rp, const void* Bc, const void* mc,
+                         const uint8_t* maskc, const void* Bs, const void* ms,
+                         const uint8_t* masks, float scale, float* dBc, float* dmc, float* dBs,
+                         float* dms, int N, int r, int param_dtype, void* stream);
+/* out[n] = alpha * sum_m x[m, n] (bf16 in, fp32 out): the bias gradient.  Deterministic two-stage
+ * sum through a caller workspace of vst_colsum_workspace_bytes(M, N) bytes. */
+int64_t vst_colsum_workspace_bytes(int64_t M, int N);
+int vst_colsum(const void* x, int64_t ld, int64_t M, int N, float alpha, float* out,
+               void* workspace, int64_t workspace_bytes, void* stream);
+
 /* ---- §8f-1 (next): GEGLU gate of the motion feed-forward ------------------------------------
  * out[r, j] = hg[r, j] * gelu(hg[r, inner + j]); diffusers FeedForward("geglu") (un-vendored),
  * exact GELU as animatediff/temporal_transformer.py:55.  bf16. */

@@ -71,3 +71,116 @@ def test_gemm_split_k_is_deterministic(ops):
     assert torch.equal(a, b)
     want = dy.float().T @ u.float()
     assert rel_err(a, want) < 2e-3
+
+
+# ---- a4 / a7: parameter and input gradients of the LoRA layers against the reference's own autograd
+#      results (tests/golden/*.npz, written by oracle/make_golden.py from the reference modules) ----
+import os
+
+import numpy as np
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _sub(g, prefix):
+    return {k[len(prefix):]: torch.from_numpy(np.asarray(g[k])) for k in g.files if k.startswith(prefix)}
+
+
+def _close(got, want, what, tol=2e-2):
+    assert got is not None, f"{what}: no gradient"
+    assert got.shape == want.shape, (what, got.shape, want.shape)
+    e = rel_err(got, want)
+    assert e < tol, f"{what}: rel err {e}"
+
+
+@pytest.mark.parametrize("ft", ["both", "content", "style"])
+@pytest.mark.parametrize("masked", [0, 1])
+def test_unziplora_train_gradients_golden(ft, masked):
+    """unziplora_linear_layer.py:221-263 forward + backward: dx (both streams), dA, dB and the merger
+    gradients of both branches, hard column masks on and off."""
+    from video_style_transfer_b200.unziplora_unet.unziplora_linear_layer import UnZipLoRALinearLayer
+    g = np.load(os.path.join(GOLD, "unziplora.npz"))
+    p, t = _sub(g, "infer/"), _sub(g, "train/")
+    lay = UnZipLoRALinearLayer(48, 40, 8, ["content", "style"], lora_matrix_num=2)
+    with torch.no_grad():
+        for k in ("content_down", "content_up", "style_down", "style_up"):
+            lay.lora_matrix_dic[k].weight.copy_(t[k])
+        lay.merge_content.copy_(t["merge_content"])
+        lay.merge_style.copy_(t["merge_style"])
+    lay = lay.cuda()
+    lay.mask_content, lay.mask_style = t["mask_content"].cuda(), t["mask_style"].cuda()
+    lay.set_forward(ft)
+    lay.set_layer_mask("content", bool(masked))
+    lay.set_layer_mask("style", bool(masked))
+    x = p["x"].cuda().requires_grad_(True)
+    x2 = p["x2"].cuda().requires_grad_(True)
+    y = lay(x, x2)
+    w = _sub(g, f"train/{ft}_{masked}/")
+    _close(y, w["y"], "y")
+    y.backward(t["dy"].cuda())
+    d = lay.lora_matrix_dic
+    if "dx" in w:
+        _close(x.grad, w["dx"], "dx")
+    if "dx2" in w:
+        _close(x2.grad, w["dx2"], "dx2")
+    for key in ("content", "style"):
+        if f"d_{key}_down" in w:
+            _close(d[f"{key}_down"].weight.grad, w[f"d_{key}_down"], f"d_{key}_down")
+            _close(d[f"{key}_up"].weight.grad, w[f"d_{key}_up"], f"d_{key}_up")
+    if "dmc" in w:
+        _close(lay.merge_content.grad, w["dmc"], "dmc")
+        _close(lay.merge_style.grad, w["dms"], "dms")
+
+
+def test_temporal_lora_gradients_golden():
+    """temporal_lora.py:29-32: dx, dA, dB with the base frozen (its grads must stay None)."""
+    from video_style_transfer_b200.animatediff.temporal_lora import TemporalLoRALinear
+    g = np.load(os.path.join(GOLD, "lora_linear.npz"))
+    T = lambda a: torch.from_numpy(np.asarray(a))
+    base = torch.nn.Linear(48, 40)
+    with torch.no_grad():
+        base.weight.copy_(T(g["t_weight"]))
+        base.bias.copy_(T(g["t_bias"]))
+    m = TemporalLoRALinear(base, rank=4, alpha=2.0)
+    with torch.no_grad():
+        m.lora_A.copy_(T(g["t_A"]))
+        m.lora_B.copy_(T(g["t_B"]))
+    m = m.cuda()
+    x = T(g["t_x"]).cuda().requires_grad_(True)
+    y = m(x)
+    _close(y, T(g["t_y"]), "y")
+    y.backward(T(g["t_dy"]).cuda())
+    _close(x.grad, T(g["t_dx"]), "dx")
+    _close(m.lora_A.grad, T(g["t_dA"]), "dA")
+    _close(m.lora_B.grad, T(g["t_dB"]), "dB")
+    assert m.base.weight.grad is None and m.base.bias.grad is None
+
+
+def test_plain_linear_weight_and_bias_gradients(ops):
+    """Trainable projections of the motion module (proj_in / proj_out / feed-forward keep their
+    weights trainable, animatediff/utils.py:66-96): dW = dy^T x, db = colsum(dy), dx = dy W."""
+    from video_style_transfer_b200._host import fused_linear
+    torch.manual_seed(5)
+    m, k, n = 1000, 320, 640
+    x = torch.randn(m, k).to(torch.bfloat16)
+    w = torch.nn.Parameter(torch.randn(n, k) * 0.05)
+    b = torch.nn.Parameter(torch.randn(n))
+    res = torch.randn(m, n).to(torch.bfloat16)
+    dy = torch.randn(m, n).to(torch.bfloat16)
+    xr, rr = x.float().requires_grad_(True), res.float().requires_grad_(True)
+    want = (torch.nn.functional.linear(xr, w.detach().to(torch.bfloat16).float().requires_grad_(True), b.detach()) + rr) * 0.5
+    wref = [t for t in (xr, rr)]
+    # reference gradients in fp32 on the bf16-rounded operands
+    w32 = w.detach().to(torch.bfloat16).float().requires_grad_(True)
+    b32 = b.detach().clone().requires_grad_(True)
+    y32 = (torch.nn.functional.linear(xr, w32, b32) + rr) * 0.5
+    y32.backward(dy.float())
+    wd, bd = torch.nn.Parameter(w.detach().cuda()), torch.nn.Parameter(b.detach().cuda())
+    xd, rd = x.cuda().requires_grad_(True), res.cuda().requires_grad_(True)
+    y = fused_linear(xd, wd, bd, None, rd, 0.5)
+    _close(y, y32.detach(), "y")
+    y.backward(dy.cuda())
+    _close(xd.grad, xr.grad, "dx")
+    _close(rd.grad, rr.grad, "dres")
+    _close(wd.grad, w32.grad, "dW")
+    _close(bd.grad, b32.grad, "db")

@@ -300,9 +300,16 @@ def test_positional_encoding_matches_reference_table():
 def test_bf16_cache_invalidates_on_inplace_update():
     from video_style_transfer_b200._host import bf16_cached
     w = torch.nn.Parameter(torch.randn(8, 8))
-    a = bf16_cached(w)
-    assert bf16_cached(w) is a
+    with torch.no_grad():
+        a = bf16_cached(w)
+        assert bf16_cached(w) is a
+    # with autograd recording, the same cached storage comes back wrapped in a graph node whose
+    # backward hands the operand gradient to the parameter (cast to its dtype)
+    t = bf16_cached(w)
+    assert t.requires_grad and t.data_ptr() == a.data_ptr()
+    t.backward(torch.ones_like(t))
+    assert w.grad is not None and w.grad.dtype == w.dtype and torch.equal(w.grad, torch.ones_like(w))
     with torch.no_grad():
         w.add_(1.0)
-    b = bf16_cached(w)
+        b = bf16_cached(w)
     assert b is not a and torch.equal(b, w.detach().to(torch.bfloat16))

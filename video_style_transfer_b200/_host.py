@@ -32,10 +32,16 @@ def bf16_cached(*tensors: torch.Tensor, pad_rows: bool = False) -> torch.Tensor:
     until any of them is modified in place (tensor._version) or re-allocated (data_ptr).
     pad_rows: zero-pad each tensor's row count to a multiple of 8 first (LoRA down matrices)."""
     pad_rows = pad_rows and any(t.shape[0] % 8 for t in tensors)
+    track = torch.is_grad_enabled() and any(t.requires_grad for t in tensors)
     if len(tensors) == 1 and not pad_rows:
         t = tensors[0]
         if t.dtype == torch.bfloat16 and t.is_contiguous():
-            return t.detach()
+            return t if track else t.detach()
+    if track:
+        from ._autograd import CastCatFn
+        with torch.no_grad():
+            val = bf16_cached(*tensors, pad_rows=pad_rows)
+        return CastCatFn.apply(pad_rows, val, *tensors)
     key = tuple(id(t) for t in tensors) + (pad_rows,)
     stamp = tuple((t._version, t.data_ptr()) for t in tensors)
     hit = _cache.get(key)
@@ -70,7 +76,9 @@ def fused_linear(x2: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Te
     """y = (act(x W^T + u B'^T + bias) + residual) * out_scale on the tcgen05 GEMM.
     low_rank = (u (M,R) bf16, B' (N,R) bf16) or None."""
     w = bf16_cached(weight)
-    b = None if bias is None else bias.detach()
+    b = bias
+    if b is not None and not (torch.is_grad_enabled() and b.requires_grad):
+        b = b.detach()
     if b is not None and b.dtype not in (torch.float32, torch.bfloat16):
         b = b.float()
     u, bp = low_rank if low_rank is not None else (None, None)
@@ -89,4 +97,29 @@ def cached_build(tensors: Sequence[torch.Tensor], extra, builder):
     with torch.no_grad():
         val = builder()
     _cache[key] = (tuple(weakref.ref(t) for t in tensors), stamp, val)
+    return val
+
+
+def packed_up(b_c, m_c, mask_c, b_s, m_s, mask_s, scale: float, rank: int, extra=()) -> torch.Tensor:
+    """B' = scale * [m_c . mask_c . B_c | m_s . mask_s . B_s] as a bf16 (N, nbr*pad8(rank)) GEMM operand
+    (vst_lora_pack_up), cached on the parameter versions; differentiable w.r.t. B_* and m_* when they
+    require grad (vst_lora_pack_up_bwd)."""
+    ref = b_c if b_c is not None else b_s
+    nbr = (b_c is not None) + (b_s is not None)
+    deps = [t for t in (b_c, m_c, mask_c, b_s, m_s, mask_s) if t is not None]
+    same = lambda t: None if t is None else t.detach().to(device=ref.device, dtype=ref.dtype).contiguous()
+    dev = lambda t: None if t is None else t.to(ref.device)
+
+    def build():
+        bp = ops.lora_pack_up(None if b_c is None else b_c.detach().contiguous(), same(m_c), dev(mask_c),
+                              None if b_s is None else b_s.detach().contiguous(), same(m_s), dev(mask_s),
+                              float(scale))
+        return pad_branch_cols(bp, nbr, rank)
+
+    sig = ("packup", float(scale), b_c is not None, m_c is not None, mask_c is not None,
+           b_s is not None, m_s is not None, mask_s is not None) + tuple(extra)
+    val = cached_build(deps, sig, build)
+    if torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in (b_c, m_c, b_s, m_s)):
+        from ._autograd import PackUpFn
+        return PackUpFn.apply(val, float(scale), rank, dev(mask_c), dev(mask_s), b_c, m_c, b_s, m_s)
     return val

@@ -33,6 +33,9 @@ SIGNATURES = {
     "vst_gemm_workspace_bytes": (_l, [_l, _i, _l, _l]),
     "vst_gemm": (_i, [_p, _l, _p, _l, _l, _p, _l, _p, _l, _l, _i, _i, _p, _l, _l, _i, _f, _i, _i, _p,
                       _l, _p]),
+    "vst_lora_pack_up_bwd": (_i, [_p, _l, _i, _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _i, _i, _i, _p]),
+    "vst_colsum_workspace_bytes": (_l, [_l, _i]),
+    "vst_colsum": (_i, [_p, _l, _l, _i, _f, _p, _p, _l, _p]),
     "vst_geglu": (_i, [_p, _p, _l, _i, _l, _l, _p]),
     "vst_attn_fwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _l, _l, _l, _l, _i, _f, _p]),
 }

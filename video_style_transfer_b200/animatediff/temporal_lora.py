@@ -11,7 +11,7 @@ import torch
 import torch.nn as nn
 
 from .. import ops
-from .._host import as_rows_bf16, bf16_cached, cached_build, fused_linear, pad_branch_cols
+from .._host import as_rows_bf16, bf16_cached, cached_build, fused_linear, packed_up, pad_branch_cols
 
 
 class TemporalLoRALinear(nn.Module):
@@ -43,11 +43,7 @@ class TemporalLoRALinear(nn.Module):
 
     def site_up(self, scale: float = 1.0):
         """(alpha/r) * B as bf16 (out, pad8(r)), cached on lora_B's version."""
-        def build():
-            bp = ops.lora_pack_up(None, None, None, self.lora_B.detach().contiguous(), None, None,
-                                  float(self.scale))
-            return pad_branch_cols(bp, 1, self.rank)
-        return cached_build([self.lora_B], float(self.scale), build)
+        return packed_up(None, None, None, self.lora_B, None, None, float(self.scale), self.rank)
 
     def fused_forward(self, x2: torch.Tensor, scale: float = 1.0, residual=None,
                       out_scale: float = 1.0, act: str = "none",

@@ -78,7 +78,10 @@ def project_fused(layers: Sequence, x2: torch.Tensor, scale: float = 1.0) -> Lis
     w = bf16_cached(*ws)
     bias = None
     if biases[0] is not None:
-        bias = cached_build(list(biases), "catbias", lambda: torch.cat([b.detach().float() for b in biases]))
+        if torch.is_grad_enabled() and any(b.requires_grad for b in biases):
+            bias = torch.cat([b.float() for b in biases])
+        else:
+            bias = cached_build(list(biases), "catbias", lambda: torch.cat([b.detach().float() for b in biases]))
     k2 = k2s.pop()
     if k2 is None:
         y = ops.lora_gemm(x2, w, bias=bias)
@@ -86,7 +89,10 @@ def project_fused(layers: Sequence, x2: torch.Tensor, scale: float = 1.0) -> Lis
         flat = [a for d in downs for a in d]
         a_cat = bf16_cached(*flat, pad_rows=True)                       # (G*K2, in)
         assert a_cat.shape[0] == len(sites) * k2
-        bp = cached_build(list(ups), "catup", lambda: torch.cat(list(ups), dim=0).contiguous())
+        if torch.is_grad_enabled() and any(u_.requires_grad for u_ in ups):
+            bp = torch.cat(list(ups), dim=0)
+        else:
+            bp = cached_build(list(ups), "catup", lambda: torch.cat(list(ups), dim=0).contiguous())
         u = ops.lora_gemm(x2, a_cat)                                    # (M, G*K2)
         y = ops.lora_gemm(x2, w, u, bp, bias=bias, k2_group_n=n0)
     return [y[:, i * n0:(i + 1) * n0] for i in range(len(sites))]

@@ -158,12 +158,34 @@ def _mat(t: torch.Tensor, name: str):
     return t
 
 
+def _needs_grad(*ts) -> bool:
+    return torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in ts)
+
+
 def lora_gemm(a1: torch.Tensor, b1: torch.Tensor, a2: Optional[torch.Tensor] = None,
               b2: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None,
               residual: Optional[torch.Tensor] = None, out_scale: float = 1.0,
               act: str = "none", k2_group_n: int = 0, out: Optional[torch.Tensor] = None,
               out_dtype: torch.dtype = torch.bfloat16) -> torch.Tensor:
-    """out[M,N] = (act(a1 b1^T + a2 b2^T + bias) + residual) * out_scale; act in {none, gelu}."""
+    """out[M,N] = (act(a1 b1^T + a2 b2^T + bias) + residual) * out_scale; act in {none, gelu}.
+    Differentiable (act none): the backward runs vst_gemm / vst_colsum (see _autograd.py)."""
+    if _needs_grad(a1, b1, a2, b2, bias, residual):
+        if out is not None:
+            raise RuntimeError("lora_gemm: out= cannot be combined with autograd")
+        from ._autograd import LoraGemmFn
+        return LoraGemmFn.apply(a1, b1, a2, b2, bias, residual, float(out_scale), act,
+                                int(k2_group_n), out_dtype)
+    return lora_gemm_raw(a1, b1, a2, b2, bias, residual, out_scale, act, k2_group_n, out, out_dtype)
+
+
+def lora_gemm_raw(a1: torch.Tensor, b1: torch.Tensor, a2: Optional[torch.Tensor] = None,
+                  b2: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None,
+                  residual: Optional[torch.Tensor] = None, out_scale: float = 1.0,
+                  act: str = "none", k2_group_n: int = 0, out: Optional[torch.Tensor] = None,
+                  out_dtype: torch.dtype = torch.bfloat16) -> torch.Tensor:
+    a1, b1, a2, b2 = (None if t is None else t.detach() for t in (a1, b1, a2, b2))
+    bias = None if bias is None else bias.detach()
+    residual = None if residual is None else residual.detach()
     _cuda(a1, b1, a2, b2, bias, residual, out)
     _mat(a1, "a1"), _mat(b1, "b1")
     m, k1 = a1.shape
@@ -240,6 +262,37 @@ def gemm(a1: torch.Tensor, b1: torch.Tensor, a2: Optional[torch.Tensor] = None,
                        b2.stride(0) if b2 is not None else 0, k2, int(trans_a), int(trans_b),
                        out.data_ptr(), out.stride(0), m, n, alpha, int(accumulate), _dt(out),
                        _ptr(ws), wsb, _stream()), "vst_gemm")
+    return out
+
+
+def lora_pack_up_bwd(d_bp: torch.Tensor, rank: int, b_c, m_c, mask_c, b_s, m_s, mask_s, scale: float):
+    """Adjoint of lora_pack_up: d_bp (N, nbr*pad8(r)) fp32 -> (dB_c, dm_c, dB_s, dm_s) fp32 (None
+    where the branch / merger is absent)."""
+    ref = b_c if b_c is not None else b_s
+    n, r = ref.shape
+    assert d_bp.dtype == torch.float32 and d_bp.stride(1) == 1
+    rp = (rank + 7) // 8 * 8
+    new = lambda like, shape: None if like is None else torch.empty(shape, dtype=torch.float32, device=ref.device)
+    dbc, dbs = new(b_c, (n, r)), new(b_s, (n, r))
+    dmc, dms = new(m_c if b_c is not None else None, (n,)), new(m_s if b_s is not None else None, (n,))
+    masks = [None if mk is None else mk.to(torch.uint8).contiguous() for mk in (mask_c, mask_s)]
+    check(lib.vst_lora_pack_up_bwd(d_bp.data_ptr(), d_bp.stride(0), rp, _ptr(b_c), _ptr(m_c),
+                                   _ptr(masks[0]), _ptr(b_s), _ptr(m_s), _ptr(masks[1]), scale,
+                                   _ptr(dbc), _ptr(dmc), _ptr(dbs), _ptr(dms), n, r, _dt(ref),
+                                   _stream()), "vst_lora_pack_up_bwd")
+    return dbc, dmc, dbs, dms
+
+
+def colsum(x: torch.Tensor, alpha: float = 1.0) -> torch.Tensor:
+    """fp32 column sums of a bf16 (M, N) matrix (the bias gradient)."""
+    _cuda(x)
+    _mat(x, "x")
+    m, n = x.shape
+    out = torch.empty(n, dtype=torch.float32, device=x.device)
+    wsb = lib.vst_colsum_workspace_bytes(m, n)
+    ws = torch.empty(wsb, dtype=torch.uint8, device=x.device)
+    check(lib.vst_colsum(x.data_ptr(), x.stride(0), m, n, alpha, out.data_ptr(), ws.data_ptr(), wsb,
+                         _stream()), "vst_colsum")
     return out
 
 

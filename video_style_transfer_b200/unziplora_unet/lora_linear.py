@@ -11,7 +11,7 @@ import torch
 from torch import nn
 
 from .. import ops
-from .._host import as_rows_bf16, bf16_cached, cached_build, fused_linear, pad_branch_cols
+from .._host import as_rows_bf16, bf16_cached, cached_build, fused_linear, packed_up, pad_branch_cols
 
 
 class LoRALinearLayer(nn.Module):
@@ -37,11 +37,7 @@ class LoRALinearLayer(nn.Module):
     def site_up(self, scale: float = 1.0):
         s = scale if self.network_alpha is None else scale * self.network_alpha / self.rank
 
-        def build():
-            bp = ops.lora_pack_up(None, None, None, self.up.weight.detach().contiguous(), None,
-                                  None, float(s))
-            return pad_branch_cols(bp, 1, self.rank)
-        return cached_build([self.up.weight], float(s), build)
+        return packed_up(None, None, None, self.up.weight, None, None, float(s), self.rank)
 
     def fused_operands(self, x_content, x_style=None, scale: float = 1.0):
         u = ops.lora_gemm(x_content, bf16_cached(self.down.weight, pad_rows=True))

@@ -15,7 +15,7 @@ import torch
 from torch import nn
 
 from .. import ops
-from .._host import as_rows_bf16, bf16_cached, cached_build, pad8, pad_branch_cols
+from .._host import as_rows_bf16, bf16_cached, cached_build, pad8, packed_up, pad_branch_cols
 
 _KEYS = ("content", "style")
 
@@ -80,26 +80,13 @@ class _UnZipBase(nn.Module):
         if not act:
             return None
         d = self.lora_matrix_dic
-        ups, mrg, msk, deps = {}, {}, {}, []
+        ups, mrg, msk = {}, {}, {}
         for k, use_merger, mask in act:
             ups[k] = d[f"{k}_up"].weight
             mrg[k] = getattr(self, f"merge_{k}") if use_merger else None
             msk[k] = mask
-            deps += [t for t in (ups[k], mrg[k], mask) if t is not None]
-        sig = (float(scale), tuple((k, um, mk is not None) for k, um, mk in act))
-
-        def build():
-            g = lambda t, like: None if t is None else t.detach().to(device=like.device, dtype=like.dtype).contiguous()
-            uc, us = ups.get("content"), ups.get("style")
-            like = uc if uc is not None else us
-            bp = ops.lora_pack_up(
-                None if uc is None else uc.detach().contiguous(), g(mrg.get("content"), like),
-                None if msk.get("content") is None else msk["content"].to(like.device),
-                None if us is None else us.detach().contiguous(), g(mrg.get("style"), like),
-                None if msk.get("style") is None else msk["style"].to(like.device), float(scale))
-            return pad_branch_cols(bp, len(act), self.rank)
-
-        return cached_build(deps, sig, build)
+        return packed_up(ups.get("content"), mrg.get("content"), msk.get("content"),
+                         ups.get("style"), mrg.get("style"), msk.get("style"), float(scale), self.rank)
 
     def fused_operands(self, x_content: torch.Tensor, x_style: Optional[torch.Tensor],
                        scale: float = 1.0) -> Optional[Tuple[torch.Tensor, torch.Tensor]]:
@@ -114,6 +101,9 @@ class _UnZipBase(nn.Module):
         downs = self.site_downs()
         if len(act) == 2 and x_style is x_content:
             u = ops.lora_gemm(x_content, bf16_cached(*downs, pad_rows=True))   # one GEMM, N = 2r
+        elif torch.is_grad_enabled() and any(t.requires_grad for t in (x_content, x_style, *downs)):
+            u = torch.cat([ops.lora_gemm(xs[k], bf16_cached(downs[i], pad_rows=True))
+                           for i, (k, _, _) in enumerate(act)], dim=1)
         else:
             m, r8 = x_content.shape[0], pad8(self.rank)
             u = torch.empty((m, len(act) * r8), dtype=torch.bfloat16, device=x_content.device)
