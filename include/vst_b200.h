@@ -157,6 +157,20 @@ int vst_attn_fwd(const void* q, const void* k, const void* v, void* o, float* ls
                  int heads, int Sq, int Sk, int d, int64_t ldq, int64_t ldk, int64_t ldv,
                  int64_t ldo, int kv_group, float scale, void* stream);
 
+/* ---- a2 backward ------------------------------------------------------------------------------
+ * Gradients of vst_attn_fwd (autograd through F.scaled_dot_product_attention,
+ * animatediff/attention_processor.py:78-80).  o / lse are the forward's outputs, d_o the incoming
+ * gradient; dq (Bt,Sq,C), dk / dv (Bt/kv_group,Sk,C) are written in bf16 (the text K/V gradients
+ * are summed over the kv_group frames that shared them, :62-66).  `workspace`: 256-byte aligned,
+ * vst_attn_bwd_workspace_bytes(...) bytes (D = rowsum(dO.O), the fp32 dQ accumulator and, for
+ * kv_group > 1, fp32 dK / dV accumulators). */
+int64_t vst_attn_bwd_workspace_bytes(int Bt, int heads, int Sq, int Sk, int kv_group);
+int vst_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o,
+                 const float* lse, void* dq, void* dk, void* dv, int Bt, int heads, int Sq, int Sk,
+                 int d, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, int64_t lddo,
+                 int64_t lddq, int64_t lddk, int64_t lddv, int kv_group, float scale,
+                 void* workspace, int64_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

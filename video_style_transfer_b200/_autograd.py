@@ -114,3 +114,25 @@ class PackUpFn(torch.autograd.Function):
                                                   ctx.masks[0], cont(b_s), same(m_s), ctx.masks[1], scale)
         like = lambda gr, t: None if (gr is None or t is None) else gr.to(t.dtype)
         return (None, None, None, None, None, like(dbc, b_c), like(dmc, m_c), like(dbs, b_s), like(dms, m_s))
+
+
+class AttnFn(torch.autograd.Function):
+    """softmax(q k^T * scale) v per head (vst_attn_fwd) with the flash backward (vst_attn_bwd)."""
+
+    @staticmethod
+    def forward(ctx, q, k, v, heads, scale):
+        o, lse = ops.attn_fwd_raw(q, k, v, heads, scale, return_lse=True)
+        ctx.save_for_backward(q, k, v, o, lse)
+        ctx.cfg = (heads, scale)
+        return o
+
+    @staticmethod
+    def backward(ctx, d_o):
+        q, k, v, o, lse = ctx.saved_tensors
+        heads, scale = ctx.cfg
+        g = d_o.detach()
+        if g.dtype != torch.bfloat16 or g.stride(2) != 1 or g.stride(0) != g.shape[1] * g.stride(1) \
+                or g.stride(1) % 8:
+            g = g.to(torch.bfloat16).contiguous()
+        dq, dk, dv = ops.attn_bwd(q.detach(), k.detach(), v.detach(), o, g, lse, heads, scale)
+        return dq, dk, dv, None, None

@@ -37,6 +37,8 @@ SIGNATURES = {
     "vst_colsum_workspace_bytes": (_l, [_l, _i]),
     "vst_colsum": (_i, [_p, _l, _l, _i, _f, _p, _p, _l, _p]),
     "vst_geglu": (_i, [_p, _p, _l, _i, _l, _l, _p]),
+    "vst_attn_bwd_workspace_bytes": (_l, [_i, _i, _i, _i, _i]),
+    "vst_attn_bwd": (_i, [_p] * 9 + [_i] * 5 + [_l] * 8 + [_i, _f, _p, _l, _p]),
     "vst_attn_fwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _l, _l, _l, _l, _i, _f, _p]),
 }
 

@@ -1,0 +1,473 @@
+// a2 backward: gradients of softmax(Q K^T * scale) V for head dim 64 on tcgen05 + TMEM + TMA.
+// Reference: autograd through F.scaled_dot_product_attention, animatediff/attention_processor.py
+// :78-80 (train_animatediff.py back-propagates through every spatial attention to reach the
+// motion modules and the mergers).
+//
+// Standard flash backward with the probabilities recomputed from the saved log-sum-exp:
+//   D_i = sum_d dO_id O_id                                   (attn_bwd_dot_kernel)
+//   P = exp(S * scale - LSE),  dP = dO V^T,  dS = P (.) (dP - D) * scale
+//   dV = P^T dO,  dK = dS^T Q,  dQ = dS K
+// One CTA owns a 128-key tile of one (batch, head) and walks the query tiles.  Five tcgen05 GEMMs
+// per (query tile, key tile) pair, all operands straight from their row-major TMA tiles:
+//   S  = Q K^T        A = Q   [q x d]  K-major      B = K  [k x d]  K-major
+//   dP = dO V^T       A = dO  [q x d]  K-major      B = V  [k x d]  K-major
+//   dV += P^T dO      A = P   [q x k] as MN-major   B = dO [q x d]  as MN-major   (contraction: q)
+//   dK += dS^T Q      A = dS  [q x k] as MN-major   B = Q  [q x d]  as MN-major
+//   dQ  = dS K        A = dS  [q x k]  K-major      B = K  [k x d]  as MN-major   (contraction: k)
+// P and dS are written once to shared memory (bf16, 128-byte swizzle, [q rows][64-key blocks]); the
+// same bytes serve as the MN-major A of dV / dK and the K-major A of dQ.  dV / dK accumulate in
+// TMEM over the whole walk; dQ of each pair is added to an fp32 accumulator in global memory
+// (vector atomics, [Bt, heads, Sq, 64] so a warp adds whole 128-byte lines) and converted to bf16
+// afterwards.  TMEM: S [0,128) dP [128,256) dV [256,320) dK [320,384) dQ [384,448).
+// 448 threads: warps 0..7 softmax (warp w: TMEM lane quarter w%4, key half w/4), warp 8 TMA,
+// warp 9 MMA issue (elected lane), warps 10..13 dQ drain.
+// Roofline: tensor pipe; FLOPs = 2.5 x forward = 10 * Bt*h*Sq*Sk*d.
+#include "common.cuh"
+
+namespace {
+
+constexpr int BQ = 128, BKV = 128, HD = 64;
+constexpr int kTile = 128 * HD * 2;     // 16 KB: one [128 x 64] bf16 tile
+constexpr int kPBytes = 128 * 128 * 2;  // 32 KB: P or dS, two 64-key blocks of [128 q x 128 B]
+constexpr int kSoftmaxWarps = 8;
+constexpr int kTmaWarp = 8, kMmaWarp = 9;   // warps 10..13: dQ drain
+constexpr int kThreads = 32 * 14;
+constexpr int kSmemBytes = 2 * kTile /*K,V*/ + 4 * kTile /*Q,dO x2*/ + 2 * kPBytes + 1024 + 256;
+
+__device__ __forceinline__ float ex2f(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+struct BwdArgs {
+  const float* lse;   // [Bt, heads, Sq] natural log
+  const float* dvec;  // [Bt, heads, Sq] D = rowsum(dO . O)
+  float* dq_acc;      // [Bt, heads, Sq, 64] fp32, zeroed
+  void* dk;           // bf16 [Bk, Sk, C] (kv_group == 1) or fp32 accumulator [Bk, Sk, C]
+  void* dv;
+  int64_t ldk, ldv;   // row strides (elements) of dk / dv
+  int Sq, Sk, heads, kv_group;
+  float scale, scale_log2;
+};
+
+// ---- D = rowsum(dO . O): 8 lanes per (row, head), 16-byte loads ---------------------------------
+__global__ void attn_bwd_dot_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
+                                    float* __restrict__ dvec, int64_t rows, int Sq, int heads,
+                                    int64_t ldo, int64_t lddo) {
+  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t item = gid >> 3;          // (row, head)
+  const int sub = (int)(gid & 7);
+  if (item >= rows * heads) return;
+  const int64_t row = item / heads;
+  const int h = (int)(item % heads);
+  const uint4 a = *reinterpret_cast<const uint4*>(o + row * ldo + h * HD + sub * 8);
+  const uint4 b = *reinterpret_cast<const uint4*>(d_o + row * lddo + h * HD + sub * 8);
+  const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 x = unpack_bf16(aw[i]), y = unpack_bf16(bw[i]);
+    s += x.x * y.x + x.y * y.y;
+  }
+  s += __shfl_xor_sync(0xffffffffu, s, 1);
+  s += __shfl_xor_sync(0xffffffffu, s, 2);
+  s += __shfl_xor_sync(0xffffffffu, s, 4);
+  if (sub == 0) {
+    const int64_t b_ = row / Sq, q = row % Sq;
+    dvec[(b_ * heads + h) * Sq + q] = s;
+  }
+}
+
+// ---- fp32 [B, heads, S, 64] accumulator -> bf16 [B, S, heads*64] (row stride ld) -------------------
+__global__ void attn_bwd_dq_convert_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ out,
+                                           int64_t rows, int S, int heads, int64_t ld) {
+  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;   // 8 elements each
+  const int64_t item = gid >> 3;
+  const int sub = (int)(gid & 7);
+  if (item >= rows * heads) return;
+  const int64_t row = item / heads;
+  const int h = (int)(item % heads);
+  const int64_t b_ = row / S, q = row % S;
+  const float* src = acc + (((b_ * heads + h) * S + q) * HD) + sub * 8;
+  const float4 x = *reinterpret_cast<const float4*>(src), y = *reinterpret_cast<const float4*>(src + 4);
+  uint4 w;
+  w.x = pack_bf16(x.x, x.y); w.y = pack_bf16(x.z, x.w);
+  w.z = pack_bf16(y.x, y.y); w.w = pack_bf16(y.z, y.w);
+  *reinterpret_cast<uint4*>(out + row * ld + h * HD + sub * 8) = w;
+}
+// fp32 [rows, C] (row stride C) -> bf16 [rows, C] (row stride ld)
+__global__ void attn_bwd_rows_convert_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ out,
+                                             int64_t rows, int C, int64_t ld) {
+  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;   // 8 elements each
+  const int per_row = C / 8;
+  if (gid >= rows * per_row) return;
+  const int64_t row = gid / per_row;
+  const int c = (int)(gid % per_row) * 8;
+  const float* src = acc + row * C + c;
+  const float4 x = *reinterpret_cast<const float4*>(src), y = *reinterpret_cast<const float4*>(src + 4);
+  uint4 w;
+  w.x = pack_bf16(x.x, x.y); w.y = pack_bf16(x.z, x.w);
+  w.z = pack_bf16(y.x, y.y); w.w = pack_bf16(y.z, y.w);
+  *reinterpret_cast<uint4*>(out + row * ld + c) = w;
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
+                BwdArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  uint8_t* sK = smem;
+  uint8_t* sV = sK + kTile;
+  uint8_t* sQ = sV + kTile;          // [2]
+  uint8_t* sdO = sQ + 2 * kTile;     // [2]
+  uint8_t* sP = sdO + 2 * kTile;     // [2 key blocks][128 q][128 B]
+  uint8_t* sdS = sP + kPBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sdS + kPBytes);
+  uint64_t* kv_full = bars;
+  uint64_t* q_full = bars + 1;       // [2]
+  uint64_t* q_empty = q_full + 2;    // [2]
+  uint64_t* sdp_full = q_empty + 2;  // S_i, dP_i complete in TMEM
+  uint64_t* sdp_free = sdp_full + 1; // ... and copied to registers by the 256 softmax threads
+  uint64_t* pds_full = sdp_free + 1; // P_i, dS_i in shared memory
+  uint64_t* pds_free = pds_full + 1; // dV / dK / dQ MMAs of pair i have read them
+  uint64_t* dq_full = pds_free + 1;  // dQ_i complete in TMEM
+  uint64_t* dq_free = dq_full + 1;   // ... and drained by the 128 dQ threads
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(dq_free + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int kv0 = blockIdx.x * BKV, head = blockIdx.y, b = blockIdx.z;
+  const int bk = b / a.kv_group;
+  const int nq = (a.Sq + BQ - 1) / BQ;
+
+  if (threadIdx.x == 0) {
+    mbar_init(kv_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&q_full[i], 1);
+      mbar_init(&q_empty[i], 1);
+    }
+    mbar_init(sdp_full, 1);
+    mbar_init(sdp_free, 32 * kSoftmaxWarps);
+    mbar_init(pds_full, 32 * kSoftmaxWarps);
+    mbar_init(pds_free, 1);
+    mbar_init(dq_full, 1);
+    mbar_init(dq_free, 128);
+    fence_mbar_init();
+  }
+  if (warp == kMmaWarp) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tS = tmem_base, tdP = tmem_base + 128, tdV = tmem_base + 256,
+                 tdK = tmem_base + 320, tdQ = tmem_base + 384;
+
+  if (warp == kTmaWarp) {
+    // ================= TMA producer =================
+    if (lane == 0) {
+      tma_prefetch_desc(&tmQ);
+      tma_prefetch_desc(&tmK);
+      tma_prefetch_desc(&tmV);
+      tma_prefetch_desc(&tmdO);
+      mbar_arrive_expect_tx(kv_full, 2 * kTile);
+      tma_load_3d(sK, &tmK, kv_full, head * HD, kv0, bk);
+      tma_load_3d(sV, &tmV, kv_full, head * HD, kv0, bk);
+      for (int i = 0; i < nq; ++i) {
+        const int st = i & 1;
+        mbar_wait(&q_empty[st], ((i >> 1) & 1) ^ 1, 10);
+        mbar_arrive_expect_tx(&q_full[st], 2 * kTile);
+        tma_load_3d(sQ + st * kTile, &tmQ, &q_full[st], head * HD, i * BQ, b);
+        tma_load_3d(sdO + st * kTile, &tmdO, &q_full[st], head * HD, i * BQ, b);
+      }
+    }
+  } else if (warp == kMmaWarp) {
+    // ================= MMA issuer (warp-uniform loop, elected lane issues) =================
+    const bool issuer = elect_one();
+    constexpr uint32_t idesc_s = umma_idesc_bf16(BQ, BKV, 0, 0);    // S, dP: both K-major
+    constexpr uint32_t idesc_t = umma_idesc_bf16(BKV, HD, 1, 1);    // dV, dK: both MN-major
+    constexpr uint32_t idesc_q = umma_idesc_bf16(BQ, HD, 0, 1);     // dQ: A K-major, B MN-major
+    constexpr uint64_t kRow16 = 2048 >> 4;                          // 16 rows of 128 B (MN-major k-step)
+    const uint64_t dK_k = umma_desc_sw128(smem_u32(sK), 1024);          // K as K-major B (S)
+    const uint64_t dK_mn = umma_desc_sw128(smem_u32(sK), 1024, 8192);   // K as MN-major B (dQ)
+    const uint64_t dV_k = umma_desc_sw128(smem_u32(sV), 1024);
+    const uint64_t dP_mn = umma_desc_sw128(smem_u32(sP), 1024, 16384);  // P^T: MN blocks 16 KB apart
+    const uint64_t dS_mn = umma_desc_sw128(smem_u32(sdS), 1024, 16384);
+    mbar_wait(kv_full, 0, 20);
+    auto issue_sdp = [&](int i) {
+      const int st = i & 1;
+      mbar_wait(&q_full[st], (i >> 1) & 1, 21);
+      tc_fence_after();
+      const uint64_t dQ_k = umma_desc_sw128(smem_u32(sQ + st * kTile), 1024);
+      const uint64_t ddO_k = umma_desc_sw128(smem_u32(sdO + st * kTile), 1024);
+      if (issuer) {
+#pragma unroll
+        for (int k = 0; k < HD / 16; ++k) umma_bf16_ss(tS, dQ_k + 2 * k, dK_k + 2 * k, idesc_s, k != 0);
+#pragma unroll
+        for (int k = 0; k < HD / 16; ++k) umma_bf16_ss(tdP, ddO_k + 2 * k, dV_k + 2 * k, idesc_s, k != 0);
+        umma_commit(sdp_full);
+      }
+      __syncwarp();
+    };
+    issue_sdp(0);
+    for (int i = 0; i < nq; ++i) {
+      const int st = i & 1;
+      if (i + 1 < nq) {
+        mbar_wait(sdp_free, i & 1, 22);
+        issue_sdp(i + 1);
+      }
+      mbar_wait(pds_full, i & 1, 23);
+      if (i > 0) mbar_wait(dq_free, (i - 1) & 1, 24);
+      tc_fence_after();
+      const uint64_t ddO_mn = umma_desc_sw128(smem_u32(sdO + st * kTile), 1024, 8192);
+      const uint64_t dQ_mn = umma_desc_sw128(smem_u32(sQ + st * kTile), 1024, 8192);
+      if (issuer) {
+#pragma unroll
+        for (int k = 0; k < BQ / 16; ++k)     // dV += P^T dO : contraction over the 128 query rows
+          umma_bf16_ss(tdV, dP_mn + kRow16 * k, ddO_mn + kRow16 * k, idesc_t, (i | k) != 0);
+#pragma unroll
+        for (int k = 0; k < BQ / 16; ++k)     // dK += dS^T Q
+          umma_bf16_ss(tdK, dS_mn + kRow16 * k, dQ_mn + kRow16 * k, idesc_t, (i | k) != 0);
+#pragma unroll
+        for (int k = 0; k < BKV / 16; ++k) {  // dQ = dS K : contraction over the 128 keys
+          const uint64_t dS_k = umma_desc_sw128(smem_u32(sdS + (k >> 2) * 16384), 1024);
+          umma_bf16_ss(tdQ, dS_k + 2 * (k & 3), dK_mn + kRow16 * k, idesc_q, k != 0);
+        }
+        umma_commit(&q_empty[st]);
+        umma_commit(pds_free);
+        umma_commit(dq_full);
+      }
+      __syncwarp();
+    }
+  } else if (warp < kSoftmaxWarps) {
+    // ================= softmax warps: P and dS of this warp's 32 rows x 64 keys =================
+    const int quarter = warp & 3, half = warp >> 2;
+    const int row = quarter * 32 + lane;
+    const uint32_t lane_off = uint32_t(quarter * 32) << 16;
+    const int64_t vec_base = ((int64_t)b * a.heads + head) * a.Sq;
+    uint8_t* prow = sP + half * 16384 + row * 128;
+    uint8_t* dsrow = sdS + half * 16384 + row * 128;
+    const int rx = row & 7;
+    for (int i = 0; i < nq; ++i) {
+      const int q = i * BQ + row;
+      const bool valid = q < a.Sq;
+      // rows past Sq: LSE = +inf makes P = 0 (their Q / dO rows are zero-filled by TMA)
+      const float lse2 = valid ? a.lse[vec_base + q] * 1.4426950408889634f : INFINITY;
+      const float dv = valid ? a.dvec[vec_base + q] : 0.f;
+      uint32_t pw[32], dsw[32];
+      mbar_wait(sdp_full, i & 1, 30);
+      tc_fence_after();
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t s[32], dp[32];
+        tmem_ld32(tS + lane_off + half * 64 + c * 32, s);
+        tmem_ld32(tdP + lane_off + half * 64 + c * 32, dp);
+        tmem_ld_wait();
+        if (c == 1) {
+          tc_fence_before();
+          mbar_arrive(sdp_free);       // S / dP may be overwritten by the next pair
+        }
+        const int key0 = kv0 + half * 64 + c * 32;
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          float p0 = ex2f(fmaf(__uint_as_float(s[2 * e]), a.scale_log2, -lse2));
+          float p1 = ex2f(fmaf(__uint_as_float(s[2 * e + 1]), a.scale_log2, -lse2));
+          if (key0 + 2 * e >= a.Sk) p0 = 0.f;
+          if (key0 + 2 * e + 1 >= a.Sk) p1 = 0.f;
+          const float d0 = p0 * (__uint_as_float(dp[2 * e]) - dv) * a.scale;
+          const float d1 = p1 * (__uint_as_float(dp[2 * e + 1]) - dv) * a.scale;
+          pw[c * 16 + e] = pack_bf16(p0, p1);
+          dsw[c * 16 + e] = pack_bf16(d0, d1);
+        }
+      }
+      if (i > 0) mbar_wait(pds_free, (i - 1) & 1, 31);   // previous pair's MMAs are done with sP / sdS
+#pragma unroll
+      for (int cc = 0; cc < 8; ++cc) {
+        const int off = (cc ^ rx) * 16;
+        *reinterpret_cast<uint4*>(prow + off) = make_uint4(pw[4 * cc], pw[4 * cc + 1], pw[4 * cc + 2], pw[4 * cc + 3]);
+        *reinterpret_cast<uint4*>(dsrow + off) = make_uint4(dsw[4 * cc], dsw[4 * cc + 1], dsw[4 * cc + 2], dsw[4 * cc + 3]);
+      }
+      fence_proxy_async_smem();
+      mbar_arrive(pds_full);
+    }
+    // ---- dV (half 0) / dK (half 1): TMEM lane = key row ----
+    mbar_wait(pds_free, (nq - 1) & 1, 32);
+    tc_fence_after();
+    const int key = kv0 + row;
+    const uint32_t tsrc = (half == 0 ? tdV : tdK) + lane_off;
+    void* dst_base = half == 0 ? a.dv : a.dk;
+    const int64_t ld = half == 0 ? a.ldv : a.ldk;
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      uint32_t o[32];
+      tmem_ld32(tsrc + c * 32, o);
+      tmem_ld_wait();
+      if (key < a.Sk) {
+        if (a.kv_group == 1) {
+          __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(dst_base) +
+                               ((int64_t)bk * a.Sk + key) * ld + head * HD + c * 32;
+#pragma unroll
+          for (int v = 0; v < 4; ++v) {
+            uint4 w;
+            w.x = pack_bf16(__uint_as_float(o[8 * v]), __uint_as_float(o[8 * v + 1]));
+            w.y = pack_bf16(__uint_as_float(o[8 * v + 2]), __uint_as_float(o[8 * v + 3]));
+            w.z = pack_bf16(__uint_as_float(o[8 * v + 4]), __uint_as_float(o[8 * v + 5]));
+            w.w = pack_bf16(__uint_as_float(o[8 * v + 6]), __uint_as_float(o[8 * v + 7]));
+            *reinterpret_cast<uint4*>(dst + 8 * v) = w;
+          }
+        } else {
+          // text K / V are shared by kv_group frames: sum their gradients in fp32
+          float* dst = reinterpret_cast<float*>(dst_base) +
+                       ((int64_t)bk * a.Sk + key) * (a.heads * HD) + head * HD + c * 32;
+#pragma unroll
+          for (int v = 0; v < 8; ++v)
+            atomicAdd(reinterpret_cast<float4*>(dst + 4 * v),
+                      make_float4(__uint_as_float(o[4 * v]), __uint_as_float(o[4 * v + 1]),
+                                  __uint_as_float(o[4 * v + 2]), __uint_as_float(o[4 * v + 3])));
+        }
+      }
+    }
+  } else {
+    // ================= dQ drain (warps 10..13): add each pair's dQ tile to the fp32 accumulator ===
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    const uint32_t lane_off = uint32_t(quarter * 32) << 16;
+    for (int i = 0; i < nq; ++i) {
+      mbar_wait(dq_full, i & 1, 40);
+      tc_fence_after();
+      uint32_t o[64];
+      tmem_ld32(tdQ + lane_off, o);
+      tmem_ld32(tdQ + lane_off + 32, o + 32);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(dq_free);
+      const int q = i * BQ + row;
+      if (q < a.Sq) {
+        float* dst = a.dq_acc + (((int64_t)b * a.heads + head) * a.Sq + q) * HD;
+#pragma unroll
+        for (int v = 0; v < 16; ++v)
+          atomicAdd(reinterpret_cast<float4*>(dst + 4 * v),
+                    make_float4(__uint_as_float(o[4 * v]), __uint_as_float(o[4 * v + 1]),
+                                __uint_as_float(o[4 * v + 2]), __uint_as_float(o[4 * v + 3])));
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kMmaWarp) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+int make_map3(CUtensorMap* m, const void* p, int64_t B, int64_t S, int width, int64_t ld) {
+  const uint64_t dims[3] = {(uint64_t)width, (uint64_t)S, (uint64_t)B};
+  const uint64_t strides[3] = {2, (uint64_t)ld * 2, (uint64_t)S * ld * 2};
+  const uint32_t box[3] = {HD, 128, 1};
+  return vst_make_tmap(m, p, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+int64_t align256(int64_t x) { return (x + 255) / 256 * 256; }
+
+}  // namespace
+
+extern "C" int64_t vst_attn_bwd_workspace_bytes(int Bt, int heads, int Sq, int Sk, int kv_group) {
+  if (Bt <= 0 || heads <= 0 || Sq <= 0 || Sk <= 0 || kv_group <= 0) return 0;
+  int64_t n = align256((int64_t)Bt * heads * Sq * 4);             // D
+  n += align256((int64_t)Bt * heads * Sq * HD * 4);               // dQ accumulator
+  if (kv_group > 1) n += 2 * align256((int64_t)(Bt / kv_group) * Sk * heads * HD * 4);   // dK, dV accumulators
+  return n;
+}
+
+extern "C" int vst_attn_bwd(const void* q, const void* k, const void* v, const void* o,
+                            const void* d_o, const float* lse, void* dq, void* dk, void* dv, int Bt,
+                            int heads, int Sq, int Sk, int d, int64_t ldq, int64_t ldk, int64_t ldv,
+                            int64_t ldo, int64_t lddo, int64_t lddq, int64_t lddk, int64_t lddv,
+                            int kv_group, float scale, void* workspace, int64_t workspace_bytes,
+                            void* stream) {
+  VST_REQUIRE(Bt >= 0 && heads > 0 && Sq >= 0 && Sk > 0, VST_E_BADARG, "attn_bwd: bad shape");
+  if (Bt == 0 || Sq == 0) return VST_OK;
+  VST_REQUIRE(q && k && v && o && d_o && lse && dq && dk && dv, VST_E_BADARG, "attn_bwd: null pointer");
+  VST_REQUIRE(d == HD, VST_E_UNSUPPORTED, "attn_bwd: head dim %d unsupported (SDXL spatial d=64)", d);
+  VST_REQUIRE(kv_group >= 1 && Bt % kv_group == 0, VST_E_BADARG, "attn_bwd: Bt %% kv_group != 0");
+  VST_REQUIRE(ldq % 8 == 0 && ldk % 8 == 0 && ldv % 8 == 0 && ldo % 8 == 0 && lddo % 8 == 0 &&
+                  lddq % 8 == 0 && lddk % 8 == 0 && lddv % 8 == 0,
+              VST_E_UNSUPPORTED, "attn_bwd: row strides must be multiples of 8 elements");
+  VST_REQUIRE(heads <= 65535 && Bt <= 65535, VST_E_UNSUPPORTED, "attn_bwd: grid too large");
+  const int64_t need = vst_attn_bwd_workspace_bytes(Bt, heads, Sq, Sk, kv_group);
+  VST_REQUIRE(workspace && workspace_bytes >= need && (reinterpret_cast<uintptr_t>(workspace) & 255) == 0,
+              VST_E_BADARG, "attn_bwd: a 256-byte aligned workspace of %lld bytes is required", (long long)need);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int C = heads * HD, Bk = Bt / kv_group;
+  uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
+  float* dvec = reinterpret_cast<float*>(ws);
+  ws += align256((int64_t)Bt * heads * Sq * 4);
+  float* dq_acc = reinterpret_cast<float*>(ws);
+  const int64_t dq_bytes = (int64_t)Bt * heads * Sq * HD * 4;
+  ws += align256(dq_bytes);
+  float *dk_acc = nullptr, *dv_acc = nullptr;
+  const int64_t kv_bytes = (int64_t)Bk * Sk * C * 4;
+  if (kv_group > 1) {
+    dk_acc = reinterpret_cast<float*>(ws);
+    ws += align256(kv_bytes);
+    dv_acc = reinterpret_cast<float*>(ws);
+    VST_CUDA_OK(cudaMemsetAsync(dk_acc, 0, kv_bytes, st));
+    VST_CUDA_OK(cudaMemsetAsync(dv_acc, 0, kv_bytes, st));
+  }
+  VST_CUDA_OK(cudaMemsetAsync(dq_acc, 0, dq_bytes, st));
+
+  const int64_t rows = (int64_t)Bt * Sq;
+  {
+    const int64_t threads = rows * heads * 8;
+    attn_bwd_dot_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(
+        (const __nv_bfloat16*)o, (const __nv_bfloat16*)d_o, dvec, rows, Sq, heads, ldo, lddo);
+    VST_LAUNCH_OK();
+  }
+  CUtensorMap tQ, tK, tV, tdO;
+  int rc;
+  if ((rc = make_map3(&tQ, q, Bt, Sq, C, ldq))) return rc;
+  if ((rc = make_map3(&tK, k, Bk, Sk, C, ldk))) return rc;
+  if ((rc = make_map3(&tV, v, Bk, Sk, C, ldv))) return rc;
+  if ((rc = make_map3(&tdO, d_o, Bt, Sq, C, lddo))) return rc;
+  static bool configured = false;
+  if (!configured) {
+    VST_CUDA_OK(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    configured = true;
+  }
+  BwdArgs a;
+  a.lse = lse;
+  a.dvec = dvec;
+  a.dq_acc = dq_acc;
+  a.dk = kv_group > 1 ? (void*)dk_acc : dk;
+  a.dv = kv_group > 1 ? (void*)dv_acc : dv;
+  a.ldk = lddk;
+  a.ldv = lddv;
+  a.Sq = Sq;
+  a.Sk = Sk;
+  a.heads = heads;
+  a.kv_group = kv_group;
+  a.scale = scale;
+  a.scale_log2 = scale * 1.4426950408889634f;
+  dim3 grid((Sk + BKV - 1) / BKV, heads, Bt);
+  attn_bwd_kernel<<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tdO, a);
+  VST_LAUNCH_OK();
+  {
+    const int64_t threads = rows * heads * 8;
+    attn_bwd_dq_convert_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(
+        dq_acc, (__nv_bfloat16*)dq, rows, Sq, heads, lddq);
+    VST_LAUNCH_OK();
+  }
+  if (kv_group > 1) {
+    const int64_t krows = (int64_t)Bk * Sk;
+    const int64_t threads = krows * (C / 8);
+    attn_bwd_rows_convert_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(
+        dk_acc, (__nv_bfloat16*)dk, krows, C, lddk);
+    VST_LAUNCH_OK();
+    attn_bwd_rows_convert_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(
+        dv_acc, (__nv_bfloat16*)dv, krows, C, lddv);
+    VST_LAUNCH_OK();
+  }
+  return VST_OK;
+}

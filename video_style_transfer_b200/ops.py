@@ -299,7 +299,17 @@ def colsum(x: torch.Tensor, alpha: float = 1.0) -> torch.Tensor:
 # ---- a2 -------------------------------------------------------------------------------------------
 def attn_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int,
              scale: Optional[float] = None, return_lse: bool = False):
-    """q (Bt,Sq,h*64), k/v (Bk,Sk,h*64) bf16, Bt % Bk == 0 (batch b reads kv batch b//(Bt/Bk))."""
+    """q (Bt,Sq,h*64), k/v (Bk,Sk,h*64) bf16, Bt % Bk == 0 (batch b reads kv batch b//(Bt/Bk)).
+    Differentiable: the backward is vst_attn_bwd (see _autograd.AttnFn)."""
+    if _needs_grad(q, k, v) and not return_lse:
+        from ._autograd import AttnFn
+        return AttnFn.apply(q, k, v, heads, scale)
+    return attn_fwd_raw(q, k, v, heads, scale, return_lse)
+
+
+def attn_fwd_raw(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int,
+                 scale: Optional[float] = None, return_lse: bool = False):
+    q, k, v = q.detach(), k.detach(), v.detach()
     _cuda(q, k, v)
     bt, sq, c = q.shape
     bk, sk, _ = k.shape
@@ -315,6 +325,35 @@ def attn_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int,
                            bt // bk, scale if scale is not None else 1.0 / math.sqrt(d), _stream()),
           "vst_attn_fwd")
     return (o, lse) if return_lse else o
+
+
+def _bsc(t: torch.Tensor, name: str):
+    if t.dtype != torch.bfloat16 or t.stride(2) != 1 or t.stride(0) != t.shape[1] * t.stride(1):
+        raise ValueError(f"attn_bwd: {name} must be bf16 (B,S,C) with contiguous C and dense (B,S)")
+
+
+def attn_bwd(q, k, v, o, d_o, lse, heads: int, scale: Optional[float] = None):
+    """(dq, dk, dv) of attn_fwd; dk / dv have the (Bk, Sk, C) shape of k / v."""
+    _cuda(q, k, v, o, d_o, lse)
+    bt, sq, c = q.shape
+    bk, sk, _ = k.shape
+    d = c // heads
+    for t, nm in ((q, "q"), (k, "k"), (v, "v"), (o, "o"), (d_o, "d_o")):
+        _bsc(t, nm)
+    assert lse.dtype == torch.float32 and lse.is_contiguous() and lse.shape == (bt, heads, sq)
+    dq = torch.empty((bt, sq, c), dtype=torch.bfloat16, device=q.device)
+    dk = torch.empty((bk, sk, c), dtype=torch.bfloat16, device=q.device)
+    dv = torch.empty((bk, sk, c), dtype=torch.bfloat16, device=q.device)
+    wsb = lib.vst_attn_bwd_workspace_bytes(bt, heads, sq, sk, bt // bk)
+    ws = torch.empty(wsb + 256, dtype=torch.uint8, device=q.device)
+    off = (-ws.data_ptr()) % 256
+    check(lib.vst_attn_bwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), d_o.data_ptr(),
+                           lse.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), bt, heads,
+                           sq, sk, d, q.stride(1), k.stride(1), v.stride(1), o.stride(1),
+                           d_o.stride(1), dq.stride(1), dk.stride(1), dv.stride(1), bt // bk,
+                           scale if scale is not None else 1.0 / math.sqrt(d),
+                           ws.data_ptr() + off, wsb, _stream()), "vst_attn_bwd")
+    return dq, dk, dv
 
 
 # ---- §8f-1 ----------------------------------------------------------------------------------------
