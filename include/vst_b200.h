@@ -157,6 +157,35 @@ int vst_attn_fwd(const void* q, const void* k, const void* v, void* o, float* ls
                  int heads, int Sq, int Sk, int d, int64_t ldq, int64_t ldk, int64_t ldv,
                  int64_t ldo, int kv_group, float scale, void* stream);
 
+/* ---- a8 backward: gradients of vst_temporal_attn_fwd (probabilities recomputed; no saved state) --
+ * q,k,v,d_o: (N,F,heads*d) bf16, 16-byte aligned rows; dq,dk,dv: same shape, bf16. */
+int vst_temporal_attn_bwd(const void* q, const void* k, const void* v, const void* d_o, void* dq,
+                          void* dk, void* dv, int64_t N, int F, int heads, int d, int64_t ldq,
+                          int64_t ldk, int64_t ldv, int64_t lddo, int64_t lddq, int64_t lddk,
+                          int64_t lddv, float scale, void* stream);
+
+/* ---- K9 / §8f-1 / a10 backward (config 4: the motion module trains its norms and projections,
+ * animatediff/utils.py:66-96) ------------------------------------------------------------------
+ * layernorm_bwd: x, dy, dx bf16 contiguous (rows, C), C <= 1280; dgamma / dbeta fp32 (C), may be
+ *   NULL; statistics are recomputed from x.  Workspace: vst_layernorm_bwd_workspace_bytes.
+ * geglu_bwd: dhg[:, :inner] = dout * gelu(b), dhg[:, inner:] = dout * a * gelu'(b).
+ * groupnorm5d_bwd: x, dy, dx (and the optional `add`, summed into dx: the motion module's residual
+ *   branch) are frames-major contiguous (B*F, C, HW) bf16; mean / rstd from vst_groupnorm5d_finalize. */
+int64_t vst_layernorm_bwd_workspace_bytes(int64_t rows, int C);
+int vst_layernorm_bwd(const void* x, const void* dy, const void* gamma, void* dx, float* dgamma,
+                      float* dbeta, int64_t rows, int C, float eps, int param_dtype,
+                      void* workspace, int64_t workspace_bytes, void* stream);
+int vst_geglu_bwd(const void* hg, const void* dout, void* dhg, int64_t rows, int inner,
+                  int64_t ld_in, int64_t ld_do, int64_t ld_out, void* stream);
+/* dz = alpha * dy * gelu'(z): the VST_ACT_GELU epilogue of vst_lora_gemm, differentiated. */
+int vst_gelu_bwd(const void* z, const void* dy, void* dz, int64_t rows, int N, int64_t ld_z,
+                 int64_t ld_dy, int64_t ld_dz, float alpha, void* stream);
+int64_t vst_groupnorm5d_bwd_workspace_bytes(int B, int C, int F, int groups);
+int vst_groupnorm5d_bwd(const void* x, const void* dy, const void* add, void* dx, const float* mean,
+                        const float* rstd, const void* gamma, float* dgamma, float* dbeta, int B,
+                        int C, int F, int HW, int groups, int param_dtype, void* workspace,
+                        int64_t workspace_bytes, void* stream);
+
 /* ---- a2 backward ------------------------------------------------------------------------------
  * Gradients of vst_attn_fwd (autograd through F.scaled_dot_product_attention,
  * animatediff/attention_processor.py:78-80).  o / lse are the forward's outputs, d_o the incoming

@@ -24,23 +24,30 @@ class LoraGemmFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, a1, b1, a2, b2, bias, residual, out_scale, act, k2_group_n, out_dtype):
-        if act != "none":
-            raise NotImplementedError("lora_gemm: only act='none' is differentiable (the GELU feed-forward "
-                                      "of temporal_transformer.py is inference-only on this path)")
         y = ops.lora_gemm_raw(a1, b1, a2, b2, bias, residual, out_scale, act, k2_group_n, None, out_dtype)
-        ctx.save_for_backward(a1, b1, a2, b2)
+        z = None
+        if act == "gelu":
+            # the pre-activation, kept for gelu'(z): one more GEMM, in training mode only
+            z = ops.lora_gemm_raw(a1, b1, a2, b2, bias, None, 1.0, "none", k2_group_n, None, torch.bfloat16)
+        ctx.save_for_backward(a1, b1, a2, b2, z)
         ctx.cfg = (out_scale, k2_group_n, None if bias is None else bias.dtype,
                    None if residual is None else residual.dtype)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        a1, b1, a2, b2 = ctx.saved_tensors
+        a1, b1, a2, b2, z = ctx.saved_tensors
         out_scale, gn, bias_dtype, res_dtype = ctx.cfg
         need = ctx.needs_input_grad
         g = _rows_bf16(dy)
         m, n = g.shape
         da1 = db1 = da2 = db2 = dbias = dres = None
+        if need[5]:
+            dres = g if out_scale == 1.0 else g * out_scale
+            dres = dres.to(res_dtype).reshape(dy.shape)
+        if z is not None:            # y = (gelu(z) + residual) * out_scale
+            g = ops.gelu_bwd(z, g, out_scale)
+            out_scale = 1.0
         if need[0]:     # dx = dy W                      (W stored [N, K1]: trans_b)
             da1 = ops.gemm(g, b1, trans_b=True, alpha=out_scale)
         if need[1]:     # dW = dy^T x                    (contraction over the rows of both)
@@ -66,9 +73,6 @@ class LoraGemmFn(torch.autograd.Function):
                                  trans_b=True, alpha=out_scale, out=db2[i * gn:(i + 1) * gn])
         if need[4]:
             dbias = ops.colsum(g, out_scale).to(bias_dtype)
-        if need[5]:
-            dres = g if out_scale == 1.0 else g * out_scale
-            dres = dres.to(res_dtype).reshape(dy.shape)
         return da1, db1, da2, db2, dbias, dres, None, None, None, None
 
 
@@ -136,3 +140,128 @@ class AttnFn(torch.autograd.Function):
             g = g.to(torch.bfloat16).contiguous()
         dq, dk, dv = ops.attn_bwd(q.detach(), k.detach(), v.detach(), o, g, lse, heads, scale)
         return dq, dk, dv, None, None
+
+
+def _dense_bf16(t: torch.Tensor) -> torch.Tensor:
+    t = t.detach()
+    return t if (t.dtype == torch.bfloat16 and t.is_contiguous()) else t.to(torch.bfloat16).contiguous()
+
+
+class TemporalAttnFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, q, k, v, heads, scale):
+        ctx.save_for_backward(q, k, v)
+        ctx.cfg = (heads, scale)
+        return ops.temporal_attn_raw(q, k, v, heads, scale)
+
+    @staticmethod
+    def backward(ctx, d_o):
+        q, k, v = ctx.saved_tensors
+        heads, scale = ctx.cfg
+        dq, dk, dv = ops.temporal_attn_bwd(q.detach(), k.detach(), v.detach(), _dense_bf16(d_o), heads, scale)
+        return dq, dk, dv, None, None
+
+
+class LayerNormFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, eps, pe, frames, out_dtype):
+        y = ops.layernorm_raw(x, gamma, beta, eps, pe, frames, out_dtype)
+        ctx.save_for_backward(x, gamma)
+        ctx.cfg = (eps, None if gamma is None else gamma.dtype, None if beta is None else beta.dtype)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, gamma = ctx.saved_tensors
+        eps, gdt, bdt = ctx.cfg
+        c = x.shape[-1]
+        x2 = _dense_bf16(x).reshape(-1, c)
+        dy2 = _dense_bf16(dy).reshape(-1, c)
+        want = ctx.needs_input_grad[1] or ctx.needs_input_grad[2]
+        dx, dg, db = ops.layernorm_bwd(x2, dy2, None if gamma is None else gamma.detach(), eps, want)
+        dx = dx.reshape(x.shape).to(x.dtype) if ctx.needs_input_grad[0] else None
+        dg = dg.to(gdt) if (ctx.needs_input_grad[1] and dg is not None) else None
+        db = db.to(bdt) if (ctx.needs_input_grad[2] and db is not None) else None
+        return dx, dg, db, None, None, None, None
+
+
+class GegluFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, hg):
+        ctx.save_for_backward(hg)
+        return ops.geglu_raw(hg)
+
+    @staticmethod
+    def backward(ctx, d_out):
+        (hg,) = ctx.saved_tensors
+        return ops.geglu_bwd(hg.detach(), _dense_bf16(d_out))
+
+
+def _frames_major_storage(x5: torch.Tensor) -> torch.Tensor:
+    """(B,C,F,H,W) view of a contiguous (B,F,C,H,W) tensor -> that (B*F, C, H, W) tensor."""
+    b, c, f, h, w = x5.shape
+    xf = x5.permute(0, 2, 1, 3, 4)
+    if not xf.is_contiguous():
+        raise ValueError("the motion-module input must be the (B,C,F,H,W) view of a contiguous "
+                         "(B*F,C,H,W) tensor for the backward pass")
+    return xf.reshape(b * f, c, h, w)
+
+
+class GroupNormRearrangeFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x5, gamma, beta, groups, eps):
+        tok, mean, rstd = ops.groupnorm5d_rearrange_raw(x5, gamma, beta, groups, eps)
+        ctx.save_for_backward(x5, gamma, mean, rstd)
+        ctx.cfg = (groups, beta.dtype)
+        ctx.mark_non_differentiable(mean, rstd)
+        return tok, mean, rstd
+
+    @staticmethod
+    def backward(ctx, d_tok, _dm, _dr):
+        x5, gamma, mean, rstd = ctx.saved_tensors
+        groups, bdt = ctx.cfg
+        b, c, f, h, w = x5.shape
+        x_fm = _frames_major_storage(x5.detach())
+        # tokens -> frames-major, then a plain GroupNorm backward in x's own layout
+        dy5 = ops.rearrange_bwd_raw(_dense_bf16(d_tok).view(b * h * w, f, c), b, h, w, None, True)
+        dy_fm = dy5.permute(0, 2, 1, 3, 4).reshape(b * f, c, h, w)
+        dx, dg, db = ops.groupnorm5d_bwd(x_fm, dy_fm, mean, rstd, gamma.detach(), b, f, groups)
+        dx5 = dx.view(b, f, c, h, w).permute(0, 2, 1, 3, 4)
+        return dx5, dg.to(gamma.dtype), db.to(bdt), None, None
+
+
+class RearrangeBwdFn(torch.autograd.Function):
+    """tokens (B*H*W, F, C) -> (B,C,F,H,W) (+ residual); the adjoint is the forward rearrange."""
+
+    @staticmethod
+    def forward(ctx, y, residual5, b, h, w, frames_major):
+        ctx.has_res = residual5 is not None
+        return ops.rearrange_bwd_raw(y, b, h, w, residual5, frames_major)
+
+    @staticmethod
+    def backward(ctx, d_out5):
+        g = d_out5.detach()
+        if g.dtype not in (torch.bfloat16, torch.float32):
+            g = g.to(torch.bfloat16)
+        hh, ww = g.shape[3], g.shape[4]
+        if hh * ww > 1 and not (g.stride(4) == 1 and (hh == 1 or g.stride(3) == ww)):
+            g = g.contiguous()
+        dy = ops.rearrange_fwd(g) if ctx.needs_input_grad[0] else None
+        dres = d_out5 if (ctx.has_res and ctx.needs_input_grad[1]) else None
+        return dy, dres, None, None, None, None
+
+
+class RearrangeFwdFn(torch.autograd.Function):
+    """(B,C,F,H,W) -> tokens (B*H*W, F, C) (+ pe, no gradient); the adjoint is rearrange_bwd."""
+
+    @staticmethod
+    def forward(ctx, x5, pe):
+        ctx.geom = (x5.shape, x5.dtype)
+        with torch.no_grad():
+            return ops.rearrange_fwd(x5.detach(), pe)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (b, c, f, h, w), dtype = ctx.geom
+        g = dy.detach().contiguous()
+        return ops.rearrange_bwd_raw(g.view(b * h * w, f, c), b, h, w).to(dtype), None

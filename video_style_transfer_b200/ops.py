@@ -42,7 +42,12 @@ def _planar_strides(x5: torch.Tensor) -> Tuple[int, int, int]:
 
 # ---- a9 -------------------------------------------------------------------------------------------
 def rearrange_fwd(x5: torch.Tensor, pe: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """(B,C,F,H,W) view -> (B*H*W, F, C) [+ pe[:F]]; temporal_transformer.py:129-133."""
+    """(B,C,F,H,W) view -> (B*H*W, F, C) [+ pe[:F]]; temporal_transformer.py:129-133.
+    Differentiable w.r.t. x5 (adjoint: rearrange_bwd)."""
+    if _needs_grad(x5):
+        from ._autograd import RearrangeFwdFn
+        return RearrangeFwdFn.apply(x5, pe)
+    x5 = x5.detach()
     _cuda(x5, pe)
     b, c, f, h, w = x5.shape
     sB, sC, sF = _planar_strides(x5)
@@ -60,7 +65,17 @@ def rearrange_bwd(y: torch.Tensor, b: int, h: int, w: int, residual5: Optional[t
                   frames_major: bool = False) -> torch.Tensor:
     """(B*H*W, F, C) -> (B,C,F,H,W) contiguous (temporal_transformer.py:143-144), or, with
     frames_major, the (B,C,F,H,W) view of a fresh (B*F,C,H,W) tensor.  residual5 (same view
-    geometry as the output) is added in the store."""
+    geometry as the output) is added in the store.  Differentiable (adjoint: rearrange_fwd)."""
+    if _needs_grad(y, residual5):
+        from ._autograd import RearrangeBwdFn
+        return RearrangeBwdFn.apply(y, residual5, b, h, w, frames_major)
+    return rearrange_bwd_raw(y, b, h, w, residual5, frames_major)
+
+
+def rearrange_bwd_raw(y: torch.Tensor, b: int, h: int, w: int, residual5: Optional[torch.Tensor] = None,
+                      frames_major: bool = False) -> torch.Tensor:
+    y = y.detach()
+    residual5 = None if residual5 is None else residual5.detach()
     _cuda(y, residual5)
     n, f, c = y.shape
     assert n == b * h * w and y.is_contiguous()
@@ -98,7 +113,17 @@ def groupnorm5d_stats(x5: torch.Tensor, groups: int = 32, eps: float = 1e-6):
 def groupnorm5d_rearrange(x5: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor,
                           groups: int = 32, eps: float = 1e-6):
     """GroupNorm over (C/groups, F, H, W) of the (B,C,F,H,W) view, written straight into the
-    (B*H*W, F, C) token layout.  Returns (tokens, mean, rstd)."""
+    (B*H*W, F, C) token layout.  Returns (tokens, mean, rstd).  Differentiable w.r.t. x5, gamma, beta."""
+    if _needs_grad(x5, gamma, beta):
+        from ._autograd import GroupNormRearrangeFn
+        tok, mean, rstd = GroupNormRearrangeFn.apply(x5, gamma, beta, groups, eps)
+        return tok, mean, rstd
+    return groupnorm5d_rearrange_raw(x5, gamma, beta, groups, eps)
+
+
+def groupnorm5d_rearrange_raw(x5: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor,
+                              groups: int = 32, eps: float = 1e-6):
+    x5, gamma, beta = x5.detach(), gamma.detach(), beta.detach()
     _cuda(x5, gamma, beta)
     b, c, f, h, w = x5.shape
     mean, rstd = groupnorm5d_stats(x5, groups, eps)
@@ -117,6 +142,19 @@ def groupnorm5d_rearrange(x5: torch.Tensor, gamma: torch.Tensor, beta: torch.Ten
 def layernorm(x: torch.Tensor, gamma: Optional[torch.Tensor], beta: Optional[torch.Tensor],
               eps: float = 1e-5, pe: Optional[torch.Tensor] = None, frames: int = 1,
               out_dtype: Optional[torch.dtype] = None) -> torch.Tensor:
+    """LayerNorm over the last dim (+ pe[row % frames]).  Differentiable w.r.t. x, gamma, beta."""
+    if _needs_grad(x, gamma, beta):
+        from ._autograd import LayerNormFn
+        return LayerNormFn.apply(x, gamma, beta, eps, pe, frames, out_dtype)
+    return layernorm_raw(x, gamma, beta, eps, pe, frames, out_dtype)
+
+
+def layernorm_raw(x: torch.Tensor, gamma: Optional[torch.Tensor], beta: Optional[torch.Tensor],
+                  eps: float = 1e-5, pe: Optional[torch.Tensor] = None, frames: int = 1,
+                  out_dtype: Optional[torch.dtype] = None) -> torch.Tensor:
+    x = x.detach()
+    gamma = None if gamma is None else gamma.detach()
+    beta = None if beta is None else beta.detach()
     _cuda(x, gamma, beta, pe)
     c = x.shape[-1]
     x2 = x.reshape(-1, c)
@@ -136,7 +174,33 @@ def layernorm(x: torch.Tensor, gamma: Optional[torch.Tensor], beta: Optional[tor
 # ---- a8 -------------------------------------------------------------------------------------------
 def temporal_attn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int,
                   scale: Optional[float] = None) -> torch.Tensor:
-    """q,k,v (N, F, heads*d) bf16 (last dim contiguous; row stride free) -> o (N, F, heads*d)."""
+    """q,k,v (N, F, heads*d) bf16 (last dim contiguous; row stride free) -> o (N, F, heads*d).
+    Differentiable: the backward is vst_temporal_attn_bwd."""
+    if _needs_grad(q, k, v):
+        from ._autograd import TemporalAttnFn
+        return TemporalAttnFn.apply(q, k, v, heads, scale)
+    return temporal_attn_raw(q, k, v, heads, scale)
+
+
+def temporal_attn_bwd(q, k, v, d_o, heads: int, scale: Optional[float] = None):
+    _cuda(q, k, v, d_o)
+    n, f, c = q.shape
+    d = c // heads
+    for t in (q, k, v, d_o):
+        if t.dtype != torch.bfloat16 or t.stride(2) != 1 or t.stride(0) != f * t.stride(1):
+            raise ValueError("temporal_attn_bwd: bf16 (N,F,C) tensors with contiguous C and dense (N,F)")
+    dq, dk, dv = (torch.empty((n, f, c), dtype=torch.bfloat16, device=q.device) for _ in range(3))
+    check(lib.vst_temporal_attn_bwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), d_o.data_ptr(),
+                                    dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), n, f, heads, d,
+                                    q.stride(1), k.stride(1), v.stride(1), d_o.stride(1), c, c, c,
+                                    scale if scale is not None else 1.0 / math.sqrt(d), _stream()),
+          "vst_temporal_attn_bwd")
+    return dq, dk, dv
+
+
+def temporal_attn_raw(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int,
+                      scale: Optional[float] = None) -> torch.Tensor:
+    q, k, v = q.detach(), k.detach(), v.detach()
     _cuda(q, k, v)
     n, f, c = q.shape
     d = c // heads
@@ -358,7 +422,73 @@ def attn_bwd(q, k, v, o, d_o, lse, heads: int, scale: Optional[float] = None):
 
 # ---- §8f-1 ----------------------------------------------------------------------------------------
 def geglu(hg: torch.Tensor) -> torch.Tensor:
-    """hg (rows, 2*inner) bf16 -> hg[:, :inner] * gelu(hg[:, inner:])."""
+    """hg (rows, 2*inner) bf16 -> hg[:, :inner] * gelu(hg[:, inner:]).  Differentiable."""
+    if _needs_grad(hg):
+        from ._autograd import GegluFn
+        return GegluFn.apply(hg)
+    return geglu_raw(hg)
+
+
+def geglu_bwd(hg: torch.Tensor, d_out: torch.Tensor) -> torch.Tensor:
+    _cuda(hg, d_out)
+    rows, two = hg.shape
+    inner = two // 2
+    assert d_out.shape == (rows, inner) and d_out.dtype == torch.bfloat16 and d_out.stride(1) == 1
+    dhg = torch.empty((rows, two), dtype=torch.bfloat16, device=hg.device)
+    check(lib.vst_geglu_bwd(hg.data_ptr(), d_out.data_ptr(), dhg.data_ptr(), rows, inner, hg.stride(0),
+                            d_out.stride(0), dhg.stride(0), _stream()), "vst_geglu_bwd")
+    return dhg
+
+
+def gelu_bwd(z: torch.Tensor, dy: torch.Tensor, alpha: float = 1.0) -> torch.Tensor:
+    """alpha * dy * gelu'(z) for bf16 (rows, N) matrices."""
+    _cuda(z, dy)
+    _mat(z, "z"), _mat(dy, "dy")
+    rows, n = z.shape
+    dz = torch.empty((rows, n), dtype=torch.bfloat16, device=z.device)
+    check(lib.vst_gelu_bwd(z.data_ptr(), dy.data_ptr(), dz.data_ptr(), rows, n, z.stride(0), dy.stride(0),
+                           dz.stride(0), alpha, _stream()), "vst_gelu_bwd")
+    return dz
+
+
+def layernorm_bwd(x2: torch.Tensor, dy2: torch.Tensor, gamma: Optional[torch.Tensor], eps: float,
+                  want_params: bool = True):
+    """x2, dy2: contiguous bf16 (rows, C) -> (dx bf16, dgamma fp32 | None, dbeta fp32 | None)."""
+    _cuda(x2, dy2, gamma)
+    rows, c = x2.shape
+    assert x2.dtype == dy2.dtype == torch.bfloat16 and x2.is_contiguous() and dy2.is_contiguous()
+    dx = torch.empty_like(x2)
+    dg = torch.empty(c, dtype=torch.float32, device=x2.device) if want_params else None
+    db = torch.empty(c, dtype=torch.float32, device=x2.device) if want_params else None
+    wsb = lib.vst_layernorm_bwd_workspace_bytes(rows, c)
+    ws = torch.empty(wsb, dtype=torch.uint8, device=x2.device)
+    check(lib.vst_layernorm_bwd(x2.data_ptr(), dy2.data_ptr(), _ptr(gamma), dx.data_ptr(), _ptr(dg),
+                                _ptr(db), rows, c, eps, _dt(gamma) if gamma is not None else VST_F32,
+                                ws.data_ptr(), wsb, _stream()), "vst_layernorm_bwd")
+    return dx, dg, db
+
+
+def groupnorm5d_bwd(x_fm: torch.Tensor, dy_fm: torch.Tensor, mean, rstd, gamma, b: int, f: int,
+                    groups: int, add: Optional[torch.Tensor] = None):
+    """x_fm, dy_fm (and add): frames-major contiguous (B*F, C, H, W) bf16 -> (dx, dgamma, dbeta)."""
+    _cuda(x_fm, dy_fm, mean, rstd, gamma, add)
+    bf, c, h, w = x_fm.shape
+    assert bf == b * f and x_fm.is_contiguous() and dy_fm.is_contiguous() and dy_fm.shape == x_fm.shape
+    assert x_fm.dtype == dy_fm.dtype == torch.bfloat16
+    dx = torch.empty_like(x_fm)
+    dg = torch.empty(c, dtype=torch.float32, device=x_fm.device)
+    db = torch.empty(c, dtype=torch.float32, device=x_fm.device)
+    wsb = lib.vst_groupnorm5d_bwd_workspace_bytes(b, c, f, groups)
+    ws = torch.empty(wsb, dtype=torch.uint8, device=x_fm.device)
+    check(lib.vst_groupnorm5d_bwd(x_fm.data_ptr(), dy_fm.data_ptr(), _ptr(add), dx.data_ptr(),
+                                  mean.data_ptr(), rstd.data_ptr(), gamma.data_ptr(), dg.data_ptr(),
+                                  db.data_ptr(), b, c, f, h * w, groups, _dt(gamma), ws.data_ptr(), wsb,
+                                  _stream()), "vst_groupnorm5d_bwd")
+    return dx, dg, db
+
+
+def geglu_raw(hg: torch.Tensor) -> torch.Tensor:
+    hg = hg.detach()
     _cuda(hg)
     assert hg.dtype == torch.bfloat16 and hg.dim() == 2 and hg.stride(1) == 1
     rows, two = hg.shape
