@@ -200,6 +200,40 @@ int vst_attn_bwd(const void* q, const void* k, const void* v, const void* o, con
                  int64_t lddq, int64_t lddk, int64_t lddv, int kv_group, float scale,
                  void* workspace, int64_t workspace_bytes, void* stream);
 
+/* ---- §8e: one video, sequence-parallel over the GPUs of an NVSwitch box -------------------------
+ * Spatial work is sharded over frames, temporal work over positions (the reference
+ * itself has no collective).  Each rank owns a "symmetric" device buffer (data + `world` 32-bit flag
+ * words, zeroed) that every peer maps through CUDA IPC: vst_comm_ipc_get / _open / _close move the
+ * 64-byte handles, which the host exchanges with whatever it has (torch.distributed here).
+ * vst_comm_init takes, for every rank r, the address AS MAPPED ON THIS GPU of r's data buffer and
+ * flag words, and returns the communicator.
+ * The two all-to-alls of a motion module are the motion module's own layout kernels addressing
+ * peer memory (no separate exchange pass):
+ *   vst_a2a_frames_to_hw: this rank's frames x[(b, f_local), c, hw] (strides sB, sC, sF) ->
+ *       GroupNorm-apply (when mean != NULL) -> token rows [(b, hw_local), f, c] STORED into the
+ *       buffer of the rank that owns position hw, at byte offset dst_offset_bytes, laid out
+ *       (B, HW/world, F_total, C) bf16;
+ *   vst_a2a_hw_to_frames: token rows LOADED from the owners' buffers (src_offset_bytes) ->
+ *       out[(b, f_local), c, hw] (+ residual, local).
+ * Neither call synchronises ranks: bracket them with vst_comm_barrier (a flag barrier over NVLink,
+ * st.release.sys / ld.acquire.sys; it traps after 20 s instead of hanging if a peer is gone).
+ * bf16 only; HW must be a multiple of world x 64; F_total = world x F_local. */
+int vst_comm_alloc(int64_t bytes, void** out);   /* cudaMalloc + zero fill: the symmetric buffer */
+int vst_comm_free(void* ptr);
+int vst_comm_ipc_get(const void* dev_ptr, void* handle64);
+int vst_comm_ipc_open(const void* handle64, void** out);
+int vst_comm_ipc_close(void* ptr);
+int vst_comm_init(int rank, int world, void* const* bufs, void* const* flags, void** comm_out);
+int vst_comm_fini(void* comm);
+int vst_comm_barrier(void* comm, void* stream);
+int vst_a2a_frames_to_hw(void* comm, const void* x, int64_t dst_offset_bytes, const float* mean,
+                         const float* rstd, const void* gamma, const void* beta, int B, int C,
+                         int F_local, int F_total, int HW, int64_t sB, int64_t sC, int64_t sF,
+                         int groups, int param_dtype, void* stream);
+int vst_a2a_hw_to_frames(void* comm, int64_t src_offset_bytes, void* out, const void* residual, int B,
+                         int C, int F_local, int F_total, int HW, int64_t sB, int64_t sC, int64_t sF,
+                         void* stream);
+
 #ifdef __cplusplus
 }
 #endif

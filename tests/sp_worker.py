@@ -1,0 +1,46 @@
+"""torchrun worker for tests/test_sp_gpu.py: one process per GPU, CUDA-IPC mapped symmetric buffers,
+flag barrier over NVLink.  Every rank builds the same module (same seed), takes its frames of the
+same video and checks its slice of the output against the unsharded module run locally."""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+    dist.init_process_group("nccl")
+    from tests.test_sp_gpu import _module
+    from video_style_transfer_b200.sequence_parallel import SPComm, SPMotionStep, motion_module_sp
+    worst = 0.0
+    for c, hw, f in ((320, 32, 16), (640, 16, 32)):
+        mm = _module(c)
+        g = torch.Generator(device="cuda").manual_seed(1234)
+        x = torch.randn(f, c, hw, hw, device="cuda", generator=g).to(torch.bfloat16)
+        comm = SPComm.from_process_group(SPMotionStep.buffer_bytes(1, c, hw * hw, f, world))
+        fl = f // world
+        with torch.no_grad():
+            want = mm(x, num_frames=f)[rank * fl:(rank + 1) * fl]
+            for it in range(3):      # repeated calls exercise buffer reuse and the barrier epochs
+                got = motion_module_sp(mm, comm, x[rank * fl:(rank + 1) * fl].contiguous(), f)
+        torch.cuda.synchronize()
+        err = ((got.float() - want.float()).abs().max() / want.float().abs().max()).item()
+        worst = max(worst, err)
+        dist.barrier()
+        comm.close()
+    t = torch.tensor([worst], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dist.destroy_process_group()
+    if t.item() >= 1e-2:
+        print(f"sp_worker FAILED: rel err {t.item()}")
+        sys.exit(1)
+    if rank == 0:
+        print(f"sp_worker ok (world {world}, worst rel err {t.item():.2e})")
+
+
+if __name__ == "__main__":
+    main()

@@ -46,6 +46,16 @@ SIGNATURES = {
     "vst_gelu_bwd": (_i, [_p, _p, _p, _l, _i, _l, _l, _l, _f, _p]),
     "vst_groupnorm5d_bwd_workspace_bytes": (_l, [_i, _i, _i, _i]),
     "vst_groupnorm5d_bwd": (_i, [_p] * 9 + [_i] * 6 + [_p, _l, _p]),
+    "vst_comm_alloc": (_i, [_l, C.POINTER(_p)]),
+    "vst_comm_free": (_i, [_p]),
+    "vst_comm_ipc_get": (_i, [_p, _p]),
+    "vst_comm_ipc_open": (_i, [_p, C.POINTER(_p)]),
+    "vst_comm_ipc_close": (_i, [_p]),
+    "vst_comm_init": (_i, [_i, _i, C.POINTER(_p), C.POINTER(_p), C.POINTER(_p)]),
+    "vst_comm_fini": (_i, [_p]),
+    "vst_comm_barrier": (_i, [_p, _p]),
+    "vst_a2a_frames_to_hw": (_i, [_p, _p, _l, _p, _p, _p, _p, _i, _i, _i, _i, _i, _l, _l, _l, _i, _i, _p]),
+    "vst_a2a_hw_to_frames": (_i, [_p, _l, _p, _p, _i, _i, _i, _i, _i, _l, _l, _l, _p]),
     "vst_attn_fwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _l, _l, _l, _l, _i, _f, _p]),
 }
 

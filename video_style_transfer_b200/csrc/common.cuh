@@ -50,6 +50,17 @@ int vst_make_tmap(CUtensorMap* out, const void* base, int rank, const uint64_t* 
                   CUtensorMapL2promotion l2 = CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
 
 // ---------------------------------------------------------------------------------------------
+// sequence-parallel communicator (comm.cu); the layout kernels address peer memory through it
+// ---------------------------------------------------------------------------------------------
+#define VST_MAX_RANKS 8
+struct VstComm {
+  int rank, world;
+  void* buf[VST_MAX_RANKS];        // symmetric data buffers, mapped on this GPU (buf[rank] is local)
+  uint32_t* flags[VST_MAX_RANKS];  // flags[r]: rank r's flag words, one per peer
+  uint32_t epoch;
+};
+
+// ---------------------------------------------------------------------------------------------
 // device helpers
 // ---------------------------------------------------------------------------------------------
 #ifdef __CUDACC__

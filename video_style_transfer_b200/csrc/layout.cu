@@ -6,6 +6,8 @@
 // HBM-bound: one read + one write per element.  Tile = 64 positions x 32 words staged in shared
 // memory; 16-byte global loads along hw, 16-byte global stores along c; the shared tile is
 // XOR-swizzled at 16-byte-chunk granularity so both phases are bank-conflict free for bf16.
+#include <string.h>
+
 #include "common.cuh"
 
 namespace {
@@ -47,6 +49,27 @@ __device__ __forceinline__ uint32_t norm_word(uint32_t w, float2 ab) {
   return pack_bf16(fmaf(e.x, ab.x, ab.y), fmaf(e.y, ab.x, ab.y));
 }
 
+// Sequence-parallel addressing of the TOKEN side (§8e, comm.cu).  world == 0: the token tensor is
+// local, (B*HW, F, C).  world > 0: this rank holds frames [f_offset, f_offset + F) of F_total; the
+// token rows of position hw live on rank hw / hw_per_rank, in that rank's symmetric buffer laid out
+// (B, hw_per_rank, F_total, C).  The forward modes then STORE to peer memory (push all-to-all fused
+// into the GroupNorm-apply + rearrange), the backward mode LOADS from it (pull all-to-all fused
+// into the inverse rearrange + residual add): the exchange costs no pass of its own.
+struct ShardArgs {
+  void* peer[VST_MAX_RANKS];
+  int world, hw_per_rank, f_offset, f_total;
+};
+__device__ __forceinline__ int64_t tok_offset(const ShardArgs& sh, int b, int hw, int f, int F, int HW,
+                                              int C, int* rank) {
+  if (sh.world == 0) {
+    *rank = -1;
+    return (((int64_t)b * HW + hw) * F + f) * C;
+  }
+  const int r = hw / sh.hw_per_rank;
+  *rank = r;
+  return (((int64_t)b * sh.hw_per_rank + (hw - r * sh.hw_per_rank)) * sh.f_total + sh.f_offset + f) * C;
+}
+
 // ---- bf16: two channel rows per thread, 2x2 transposes with byte permutes -------------------
 // MODE 0: forward (x[b,c,f,hw] -> y[(b,hw),f,c] + pe[f,c])
 // MODE 1: backward (y[(b,hw),f,c] -> out[b,c,f,hw] + residual[b,c,f,hw])
@@ -56,7 +79,7 @@ __global__ void __launch_bounds__(kThreads)
 rearrange_bf16_kernel(const __nv_bfloat16* __restrict__ src, __nv_bfloat16* __restrict__ dst,
                       const float* __restrict__ pe, const __nv_bfloat16* __restrict__ residual,
                       int C, int F, int HW, int64_t sB, int64_t sC, int64_t sF, int tilesHW,
-                      int tilesC, NormArgs na) {
+                      int tilesC, NormArgs na, ShardArgs sh) {
   __shared__ __align__(16) uint32_t tile[kTileHW * kTileWords];
   int t = blockIdx.x;
   const int thw = t % tilesHW;
@@ -70,7 +93,6 @@ rearrange_bf16_kernel(const __nv_bfloat16* __restrict__ src, __nv_bfloat16* __re
 
   // "planar" tensor P[b,c,f,hw] (strided) and "token" tensor T[(b,hw),f,c]
   const int64_t pbase = (int64_t)b * sB + (int64_t)f * sF;
-  const int64_t tbase = ((int64_t)b * HW * F + f) * C;  // + hw*F*C + c
 
   if (MODE == 0 || MODE == 2) {
     // load: thread = (channel pair cp, hw chunk hc); 16 B along hw from rows c, c+1
@@ -114,7 +136,10 @@ rearrange_bf16_kernel(const __nv_bfloat16* __restrict__ src, __nv_bfloat16* __re
           e = unpack_bf16(v.z); v.z = pack_bf16(e.x + p1.x, e.y + p1.y);
           e = unpack_bf16(v.w); v.w = pack_bf16(e.x + p1.z, e.y + p1.w);
         }
-        st_stream16(dst + tbase + (int64_t)hwr * F * C + cc, v);
+        int rk;
+        const int64_t toff = tok_offset(sh, b, hwr, f, F, HW, C, &rk);
+        __nv_bfloat16* tdst = rk < 0 ? dst : reinterpret_cast<__nv_bfloat16*>(sh.peer[rk]);
+        st_stream16(tdst + toff + cc, v);
       }
     }
   } else {
@@ -125,7 +150,12 @@ rearrange_bf16_kernel(const __nv_bfloat16* __restrict__ src, __nv_bfloat16* __re
       const int row = item >> 3, ch = item & 7;
       const int hwr = hw0 + row, cc = c0 + 8 * ch;
       uint4 v = make_uint4(0, 0, 0, 0);
-      if (hwr < HW && cc < C) v = ld_stream16(src + tbase + (int64_t)hwr * F * C + cc);
+      if (hwr < HW && cc < C) {
+        int rk;
+        const int64_t toff = tok_offset(sh, b, hwr, f, F, HW, C, &rk);
+        const __nv_bfloat16* tsrc = rk < 0 ? src : reinterpret_cast<const __nv_bfloat16*>(sh.peer[rk]);
+        v = ld_stream16(tsrc + toff + cc);
+      }
       *reinterpret_cast<uint4*>(&tile[swz(row, 4 * ch)]) = v;
     }
     __syncthreads();
@@ -236,19 +266,25 @@ inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 template <int MODE>
 int launch(const void* src, void* dst, const float* pe, const void* residual, int B, int C,
            int F, int HW, int64_t sB, int64_t sC, int64_t sF, int dtype, cudaStream_t st,
-           NormArgs na = NormArgs{nullptr, nullptr, nullptr, nullptr, 1, 0}) {
+           NormArgs na = NormArgs{nullptr, nullptr, nullptr, nullptr, 1, 0},
+           const ShardArgs* shard = nullptr) {
   if ((int64_t)B * C * F * HW == 0) return VST_OK;
+  ShardArgs sh;
+  memset(&sh, 0, sizeof(sh));
+  if (shard) sh = *shard;
   const bool fast = dtype == VST_BF16 && C % 8 == 0 && HW % 8 == 0 && sB % 8 == 0 &&
                     sC % 8 == 0 && sF % 8 == 0 && aligned16(src) && aligned16(dst) &&
                     (residual == nullptr || aligned16(residual)) &&
                     (pe == nullptr || aligned16(pe));
+  VST_REQUIRE(fast || shard == nullptr, VST_E_UNSUPPORTED,
+              "sequence-parallel rearrange needs bf16 and 16-byte friendly shapes / pointers");
   if (fast) {
     const int tilesHW = (HW + kTileHW - 1) / kTileHW, tilesC = (C + 63) / 64;
     const int64_t grid = (int64_t)B * F * tilesHW * tilesC;
     VST_REQUIRE(grid < (1ll << 31), VST_E_UNSUPPORTED, "rearrange: grid too large");
     rearrange_bf16_kernel<MODE><<<(unsigned)grid, kThreads, 0, st>>>(
         (const __nv_bfloat16*)src, (__nv_bfloat16*)dst, pe, (const __nv_bfloat16*)residual, C, F,
-        HW, sB, sC, sF, tilesHW, tilesC, na);
+        HW, sB, sC, sF, tilesHW, tilesC, na, sh);
   } else {
     const int tilesHW = (HW + 31) / 32, tilesC = (C + 31) / 32;
     const int64_t grid = (int64_t)B * F * tilesHW * tilesC;
@@ -308,4 +344,54 @@ extern "C" int vst_groupnorm5d_apply_rearrange(const void* x, void* y, const flo
   NormArgs na{mean, rstd, gamma, beta, groups, param_dtype == VST_BF16};
   return launch<2>(x, y, nullptr, nullptr, B, C, F, HW, sB, sC, sF, in_dtype,
                    (cudaStream_t)stream, na);
+}
+
+// ---- §8e: the two all-to-alls of a sequence-parallel motion module ------------------------------
+namespace {
+int make_shard(ShardArgs* sh, const VstComm* c, int64_t offset_bytes, int F_local, int F_total, int HW) {
+  VST_REQUIRE(c != nullptr, VST_E_BADARG, "a2a: null communicator");
+  VST_REQUIRE(F_local > 0 && F_total == F_local * c->world, VST_E_BADARG,
+              "a2a: F_total=%d must be world(%d) x F_local(%d)", F_total, c->world, F_local);
+  VST_REQUIRE(HW % (c->world * kTileHW) == 0, VST_E_UNSUPPORTED,
+              "a2a: HW=%d must be a multiple of world x %d", HW, kTileHW);
+  VST_REQUIRE(offset_bytes >= 0 && offset_bytes % 16 == 0, VST_E_BADARG, "a2a: buffer offset must be a multiple of 16");
+  memset(sh, 0, sizeof(*sh));
+  for (int r = 0; r < c->world; ++r) sh->peer[r] = reinterpret_cast<uint8_t*>(c->buf[r]) + offset_bytes;
+  sh->world = c->world;
+  sh->hw_per_rank = HW / c->world;
+  sh->f_offset = c->rank * F_local;
+  sh->f_total = F_total;
+  return VST_OK;
+}
+}  // namespace
+
+extern "C" int vst_a2a_frames_to_hw(void* comm, const void* x, int64_t dst_offset_bytes,
+                                    const float* mean, const float* rstd, const void* gamma,
+                                    const void* beta, int B, int C, int F_local, int F_total, int HW,
+                                    int64_t sB, int64_t sC, int64_t sF, int groups, int param_dtype,
+                                    void* stream) {
+  VST_REQUIRE(x != nullptr && B > 0 && C > 0, VST_E_BADARG, "a2a_frames_to_hw: bad argument");
+  ShardArgs sh;
+  int rc = make_shard(&sh, reinterpret_cast<const VstComm*>(comm), dst_offset_bytes, F_local, F_total, HW);
+  if (rc) return rc;
+  void* local = sh.peer[reinterpret_cast<const VstComm*>(comm)->rank];
+  if (mean != nullptr) {
+    VST_REQUIRE(rstd && gamma && beta && groups > 0 && C % groups == 0, VST_E_BADARG, "a2a_frames_to_hw: bad norm arguments");
+    NormArgs na{mean, rstd, gamma, beta, groups, param_dtype == VST_BF16};
+    return launch<2>(x, local, nullptr, nullptr, B, C, F_local, HW, sB, sC, sF, VST_BF16, (cudaStream_t)stream, na, &sh);
+  }
+  return launch<0>(x, local, nullptr, nullptr, B, C, F_local, HW, sB, sC, sF, VST_BF16, (cudaStream_t)stream,
+                   NormArgs{nullptr, nullptr, nullptr, nullptr, 1, 0}, &sh);
+}
+
+extern "C" int vst_a2a_hw_to_frames(void* comm, int64_t src_offset_bytes, void* out, const void* residual,
+                                    int B, int C, int F_local, int F_total, int HW, int64_t sB,
+                                    int64_t sC, int64_t sF, void* stream) {
+  VST_REQUIRE(out != nullptr && B > 0 && C > 0, VST_E_BADARG, "a2a_hw_to_frames: bad argument");
+  ShardArgs sh;
+  int rc = make_shard(&sh, reinterpret_cast<const VstComm*>(comm), src_offset_bytes, F_local, F_total, HW);
+  if (rc) return rc;
+  const void* local = sh.peer[reinterpret_cast<const VstComm*>(comm)->rank];
+  return launch<1>(local, out, nullptr, residual, B, C, F_local, HW, sB, sC, sF, VST_BF16, (cudaStream_t)stream,
+                   NormArgs{nullptr, nullptr, nullptr, nullptr, 1, 0}, &sh);
 }

@@ -110,6 +110,34 @@ def groupnorm5d_stats(x5: torch.Tensor, groups: int = 32, eps: float = 1e-6):
     return mean, rstd
 
 
+def groupnorm5d_partials(x5: torch.Tensor, groups: int = 32) -> torch.Tensor:
+    """(count, mean, M2) partials of the local frames, (B*groups, nparts, 3) fp32: what a
+    sequence-parallel rank contributes to the GroupNorm statistics."""
+    _cuda(x5)
+    x5 = x5.detach()
+    b, c, f, h, w = x5.shape
+    sB, sC, sF = _planar_strides(x5)
+    nparts = lib.vst_groupnorm5d_partials(c, f, h * w, groups)
+    if nparts <= 0:
+        raise ValueError("groupnorm5d: C must be divisible by groups")
+    partials = torch.empty((b * groups, nparts, 3), dtype=torch.float32, device=x5.device)
+    check(lib.vst_groupnorm5d_stats(x5.data_ptr(), partials.data_ptr(), b, c, f, h * w, sB, sC, sF,
+                                    groups, _dt(x5), _stream()), "vst_groupnorm5d_stats")
+    return partials
+
+
+def groupnorm5d_finalize(partials: torch.Tensor, eps: float = 1e-6):
+    """Chan-merge (fixed order) of (B*groups, nparts, 3) partials -> (mean, rstd)."""
+    _cuda(partials)
+    partials = partials.contiguous()
+    bg, nparts, _ = partials.shape
+    mean = torch.empty(bg, dtype=torch.float32, device=partials.device)
+    rstd = torch.empty_like(mean)
+    check(lib.vst_groupnorm5d_finalize(partials.data_ptr(), nparts, bg, 1, eps, mean.data_ptr(),
+                                       rstd.data_ptr(), _stream()), "vst_groupnorm5d_finalize")
+    return mean, rstd
+
+
 def groupnorm5d_rearrange(x5: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor,
                           groups: int = 32, eps: float = 1e-6):
     """GroupNorm over (C/groups, F, H, W) of the (B,C,F,H,W) view, written straight into the
