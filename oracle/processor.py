@@ -144,17 +144,10 @@ def temporal_attention(x, w: Dict[str, torch.Tensor], prefix: str, heads: int, l
     return proj("to_out.0", o)
 
 
-def motion_module(x, w: Dict[str, torch.Tensor], num_frames: int, heads: int = 8,
-                  groups: int = 32, lora=None):
-    """x (B*F, C, H, W) -> same shape.  GroupNorm5D -> (BHW,F,C) -> proj_in ->
-    [LN,+PE,attn1,+res; LN,+PE,attn2,+res; LN,GEGLU FF,+res] -> proj_out -> back -> +res.
-    Key names follow diffusers (temporal_lora.py:76-84,100-111 show the naming)."""
-    bf, c, h, wd = x.shape
-    b = bf // num_frames
-    residual = x
-    x5 = x.reshape(b, num_frames, c, h, wd).permute(0, 2, 1, 3, 4)
-    x5 = hp.groupnorm5d(x5, w["norm.weight"], w["norm.bias"], groups, 1e-6)
-    y = hp.rearrange_fwd(x5)
+def motion_module_tokens(y, w: Dict[str, torch.Tensor], num_frames: int, heads: int = 8, lora=None):
+    """The position-wise body of the motion module on token rows (N, F, C): proj_in ->
+    [LN,+PE,attn1,+res; LN,+PE,attn2,+res; LN,GEGLU FF,+res] -> proj_out.  Every row of N is
+    independent, which is what the sequence-parallel split over positions relies on."""
     y = y @ w["proj_in.weight"].t() + w["proj_in.bias"]
     pe = w["pos_embed.pe"]
     tb = "transformer_blocks.0."
@@ -167,6 +160,21 @@ def motion_module(x, w: Dict[str, torch.Tensor], num_frames: int, heads: int = 8
     hid, gate = hg.chunk(2, dim=-1)
     y = y + ((hid * hp.gelu(gate)) @ w[tb + "ff.net.2.weight"].t() + w[tb + "ff.net.2.bias"])
     y = y @ w["proj_out.weight"].t() + w["proj_out.bias"]
+    return y
+
+
+def motion_module(x, w: Dict[str, torch.Tensor], num_frames: int, heads: int = 8,
+                  groups: int = 32, lora=None):
+    """x (B*F, C, H, W) -> same shape.  GroupNorm5D -> (BHW,F,C) -> proj_in ->
+    [LN,+PE,attn1,+res; LN,+PE,attn2,+res; LN,GEGLU FF,+res] -> proj_out -> back -> +res.
+    Key names follow diffusers (temporal_lora.py:76-84,100-111 show the naming)."""
+    bf, c, h, wd = x.shape
+    b = bf // num_frames
+    residual = x
+    x5 = x.reshape(b, num_frames, c, h, wd).permute(0, 2, 1, 3, 4)
+    x5 = hp.groupnorm5d(x5, w["norm.weight"], w["norm.bias"], groups, 1e-6)
+    y = hp.rearrange_fwd(x5)
+    y = motion_module_tokens(y, w, num_frames, heads, lora)
     y5 = hp.rearrange_bwd(y, b, h, wd)                     # (B,C,F,H,W)
     out = y5.permute(0, 2, 1, 3, 4).reshape(bf, c, h, wd)
     return out + residual

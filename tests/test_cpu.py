@@ -313,3 +313,61 @@ def test_bf16_cache_invalidates_on_inplace_update():
         w.add_(1.0)
         b = bf16_cached(w)
     assert b is not a and torch.equal(b, w.detach().to(torch.bfloat16))
+
+
+# ---- §8e: the sequence-parallel split, world_size 2 over gloo on CPU ------------------------------------
+def _sp_gloo_worker(rank, world, port, q):
+    import torch.distributed as dist
+    from oracle import processor as op
+    from oracle import sp
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.manual_seed(0)                       # same weights and video on every rank
+        c, f, hw = 64, 8, 4
+        w = _motion_weights(c)
+        x = torch.randn(f, c, hw, hw)
+        want = op.motion_module(x, w, f, 8, 32, None)
+        (f0, f1), (p0, p1) = sp.sp_plan(f, hw * hw, world, rank)
+        assert (f1 - f0) * world == f and (p1 - p0) * world == hw * hw
+        got = sp.motion_module_sp(x[f0:f1].contiguous(), w, f, 8, 32, None)
+        err = ((got - want[f0:f1]).abs().max() / want.abs().max()).item()
+        q.put((rank, err))
+    finally:
+        dist.destroy_process_group()
+
+
+def _motion_weights(c):
+    g = torch.Generator().manual_seed(7)
+    r = lambda *s: torch.randn(*s, generator=g) * 0.1
+    w = {"norm.weight": 1 + r(c), "norm.bias": r(c), "proj_in.weight": r(c, c), "proj_in.bias": r(c),
+         "proj_out.weight": r(c, c), "proj_out.bias": r(c)}
+    tb = "transformer_blocks.0."
+    for n in ("norm1", "norm2", "norm3"):
+        w[tb + n + ".weight"], w[tb + n + ".bias"] = 1 + r(c), r(c)
+    for a in ("attn1", "attn2"):
+        for p in ("to_q", "to_k", "to_v"):
+            w[tb + a + "." + p + ".weight"] = r(c, c)
+        w[tb + a + ".to_out.0.weight"], w[tb + a + ".to_out.0.bias"] = r(c, c), r(c)
+    w[tb + "ff.net.0.proj.weight"], w[tb + "ff.net.0.proj.bias"] = r(8 * c, c), r(8 * c)
+    w[tb + "ff.net.2.weight"], w[tb + "ff.net.2.bias"] = r(c, 4 * c), r(c)
+    from oracle import hotpath as hp
+    w["pos_embed.pe"] = hp.positional_table(c, 32)
+    return w
+
+
+def test_sequence_parallel_split_world2_gloo():
+    """Frames sharded over 2 ranks, GroupNorm statistics all-reduced, frames<->positions exchanges:
+    the sharded oracle equals the unsharded one on every rank's frames."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29611
+    procs = [ctx.Process(target=_sp_gloo_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    errs = dict(q.get(timeout=5) for _ in range(2))
+    assert set(errs) == {0, 1} and max(errs.values()) < 1e-5, errs
