@@ -27,7 +27,9 @@ def flush_l2():
     _flush.zero_()
 
 
-def timeit(fn, iters=10, warmup=3, flush=True):
+def timeit(fn, iters=None, warmup=None, flush=True):
+    iters = iters or int(os.environ.get("KBENCH_ITERS", "10"))      # 1 / 1 under ncu --set full
+    warmup = warmup or int(os.environ.get("KBENCH_WARMUP", "3"))
     for _ in range(warmup):
         fn()
     torch.cuda.synchronize()
@@ -131,6 +133,68 @@ def main():
                 v.view(bk, sk, h, 64).transpose(1, 2)
             ms, b = timeit(lambda: torch.nn.functional.scaled_dot_product_attention(qh, kh, vh))
             report(f"  (torch SDPA) {tag}", ms, b, nb, fl)
+    if "bwd" in which:
+        # the training-step (config 2 / 4) backward kernels at the same shapes
+        for tag, m, n, k in [("L1 dx = dy W  M=65536 640x640", 65536, 640, 640),
+                             ("L2 dx = dy W  M=16384 1280x1280", 16384, 1280, 1280),
+                             ("L2 ff dx M=16384 N=1280 K=10240", 16384, 1280, 10240)]:
+            dy = torch.randn(m, k, device="cuda").to(bf)
+            w = torch.randn(k, n, device="cuda").to(bf)          # stored [out, in]: opB = W^T via trans_b
+            ms, b = timeit(lambda: ops.gemm(dy, w, trans_b=True))
+            report(f"vst_gemm NN {tag}", ms, b, None, 2 * m * n * k)
+            ms, b = timeit(lambda: dy @ w)
+            report(f"  (cuBLAS matmul) {tag}", ms, b, None, 2 * m * n * k)
+        for tag, m, n, k in [("L1 dA = u^T x  128x640 K=65536", 128, 640, 65536),
+                             ("L1 dW = dy^T x 640x640 K=65536", 640, 640, 65536),
+                             ("L2 dW = dy^T x 1280x1280 K=16384", 1280, 1280, 16384),
+                             ("L0 temporal dB 320x32 K=262144", 320, 32, 262144)]:
+            a = torch.randn(k, m, device="cuda").to(bf)
+            x = torch.randn(k, n, device="cuda").to(bf)
+            ms, b = timeit(lambda: ops.gemm(a, x, trans_a=True, trans_b=True, out_dtype=torch.float32))
+            report(f"vst_gemm TN split-K {tag}", ms, b, (a.numel() + x.numel()) * 2, 2 * m * n * k)
+            ms, b = timeit(lambda: a.t() @ x)
+            report(f"  (cuBLAS matmul) {tag}", ms, b, (a.numel() + x.numel()) * 2, 2 * m * n * k)
+        for tag, bt, h, sq, sk in [("L1 self", 16, 10, 4096, 4096), ("L2 self", 16, 20, 1024, 1024),
+                                   ("L1 cross", 16, 10, 4096, 77), ("L2 cross", 16, 20, 1024, 77)]:
+            c = h * 64
+            bk = bt if "self" in tag else 1
+            q = torch.randn(bt, sq, c, device="cuda").to(bf)
+            k = torch.randn(bk, sk, c, device="cuda").to(bf)
+            v = torch.randn(bk, sk, c, device="cuda").to(bf)
+            do = torch.randn(bt, sq, c, device="cuda").to(bf)
+            o, lse = ops.attn_fwd_raw(q, k, v, h, return_lse=True)
+            fl = 10 * bt * h * sq * sk * 64
+            ms, b = timeit(lambda: ops.attn_bwd(q, k, v, o, do, lse, h))
+            report(f"attn_bwd {tag} B={bt} h={h} Sq={sq} Sk={sk}", ms, b, None, fl)
+            if bk == bt:
+                qh, kh, vh = (t.view(bt, -1, h, 64).transpose(1, 2).detach().requires_grad_() for t in (q, k, v))
+                with torch.enable_grad():
+                    oh = torch.nn.functional.scaled_dot_product_attention(qh, kh, vh)
+                doh = do.view(bt, sq, h, 64).transpose(1, 2)
+                ms, b = timeit(lambda: torch.autograd.grad(oh, (qh, kh, vh), doh, retain_graph=True))
+                report(f"  (torch SDPA backward) {tag}", ms, b, None, fl)
+        for tag, c, hw in levels:
+            n = hw * hw
+            qkv = torch.randn(n, F, 3 * c, device="cuda").to(bf)
+            q, k, v = qkv[..., :c], qkv[..., c:2 * c], qkv[..., 2 * c:]
+            do = torch.randn(n, F, c, device="cuda").to(bf)
+            ms, b = timeit(lambda: ops.temporal_attn_bwd(q, k, v, do, 8))
+            report(f"temporal_attn_bwd {tag} N={n} d={c // 8}", ms, b, 7 * n * F * c * 2, 10 * n * F * F * c)
+            t = torch.randn(n * F, c, device="cuda").to(bf)
+            dy = torch.randn(n * F, c, device="cuda").to(bf)
+            g = torch.randn(c, device="cuda").to(bf)
+            ms, b = timeit(lambda: ops.layernorm_bwd(t, dy, g, 1e-5))
+            report(f"layernorm_bwd {tag} rows={n * F}", ms, b, 3 * t.numel() * 2)
+            hg = torch.randn(n * F, 8 * c, device="cuda").to(bf)
+            dg = torch.randn(n * F, 4 * c, device="cuda").to(bf)
+            ms, b = timeit(lambda: ops.geglu_bwd(hg, dg))
+            report(f"geglu_bwd {tag} rows={n * F} inner={4 * c}", ms, b, (2 * hg.numel() + dg.numel()) * 2)
+            del hg, dg
+            x = torch.randn(F, c, hw, hw, device="cuda").to(bf)
+            dyx = torch.randn(F, c, hw, hw, device="cuda").to(bf)
+            mean, rstd = ops.groupnorm5d_stats(x.view(1, F, c, hw, hw).permute(0, 2, 1, 3, 4))
+            ms, b = timeit(lambda: ops.groupnorm5d_bwd(x, dyx, mean, rstd, g, 1, F, 32))
+            report(f"groupnorm5d_bwd {tag}", ms, b, 5 * x.numel() * 2)
 
 
 if __name__ == "__main__":

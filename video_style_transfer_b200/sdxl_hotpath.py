@@ -147,6 +147,70 @@ def run_unet_hotpath(plan, xs4, xs3, text, frames: int):
     return outs
 
 
+@torch.no_grad()
+def run_unet_hotpath_sp(plan, xs4_local, xs3_local, text, f_total: int, comm, group=None):
+    """run_unet_hotpath for ONE video whose frames are sharded over the ranks of `comm`
+    (BASELINE config 5): the spatial processors run on this rank's frames with no
+    exchange; every motion module goes through sequence_parallel.motion_module_sp (two fused
+    NVLink all-to-alls + the 256-byte GroupNorm reduction)."""
+    from .sequence_parallel import motion_module_sp
+    outs = [None, None, None]
+    for kind, lvl, mod in plan:
+        if kind == "self":
+            outs[lvl] = mod(xs3_local[lvl])
+        elif kind == "cross":
+            outs[lvl] = mod(xs3_local[lvl], encoder_hidden_states=text)
+        else:
+            outs[lvl] = motion_module_sp(mod, comm, xs4_local[lvl], f_total, group)
+    return outs
+
+
+def freeze_for_stage2(model: nn.Module, unfreeze_mergers: bool = True):
+    """The Stage-2 trainable set (reference animatediff/utils.py:66-95, which needs diffusers to
+    import): motion-module parameters except the TemporalLoRALinear bases, plus the UnZipLoRA
+    mergers when `unfreeze_mergers`; everything else frozen.  Returns the trainable parameters."""
+    out = []
+    for name, p in model.named_parameters():
+        if "motion_modules" in name:
+            p.requires_grad_(not (".base.weight" in name or ".base.bias" in name))
+        elif unfreeze_mergers and ("merge_content" in name or "merge_style" in name):
+            p.requires_grad_(True)
+        else:
+            p.requires_grad_(False)
+        if p.requires_grad:
+            out.append(p)
+    return out
+
+
+def train_step_hotpath(model, plan, xs4, xs3, text, targets, frames: int, optimizer, spatial_index,
+                       lambda_orth: float = 1e-4, max_grad_norm: float = 1.0):
+    """One Stage-2 training step over the hot-path stack (train_animatediff.py:212-317 restricted
+    to SURVEY.md §8): forward of every module with autograd, MSE against `targets` + the temporal /
+    spatial orthogonality loss, backward, gradient clipping, optimizer step.  The inputs require
+    grad (inside the UNet every module has to return dX to the layer before it)."""
+    from .animatediff.temporal_lora import compute_orth_loss
+    optimizer.zero_grad(set_to_none=True)
+    x4 = [t.detach().requires_grad_(True) for t in xs4]
+    x3 = [None] + [t.detach().requires_grad_(True) for t in xs3[1:]]
+    loss = None
+    for kind, lvl, mod in plan:
+        if kind == "self":
+            y = mod(x3[lvl])
+        elif kind == "cross":
+            y = mod(x3[lvl], encoder_hidden_states=text)
+        else:
+            y = mod(x4[lvl], num_frames=frames)
+        term = torch.nn.functional.mse_loss(y.float(), targets[kind][lvl].float())
+        loss = term if loss is None else loss + term
+    orth = compute_orth_loss(model, spatial_index, lambda_orth)
+    loss = loss + orth.to(loss.device)
+    loss.backward()
+    params = [p for g in optimizer.param_groups for p in g["params"]]
+    torch.nn.utils.clip_grad_norm_(params, max_grad_norm)
+    optimizer.step()
+    return loss.detach()
+
+
 def hotpath_flops(plan, frames: int, latent: int = 128, batch: int = 1):
     """Algorithmic FLOPs of one UNet forward of the plan (SURVEY.md §8d formulas), by kernel family."""
     fl = {"attn_self": 0.0, "attn_cross": 0.0, "proj": 0.0, "temporal_attn": 0.0, "motion_gemm": 0.0}
