@@ -152,10 +152,15 @@ int vst_geglu(const void* hg, void* out, int64_t rows, int inner, int64_t ld_in,
  * animatediff/attention_processor.py:74-83 (head split, SDPA, head merge) in one kernel.
  * q,o: (Bt, Sq, heads*64) bf16; k,v: (Bk, Sk, heads*64) bf16 where batch b reads k/v batch
  * b / kv_group (kv_group = Bt/Bk implements the text repeat_interleave of :62-66 without
- * materialising it).  lse (optional, fp32 (Bt,heads,Sq)) is saved for the backward. */
+ * materialising it).  lse (optional, fp32 (Bt,heads,Sq)) is saved for the backward.
+ * mask (optional, NULL on the AnimateDiff-XL path): the additive attention mask of :46-48 /
+ * F.scaled_dot_product_attention(attn_mask=...), fp32, element (b, h, i, j) at
+ * mask[b*mask_sb + h*mask_sh + i*mask_sq + j]; a stride of 0 broadcasts that axis (a key-padding
+ * mask has mask_sh = mask_sq = 0).  A row whose keys are all -inf yields NaN, as torch does. */
 int vst_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int Bt,
                  int heads, int Sq, int Sk, int d, int64_t ldq, int64_t ldk, int64_t ldv,
-                 int64_t ldo, int kv_group, float scale, void* stream);
+                 int64_t ldo, int kv_group, float scale, const float* mask, int64_t mask_sb,
+                 int64_t mask_sh, int64_t mask_sq, void* stream);
 
 /* ---- a8 backward: gradients of vst_temporal_attn_fwd (probabilities recomputed; no saved state) --
  * q,k,v,d_o: (N,F,heads*d) bf16, 16-byte aligned rows; dq,dk,dv: same shape, bf16. */
@@ -192,12 +197,14 @@ int vst_groupnorm5d_bwd(const void* x, const void* dy, const void* add, void* dx
  * gradient; dq (Bt,Sq,C), dk / dv (Bt/kv_group,Sk,C) are written in bf16 (the text K/V gradients
  * are summed over the kv_group frames that shared them, :62-66).  `workspace`: 256-byte aligned,
  * vst_attn_bwd_workspace_bytes(...) bytes (D = rowsum(dO.O), the fp32 dQ accumulator and, for
- * kv_group > 1, fp32 dK / dV accumulators). */
+ * kv_group > 1, fp32 dK / dV accumulators).  mask / mask_s*: the forward's additive mask (no
+ * gradient is produced for it). */
 int64_t vst_attn_bwd_workspace_bytes(int Bt, int heads, int Sq, int Sk, int kv_group);
 int vst_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o,
                  const float* lse, void* dq, void* dk, void* dv, int Bt, int heads, int Sq, int Sk,
                  int d, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, int64_t lddo,
                  int64_t lddq, int64_t lddk, int64_t lddv, int kv_group, float scale,
+                 const float* mask, int64_t mask_sb, int64_t mask_sh, int64_t mask_sq,
                  void* workspace, int64_t workspace_bytes, void* stream);
 
 /* ---- §8e: one video, sequence-parallel over the GPUs of an NVSwitch box -------------------------

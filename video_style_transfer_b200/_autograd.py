@@ -124,10 +124,11 @@ class AttnFn(torch.autograd.Function):
     """softmax(q k^T * scale) v per head (vst_attn_fwd) with the flash backward (vst_attn_bwd)."""
 
     @staticmethod
-    def forward(ctx, q, k, v, heads, scale):
-        o, lse = ops.attn_fwd_raw(q, k, v, heads, scale, return_lse=True)
+    def forward(ctx, q, k, v, heads, scale, mask=None):
+        o, lse = ops.attn_fwd_raw(q, k, v, heads, scale, return_lse=True, mask=mask)
         ctx.save_for_backward(q, k, v, o, lse)
         ctx.cfg = (heads, scale)
+        ctx.mask = None if mask is None else mask.detach()     # no gradient w.r.t. the mask
         return o
 
     @staticmethod
@@ -138,8 +139,8 @@ class AttnFn(torch.autograd.Function):
         if g.dtype != torch.bfloat16 or g.stride(2) != 1 or g.stride(0) != g.shape[1] * g.stride(1) \
                 or g.stride(1) % 8:
             g = g.to(torch.bfloat16).contiguous()
-        dq, dk, dv = ops.attn_bwd(q.detach(), k.detach(), v.detach(), o, g, lse, heads, scale)
-        return dq, dk, dv, None, None
+        dq, dk, dv = ops.attn_bwd(q.detach(), k.detach(), v.detach(), o, g, lse, heads, scale, ctx.mask)
+        return dq, dk, dv, None, None, None
 
 
 def _dense_bf16(t: torch.Tensor) -> torch.Tensor:

@@ -38,7 +38,7 @@ SIGNATURES = {
     "vst_colsum": (_i, [_p, _l, _l, _i, _f, _p, _p, _l, _p]),
     "vst_geglu": (_i, [_p, _p, _l, _i, _l, _l, _p]),
     "vst_attn_bwd_workspace_bytes": (_l, [_i, _i, _i, _i, _i]),
-    "vst_attn_bwd": (_i, [_p] * 9 + [_i] * 5 + [_l] * 8 + [_i, _f, _p, _l, _p]),
+    "vst_attn_bwd": (_i, [_p] * 9 + [_i] * 5 + [_l] * 8 + [_i, _f, _p, _l, _l, _l, _p, _l, _p]),
     "vst_temporal_attn_bwd": (_i, [_p] * 7 + [_l, _i, _i, _i] + [_l] * 7 + [_f, _p]),
     "vst_layernorm_bwd_workspace_bytes": (_l, [_l, _i]),
     "vst_layernorm_bwd": (_i, [_p, _p, _p, _p, _p, _p, _l, _i, _f, _i, _p, _l, _p]),
@@ -56,7 +56,7 @@ SIGNATURES = {
     "vst_comm_barrier": (_i, [_p, _p]),
     "vst_a2a_frames_to_hw": (_i, [_p, _p, _l, _p, _p, _p, _p, _i, _i, _i, _i, _i, _l, _l, _l, _i, _i, _p]),
     "vst_a2a_hw_to_frames": (_i, [_p, _l, _p, _p, _i, _i, _i, _i, _i, _l, _l, _l, _p]),
-    "vst_attn_fwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _l, _l, _l, _l, _i, _f, _p]),
+    "vst_attn_fwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _l, _l, _l, _l, _i, _f, _p, _l, _l, _l, _p]),
 }
 
 

@@ -35,9 +35,6 @@ class AnimateDiffAttnProcessor2_0:
                  encoder_hidden_states: Optional[torch.Tensor] = None,
                  attention_mask: Optional[torch.Tensor] = None,
                  temb: Optional[torch.Tensor] = None, scale: float = 1.0, **kwargs) -> torch.Tensor:
-        if attention_mask is not None:
-            raise NotImplementedError("attention_mask is always None on the AnimateDiff-XL path; "
-                                      "the sm_100a kernel does not take an additive mask yet")
         residual = hidden_states
         in_dtype = hidden_states.dtype
         if attn.spatial_norm is not None:
@@ -47,6 +44,10 @@ class AnimateDiffAttnProcessor2_0:
             bsz, channel, height, width = hidden_states.shape
             hidden_states = hidden_states.view(bsz, channel, height * width).transpose(1, 2)
         batch_size, seq_q, _ = hidden_states.shape
+        if attention_mask is not None:                                       # reference :46-48
+            seq_len = seq_q if encoder_hidden_states is None else encoder_hidden_states.shape[1]
+            attention_mask = attn.prepare_attention_mask(attention_mask, seq_len, batch_size)
+            attention_mask = attention_mask.view(batch_size, attn.heads, -1, attention_mask.shape[-1])
         if attn.group_norm is not None:
             hidden_states = attn.group_norm(hidden_states.transpose(1, 2)).transpose(1, 2)
         lora_scale = scale if hasattr(attn.to_q, "lora_layer") else 1.0
@@ -71,7 +72,7 @@ class AnimateDiffAttnProcessor2_0:
             return t.as_strided((b_, s_, inner), (s_ * t.stride(0), t.stride(0), 1), t.storage_offset())
 
         o = ops.attn_fwd(rows3(q, batch_size, seq_q), rows3(k, kv_batch, seq_k),
-                         rows3(v, kv_batch, seq_k), attn.heads)
+                         rows3(v, kv_batch, seq_k), attn.heads, mask=attention_mask)
         o2 = o.view(batch_size * seq_q, inner)
 
         fuse_res = (attn.residual_connection and input_ndim == 3 and residual.dtype == torch.bfloat16

@@ -76,9 +76,12 @@ struct AttnArgs {
   float* lse;
   int Sq, Sk, heads, kv_group;
   float scale_log2;
+  const float* mask;                 // optional additive mask (natural-log domain), fp32
+  int64_t mask_sb, mask_sh, mask_sq; // element strides over (batch, head, query); 0 = broadcast
+  int mask_vec4;                     // base pointer and strides allow 16-byte loads
 };
 
-template <int kPoly>
+template <int kPoly, bool kMask>
 __global__ void __launch_bounds__(kThreads, 2 / NT)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
@@ -216,7 +219,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const int qt = q0 + t * BQ;
     float m = -INFINITY;               // running (possibly stale) row max, log2 domain
     float2 l2 = make_float2(0.f, 0.f);
-    const float2 sc2 = make_float2(a.scale_log2, a.scale_log2);
+    const float2 sc2 = kMask ? make_float2(1.f, 1.f) : make_float2(a.scale_log2, a.scale_log2);
 
     for (int j = 0; j < nblk; ++j) {
       const int kv0 = j * BKV;
@@ -234,6 +237,31 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         for (int i = 0; i < BKV; ++i)
           if (kv0 + i >= a.Sk) r[i] = 0xff800000u;  // -inf: excluded from max, exp2 -> 0
       }
+      if constexpr (kMask) {
+        // additive mask (attention_processor.py:46-48 -> F.scaled_dot_product_attention attn_mask):
+        // s <- s * scale + mask in the log2 domain, then the block proceeds with unit scale
+        const int qrow = min(qt + row, a.Sq - 1);
+        const float* mrow = a.mask + (int64_t)b * a.mask_sb + (int64_t)head * a.mask_sh +
+                            (int64_t)qrow * a.mask_sq + kv0;
+        constexpr float kLog2e = 1.4426950408889634f;
+        if (!tail && a.mask_vec4) {
+#pragma unroll
+          for (int i = 0; i < BKV; i += 4) {
+            const float4 mk = __ldg(reinterpret_cast<const float4*>(mrow + i));
+            r[i] = __float_as_uint(fmaf(__uint_as_float(r[i]), a.scale_log2, mk.x * kLog2e));
+            r[i + 1] = __float_as_uint(fmaf(__uint_as_float(r[i + 1]), a.scale_log2, mk.y * kLog2e));
+            r[i + 2] = __float_as_uint(fmaf(__uint_as_float(r[i + 2]), a.scale_log2, mk.z * kLog2e));
+            r[i + 3] = __float_as_uint(fmaf(__uint_as_float(r[i + 3]), a.scale_log2, mk.w * kLog2e));
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < BKV; ++i) {
+            const float mk = kv0 + i < a.Sk ? __ldg(mrow + i) : 0.f;
+            r[i] = __float_as_uint(fmaf(__uint_as_float(r[i]), a.scale_log2, mk * kLog2e));
+          }
+        }
+      }
+      const float sl = kMask ? 1.f : a.scale_log2;
       // four independent chains: the 3-input max has 4-cycle latency, one chain would serialise
       float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
@@ -244,7 +272,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
       const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       // lazy rescale: keep the stale max unless the new one is > 2^8 larger
-      const float m_cand = fmaxf(m, mx * a.scale_log2);
+      const float m_cand = fmaxf(m, mx * sl);
       const bool grow = m_cand - m > kRescaleThreshold;   // true on the first block (m = -inf)
       const float m_use = grow ? m_cand : m;
       const float alpha = grow ? ex2(m - m_use) : 1.f;
@@ -347,7 +375,8 @@ int make_qkv_map(CUtensorMap* m, const void* p, int64_t B, int64_t S, int width,
 
 extern "C" int vst_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse,
                             int Bt, int heads, int Sq, int Sk, int d, int64_t ldq, int64_t ldk,
-                            int64_t ldv, int64_t ldo, int kv_group, float scale, void* stream) {
+                            int64_t ldv, int64_t ldo, int kv_group, float scale, const float* mask,
+                            int64_t mask_sb, int64_t mask_sh, int64_t mask_sq, void* stream) {
   VST_REQUIRE(Bt >= 0 && heads > 0 && Sq >= 0 && Sk > 0, VST_E_BADARG, "attn_fwd: bad shape");
   if (Bt == 0 || Sq == 0) return VST_OK;
   VST_REQUIRE(q && k && v && o, VST_E_BADARG, "attn_fwd: null pointer");
@@ -369,19 +398,26 @@ extern "C" int vst_attn_fwd(const void* q, const void* k, const void* v, void* o
   if (poly < 0) {
     const char* e = getenv("VST_ATTN_POLY");
     poly = e ? atoi(e) : kDefaultPoly;
-    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<kDefaultPoly, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
   }
-  AttnArgs a{lse, Sq, Sk, heads, kv_group, scale * 1.4426950408889634f};
+  const int vec4 = mask && (reinterpret_cast<uintptr_t>(mask) & 15) == 0 && mask_sb % 4 == 0 &&
+                   mask_sh % 4 == 0 && mask_sq % 4 == 0;
+  AttnArgs a{lse, Sq, Sk, heads, kv_group, scale * 1.4426950408889634f, mask, mask_sb, mask_sh, mask_sq, vec4};
   dim3 grid((Sq + NT * BQ - 1) / (NT * BQ), heads, Bt);
   cudaStream_t st = (cudaStream_t)stream;
-  switch (poly) {
-    case 0: attn_fwd_kernel<0><<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tO, a); break;
-    case 3: attn_fwd_kernel<3><<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tO, a); break;
-    case 4: attn_fwd_kernel<4><<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tO, a); break;
-    default: attn_fwd_kernel<2><<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tO, a); break;
+  if (mask) {
+    attn_fwd_kernel<kDefaultPoly, true><<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tO, a);
+  } else {
+    switch (poly) {
+      case 0: attn_fwd_kernel<0, false><<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tO, a); break;
+      case 3: attn_fwd_kernel<3, false><<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tO, a); break;
+      case 4: attn_fwd_kernel<4, false><<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tO, a); break;
+      default: attn_fwd_kernel<2, false><<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tO, a); break;
+    }
   }
   VST_LAUNCH_OK();
   return VST_OK;

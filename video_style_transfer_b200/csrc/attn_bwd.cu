@@ -49,6 +49,8 @@ struct BwdArgs {
   int64_t ldk, ldv;   // row strides (elements) of dk / dv
   int Sq, Sk, heads, kv_group;
   float scale, scale_log2;
+  const float* mask;                  // optional additive mask of the forward (natural-log domain)
+  int64_t mask_sb, mask_sh, mask_sq;  // element strides over (batch, head, query); 0 = broadcast
 };
 
 // ---- D = rowsum(dO . O): 8 lanes per (row, head), 16-byte loads ---------------------------------
@@ -255,6 +257,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       // rows past Sq: LSE = +inf makes P = 0 (their Q / dO rows are zero-filled by TMA)
       const float lse2 = valid ? a.lse[vec_base + q] * 1.4426950408889634f : INFINITY;
       const float dv = valid ? a.dvec[vec_base + q] : 0.f;
+      const float* mrow = a.mask == nullptr ? nullptr
+                              : a.mask + (int64_t)b * a.mask_sb + (int64_t)head * a.mask_sh +
+                                    (int64_t)min(q, a.Sq - 1) * a.mask_sq;
       uint32_t pw[32], dsw[32];
       mbar_wait(sdp_full, i & 1, 30);
       tc_fence_after();
@@ -271,8 +276,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         const int key0 = kv0 + half * 64 + c * 32;
 #pragma unroll
         for (int e = 0; e < 16; ++e) {
-          float p0 = ex2f(fmaf(__uint_as_float(s[2 * e]), a.scale_log2, -lse2));
-          float p1 = ex2f(fmaf(__uint_as_float(s[2 * e + 1]), a.scale_log2, -lse2));
+          float b0 = -lse2, b1 = -lse2;
+          if (mrow != nullptr) {       // warp-uniform branch; P = exp(s * scale + mask - lse)
+            if (key0 + 2 * e < a.Sk) b0 = fmaf(__ldg(mrow + key0 + 2 * e), 1.4426950408889634f, -lse2);
+            if (key0 + 2 * e + 1 < a.Sk) b1 = fmaf(__ldg(mrow + key0 + 2 * e + 1), 1.4426950408889634f, -lse2);
+          }
+          float p0 = ex2f(fmaf(__uint_as_float(s[2 * e]), a.scale_log2, b0));
+          float p1 = ex2f(fmaf(__uint_as_float(s[2 * e + 1]), a.scale_log2, b1));
           if (key0 + 2 * e >= a.Sk) p0 = 0.f;
           if (key0 + 2 * e + 1 >= a.Sk) p1 = 0.f;
           const float d0 = p0 * (__uint_as_float(dp[2 * e]) - dv) * a.scale;
@@ -385,7 +395,8 @@ extern "C" int vst_attn_bwd(const void* q, const void* k, const void* v, const v
                             const void* d_o, const float* lse, void* dq, void* dk, void* dv, int Bt,
                             int heads, int Sq, int Sk, int d, int64_t ldq, int64_t ldk, int64_t ldv,
                             int64_t ldo, int64_t lddo, int64_t lddq, int64_t lddk, int64_t lddv,
-                            int kv_group, float scale, void* workspace, int64_t workspace_bytes,
+                            int kv_group, float scale, const float* mask, int64_t mask_sb,
+                            int64_t mask_sh, int64_t mask_sq, void* workspace, int64_t workspace_bytes,
                             void* stream) {
   VST_REQUIRE(Bt >= 0 && heads > 0 && Sq >= 0 && Sk > 0, VST_E_BADARG, "attn_bwd: bad shape");
   if (Bt == 0 || Sq == 0) return VST_OK;
@@ -450,6 +461,10 @@ extern "C" int vst_attn_bwd(const void* q, const void* k, const void* v, const v
   a.kv_group = kv_group;
   a.scale = scale;
   a.scale_log2 = scale * 1.4426950408889634f;
+  a.mask = mask;
+  a.mask_sb = mask_sb;
+  a.mask_sh = mask_sh;
+  a.mask_sq = mask_sq;
   dim3 grid((Sk + BKV - 1) / BKV, heads, Bt);
   attn_bwd_kernel<<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tdO, a);
   VST_LAUNCH_OK();

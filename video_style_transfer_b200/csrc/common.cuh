@@ -268,11 +268,14 @@ __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
-// arrive on the mbarrier at the same smem offset in CTA `rank` of the cluster
+// arrive on the mbarrier at the same smem offset in CTA `rank` of the cluster.  Default (.release
+// .cta) semantics: the accumulator hand-over is ordered by the tcgen05 fences, no generic-memory
+// data rides on this arrive -- an explicit .release.cluster costs MEMBAR.ALL.GPU + ERRBAR per call
+// (24 % of the epilogue warps' stall samples in the r01 ncu source view of lora_gemm2_kernel).
 __device__ __forceinline__ void mbar_arrive_cluster(uint64_t* bar, uint32_t rank) {
   uint32_t remote;
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(bar)), "r"(rank));
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
 }
 // TMA load whose completion bytes are counted on the LEADER CTA's mbarrier (peer bit cleared)
 __device__ __forceinline__ void tma_load_2d_2sm(void* dst, const CUtensorMap* m, uint64_t* bar,

@@ -52,109 +52,84 @@ struct EpiArgs {
   int N;
   float out_scale;
   int bias_bf16, out_f32, act;
+  int debug;   // VST_GEMM_DEBUG (profiling only; results are wrong when set): 1 = no stores,
+               // 2 = no epilogue work at all, 4 = no MMAs, 8 = no TMA loads
 };
+
+// Bias of a warp's 32-column chunk: lane l holds column l's value (one coalesced load per tile and
+// chunk, issued before the accumulator wait); the row-owning lanes read column j by shuffle.
+__device__ __forceinline__ float bias_lane(const EpiArgs& ep, int col) {
+  if (ep.bias == nullptr || col >= ep.N || (ep.debug & 64)) return 0.f;
+  return ep.bias_bf16 ? __bfloat162float(__ldg(reinterpret_cast<const __nv_bfloat16*>(ep.bias) + col))
+                      : __ldg(reinterpret_cast<const float*>(ep.bias) + col);
+}
 
 // One 32-column chunk of one accumulator row: +bias, act, +residual, *scale, store.
 __device__ __forceinline__ void epilogue_chunk(const EpiArgs& ep, const uint32_t* r, int64_t row,
-                                               bool row_ok, int n0, int c0) {
-  if (row_ok) {
+                                               bool row_ok, int n0, int c0, float bl) {
 #pragma unroll
-    for (int v8 = 0; v8 < 4; ++v8) {
-      const int col = n0 + c0 + v8 * 8;
-      if (col >= ep.N) break;
-      float o[8];
+  for (int v8 = 0; v8 < 4; ++v8) {
+    const int col = n0 + c0 + v8 * 8;
+    float o[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) o[j] = __uint_as_float(r[v8 * 8 + j]);
-      if (ep.bias != nullptr) {
-        if (ep.bias_bf16) {
-          const uint4 bv = __ldg(reinterpret_cast<const uint4*>(
-              reinterpret_cast<const __nv_bfloat16*>(ep.bias) + col));
-          const uint32_t bw[4] = {bv.x, bv.y, bv.z, bv.w};
+    for (int j = 0; j < 8; ++j) o[j] = __uint_as_float(r[v8 * 8 + j]);
+    if (ep.bias != nullptr) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const float2 e = unpack_bf16(bw[j]);
-            o[2 * j] += e.x;
-            o[2 * j + 1] += e.y;
-          }
-        } else {
-          const float4 b0 = __ldg(reinterpret_cast<const float4*>(
-              reinterpret_cast<const float*>(ep.bias) + col));
-          const float4 b1 = __ldg(reinterpret_cast<const float4*>(
-              reinterpret_cast<const float*>(ep.bias) + col + 4));
-          o[0] += b0.x; o[1] += b0.y; o[2] += b0.z; o[3] += b0.w;
-          o[4] += b1.x; o[5] += b1.y; o[6] += b1.z; o[7] += b1.w;
+      for (int j = 0; j < 8; ++j) o[j] += __shfl_sync(0xffffffffu, bl, v8 * 8 + j);
+    }
+    if (!row_ok || col >= ep.N) continue;
+    if (ep.act == 1) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        o[j] = 0.5f * o[j] * (1.f + erff(o[j] * 0.70710678118654752f));  // exact GELU
+    }
+    if (ep.out_f32) {
+      float* dp = reinterpret_cast<float*>(ep.D) + row * ep.ldd + col;
+      if (ep.residual != nullptr) {
+        const float* rp = reinterpret_cast<const float*>(ep.residual) + row * ep.ldr + col;
+        const float4 r0 = *reinterpret_cast<const float4*>(rp);
+        const float4 r1 = *reinterpret_cast<const float4*>(rp + 4);
+        o[0] += r0.x; o[1] += r0.y; o[2] += r0.z; o[3] += r0.w;
+        o[4] += r1.x; o[5] += r1.y; o[6] += r1.z; o[7] += r1.w;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] *= ep.out_scale;
+      *reinterpret_cast<float4*>(dp) = make_float4(o[0], o[1], o[2], o[3]);
+      *reinterpret_cast<float4*>(dp + 4) = make_float4(o[4], o[5], o[6], o[7]);
+    } else {
+      __nv_bfloat16* dp = reinterpret_cast<__nv_bfloat16*>(ep.D) + row * ep.ldd + col;
+      if (ep.residual != nullptr) {
+        const uint4 rv = *reinterpret_cast<const uint4*>(
+            reinterpret_cast<const __nv_bfloat16*>(ep.residual) + row * ep.ldr + col);
+        const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 e = unpack_bf16(rw[j]);
+          o[2 * j] += e.x;
+          o[2 * j + 1] += e.y;
         }
       }
-      if (ep.act == 1) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          o[j] = 0.5f * o[j] * (1.f + erff(o[j] * 0.70710678118654752f));  // exact GELU
-      }
-      if (ep.out_f32) {
-        float* dp = reinterpret_cast<float*>(ep.D) + row * ep.ldd + col;
-        if (ep.residual != nullptr) {
-          const float* rp = reinterpret_cast<const float*>(ep.residual) + row * ep.ldr + col;
-          const float4 r0 = *reinterpret_cast<const float4*>(rp);
-          const float4 r1 = *reinterpret_cast<const float4*>(rp + 4);
-          o[0] += r0.x; o[1] += r0.y; o[2] += r0.z; o[3] += r0.w;
-          o[4] += r1.x; o[5] += r1.y; o[6] += r1.z; o[7] += r1.w;
-        }
-#pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] *= ep.out_scale;
-        *reinterpret_cast<float4*>(dp) = make_float4(o[0], o[1], o[2], o[3]);
-        *reinterpret_cast<float4*>(dp + 4) = make_float4(o[4], o[5], o[6], o[7]);
-      } else {
-        __nv_bfloat16* dp = reinterpret_cast<__nv_bfloat16*>(ep.D) + row * ep.ldd + col;
-        if (ep.residual != nullptr) {
-          const uint4 rv = *reinterpret_cast<const uint4*>(
-              reinterpret_cast<const __nv_bfloat16*>(ep.residual) + row * ep.ldr + col);
-          const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const float2 e = unpack_bf16(rw[j]);
-            o[2 * j] += e.x;
-            o[2 * j + 1] += e.y;
-          }
-        }
-#pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] *= ep.out_scale;
-        uint4 w;
-        w.x = pack_bf16(o[0], o[1]); w.y = pack_bf16(o[2], o[3]);
-        w.z = pack_bf16(o[4], o[5]); w.w = pack_bf16(o[6], o[7]);
-        *reinterpret_cast<uint4*>(dp) = w;
-      }
+      for (int j = 0; j < 8; ++j) o[j] *= ep.out_scale;
+      uint4 w;
+      w.x = pack_bf16(o[0], o[1]); w.y = pack_bf16(o[2], o[3]);
+      w.z = pack_bf16(o[4], o[5]); w.w = pack_bf16(o[6], o[7]);
+      *reinterpret_cast<uint4*>(dp) = w;
     }
   }
 }
 
 // bias / activation / scale of one 32-column chunk, packed to bf16 (TMA-store path: no residual)
-__device__ __forceinline__ void epilogue_pack(const EpiArgs& ep, const uint32_t* r, int col0,
+__device__ __forceinline__ void epilogue_pack(const EpiArgs& ep, const uint32_t* r, float bl,
                                               uint32_t* w) {
 #pragma unroll
   for (int v8 = 0; v8 < 4; ++v8) {
-    const int col = col0 + v8 * 8;
     float o[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) o[j] = __uint_as_float(r[v8 * 8 + j]);
-    if (ep.bias != nullptr && col < ep.N) {
-      if (ep.bias_bf16) {
-        const uint4 bv = __ldg(reinterpret_cast<const uint4*>(
-            reinterpret_cast<const __nv_bfloat16*>(ep.bias) + col));
-        const uint32_t bw[4] = {bv.x, bv.y, bv.z, bv.w};
+    if (ep.bias != nullptr) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const float2 e = unpack_bf16(bw[j]);
-          o[2 * j] += e.x;
-          o[2 * j + 1] += e.y;
-        }
-      } else {
-        const float4 b0 = __ldg(reinterpret_cast<const float4*>(
-            reinterpret_cast<const float*>(ep.bias) + col));
-        const float4 b1 = __ldg(reinterpret_cast<const float4*>(
-            reinterpret_cast<const float*>(ep.bias) + col + 4));
-        o[0] += b0.x; o[1] += b0.y; o[2] += b0.z; o[3] += b0.w;
-        o[4] += b1.x; o[5] += b1.y; o[6] += b1.z; o[7] += b1.w;
-      }
+      for (int j = 0; j < 8; ++j) o[j] += __shfl_sync(0xffffffffu, bl, v8 * 8 + j);
     }
     if (ep.act == 1) {
 #pragma unroll
@@ -170,25 +145,58 @@ __device__ __forceinline__ void epilogue_pack(const EpiArgs& ep, const uint32_t*
 // lane quarter e % 4 and every second 32-column chunk.  bf16 output without residual goes
 // TMEM -> registers -> 64B-swizzled smem chunk -> TMA store (full-line, asynchronous writes; the
 // store clips rows >= M and columns >= N); otherwise rows are written directly.
+// Latency hiding (r01 VST_GEMM_DEBUG measurements, profiles/gemm_r01_notes.md): the per-chunk bias
+// loads used to sit on the critical path (L0 temporal projection: 18 of 75 us), so the bias of
+// the warp's chunks is fetched by `epilogue_bias` BEFORE the accumulator wait, and the TMEM load of
+// chunk i+1 is in flight while chunk i is packed and stored.  `release` is called as soon as the
+// last TMEM load has landed, so the tensor pipe gets the accumulator back before the stores.
 template <int BN>
+struct EpiBias {
+  static constexpr int kMax = (BN + 63) / 64;
+  float v[kMax];
+};
+
+template <int BN>
+__device__ __forceinline__ void epilogue_bias(const EpiArgs& ep, int n0, int ewarp, int lane,
+                                              EpiBias<BN>& b) {
+  const int half = ewarp >> 2;
+#pragma unroll
+  for (int i = 0; i < EpiBias<BN>::kMax; ++i) b.v[i] = bias_lane(ep, n0 + half * 32 + i * 64 + lane);
+}
+
+template <int BN, typename Release>
 __device__ __forceinline__ void epilogue_tile(const EpiArgs& ep, const CUtensorMap* tmD,
                                               uint32_t tacc, int m0, int n0, int ewarp, int lane,
-                                              uint8_t* stage_out, int& buf) {
+                                              uint8_t* stage_out, int& buf, const EpiBias<BN>& bias,
+                                              Release release) {
   // a warp can only read the TMEM lane quarter given by its hardware warp id % 4 (warps 2..9)
   const int quarter = (ewarp + 2) & 3, half = ewarp >> 2;
   const int64_t row = (int64_t)m0 + quarter * 32 + lane;
   const bool row_ok = row < ep.M;
   const uint32_t taddr = tacc + (uint32_t(quarter * 32) << 16);
-  const bool via_tma = ep.residual == nullptr && !ep.out_f32;
-#pragma unroll 1
-  for (int c0 = half * 32; c0 < BN; c0 += 64) {
-    uint32_t r[32];
-    tmem_ld32(taddr + c0, r);
+  const bool via_tma = ep.residual == nullptr && !ep.out_f32 && !(ep.debug & 16);   // 16: direct stores
+  constexpr int kMax = EpiBias<BN>::kMax;
+  const int nch = (BN - half * 32 + 63) / 64;          // chunks of this warp: c0 = half*32 + 64 i
+  uint32_t r[2][32];
+  tmem_ld32(taddr + half * 32, r[0]);
+#pragma unroll
+  for (int i = 0; i < kMax; ++i) {
+    if (i >= nch) break;
+    const int c0 = half * 32 + i * 64;
     tmem_ld_wait();
+    if (i + 1 < nch) {
+      tmem_ld32(taddr + c0 + 64, r[(i + 1) & 1]);
+    } else {
+      tc_fence_before();
+      __syncwarp();
+      release();
+    }
+    const uint32_t* rc = r[i & 1];
     if (n0 + c0 >= ep.N) continue;
+    if (ep.debug & 2) continue;
     if (via_tma) {
       uint32_t w[16];
-      epilogue_pack(ep, r, n0 + c0, w);
+      epilogue_pack(ep, rc, bias.v[i], w);
       uint8_t* sbuf = stage_out + buf * kStageOutBytes;
       if (lane == 0) tma_store_wait_read<1>();      // the store that last used this buffer is done
       __syncwarp();
@@ -198,15 +206,15 @@ __device__ __forceinline__ void epilogue_tile(const EpiArgs& ep, const CUtensorM
       for (int q = 0; q < 4; ++q)
         *reinterpret_cast<uint4*>(srow + ((q ^ sx) * 16)) =
             make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
-      fence_proxy_async_smem();
+      if (!(ep.debug & 32)) fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) {
+      if (lane == 0 && !(ep.debug & 1)) {
         tma_store_2d(tmD, sbuf, n0 + c0, m0 + quarter * 32);
         tma_store_commit();
       }
       buf ^= 1;
     } else {
-      epilogue_chunk(ep, r, row, row_ok, n0, c0);
+      epilogue_chunk(ep, rc, row, row_ok, n0, c0, bias.v[i]);
     }
   }
 }
@@ -319,12 +327,13 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
     if (lane == 0) tma_prefetch_desc(&tmD);
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
+      EpiBias<BN> bias;
+      epilogue_bias<BN>(ep, n0, ewarp, lane, bias);
       mbar_wait(&acc_full[acc], acc_phase, 4);
       tc_fence_after();
-      epilogue_tile<BN>(ep, &tmD, tmem_base + acc * C::kAccStride, m0, n0, ewarp, lane, my_out, buf);
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&acc_empty[acc]);
+      uint64_t* done = &acc_empty[acc];
+      epilogue_tile<BN>(ep, &tmD, tmem_base + acc * C::kAccStride, m0, n0, ewarp, lane, my_out, buf, bias,
+                        [&]() { if (lane == 0) mbar_arrive(done); });
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
     if (lane == 0) tma_store_wait<0>();
@@ -419,6 +428,11 @@ lora_gemm2_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constan
           mbar_wait(&empty[stage], phase ^ 1, 1);
           uint8_t* sa = smem + stage * C::kStageBytes;
           uint8_t* sb = sa + BM * BK * 2;
+          if (ep.debug & 8) {
+            if (leader) mbar_arrive(&full[stage]);
+            if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+            continue;
+          }
           if (leader) mbar_arrive_expect_tx(&full[stage], 2 * C::kStageBytes);
           if (kb < nk1) {
             tma_load_2d_2sm(sa, &tmA1, &full[stage], kb * BK, m0);
@@ -451,9 +465,11 @@ lora_gemm2_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constan
           const uint32_t sb = sa + BM * BK * 2;
           const uint64_t da = umma_desc_sw128(sa, 1024);
           const uint64_t db = umma_desc_sw128(sb, 1024);
+          if (!(ep.debug & 4)) {
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k)
-            umma_bf16_ss_2sm(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            for (int k = 0; k < BK / 16; ++k)
+              umma_bf16_ss_2sm(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+          }
           umma_commit_2sm(&empty[stage]);
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
@@ -471,12 +487,13 @@ lora_gemm2_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constan
     if (lane == 0) tma_prefetch_desc(&tmD);
     for (int tile = cluster_id; tile < total_tiles; tile += n_clusters) {
       const int m0 = (tile / n_tiles) * (2 * BM) + rank * BM, n0 = (tile % n_tiles) * BN;
+      EpiBias<BN> bias;
+      epilogue_bias<BN>(ep, n0, ewarp, lane, bias);
       mbar_wait(&acc_full[acc], acc_phase, 4);
       tc_fence_after();
-      epilogue_tile<BN>(ep, &tmD, tmem_base + acc * C::kAccStride, m0, n0, ewarp, lane, my_out, buf);
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(&acc_empty[acc], 0);
+      uint64_t* done = &acc_empty[acc];
+      epilogue_tile<BN>(ep, &tmD, tmem_base + acc * C::kAccStride, m0, n0, ewarp, lane, my_out, buf, bias,
+                        [&]() { if (lane == 0) mbar_arrive_cluster(done, 0); });
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
     if (lane == 0) tma_store_wait<0>();
@@ -628,8 +645,10 @@ extern "C" int vst_lora_gemm(const void* A1, int64_t lda1, const void* B1, int64
                   (reinterpret_cast<uintptr_t>(residual) & 15) == 0 &&
                   (reinterpret_cast<uintptr_t>(bias) & 15) == 0,
               VST_E_UNSUPPORTED, "lora_gemm: D/residual/bias must be 16-byte aligned");
+  static int debug = -1;
+  if (debug < 0) { const char* e = getenv("VST_GEMM_DEBUG"); debug = e ? atoi(e) : 0; }
   EpiArgs ep{bias, residual, D, ldr, ldd, M, N, out_scale, bias_dtype == VST_BF16,
-             out_dtype == VST_F32, act};
+             out_dtype == VST_F32, act, debug};
   cudaStream_t st = (cudaStream_t)stream;
   VST_REQUIRE(k2_group_n >= 0 && (k2_group_n == 0 || K2 > 0), VST_E_BADARG, "lora_gemm: bad k2_group_n");
   const int gn = (K2 > 0 && k2_group_n > 0) ? k2_group_n : 0;

@@ -389,18 +389,41 @@ def colsum(x: torch.Tensor, alpha: float = 1.0) -> torch.Tensor:
 
 
 # ---- a2 -------------------------------------------------------------------------------------------
+def _mask_args(mask: Optional[torch.Tensor], bt: int, heads: int, sq: int, sk: int):
+    """(tensor kept alive, pointer, batch / head / query strides) of an additive attention mask
+    broadcastable to (Bt, heads, Sq, Sk); bool masks follow F.scaled_dot_product_attention
+    (False = -inf)."""
+    if mask is None:
+        return None, None, 0, 0, 0
+    m = mask.detach()
+    if m.dtype == torch.bool:
+        m = torch.zeros(m.shape, dtype=torch.float32, device=m.device).masked_fill_(~m, float("-inf"))
+    while m.dim() < 4:
+        m = m.unsqueeze(0)
+    if m.dim() != 4 or m.shape[-1] != sk or any(a not in (1, b) for a, b in zip(m.shape[:3], (bt, heads, sq))):
+        raise ValueError(f"attention mask {tuple(mask.shape)} does not broadcast to {(bt, heads, sq, sk)}")
+    if m.dtype != torch.float32 or m.stride(3) != 1:
+        m = m.float().contiguous()
+    _cuda(m)
+    st = [0 if m.shape[i] == 1 else m.stride(i) for i in range(3)]
+    return m, m.data_ptr(), st[0], st[1], st[2]
+
+
 def attn_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int,
-             scale: Optional[float] = None, return_lse: bool = False):
+             scale: Optional[float] = None, return_lse: bool = False,
+             mask: Optional[torch.Tensor] = None):
     """q (Bt,Sq,h*64), k/v (Bk,Sk,h*64) bf16, Bt % Bk == 0 (batch b reads kv batch b//(Bt/Bk)).
-    Differentiable: the backward is vst_attn_bwd (see _autograd.AttnFn)."""
+    mask: optional additive (or bool) mask broadcastable to (Bt, heads, Sq, Sk).
+    Differentiable in q, k, v: the backward is vst_attn_bwd (see _autograd.AttnFn)."""
     if _needs_grad(q, k, v) and not return_lse:
         from ._autograd import AttnFn
-        return AttnFn.apply(q, k, v, heads, scale)
-    return attn_fwd_raw(q, k, v, heads, scale, return_lse)
+        return AttnFn.apply(q, k, v, heads, scale, mask)
+    return attn_fwd_raw(q, k, v, heads, scale, return_lse, mask)
 
 
 def attn_fwd_raw(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int,
-                 scale: Optional[float] = None, return_lse: bool = False):
+                 scale: Optional[float] = None, return_lse: bool = False,
+                 mask: Optional[torch.Tensor] = None):
     q, k, v = q.detach(), k.detach(), v.detach()
     _cuda(q, k, v)
     bt, sq, c = q.shape
@@ -412,9 +435,11 @@ def attn_fwd_raw(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int,
     assert v.shape == k.shape and bt % bk == 0
     o = torch.empty((bt, sq, c), dtype=torch.bfloat16, device=q.device)
     lse = torch.empty((bt, heads, sq), dtype=torch.float32, device=q.device) if return_lse else None
+    mk, mptr, msb, msh, msq = _mask_args(mask, bt, heads, sq, sk)
     check(lib.vst_attn_fwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), _ptr(lse), bt,
                            heads, sq, sk, d, q.stride(1), k.stride(1), v.stride(1), o.stride(1),
-                           bt // bk, scale if scale is not None else 1.0 / math.sqrt(d), _stream()),
+                           bt // bk, scale if scale is not None else 1.0 / math.sqrt(d), mptr, msb,
+                           msh, msq, _stream()),
           "vst_attn_fwd")
     return (o, lse) if return_lse else o
 
@@ -424,7 +449,8 @@ def _bsc(t: torch.Tensor, name: str):
         raise ValueError(f"attn_bwd: {name} must be bf16 (B,S,C) with contiguous C and dense (B,S)")
 
 
-def attn_bwd(q, k, v, o, d_o, lse, heads: int, scale: Optional[float] = None):
+def attn_bwd(q, k, v, o, d_o, lse, heads: int, scale: Optional[float] = None,
+             mask: Optional[torch.Tensor] = None):
     """(dq, dk, dv) of attn_fwd; dk / dv have the (Bk, Sk, C) shape of k / v."""
     _cuda(q, k, v, o, d_o, lse)
     bt, sq, c = q.shape
@@ -439,11 +465,12 @@ def attn_bwd(q, k, v, o, d_o, lse, heads: int, scale: Optional[float] = None):
     wsb = lib.vst_attn_bwd_workspace_bytes(bt, heads, sq, sk, bt // bk)
     ws = torch.empty(wsb + 256, dtype=torch.uint8, device=q.device)
     off = (-ws.data_ptr()) % 256
+    mk, mptr, msb, msh, msq = _mask_args(mask, bt, heads, sq, sk)
     check(lib.vst_attn_bwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), d_o.data_ptr(),
                            lse.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), bt, heads,
                            sq, sk, d, q.stride(1), k.stride(1), v.stride(1), o.stride(1),
                            d_o.stride(1), dq.stride(1), dk.stride(1), dv.stride(1), bt // bk,
-                           scale if scale is not None else 1.0 / math.sqrt(d),
+                           scale if scale is not None else 1.0 / math.sqrt(d), mptr, msb, msh, msq,
                            ws.data_ptr() + off, wsb, _stream()), "vst_attn_bwd")
     return dq, dk, dv
 
