@@ -24,6 +24,7 @@ extern "C" {
 
 #define VST_ACT_NONE 0
 #define VST_ACT_GELU 1
+#define VST_ACT_GEGLU 2
 
 #define VST_OK 0
 #define VST_E_BADARG (-1)
@@ -87,7 +88,10 @@ int vst_temporal_attn_fwd(const void* q, const void* k, const void* v, void* o, 
 
 /* ---- a3/a4/a5/a7: fused LoRA GEMM ----------------------------------------------------------
  * D[M,N] = (act(A1[M,K1] * B1[N,K1]^T + A2[M,K2] * B2[N,K2]^T + bias[N]) + residual[M,N]) * out_scale
- * act: VST_ACT_NONE, or VST_ACT_GELU (exact erf GELU: temporal_transformer.py:53-55).
+ * act: VST_ACT_NONE, VST_ACT_GELU (exact erf GELU: temporal_transformer.py:53-55), or
+ * VST_ACT_GEGLU (diffusers FeedForward("geglu"), un-vendored: B1 is (2N, K1) = [W_hidden ; W_gate],
+ * bias has 2N entries, D[:, j] = (x W_hidden^T + b)[j] * gelu((x W_gate^T + b)[N + j]); the
+ * 2N-wide pre-activation stays in TMEM.  N % 128 == 0, bf16 output, no low-rank pair / residual).
  * bf16 operands, fp32 accumulation in TMEM (tcgen05), bf16 or fp32 output.
  * It is the single GEMM behind
  *   unziplora_unet/lora_linear.py:74-81 + unziplora_linear_layer.py:298-346 (A1=x, B1=W,

@@ -238,3 +238,74 @@ def test_lora_gemm_identity_row_col_mapping(ops, m, n):
     cols = torch.arange(n).float()[None, :].expand(m, n).to(torch.bfloat16).cuda().contiguous()
     assert torch.equal(ops.lora_gemm(rows, eye), rows)
     assert torch.equal(ops.lora_gemm(cols, eye), cols)
+
+
+# ---- a2 with the optional additive mask (attention_processor.py:46-48) ---------------------------------
+@pytest.mark.parametrize("bt,bk,heads,sq,sk,mshape", [
+    (2, 2, 2, 128, 128, (2, 1, 1, 128)),        # key-padding mask, broadcast over heads and queries
+    (4, 2, 2, 200, 77, (4, 2, 1, 77)),          # per head, ragged Sk (scalar-load tail path)
+    (2, 2, 3, 256, 384, (2, 3, 256, 384)),      # full (b, h, q, k) mask, 16-byte aligned rows
+    (1, 1, 2, 64, 300, (1, 1, 64, 300)),        # per query, several key blocks + tail
+])
+def test_attn_fwd_additive_mask(ops, hp, bt, bk, heads, sq, sk, mshape):
+    torch.manual_seed(11)
+    c = heads * 64
+    q = torch.randn(bt, sq, c).to(torch.bfloat16).cuda()
+    k = torch.randn(bk, sk, c).to(torch.bfloat16).cuda()
+    v = torch.randn(bk, sk, c).to(torch.bfloat16).cuda()
+    mask = torch.randn(mshape) * 2.0
+    mask[..., ::5] = -1e4                      # some keys (nearly) masked out
+    mask[..., 0] = 0.0                         # never a fully masked row
+    o, lse = ops.attn_fwd(q, k, v, heads, return_lse=True, mask=mask.cuda())
+    g = bt // bk
+    sp = lambda t, b, s: t.cpu().float().reshape(b, s, heads, 64).transpose(1, 2)
+    kk, vv, qq = sp(k, bk, sk).repeat_interleave(g, 0), sp(v, bk, sk).repeat_interleave(g, 0), sp(q, bt, sq)
+    want = hp.sdpa(qq, kk, vv, mask).transpose(1, 2).reshape(bt, sq, c)
+    assert rel_err(o, want) < REL_TOL
+    want_lse = torch.logsumexp(qq @ kk.transpose(-1, -2) / 8.0 + mask, dim=-1)
+    assert torch.allclose(lse.cpu(), want_lse, atol=2e-2, rtol=1e-3)
+    # bool masks follow F.scaled_dot_product_attention: False = excluded
+    keep = torch.rand(bt, 1, 1, sk) > 0.3
+    keep[..., 0] = True
+    o2 = ops.attn_fwd(q, k, v, heads, mask=keep.cuda())
+    add = torch.zeros(keep.shape).masked_fill(~keep, float("-inf"))
+    want2 = hp.sdpa(qq, kk, vv, add).transpose(1, 2).reshape(bt, sq, c)
+    assert rel_err(o2, want2) < REL_TOL
+
+
+def test_attn_bwd_additive_mask(ops):
+    torch.manual_seed(12)
+    bt, heads, sq, sk = 2, 2, 200, 136
+    c = heads * 64
+    q, k, v, d_o = (torch.randn(bt, s, c).to(torch.bfloat16).cuda().requires_grad_(True)
+                    for s in (sq, sk, sk, sq))
+    mask = (torch.randn(bt, 1, 1, sk) * 2.0).cuda()
+    o = ops.attn_fwd(q, k, v, heads, mask=mask)
+    o.backward(d_o.detach())
+    qr, kr, vr = (t.detach().float().cpu().requires_grad_(True) for t in (q, k, v))
+    sp = lambda t, s: t.reshape(bt, s, heads, 64).transpose(1, 2)
+    ref = torch.nn.functional.scaled_dot_product_attention(sp(qr, sq), sp(kr, sk), sp(vr, sk),
+                                                           attn_mask=mask.cpu())
+    ref.transpose(1, 2).reshape(bt, sq, c).backward(d_o.detach().float().cpu())
+    for got, want, nm in ((q.grad, qr.grad, "dq"), (k.grad, kr.grad, "dk"), (v.grad, vr.grad, "dv")):
+        assert rel_err(got, want) < 2e-2, nm
+
+
+# ---- §8f-1: GEGLU in the GEMM epilogue (VST_ACT_GEGLU) ------------------------------------------------
+@pytest.mark.parametrize("m,k,inner", [(300, 320, 1280), (4096, 640, 2560), (1000, 64, 128), (16384, 1280, 5120)])
+@pytest.mark.parametrize("bias_dtype", [torch.bfloat16, torch.float32, None])
+def test_lora_gemm_geglu_epilogue(ops, m, k, inner, bias_dtype):
+    torch.manual_seed(13)
+    x = torch.randn(m, k).to(torch.bfloat16).cuda()
+    w = (torch.randn(2 * inner, k) / k ** 0.5).to(torch.bfloat16).cuda()
+    b = None if bias_dtype is None else torch.randn(2 * inner).to(bias_dtype).cuda()
+    got = ops.lora_gemm(x, w, bias=b, act="geglu")
+    assert got.shape == (m, inner)
+    z = x.float() @ w.float().t()
+    if b is not None:
+        z = z + b.float()
+    want = z[:, :inner] * torch.nn.functional.gelu(z[:, inner:])
+    assert rel_err(got, want) < REL_TOL
+    # and against the two-kernel path it replaces (bf16-rounded pre-activation)
+    two = ops.geglu(ops.lora_gemm(x, w, bias=b))
+    assert rel_err(got, two) < REL_TOL

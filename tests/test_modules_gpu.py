@@ -260,3 +260,53 @@ def test_motion_module_vs_oracle(c, hw, f, lora):
     y = mm.cuda()(x.cuda().to(torch.bfloat16), num_frames=f)
     assert y.shape == x.shape and y.dtype == torch.bfloat16
     assert rel(y, want) < 2 * TOL
+
+
+def test_attn_processor_with_attention_mask_vs_oracle():
+    """attention_mask path of the processor (reference :46-48): a key-padding mask over the text
+    tokens, prepared by the diffusers-protocol ``attn.prepare_attention_mask``."""
+    from oracle import processor as op
+    from video_style_transfer_b200.animatediff.attention_processor import AnimateDiffAttnProcessor2_0
+    from video_style_transfer_b200.unziplora_unet.lora_linear import LoRACompatibleLinear
+    from video_style_transfer_b200.unziplora_unet.unziplora_linear_layer import UnZipLoRALinearLayerInfer
+    torch.manual_seed(21)
+    C, heads, ctx, nb, s_, r = 128, 2, 96, 4, 64, 16
+
+    def mk(i, o, bias):
+        lin = LoRACompatibleLinear(i, o, bias=bias)
+        lay = UnZipLoRALinearLayerInfer(i, o, r, ["content", "style"])
+        with torch.no_grad():
+            lay.merge_content.uniform_(0, 1)
+            lay.merge_style.uniform_(0, 1)
+        lin.set_lora_layer(lay)
+        return lin
+
+    def oproj(l):
+        ll, d = l.lora_layer, l.lora_layer.lora_matrix_dic
+        f = lambda t: None if t is None else t.detach().float().cpu()
+        return op.UnzipProj(f(l.weight), f(l.bias), f(d["content_down"].weight), f(d["content_up"].weight),
+                            f(d["style_down"].weight), f(d["style_up"].weight), f(ll.merge_content),
+                            f(ll.merge_style))
+
+    def prepare(mask, target_length, batch_size):          # diffusers Attention.prepare_attention_mask
+        if mask.shape[0] < batch_size * heads:
+            mask = mask.repeat_interleave(heads, dim=0)
+        return mask
+
+    attn = types.SimpleNamespace(
+        spatial_norm=None, group_norm=None, norm_cross=False, heads=heads, prepare_attention_mask=prepare,
+        to_q=mk(C, C, False), to_k=mk(ctx, C, False), to_v=mk(ctx, C, False),
+        to_out=torch.nn.ModuleList([mk(C, C, True), torch.nn.Dropout(0.0)]),
+        residual_connection=False, rescale_output_factor=1.0)
+    P = op.SpatialAttnParams(heads, oproj(attn.to_q), oproj(attn.to_k), oproj(attn.to_v), oproj(attn.to_out[0]))
+    hs = torch.randn(nb, s_, C)
+    ehs = torch.randn(nb, 77, ctx)
+    mask = torch.zeros(nb, 1, 77)
+    mask[:, :, 40:] = -10000.0                              # padded text tokens
+    m4 = mask.repeat_interleave(heads, dim=0).view(nb, heads, 1, 77)
+    want = op.animatediff_attn_processor(P, hs, ehs, attention_mask=m4)
+    for m in (attn.to_q, attn.to_k, attn.to_v, attn.to_out):
+        m.cuda().to(torch.bfloat16)
+    y = AnimateDiffAttnProcessor2_0()(attn, hs.cuda().to(torch.bfloat16), ehs.cuda().to(torch.bfloat16),
+                                      attention_mask=mask.cuda())
+    assert rel(y, want) < 2 * TOL

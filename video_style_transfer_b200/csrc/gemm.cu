@@ -58,8 +58,8 @@ struct EpiArgs {
 
 // Bias of a warp's 32-column chunk: lane l holds column l's value (one coalesced load per tile and
 // chunk, issued before the accumulator wait); the row-owning lanes read column j by shuffle.
-__device__ __forceinline__ float bias_lane(const EpiArgs& ep, int col) {
-  if (ep.bias == nullptr || col >= ep.N || (ep.debug & 64)) return 0.f;
+__device__ __forceinline__ float bias_lane(const EpiArgs& ep, int col, int limit) {
+  if (ep.bias == nullptr || col >= limit || (ep.debug & 64)) return 0.f;
   return ep.bias_bf16 ? __bfloat162float(__ldg(reinterpret_cast<const __nv_bfloat16*>(ep.bias) + col))
                       : __ldg(reinterpret_cast<const float*>(ep.bias) + col);
 }
@@ -161,7 +161,7 @@ __device__ __forceinline__ void epilogue_bias(const EpiArgs& ep, int n0, int ewa
                                               EpiBias<BN>& b) {
   const int half = ewarp >> 2;
 #pragma unroll
-  for (int i = 0; i < EpiBias<BN>::kMax; ++i) b.v[i] = bias_lane(ep, n0 + half * 32 + i * 64 + lane);
+  for (int i = 0; i < EpiBias<BN>::kMax; ++i) b.v[i] = bias_lane(ep, n0 + half * 32 + i * 64 + lane, ep.N);
 }
 
 template <int BN, typename Release>
@@ -216,6 +216,83 @@ __device__ __forceinline__ void epilogue_tile(const EpiArgs& ep, const CUtensorM
     } else {
       epilogue_chunk(ep, rc, row, row_ok, n0, c0, bias.v[i]);
     }
+  }
+}
+
+// ---- VST_ACT_GEGLU: D[:, j] = (acc[:, j] + bias[j]) * gelu(acc[:, BN/2 + j] + bias[N + j]) ----------
+// The tile's B rows are [W_hidden[n0 : n0+BN/2] ; W_gate[n0 : n0+BN/2]] (the leader CTA loads the
+// hidden half, its peer the gate half), so value and gate of an output column sit BN/2 accumulator
+// columns apart and the 2*inner-wide pre-activation never goes to HBM (diffusers GEGLU:
+// hidden, gate = proj(x).chunk(2); hidden * gelu(gate)).
+// erf by Abramowitz-Stegun 7.1.26 (|err| < 1.5e-7, below fp32 accumulation noise; the products are
+// rounded to bf16): 1 MUFU.RCP + 1 MUFU.EX2 + 9 FMA-pipe ops instead of erff's ~25.
+__device__ __forceinline__ float gelu_as(float x) {
+  const float z = fabsf(x) * 0.70710678118654752f;
+  float t;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.f)));
+  float p = fmaf(1.061405429f, t, -1.453152027f);
+  p = fmaf(p, t, 1.421413741f);
+  p = fmaf(p, t, -0.284496736f);
+  p = fmaf(p, t, 0.254829592f);
+  float e;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-1.4426950408889634f * z * z));
+  const float erfa = fmaf(-p * t, e, 1.f);            // erf(|x| / sqrt 2)
+  return 0.5f * fmaf(fabsf(x), erfa, x);              // 0.5 x (1 + sign(x) erf) = 0.5 (x + |x| erf)
+}
+
+template <int BN, typename Release>
+__device__ __forceinline__ void epilogue_tile_geglu(const EpiArgs& ep, const CUtensorMap* tmD,
+                                                    uint32_t tacc, int m0, int n0, int ewarp, int lane,
+                                                    uint8_t* stage_out, int& buf, const float* bh,
+                                                    const float* bg, Release release) {
+  constexpr int HALF = BN / 2;
+  constexpr int kMax = (HALF + 63) / 64;
+  const int quarter = (ewarp + 2) & 3, half = ewarp >> 2;
+  const uint32_t taddr = tacc + (uint32_t(quarter * 32) << 16);
+  const int nch = (HALF - half * 32 + 63) / 64;
+#pragma unroll
+  for (int i = 0; i < kMax; ++i) {
+    if (i >= nch) break;
+    const int c0 = half * 32 + i * 64;
+    uint32_t rh[32], rg[32];
+    tmem_ld32(taddr + c0, rh);
+    tmem_ld32(taddr + HALF + c0, rg);
+    tmem_ld_wait();
+    if (i + 1 >= nch) {
+      tc_fence_before();
+      __syncwarp();
+      release();
+    }
+    if (n0 + c0 >= ep.N) continue;
+    uint32_t w[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      float h0 = __uint_as_float(rh[2 * j]), h1 = __uint_as_float(rh[2 * j + 1]);
+      float g0 = __uint_as_float(rg[2 * j]), g1 = __uint_as_float(rg[2 * j + 1]);
+      if (ep.bias != nullptr) {
+        h0 += __shfl_sync(0xffffffffu, bh[i], 2 * j);
+        h1 += __shfl_sync(0xffffffffu, bh[i], 2 * j + 1);
+        g0 += __shfl_sync(0xffffffffu, bg[i], 2 * j);
+        g1 += __shfl_sync(0xffffffffu, bg[i], 2 * j + 1);
+      }
+      w[j] = pack_bf16(h0 * gelu_as(g0) * ep.out_scale, h1 * gelu_as(g1) * ep.out_scale);
+    }
+    uint8_t* sbuf = stage_out + buf * kStageOutBytes;
+    if (lane == 0) tma_store_wait_read<1>();
+    __syncwarp();
+    uint8_t* srow = sbuf + lane * 64;
+    const int sx = (lane >> 1) & 3;
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      *reinterpret_cast<uint4*>(srow + ((q ^ sx) * 16)) =
+          make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+      tma_store_2d(tmD, sbuf, n0 + c0, m0 + quarter * 32);
+      tma_store_commit();
+    }
+    buf ^= 1;
   }
 }
 
@@ -422,8 +499,10 @@ lora_gemm2_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constan
       uint32_t phase = 0;
       for (int tile = cluster_id; tile < total_tiles; tile += n_clusters) {
         const int m0 = (tile / n_tiles) * (2 * BM) + rank * BM;
-        const int n0 = (tile % n_tiles) * BN;
-        const int nb = n0 + rank * C::kBRows;          // this CTA's half of the B tile
+        const bool geglu = ep.act == 2;
+        const int n0 = (tile % n_tiles) * (geglu ? BN / 2 : BN);
+        // this CTA's half of the B tile (GEGLU: leader = hidden rows, peer = gate rows N + n0..)
+        const int nb = geglu ? n0 + rank * ep.N : n0 + rank * C::kBRows;
         for (int kb = 0; kb < nk; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1, 1);
           uint8_t* sa = smem + stage * C::kStageBytes;
@@ -486,14 +565,31 @@ lora_gemm2_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constan
     uint32_t acc_phase = 0;
     if (lane == 0) tma_prefetch_desc(&tmD);
     for (int tile = cluster_id; tile < total_tiles; tile += n_clusters) {
-      const int m0 = (tile / n_tiles) * (2 * BM) + rank * BM, n0 = (tile % n_tiles) * BN;
+      const int m0 = (tile / n_tiles) * (2 * BM) + rank * BM;
+      uint64_t* done = &acc_empty[acc];
+      auto release = [&]() { if (lane == 0) mbar_arrive_cluster(done, 0); };
+      if (ep.act == 2) {
+        const int n0 = (tile % n_tiles) * (BN / 2);
+        float bh[(BN / 2 + 63) / 64], bg[(BN / 2 + 63) / 64];
+#pragma unroll
+        for (int i = 0; i < (BN / 2 + 63) / 64; ++i) {
+          const int col = n0 + (ewarp >> 2) * 32 + i * 64 + lane;
+          bh[i] = bias_lane(ep, col, ep.N);
+          bg[i] = bias_lane(ep, col < ep.N ? ep.N + col : 2 * ep.N, 2 * ep.N);
+        }
+        mbar_wait(&acc_full[acc], acc_phase, 4);
+        tc_fence_after();
+        epilogue_tile_geglu<BN>(ep, &tmD, tmem_base + acc * C::kAccStride, m0, n0, ewarp, lane, my_out, buf,
+                                bh, bg, release);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        continue;
+      }
+      const int n0 = (tile % n_tiles) * BN;
       EpiBias<BN> bias;
       epilogue_bias<BN>(ep, n0, ewarp, lane, bias);
       mbar_wait(&acc_full[acc], acc_phase, 4);
       tc_fence_after();
-      uint64_t* done = &acc_empty[acc];
-      epilogue_tile<BN>(ep, &tmD, tmem_base + acc * C::kAccStride, m0, n0, ewarp, lane, my_out, buf, bias,
-                        [&]() { if (lane == 0) mbar_arrive_cluster(done, 0); });
+      epilogue_tile<BN>(ep, &tmD, tmem_base + acc * C::kAccStride, m0, n0, ewarp, lane, my_out, buf, bias, release);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
     if (lane == 0) tma_store_wait<0>();
@@ -570,8 +666,9 @@ int launch2(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, 
   using C = Cfg2<BN>;
   CUtensorMap tA1, tB1, tA2, tB2;
   int rc;
+  const bool geglu = ep.act == 2;     // B1 = [W_hidden ; W_gate]: 2N rows
   if ((rc = make_operand_map(&tA1, A1, ep.M, K1, lda1, BM))) return rc;
-  if ((rc = make_operand_map(&tB1, B1, ep.N, K1, ldb1, C::kBRows))) return rc;
+  if ((rc = make_operand_map(&tB1, B1, geglu ? 2 * ep.N : ep.N, K1, ldb1, C::kBRows))) return rc;
   if (K2 > 0) {
     const int groups = k2_group_n > 0 ? (ep.N + k2_group_n - 1) / k2_group_n : 1;
     if ((rc = make_operand_map(&tA2, A2, ep.M, K2 * groups, lda2, BM))) return rc;
@@ -589,7 +686,7 @@ int launch2(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, 
                                      C::kSmemBytes));
     configured = true;
   }
-  const int m_tiles = (int)((ep.M + 2 * BM - 1) / (2 * BM)), n_tiles = ep.N / BN;
+  const int m_tiles = (int)((ep.M + 2 * BM - 1) / (2 * BM)), n_tiles = geglu ? ep.N / (BN / 2) : ep.N / BN;
   const int64_t tiles = (int64_t)m_tiles * n_tiles;
   const int pairs = vst_sm_count() / 2;
   const int grid = 2 * (int)(tiles < pairs ? tiles : pairs);
@@ -637,7 +734,11 @@ extern "C" int vst_lora_gemm(const void* A1, int64_t lda1, const void* B1, int64
   VST_REQUIRE(lda1 % 8 == 0 && ldb1 % 8 == 0 && (K2 == 0 || (lda2 % 8 == 0 && ldb2 % 8 == 0)),
               VST_E_UNSUPPORTED, "lora_gemm: operand row strides must be multiples of 8 elements");
   VST_REQUIRE(out_dtype == VST_F32 || out_dtype == VST_BF16, VST_E_BADARG, "lora_gemm: out dtype");
-  VST_REQUIRE(act == VST_ACT_NONE || act == VST_ACT_GELU, VST_E_BADARG, "lora_gemm: bad act %d", act);
+  VST_REQUIRE(act == VST_ACT_NONE || act == VST_ACT_GELU || act == VST_ACT_GEGLU, VST_E_BADARG,
+              "lora_gemm: bad act %d", act);
+  if (act == VST_ACT_GEGLU)
+    VST_REQUIRE(K2 == 0 && residual == nullptr && out_dtype == VST_BF16 && N % 128 == 0, VST_E_UNSUPPORTED,
+                "lora_gemm: VST_ACT_GEGLU needs N %% 128 == 0, bf16 output, no low-rank pair, no residual");
   const int oa = out_dtype == VST_F32 ? 4 : 8;
   VST_REQUIRE(ldd % oa == 0 && (residual == nullptr || ldr % oa == 0), VST_E_UNSUPPORTED,
               "lora_gemm: output/residual row strides must keep 16-byte alignment");
@@ -656,6 +757,7 @@ extern "C" int vst_lora_gemm(const void* A1, int64_t lda1, const void* B1, int64
 #define FITS(BNV) (N % BNV == 0 && (gn == 0 || gn % BNV == 0))
 #define GO2(BNV) return launch2<BNV>(A1, lda1, B1, ldb1, K1, A2, lda2, B2, ldb2, K2, gn, ep, st)
   // CTA pairs (256-row tiles) once there is at least one tile per SM pair to keep busy
+  if (act == VST_ACT_GEGLU) GO2(256);
   const bool big = M >= 2048 && !vst_force_single_cta();
   if (big && FITS(256) && (M / 256) * (N / 256) >= vst_sm_count() / 2) GO2(256);
   if (big && FITS(160) && (M / 256) * (N / 160) >= vst_sm_count() / 2) GO2(160);

@@ -142,68 +142,110 @@ __global__ void gn_finalize_kernel(const float* __restrict__ partials, int npart
   }
 }
 
-// ---- LayerNorm: one warp per row, row cached in registers ---------------------------------------
-template <typename TI, typename TO, typename TP, int MAXV>
+// ---- LayerNorm: one warp per ROWS rows, rows cached in registers --------------------------------
+// Memory-bound (2 B read + 2 B written per element).  All of a warp's rows are loaded before the
+// first reduction (ROWS x MAXV 16-byte loads in flight per lane), gamma / beta / the position row
+// are read with 16-byte cached loads, and gamma / beta are shared by the warp's rows.  The first
+// version issued 24 scalar parameter loads per 16 bytes of activation and ran at 0.25 of HBM.
+template <typename TP>
+__device__ __forceinline__ void loadp8(const TP* p, float* v);
+template <>
+__device__ __forceinline__ void loadp8<__nv_bfloat16>(const __nv_bfloat16* p, float* v) {
+  const uint4 r = __ldg(reinterpret_cast<const uint4*>(p));
+  float2 e;
+  e = unpack_bf16(r.x); v[0] = e.x; v[1] = e.y;
+  e = unpack_bf16(r.y); v[2] = e.x; v[3] = e.y;
+  e = unpack_bf16(r.z); v[4] = e.x; v[5] = e.y;
+  e = unpack_bf16(r.w); v[6] = e.x; v[7] = e.y;
+}
+template <>
+__device__ __forceinline__ void loadp8<float>(const float* p, float* v) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p + 4));
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+
+template <typename TI, typename TO, typename TP, int MAXV, int ROWS>
 __global__ void __launch_bounds__(256)
 layernorm_kernel(const TI* __restrict__ x, TO* __restrict__ y, const TP* __restrict__ gamma,
                  const TP* __restrict__ beta, const float* __restrict__ pe, int64_t rows, int C,
                  int F, float eps) {
   const int lane = threadIdx.x & 31;
-  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (row >= rows) return;
-  const TI* xr = x + row * C;
+  const int64_t row0 = ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * ROWS;
+  if (row0 >= rows) return;
   const int nvec = C >> 3;
-  float v[MAXV][8];
-  float sum = 0.f;
+  float v[ROWS][MAXV][8];
 #pragma unroll
-  for (int i = 0; i < MAXV; ++i) {
-    const int vi = lane + 32 * i;
-    if (vi < nvec) {
-      load8<TI>(xr + vi * 8, v[i]);
+  for (int r = 0; r < ROWS; ++r) {
+    const bool ok = row0 + r < rows;
+    const TI* xr = x + (row0 + r) * C;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) sum += v[i][j];
-    }
-  }
-  const float mean = warp_sum(sum) / (float)C;
-  float m2 = 0.f;
+    for (int i = 0; i < MAXV; ++i) {
+      const int vi = lane + 32 * i;
+      if (ok && vi < nvec) {
+        load8<TI>(xr + vi * 8, v[r][i]);
+      } else {
 #pragma unroll
-  for (int i = 0; i < MAXV; ++i) {
-    const int vi = lane + 32 * i;
-    if (vi < nvec) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float d = v[i][j] - mean;
-        m2 = fmaf(d, d, m2);
+        for (int j = 0; j < 8; ++j) v[r][i][j] = 0.f;
       }
     }
   }
-  const float rstd = rsqrtf(warp_sum(m2) / (float)C + eps);
-  const float* per = pe ? pe + (int64_t)(row % F) * C : nullptr;
-  TO* yr = y + row * C;
+  float mean[ROWS], rstd[ROWS];
+#pragma unroll
+  for (int r = 0; r < ROWS; ++r) {
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) sum += v[r][i][j];
+    mean[r] = warp_sum(sum) / (float)C;
+  }
+#pragma unroll
+  for (int r = 0; r < ROWS; ++r) {
+    float m2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      if (lane + 32 * i < nvec) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float d = v[r][i][j] - mean[r];
+          m2 = fmaf(d, d, m2);
+        }
+      }
+    }
+    rstd[r] = rsqrtf(warp_sum(m2) / (float)C + eps);
+  }
 #pragma unroll
   for (int i = 0; i < MAXV; ++i) {
     const int vi = lane + 32 * i;
-    if (vi < nvec) {
+    if (vi >= nvec) continue;
+    float g[8], bt[8];
+    if (gamma) loadp8<TP>(gamma + vi * 8, g);
+    if (beta) loadp8<TP>(beta + vi * 8, bt);
+#pragma unroll
+    for (int r = 0; r < ROWS; ++r) {
+      if (row0 + r >= rows) continue;
       float o[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const int c = vi * 8 + j;
-        float r = (v[i][j] - mean) * rstd;
-        if (gamma) r = r * (float)gamma[c];
-        if (beta) r = r + (float)beta[c];
-        o[j] = r;
+        float t = (v[r][i][j] - mean[r]) * rstd[r];
+        if (gamma) t = t * g[j];
+        if (beta) t = t + bt[j];
+        o[j] = t;
       }
-      if (per) {
+      if (pe) {
         // LN output is first rounded to the activation dtype, then the position row is added
         // (diffusers: norm_hidden_states = pos_embed(norm1(x))) -- two roundings, as in torch.
+        float pr[8];
+        loadp8<float>(pe + (int64_t)((row0 + r) % F) * C + vi * 8, pr);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] = (float)(TO)o[j] + per[vi * 8 + j];
+        for (int j = 0; j < 8; ++j) o[j] = (float)(TO)o[j] + pr[j];
       }
+      TO* yr = y + (row0 + r) * C;
       if (sizeof(TO) == 2) {
         uint4 w;
         w.x = pack_bf16(o[0], o[1]); w.y = pack_bf16(o[2], o[3]);
         w.z = pack_bf16(o[4], o[5]); w.w = pack_bf16(o[6], o[7]);
-        *reinterpret_cast<uint4*>(yr + vi * 8) = w;
+        st_stream16(yr + vi * 8, w);
       } else {
         float4* d = reinterpret_cast<float4*>(yr + vi * 8);
         d[0] = make_float4(o[0], o[1], o[2], o[3]);
@@ -213,21 +255,152 @@ layernorm_kernel(const TI* __restrict__ x, TO* __restrict__ y, const TP* __restr
   }
 }
 
+// C in {320, 640, 1280} (the SDXL motion-module widths): 160 / NVEC rows per warp laid out as ONE
+// flat span of 160 16-byte vectors = exactly 5 per lane, so no lane idles (the per-row mapping
+// leaves 24 of 32 lanes idle on the second vector of a 40-vector row) and 5 loads are in flight
+// per lane before the first reduction.
+template <typename TI, typename TO, typename TP, int NVEC>
+__global__ void __launch_bounds__(256)
+layernorm_flat_kernel(const TI* __restrict__ x, TO* __restrict__ y, const TP* __restrict__ gamma,
+                      const TP* __restrict__ beta, const float* __restrict__ pe, int64_t rows, int F,
+                      float eps) {
+  constexpr int ROWS = 160 / NVEC, C = NVEC * 8;
+  const int lane = threadIdx.x & 31;
+  const int64_t row0 = ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * ROWS;
+  if (row0 >= rows) return;
+  float v[5][8];
+  int rr[5], vv[5];
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    const int f = i * 32 + lane;
+    rr[i] = f / NVEC;
+    vv[i] = f - rr[i] * NVEC;
+    if (row0 + rr[i] < rows) {
+      load8<TI>(x + (row0 + rr[i]) * C + vv[i] * 8, v[i]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[i][j] = 0.f;
+    }
+  }
+  float mean[ROWS], rstd[ROWS];
+  {
+    float part[ROWS];
+#pragma unroll
+    for (int r = 0; r < ROWS; ++r) part[r] = 0.f;
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+      float s8 = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s8 += v[i][j];
+#pragma unroll
+      for (int r = 0; r < ROWS; ++r) part[r] += rr[i] == r ? s8 : 0.f;
+    }
+#pragma unroll
+    for (int r = 0; r < ROWS; ++r) mean[r] = warp_sum(part[r]) * (1.f / (float)C);
+  }
+  float mu[5];
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    mu[i] = mean[0];
+#pragma unroll
+    for (int r = 1; r < ROWS; ++r) mu[i] = rr[i] == r ? mean[r] : mu[i];
+  }
+  {
+    float part[ROWS];
+#pragma unroll
+    for (int r = 0; r < ROWS; ++r) part[r] = 0.f;
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+      float s8 = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float d = v[i][j] - mu[i];
+        s8 = fmaf(d, d, s8);
+      }
+#pragma unroll
+      for (int r = 0; r < ROWS; ++r) part[r] += rr[i] == r ? s8 : 0.f;
+    }
+#pragma unroll
+    for (int r = 0; r < ROWS; ++r) rstd[r] = rsqrtf(warp_sum(part[r]) * (1.f / (float)C) + eps);
+  }
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    const int64_t row = row0 + rr[i];
+    if (row >= rows) continue;
+    float rs = rstd[0];
+#pragma unroll
+    for (int r = 1; r < ROWS; ++r) rs = rr[i] == r ? rstd[r] : rs;
+    float o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mu[i]) * rs;
+    if (gamma) {
+      float g[8];
+      loadp8<TP>(gamma + vv[i] * 8, g);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] *= g[j];
+    }
+    if (beta) {
+      float bt[8];
+      loadp8<TP>(beta + vv[i] * 8, bt);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] += bt[j];
+    }
+    if (pe) {
+      float pr[8];
+      loadp8<float>(pe + (int)(row % F) * C + vv[i] * 8, pr);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = (float)(TO)o[j] + pr[j];   // two roundings, as in torch
+    }
+    TO* yp = y + row * C + vv[i] * 8;
+    if (sizeof(TO) == 2) {
+      uint4 w;
+      w.x = pack_bf16(o[0], o[1]); w.y = pack_bf16(o[2], o[3]);
+      w.z = pack_bf16(o[4], o[5]); w.w = pack_bf16(o[6], o[7]);
+      st_stream16(yp, w);
+    } else {
+      float4* d = reinterpret_cast<float4*>(yp);
+      d[0] = make_float4(o[0], o[1], o[2], o[3]);
+      d[1] = make_float4(o[4], o[5], o[6], o[7]);
+    }
+  }
+}
+
+template <typename TI, typename TO, typename TP, int NVEC>
+int launch_ln_flat(const void* x, void* y, const void* g, const void* b, const float* pe, int64_t rows,
+                   int F, float eps, cudaStream_t st) {
+  constexpr int ROWS = 160 / NVEC;
+  const int wpb = 8;
+  const int64_t grid = (rows + (int64_t)wpb * ROWS - 1) / ((int64_t)wpb * ROWS);
+  VST_REQUIRE(grid < (1ll << 31), VST_E_UNSUPPORTED, "layernorm: too many rows");
+  layernorm_flat_kernel<TI, TO, TP, NVEC><<<(unsigned)grid, wpb * 32, 0, st>>>(
+      (const TI*)x, (TO*)y, (const TP*)g, (const TP*)b, pe, rows, F, eps);
+  VST_LAUNCH_OK();
+  return VST_OK;
+}
+
+template <typename TI, typename TO, typename TP, int MAXV, int ROWS>
+int launch_ln_cfg(const void* x, void* y, const void* g, const void* b, const float* pe, int64_t rows,
+                  int C, int F, float eps, cudaStream_t st) {
+  const int wpb = 8;
+  const int64_t grid = (rows + (int64_t)wpb * ROWS - 1) / ((int64_t)wpb * ROWS);
+  VST_REQUIRE(grid < (1ll << 31), VST_E_UNSUPPORTED, "layernorm: too many rows");
+  layernorm_kernel<TI, TO, TP, MAXV, ROWS><<<(unsigned)grid, wpb * 32, 0, st>>>(
+      (const TI*)x, (TO*)y, (const TP*)g, (const TP*)b, pe, rows, C, F, eps);
+  VST_LAUNCH_OK();
+  return VST_OK;
+}
+
 template <typename TI, typename TO, typename TP>
 int launch_ln(const void* x, void* y, const void* g, const void* b, const float* pe, int64_t rows,
               int C, int F, float eps, cudaStream_t st) {
-  const int wpb = 8;
-  const int64_t grid = (rows + wpb - 1) / wpb;
-  VST_REQUIRE(grid < (1ll << 31), VST_E_UNSUPPORTED, "layernorm: too many rows");
   const int nvec = C / 8;
-  if (nvec <= 64)
-    layernorm_kernel<TI, TO, TP, 2><<<(unsigned)grid, wpb * 32, 0, st>>>(
-        (const TI*)x, (TO*)y, (const TP*)g, (const TP*)b, pe, rows, C, F, eps);
-  else
-    layernorm_kernel<TI, TO, TP, 8><<<(unsigned)grid, wpb * 32, 0, st>>>(
-        (const TI*)x, (TO*)y, (const TP*)g, (const TP*)b, pe, rows, C, F, eps);
-  VST_LAUNCH_OK();
-  return VST_OK;
+  if (nvec == 40) return launch_ln_flat<TI, TO, TP, 40>(x, y, g, b, pe, rows, F, eps, st);
+  if (nvec == 80) return launch_ln_flat<TI, TO, TP, 80>(x, y, g, b, pe, rows, F, eps, st);
+  if (nvec == 160) return launch_ln_flat<TI, TO, TP, 160>(x, y, g, b, pe, rows, F, eps, st);
+  if (nvec <= 64) return launch_ln_cfg<TI, TO, TP, 2, 4>(x, y, g, b, pe, rows, C, F, eps, st);
+  if (nvec <= 96) return launch_ln_cfg<TI, TO, TP, 3, 2>(x, y, g, b, pe, rows, C, F, eps, st);
+  if (nvec <= 160) return launch_ln_cfg<TI, TO, TP, 5, 1>(x, y, g, b, pe, rows, C, F, eps, st);
+  return launch_ln_cfg<TI, TO, TP, 8, 1>(x, y, g, b, pe, rows, C, F, eps, st);
 }
 
 }  // namespace

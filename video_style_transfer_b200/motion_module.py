@@ -66,8 +66,14 @@ class FeedForward(nn.Module):
         self.net = nn.ModuleList([GEGLU(dim, dim * mult), nn.Dropout(0.0), nn.Linear(dim * mult, dim)])
 
     def forward_tokens(self, xn: torch.Tensor, residual: torch.Tensor):
-        hg = fused_linear(xn, self.net[0].proj.weight, self.net[0].proj.bias)
-        return fused_linear(ops.geglu(hg), self.net[2].weight, self.net[2].bias, residual=residual)
+        proj = self.net[0].proj
+        inner = proj.out_features // 2
+        if inner % 128 == 0 and not (torch.is_grad_enabled() and ops._needs_grad(xn, proj.weight, proj.bias)):
+            # inference: hidden * gelu(gate) in the GEMM epilogue, the 2*inner-wide tensor never exists
+            h = fused_linear(xn, proj.weight, proj.bias, act="geglu")
+        else:
+            h = ops.geglu(fused_linear(xn, proj.weight, proj.bias))
+        return fused_linear(h, self.net[2].weight, self.net[2].bias, residual=residual)
 
 
 class TemporalBasicTransformerBlock(nn.Module):

@@ -259,9 +259,13 @@ def lora_gemm(a1: torch.Tensor, b1: torch.Tensor, a2: Optional[torch.Tensor] = N
               residual: Optional[torch.Tensor] = None, out_scale: float = 1.0,
               act: str = "none", k2_group_n: int = 0, out: Optional[torch.Tensor] = None,
               out_dtype: torch.dtype = torch.bfloat16) -> torch.Tensor:
-    """out[M,N] = (act(a1 b1^T + a2 b2^T + bias) + residual) * out_scale; act in {none, gelu}.
-    Differentiable (act none): the backward runs vst_gemm / vst_colsum (see _autograd.py)."""
+    """out[M,N] = (act(a1 b1^T + a2 b2^T + bias) + residual) * out_scale; act in {none, gelu}, or
+    "geglu" (b1 (2N,K), bias (2N,): hidden * gelu(gate) in the epilogue; inference only).
+    Differentiable (act none / gelu): the backward runs vst_gemm / vst_colsum (see _autograd.py)."""
     if _needs_grad(a1, b1, a2, b2, bias, residual):
+        if act == "geglu":
+            raise RuntimeError("lora_gemm: act='geglu' is the fused inference epilogue; use "
+                               "lora_gemm + geglu under autograd")
         if out is not None:
             raise RuntimeError("lora_gemm: out= cannot be combined with autograd")
         from ._autograd import LoraGemmFn
@@ -282,6 +286,9 @@ def lora_gemm_raw(a1: torch.Tensor, b1: torch.Tensor, a2: Optional[torch.Tensor]
     _mat(a1, "a1"), _mat(b1, "b1")
     m, k1 = a1.shape
     n = b1.shape[0]
+    if act == "geglu":           # b1 = [W_hidden ; W_gate] (2N, K), bias (2N,) -> out (M, N)
+        assert n % 2 == 0 and a2 is None and residual is None
+        n //= 2
     assert b1.shape[1] == k1
     k2 = 0
     if a2 is not None:
@@ -300,7 +307,8 @@ def lora_gemm_raw(a1: torch.Tensor, b1: torch.Tensor, a2: Optional[torch.Tensor]
         b2.stride(0) if b2 is not None else 0, k2, k2_group_n if a2 is not None else 0,
         _ptr(bias), _dt(bias) if bias is not None else VST_F32,
         _ptr(residual), residual.stride(0) if residual is not None else 0, out_scale,
-        {"none": 0, "gelu": 1}[act], out.data_ptr(), out.stride(0), m, n, _dt(out), _stream()), "vst_lora_gemm")
+        {"none": 0, "gelu": 1, "geglu": 2}[act], out.data_ptr(), out.stride(0), m, n, _dt(out), _stream()),
+        "vst_lora_gemm")
     return out
 
 

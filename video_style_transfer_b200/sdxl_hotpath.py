@@ -147,6 +147,45 @@ def run_unet_hotpath(plan, xs4, xs3, text, frames: int):
     return outs
 
 
+class GraphedDenoiseStep:
+    """One denoising step's worth of hot-path work (one run_unet_hotpath per text embedding: uncond
+    + cond) captured ONCE into a CUDA graph and replayed: the step is ~2,300 kernel launches of
+    10-800 us each, and the Python + launch overhead between them (~10 % of the step at 16 frames)
+    disappears on replay.  Inputs live in static device buffers (`x4`, `x3`, `texts`); copy new
+    data into them (e.g. ``step.x4[0].copy_(host, non_blocking=True)``) before ``replay()``.
+    Everything the C ABI needs is graph-safe: no host synchronisation, workspaces come from the
+    caching allocator's graph pool, tensor maps travel as kernel parameters."""
+
+    def __init__(self, plan, xs4, xs3, texts, frames: int, warmup: int = 2):
+        from . import _lib
+        self.plan, self.frames = plan, frames
+        self.x4 = [t.clone() for t in xs4]
+        self.x3 = [None] + [t.clone() for t in xs3[1:]]
+        self.texts = [t.clone() for t in texts]
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):                   # bf16 caches, smem attributes, allocator warm-up
+            for _ in range(warmup):
+                self._run()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        n0 = _lib.launch_count
+        with torch.cuda.graph(self.graph):
+            self.outs = self._run()
+        self.launches = _lib.launch_count - n0           # C-ABI calls captured per replay
+
+    def _run(self):
+        outs = None
+        for text in self.texts:
+            outs = run_unet_hotpath(self.plan, self.x4, self.x3, text, self.frames)
+        return outs
+
+    def replay(self):
+        self.graph.replay()
+        return self.outs
+
+
 @torch.no_grad()
 def run_unet_hotpath_sp(plan, xs4_local, xs3_local, text, f_total: int, comm, group=None):
     """run_unet_hotpath for ONE video whose frames are sharded over the ranks of `comm`
