@@ -321,8 +321,10 @@ def run_ours(args):
     attn_fl = sum(f for _, _, f in ev)
     achieved = attn_fl / (attn_ms * 1e-3) / 1e12
     peak_tf = pk.get("bf16_tflops_sustained", pk["bf16_tflops"])
-    fl = hpth.hotpath_flops(plan, F, S)
+    from video_style_transfer_b200 import fused as fusedmod
+    fl = hpth.hotpath_flops(plan, F, S, merged=fusedmod.MERGE_LORA)        # FLOPs executed
     step_flops = 2.0 * sum(fl.values())
+    step_flops_lowrank = 2.0 * sum(hpth.hotpath_flops(plan, F, S).values())  # SURVEY §8d low-rank form
 
     if rank != 0:
         return
@@ -339,7 +341,10 @@ def run_ours(args):
                    "unziplora_rank": 64, "temporal_lora_rank": 32, "parallelism": f"dp{world} (videos)",
                    "launch": "eager (one Python call per kernel)" if graphed is None else "CUDA graph replay",
                    "l2": "per-step working set (2.4 GB of weights + 0.4 GB activations) exceeds the 126 MB L2",
-                   "step_tflop": step_flops / 1e12},
+                   "adapters": ("folded into the weights once per parameter version (W + B'A), one GEMM per "
+                                "projection" if fusedmod.MERGE_LORA else
+                                "low-rank form: u = x A^T pre-pass + extra K blocks in the fused GEMM"),
+                   "step_tflop": step_flops / 1e12, "step_tflop_lowrank_form": step_flops_lowrank / 1e12},
         "e2e": {"value": world * 1e3 / (ms_e2e / args.steps), "unit": "steps/s",
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": launches,

@@ -310,3 +310,34 @@ def test_attn_processor_with_attention_mask_vs_oracle():
     y = AnimateDiffAttnProcessor2_0()(attn, hs.cuda().to(torch.bfloat16), ehs.cuda().to(torch.bfloat16),
                                       attention_mask=mask.cuda())
     assert rel(y, want) < 2 * TOL
+
+
+@pytest.mark.parametrize("kind", ["self", "cross"])
+def test_attn_processor_low_rank_form_matches_folded_weights(kind, monkeypatch):
+    """Inference folds frozen adapters into the weights (fused.merged_weight); the low-rank fused
+    GEMM (u = x A^T, extra K blocks) stays the training / three-stream path.  Both must reproduce
+    the reference's golden output, and the folded weight must track in-place parameter updates."""
+    from video_style_transfer_b200 import fused
+    from video_style_transfer_b200.animatediff.attention_processor import AnimateDiffAttnProcessor2_0
+    g = np.load(os.path.join(GOLD, "attn_processor.npz"))
+    attn = _build_attn(g, kind, torch.bfloat16)
+    proc = AnimateDiffAttnProcessor2_0()
+    hs = T(g[f"{kind}/hs"]).cuda().to(torch.bfloat16)
+    ehs = T(g["cross/ehs"]).cuda().to(torch.bfloat16) if kind == "cross" else None
+    want = T(g[f"{kind}/y"])
+    monkeypatch.setattr(fused, "MERGE_LORA", True)
+    y_fold = proc(attn, hs, ehs, scale=0.9)
+    monkeypatch.setattr(fused, "MERGE_LORA", False)
+    y_low = proc(attn, hs, ehs, scale=0.9)
+    assert rel(y_fold, want) < 2 * TOL and rel(y_low, want) < 2 * TOL
+    assert rel(y_fold, y_low.float().cpu()) < 2 * TOL
+    # an in-place merger update must invalidate the folded weight
+    monkeypatch.setattr(fused, "MERGE_LORA", True)
+    with torch.no_grad():
+        attn.to_q.lora_layer.merge_content.mul_(0.0)
+        attn.to_q.lora_layer.merge_style.mul_(0.0)
+    y2 = proc(attn, hs, ehs, scale=0.9)
+    monkeypatch.setattr(fused, "MERGE_LORA", False)
+    y2_low = proc(attn, hs, ehs, scale=0.9)
+    assert rel(y2, y2_low.float().cpu()) < 2 * TOL
+    assert rel(y2, y_fold.float().cpu()) > 1e-3          # the output did change

@@ -48,9 +48,10 @@ class TemporalLoRALinear(nn.Module):
     def fused_forward(self, x2: torch.Tensor, scale: float = 1.0, residual=None,
                       out_scale: float = 1.0, act: str = "none",
                       out_dtype: torch.dtype = torch.bfloat16) -> torch.Tensor:
-        u = ops.lora_gemm(x2, bf16_cached(self.lora_A, pad_rows=True))
-        return fused_linear(x2, self.base.weight, self.base.bias, (u, self.site_up()), residual,
-                            out_scale, act, out_dtype)
+        # fused.project_one: frozen adapter -> cached W + (alpha/r) B A and one plain GEMM (the
+        # reference's own merged_weight, :35-41); trainable adapter -> u = x A^T + fused GEMM
+        from ..fused import project_one
+        return project_one(self, x2, 1.0, residual, out_scale, act, out_dtype)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         y = self.fused_forward(as_rows_bf16(x))

@@ -8,17 +8,58 @@ tiles the 148 SMs with far less wave-quantisation loss than three C-wide GEMMs. 
 term is *grouped* (vst_lora_gemm k2_group_n): output columns of projection g only read their own
 K2 columns of u, so no block-diagonal zero padding is multiplied.
 
+Inference with frozen adapters (no parameter of the site requires grad) goes one step further:
+the low-rank update is folded into the weight once, W_eff = W + B' A (``merged_weight``, built by
+vst_gemm and cached on the parameters' versions, i.e. rebuilt after an optimiser step, a merger
+clamp, a mask or a forward-type change), and the projection is ONE plain GEMM: no u = x A^T
+pre-pass, no extra K blocks.  The reference materialises A^T B^T on every call
+(unziplora_linear_layer.py:311-322) and itself ships ``merged_weight`` for the temporal LoRA
+(temporal_lora.py:35-41).  Training (any adapter tensor requires grad) and the three-stream
+Stage-1 form (lora_unzip.py:66-75, low-rank branches read other activations) keep the fused
+low-rank GEMM.  VST_MERGE_LORA=0 (or ``fused.MERGE_LORA = False``) disables the folding.
+
 Every linear taking part implements the "LoRA site" protocol: site_weight(), site_bias(),
 site_downs() -> [A_i (r, in)], site_up(scale) -> B' (out, K2) or None.  Concatenated / packed
 operands are cached on the parameters' in-place versions (``_host.bf16_cached/cached_build``), so
 an optimiser step or a merger clamp invalidates them.
 """
+import os
 from typing import List, Optional, Sequence
 
 import torch
 
 from . import ops
 from ._host import bf16_cached, cached_build, fused_linear, pad8
+
+
+MERGE_LORA = os.environ.get("VST_MERGE_LORA", "1") != "0"
+
+
+def _frozen(tensors) -> bool:
+    return not (torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in tensors))
+
+
+def merged_weight(ws: Sequence[torch.Tensor], downs: Sequence[Sequence[torch.Tensor]],
+                  ups: Sequence[Optional[torch.Tensor]]) -> torch.Tensor:
+    """bf16 [W_0 + B'_0 A_0 ; W_1 + B'_1 A_1 ; ...] (sum out, in): one vst_gemm per site
+    accumulating the rank-K2 product onto a copy of the cached bf16 weight, memoised on every
+    tensor involved.  ups[g] is the packed, merger- and scale-folded up-projection of site g."""
+    flat = [a for d in downs for a in d]
+    deps = list(ws) + flat + [u for u in ups if u is not None]
+
+    def build():
+        w = bf16_cached(*ws).clone()
+        row = 0
+        for wg, dg, ug in zip(ws, downs, ups):
+            n = wg.shape[0]
+            if ug is not None and dg:
+                a = bf16_cached(*dg, pad_rows=True)                     # (K2, in)
+                assert a.shape[0] == ug.shape[1]
+                ops.gemm(ug.detach(), a, trans_b=True, out=w[row:row + n], accumulate=True)
+            row += n
+        return w
+
+    return cached_build(deps, "merged_weight", build)
 
 
 def _site(layer):
@@ -57,6 +98,9 @@ def project_one(layer, x2: torch.Tensor, scale: float = 1.0, residual=None, out_
     if downs:
         bp = s.site_up(scale)
         if bp is not None:
+            if MERGE_LORA and _frozen([s.site_weight(), bp] + list(downs)):
+                w_eff = merged_weight([s.site_weight()], [downs], [bp])
+                return fused_linear(x2, w_eff, s.site_bias(), None, residual, out_scale, act, out_dtype)
             low = (ops.lora_gemm(x2, bf16_cached(*downs, pad_rows=True)), bp)
     return fused_linear(x2, s.site_weight(), s.site_bias(), low, residual, out_scale, act, out_dtype)
 
@@ -75,7 +119,10 @@ def project_fused(layers: Sequence, x2: torch.Tensor, scale: float = 1.0) -> Lis
             and len(k2s) == 1 and (all(b is None for b in biases) or all(b is not None for b in biases)))
     if not same:
         return [project_one(l, x2, scale) for l in layers]
-    w = bf16_cached(*ws)
+    k2_any = next(iter(k2s))
+    merge = (k2_any is not None and MERGE_LORA
+             and _frozen(list(ws) + [a for d in downs for a in d] + [u for u in ups if u is not None]))
+    w = merged_weight(ws, downs, ups) if merge else bf16_cached(*ws)
     bias = None
     if biases[0] is not None:
         if torch.is_grad_enabled() and any(b.requires_grad for b in biases):
@@ -83,7 +130,7 @@ def project_fused(layers: Sequence, x2: torch.Tensor, scale: float = 1.0) -> Lis
         else:
             bias = cached_build(list(biases), "catbias", lambda: torch.cat([b.detach().float() for b in biases]))
     k2 = k2s.pop()
-    if k2 is None:
+    if k2 is None or merge:
         y = ops.lora_gemm(x2, w, bias=bias)
     else:
         flat = [a for d in downs for a in d]

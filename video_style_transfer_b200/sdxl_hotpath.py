@@ -250,15 +250,18 @@ def train_step_hotpath(model, plan, xs4, xs3, text, targets, frames: int, optimi
     return loss.detach()
 
 
-def hotpath_flops(plan, frames: int, latent: int = 128, batch: int = 1):
-    """Algorithmic FLOPs of one UNet forward of the plan (SURVEY.md §8d formulas), by kernel family."""
+def hotpath_flops(plan, frames: int, latent: int = 128, batch: int = 1, merged: bool = False):
+    """Algorithmic FLOPs of one UNet forward of the plan (SURVEY.md §8d formulas), by kernel family.
+    merged=True: the FLOPs actually executed when the frozen adapters are folded into the weights
+    (fused.merged_weight): the low-rank terms cost nothing per call."""
     fl = {"attn_self": 0.0, "attn_cross": 0.0, "proj": 0.0, "temporal_attn": 0.0, "motion_gemm": 0.0}
     side = [latent, latent // 2, latent // 4]
     dims = [320, 640, 1280]
     for kind, lvl, _ in plan:
         c, hw = dims[lvl], side[lvl] ** 2
         m = batch * frames * hw
-        r2 = 128
+        r2 = 0 if merged else 128
+        rt = 0 if merged else 32
         if kind == "self":
             fl["attn_self"] += 4.0 * batch * frames * hw * hw * c
             fl["proj"] += 4 * (2.0 * m * c * c + 2.0 * m * r2 * (c + c))
@@ -271,6 +274,6 @@ def hotpath_flops(plan, frames: int, latent: int = 128, batch: int = 1):
             n = batch * hw
             fl["temporal_attn"] += 2 * 4.0 * n * frames * frames * c
             fl["motion_gemm"] += 2.0 * m * c * c * 2                       # proj_in, proj_out
-            fl["motion_gemm"] += 8 * (2.0 * m * c * c + 2.0 * m * 32 * 2 * c)   # 2 x (q,k,v,out) + LoRA
+            fl["motion_gemm"] += 8 * (2.0 * m * c * c + 2.0 * m * rt * 2 * c)   # 2 x (q,k,v,out) + LoRA
             fl["motion_gemm"] += 2.0 * m * c * 8 * c + 2.0 * m * 4 * c * c   # GEGLU FF
     return fl

@@ -83,6 +83,14 @@ class LoRACompatibleLinear(nn.Linear):
             if not hasattr(self.lora_layer, "fused_operands"):
                 raise TypeError("lora_layer must be a video_style_transfer_b200 LoRA layer "
                                 "(no eager fallback on the sm_100a path)")
+            if x_content is None and x_style is None:
+                # single-stream inference with frozen adapters: W_eff = W + B' A, one plain GEMM
+                from .. import fused
+                downs = self.site_downs()
+                bp = self.site_up(scale) if downs else None
+                if bp is not None and fused.MERGE_LORA and fused._frozen([self.weight, bp] + list(downs)):
+                    w_eff = fused.merged_weight([self.weight], [downs], [bp])
+                    return fused_linear(x2, w_eff, self.bias, None, residual, out_scale)
             xc = x2 if x_content is None else x_content
             low_rank = self.lora_layer.fused_operands(xc, x_style, scale)
         return fused_linear(x2, self.weight, self.bias, low_rank, residual, out_scale)
