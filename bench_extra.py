@@ -243,7 +243,7 @@ def run_cfg5(args, common):
         nbytes = max(SPMotionStep.buffer_bytes(1, s[1], s[2] * s[3], F, world) for s in shapes)
         comm = SPComm.from_process_group(nbytes)
 
-    def step():
+    def step_eager():
         outs = None
         for text in texts:
             if world > 1:
@@ -252,14 +252,21 @@ def run_cfg5(args, common):
                 outs = hpth.run_unet_hotpath(plan, xs4, xs3, text, F)
         return outs
 
+    graphed = None
+    if not args.no_graph:       # every rank captures the same launch sequence, replays in lockstep
+        graphed = (hpth.GraphedSPDenoiseStep(plan, xs4, xs3, texts, F, comm) if world > 1
+                   else hpth.GraphedDenoiseStep(plan, xs4, xs3, texts, F))
+    step = step_eager if graphed is None else graphed.replay
+
     for _ in range(max(3, args.warmup)):
         step()
     torch.cuda.synchronize()
     l0 = _lib.launch_count
     with common["ClockSampler"](local) as clk:
         ms = _timed(step, args.steps, world, dev)
-    launches = (_lib.launch_count - l0) // args.steps
-    fl = hpth.hotpath_flops(plan, F, S)
+    launches = (_lib.launch_count - l0) // args.steps if graphed is None else graphed.launches
+    from video_style_transfer_b200 import fused as fusedmod
+    fl = hpth.hotpath_flops(plan, F, S, merged=fusedmod.MERGE_LORA)
     step_fl = 2.0 * sum(fl.values())
     if comm is not None:
         torch.cuda.synchronize()
@@ -278,6 +285,7 @@ def run_cfg5(args, common):
                 "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
                 "config": {"workload": "cfg5-sequence-parallel", "frames": F, "latent": S,
                            "frames_per_rank": fl_, "parallelism": f"sp{world} (frames <-> positions)",
+                           "launch": "eager" if graphed is None else "CUDA graph replay (one graph per rank)",
                            "nvlink_bytes_per_rank_per_step": egress, "step_tflop": step_fl / 1e12},
                 "tflops_hotpath": step_fl / (ms * 1e-3) / 1e12, "gpu_launches": launches,
                 "clocks": clk.summary()}

@@ -237,6 +237,13 @@ int vst_comm_ipc_close(void* ptr);
 int vst_comm_init(int rank, int world, void* const* bufs, void* const* flags, void** comm_out);
 int vst_comm_fini(void* comm);
 int vst_comm_barrier(void* comm, void* stream);
+/* rank p's GroupNorm partials (rows, nparts, 3) fp32 -> columns [p*nparts, (p+1)*nparts) of a
+ * (rows, world*nparts, 3) array at dst_offset_bytes of EVERY rank's symmetric buffer (peer stores
+ * over NVLink; bracket with vst_comm_barrier).  The flag block of a rank must be >= 256 bytes:
+ * one word per peer plus the rank's barrier count (kept on the device so that a captured CUDA
+ * graph of a sequence-parallel step replays correctly). */
+int vst_comm_allgather_partials(void* comm, const float* partials, int rows, int nparts,
+                                int64_t dst_offset_bytes, void* stream);
 int vst_a2a_frames_to_hw(void* comm, const void* x, int64_t dst_offset_bytes, const float* mean,
                          const float* rstd, const void* gamma, const void* beta, int B, int C,
                          int F_local, int F_total, int HW, int64_t sB, int64_t sC, int64_t sF,

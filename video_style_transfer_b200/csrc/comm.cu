@@ -18,29 +18,59 @@ namespace {
 
 struct BarrierArgs {
   uint32_t* flags[VST_MAX_RANKS];
+  uint32_t* epoch_ctr;     // this rank's barrier count, in its own flag block (device memory, so a
+                           // captured CUDA graph advances it on every replay)
   int rank, world;
-  uint32_t epoch;
 };
 
 // One thread per peer: publish "rank reached epoch" in the peer's flag word for this rank, then
 // wait for the peer's word in our own flags.  Every rank runs this kernel on its own GPU.
 __global__ void comm_barrier_kernel(BarrierArgs a) {
+  __shared__ uint32_t s_epoch;
   const int r = threadIdx.x;
-  if (r >= a.world) return;
-  __threadfence_system();   // everything this GPU wrote before the barrier is visible system-wide
-  uint32_t* theirs = a.flags[r] + a.rank;
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(theirs), "r"(a.epoch) : "memory");
-  const uint32_t* mine = a.flags[a.rank] + r;
-  const uint64_t t0 = globaltimer_ns();
-  uint32_t v;
-  do {
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
-    if ((int32_t)(v - a.epoch) >= 0) break;
-    if (globaltimer_ns() - t0 > 20000000000ull) {   // 20 s: a peer died; fail loudly, do not hang the box
-      printf("vst comm barrier: rank %d timed out waiting for rank %d (epoch %u, saw %u)\n", a.rank, r, a.epoch, v);
-      __trap();
-    }
-  } while (true);
+  if (r == 0) s_epoch = *a.epoch_ctr + 1;
+  __syncthreads();
+  const uint32_t epoch = s_epoch;
+  if (r < a.world) {
+    __threadfence_system();   // everything this GPU wrote before the barrier is visible system-wide
+    uint32_t* theirs = a.flags[r] + a.rank;
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(theirs), "r"(epoch) : "memory");
+    const uint32_t* mine = a.flags[a.rank] + r;
+    const uint64_t t0 = globaltimer_ns();
+    uint32_t v;
+    do {
+      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
+      if ((int32_t)(v - epoch) >= 0) break;
+      if (globaltimer_ns() - t0 > 20000000000ull) {   // 20 s: a peer died; fail loudly, do not hang the box
+        printf("vst comm barrier: rank %d timed out waiting for rank %d (epoch %u, saw %u)\n", a.rank, r, epoch, v);
+        __trap();
+      }
+    } while (true);
+  }
+  __syncthreads();
+  if (r == 0) *a.epoch_ctr = epoch;
+}
+
+struct GatherArgs {
+  void* buf[VST_MAX_RANKS];
+  int rank, world;
+};
+
+// GroupNorm partials of the frames-sharded layout (the one reduction the math
+// forces): rank p's (rows, nparts, 3) fp32 block lands at columns [p*nparts, (p+1)*nparts) of a
+// (rows, world*nparts, 3) array in EVERY rank's symmetric buffer, i.e. exactly the partial order of
+// the unsharded statistics kernel, so vst_groupnorm5d_finalize gives bit-identical mean / rstd.
+// grid = world blocks (block r stores into rank r's buffer over NVLink).
+__global__ void comm_allgather_partials_kernel(GatherArgs a, const float* __restrict__ src, int rows,
+                                               int nparts, int64_t dst_offset_bytes) {
+  float* dst = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(a.buf[blockIdx.x]) + dst_offset_bytes);
+  const int per_row = nparts * 3;
+  const int64_t total = (int64_t)rows * per_row;
+  for (int64_t i = threadIdx.x; i < total; i += blockDim.x) {
+    const int64_t row = i / per_row;
+    const int e = (int)(i - row * per_row);
+    dst[(row * a.world + a.rank) * per_row + e] = src[i];
+  }
 }
 
 }  // namespace
@@ -90,7 +120,6 @@ extern "C" int vst_comm_init(int rank, int world, void* const* bufs, void* const
   VstComm* c = new VstComm();
   c->rank = rank;
   c->world = world;
-  c->epoch = 0;
   for (int r = 0; r < world; ++r) {
     VST_REQUIRE(bufs[r] && flags[r], VST_E_BADARG, "comm_init: null peer pointer for rank %d", r);
     c->buf[r] = bufs[r];
@@ -112,8 +141,24 @@ extern "C" int vst_comm_barrier(void* comm, void* stream) {
   for (int r = 0; r < VST_MAX_RANKS; ++r) a.flags[r] = r < c->world ? c->flags[r] : nullptr;
   a.rank = c->rank;
   a.world = c->world;
-  a.epoch = ++c->epoch;
+  a.epoch_ctr = c->flags[c->rank] + VST_COMM_EPOCH_WORD;
   comm_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(a);
+  VST_LAUNCH_OK();
+  return VST_OK;
+}
+
+extern "C" int vst_comm_allgather_partials(void* comm, const float* partials, int rows, int nparts,
+                                           int64_t dst_offset_bytes, void* stream) {
+  VST_REQUIRE(comm && partials && rows > 0 && nparts > 0 && dst_offset_bytes >= 0 &&
+                  dst_offset_bytes % 16 == 0,
+              VST_E_BADARG, "comm_allgather_partials: bad argument");
+  VstComm* c = reinterpret_cast<VstComm*>(comm);
+  GatherArgs a;
+  for (int r = 0; r < VST_MAX_RANKS; ++r) a.buf[r] = r < c->world ? c->buf[r] : nullptr;
+  a.rank = c->rank;
+  a.world = c->world;
+  comm_allgather_partials_kernel<<<c->world, 256, 0, (cudaStream_t)stream>>>(a, partials, rows, nparts,
+                                                                             dst_offset_bytes);
   VST_LAUNCH_OK();
   return VST_OK;
 }

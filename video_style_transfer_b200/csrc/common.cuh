@@ -56,9 +56,10 @@ int vst_make_tmap(CUtensorMap* out, const void* base, int rank, const uint64_t* 
 struct VstComm {
   int rank, world;
   void* buf[VST_MAX_RANKS];        // symmetric data buffers, mapped on this GPU (buf[rank] is local)
-  uint32_t* flags[VST_MAX_RANKS];  // flags[r]: rank r's flag words, one per peer
-  uint32_t epoch;
+  uint32_t* flags[VST_MAX_RANKS];  // flags[r]: rank r's flag block: one word per peer, then (word
+                                   // VST_COMM_EPOCH_WORD) r's own barrier count
 };
+#define VST_COMM_EPOCH_WORD 32
 
 // ---------------------------------------------------------------------------------------------
 // device helpers

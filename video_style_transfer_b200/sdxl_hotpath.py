@@ -186,6 +186,24 @@ class GraphedDenoiseStep:
         return self.outs
 
 
+class GraphedSPDenoiseStep(GraphedDenoiseStep):
+    """GraphedDenoiseStep for ONE video sharded over the ranks of an SPComm: every rank captures its
+    own graph of the same launch sequence (spatial processors on its frames, motion modules through
+    the fused NVLink all-to-alls and flag barriers) and all ranks replay in lockstep.  `frames` is
+    the video's total frame count; xs4 / xs3 hold this rank's frames."""
+
+    def __init__(self, plan, xs4_local, xs3_local, texts, frames: int, comm, warmup: int = 2):
+        self.comm = comm
+        super().__init__(plan, xs4_local, xs3_local, texts, frames, warmup)
+
+    def _run(self):
+        outs = None
+        for text in self.texts:
+            outs = run_unet_hotpath_sp(self.plan, self.x4, self.x3, text, self.frames, self.comm)
+        return outs
+
+
+
 @torch.no_grad()
 def run_unet_hotpath_sp(plan, xs4_local, xs3_local, text, f_total: int, comm, group=None):
     """run_unet_hotpath for ONE video whose frames are sharded over the ranks of `comm`

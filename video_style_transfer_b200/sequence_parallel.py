@@ -5,12 +5,15 @@ temporal op (the motion module body) per spatial position, so rank p keeps frame
 The two transposes per motion module are done by the module's own layout kernels writing to /
 reading from peer memory over NVLink (csrc/layout.cu ShardArgs, csrc/comm.cu):
 
-    frames-sharded x --[GroupNorm stats: 256-byte all-gather]--> vst_a2a_frames_to_hw (push)
-        --barrier--> proj_in .. proj_out on N/P sequences --barrier--> vst_a2a_hw_to_frames (pull,
-        + residual) --barrier--> frames-sharded output
+    frames-sharded x --GroupNorm partials stored into every peer (vst_comm_allgather_partials)
+        --barrier--> vst_a2a_frames_to_hw (push, GroupNorm applied on the way)
+        --barrier--> proj_in .. proj_out on N/P sequences
+        --barrier--> vst_a2a_hw_to_frames (pull, + residual) --barrier--> frames-sharded output
 
-torch.distributed (NCCL) is plumbing only: it carries the IPC handles at start-up and the
-GroupNorm partials.  The reference has no multi-GPU path for a single video at all.
+torch.distributed (NCCL) is plumbing only: it carries the IPC handles at start-up.  No NCCL call
+and no host synchronisation sits on the data path, so a whole sequence-parallel denoising step is
+capturable in one CUDA graph per rank (the barrier's epoch lives in device memory).  The reference
+has no multi-GPU path for a single video at all.
 """
 import ctypes as C
 from typing import List, Optional, Sequence
@@ -109,6 +112,15 @@ class SPComm:
     def barrier(self):
         check(lib.vst_comm_barrier(self.handle, torch.cuda.current_stream().cuda_stream), "vst_comm_barrier")
 
+    def allgather_partials(self, partials: torch.Tensor, dst_offset: int):
+        """partials (rows, nparts, 3) fp32 -> (rows, world*nparts, 3) at dst_offset of every rank."""
+        rows, nparts, three = partials.shape
+        assert three == 3 and partials.dtype == torch.float32 and partials.is_contiguous()
+        assert dst_offset + rows * nparts * self.world * 12 <= self.data_bytes, "symmetric buffer too small"
+        check(lib.vst_comm_allgather_partials(self.handle, partials.data_ptr(), rows, nparts, dst_offset,
+                                              torch.cuda.current_stream().cuda_stream),
+              "vst_comm_allgather_partials")
+
     def view(self, offset_bytes: int, shape, dtype=torch.bfloat16) -> torch.Tensor:
         """A tensor over this rank's own symmetric buffer."""
         n = 1
@@ -162,12 +174,24 @@ class SPMotionStep:
         hwl = h * w // comm.world
         self.n_local = self.b * hwl
         self.tok_bytes = _align(self.n_local * f_total * c * 2)
+        self.part_off = 2 * self.tok_bytes
+        self._part_shape = None
 
     def local_partials(self) -> torch.Tensor:
         return ops.groupnorm5d_partials(self.x5, self.tt.groups)
 
-    def push(self, partials_all: torch.Tensor):
-        """partials_all: the ranks' partials concatenated along dim 1 (rank order)."""
+    def share_partials(self):
+        """Store this rank's GroupNorm partials into every rank's buffer (peer stores)."""
+        part = self.local_partials()
+        rows, nparts, _ = part.shape
+        self._part_shape = (rows, nparts * self.comm.world, 3)
+        self.comm.allgather_partials(part, self.part_off)
+
+    def push(self, partials_all: Optional[torch.Tensor] = None):
+        """partials_all: the ranks' partials concatenated along dim 1 (rank order); None = the
+        block `share_partials` of all ranks filled in this rank's buffer."""
+        if partials_all is None:
+            partials_all = self.comm.view(self.part_off, self._part_shape, torch.float32)
         mean, rstd = ops.groupnorm5d_finalize(partials_all, self.tt.norm.eps)
         n = self.tt.norm
         self.comm.frames_to_hw(self.x5, self.f_total, 0, (mean, rstd, n.weight.detach(), n.bias.detach(), self.tt.groups))
@@ -191,19 +215,19 @@ class SPMotionStep:
         return out
 
     @staticmethod
-    def buffer_bytes(b: int, c: int, hw: int, f_total: int, world: int) -> int:
-        return 2 * _align(b * (hw // world) * f_total * c * 2)
+    def buffer_bytes(b: int, c: int, hw: int, f_total: int, world: int, groups: int = 32) -> int:
+        nparts = lib.vst_groupnorm5d_partials(c, f_total // world, hw, groups)
+        return 2 * _align(b * (hw // world) * f_total * c * 2) + _align(b * groups * nparts * world * 12)
 
 
 @torch.no_grad()
 def motion_module_sp(module, comm: SPComm, x_local: torch.Tensor, f_total: int, group=None) -> torch.Tensor:
-    """Inference forward of one motion module with the video's frames sharded over `group`."""
-    import torch.distributed as dist
+    """Inference forward of one motion module with the video's frames sharded over the ranks of
+    `comm`.  Graph-capturable: only kernels of this library, on the current stream."""
     step = SPMotionStep(module, comm, x_local, f_total)
-    part = step.local_partials()                                   # (B*groups, nparts, 3) fp32
-    gathered = [torch.empty_like(part) for _ in range(comm.world)]
-    dist.all_gather(gathered, part, group=group)
-    step.push(torch.cat(gathered, dim=1))
+    step.share_partials()                                          # (B*groups, nparts, 3) fp32 -> peers
+    comm.barrier()
+    step.push()
     comm.barrier()
     step.compute()
     comm.barrier()
