@@ -34,6 +34,23 @@ extern "C" {
 /* library version (major*10000 + minor*100 + patch) and last error text (thread-local). */
 int vst_version(void);
 const char* vst_last_error(void);
+/* Workspace size of any op (SURVEY.md §8b `vst_workspace_bytes(op, shape...)`): dims are the
+ * arguments of the op's own *_workspace_bytes function, in order; ops without a workspace return 0,
+ * an unknown op or too few dims a negative status. */
+#define VST_OP_REARRANGE 0
+#define VST_OP_GROUPNORM5D 1
+#define VST_OP_LAYERNORM 2
+#define VST_OP_LORA_GEMM 3
+#define VST_OP_ATTN_FWD 4
+#define VST_OP_TEMPORAL_ATTN_FWD 5
+#define VST_OP_GEGLU 6
+#define VST_OP_GEMM 7               /* dims: M, N, K1, K2 */
+#define VST_OP_COLSUM 8             /* dims: M, N */
+#define VST_OP_ATTN_BWD 9           /* dims: Bt, heads, Sq, Sk, kv_group */
+#define VST_OP_TEMPORAL_ATTN_BWD 10
+#define VST_OP_LAYERNORM_BWD 11     /* dims: rows, C */
+#define VST_OP_GROUPNORM5D_BWD 12   /* dims: B, C, F, groups */
+int64_t vst_workspace_bytes(int op, const int64_t* dims, int ndims);
 /* SM count / compute capability of the current device. */
 int vst_device_info(int* sm_count, int* cc_major, int* cc_minor);
 

@@ -371,3 +371,21 @@ def test_sequence_parallel_split_world2_gloo():
         assert p.exitcode == 0
     errs = dict(q.get(timeout=5) for _ in range(2))
     assert set(errs) == {0, 1} and max(errs.values()) < 1e-5, errs
+
+
+def test_generic_workspace_entry_matches_per_op_functions():
+    """vst_workspace_bytes(op, dims) is pure host arithmetic: no GPU needed."""
+    import ctypes as C
+    from video_style_transfer_b200._lib import lib
+
+    def generic(op, *dims):
+        arr = (C.c_int64 * len(dims))(*dims)
+        return lib.vst_workspace_bytes(op, arr, len(dims))
+
+    assert generic(7, 640, 640, 65536, 0) == lib.vst_gemm_workspace_bytes(640, 640, 65536, 0) > 0
+    assert generic(8, 65536, 640) == lib.vst_colsum_workspace_bytes(65536, 640)
+    assert generic(9, 16, 20, 1024, 77, 16) == lib.vst_attn_bwd_workspace_bytes(16, 20, 1024, 77, 16) > 0
+    assert generic(11, 4096, 320) == lib.vst_layernorm_bwd_workspace_bytes(4096, 320)
+    assert generic(12, 1, 320, 16, 32) == lib.vst_groupnorm5d_bwd_workspace_bytes(1, 320, 16, 32)
+    assert generic(4) == 0 and generic(3, 1, 2, 3) == 0          # ops without a workspace
+    assert generic(99) < 0 and generic(7, 1, 2) < 0              # unknown op / too few dims

@@ -54,6 +54,7 @@ SIGNATURES = {
     "vst_comm_init": (_i, [_i, _i, C.POINTER(_p), C.POINTER(_p), C.POINTER(_p)]),
     "vst_comm_fini": (_i, [_p]),
     "vst_comm_barrier": (_i, [_p, _p]),
+    "vst_workspace_bytes": (_l, [_i, _p, _i]),
     "vst_comm_allgather_partials": (_i, [_p, _p, _i, _i, _l, _p]),
     "vst_a2a_frames_to_hw": (_i, [_p, _p, _l, _p, _p, _p, _p, _i, _i, _i, _i, _i, _l, _l, _l, _i, _i, _p]),
     "vst_a2a_hw_to_frames": (_i, [_p, _l, _p, _p, _i, _i, _i, _i, _i, _l, _l, _l, _p]),

@@ -18,6 +18,33 @@ void vst_set_error(const char* fmt, ...) {
 extern "C" int vst_version(void) { return 100; /* 0.1.0 */ }
 extern "C" const char* vst_last_error(void) { return g_err; }
 
+// one entry point that answers "how much caller-provided workspace does op need"
+// for every op that takes one; the per-op functions stay exported too.
+extern "C" int64_t vst_workspace_bytes(int op, const int64_t* dims, int ndims) {
+  auto need = [&](int n) {
+    if (dims != nullptr && ndims >= n) return true;
+    vst_set_error("vst_workspace_bytes: op %d takes %d dims", op, n);
+    return false;
+  };
+  switch (op) {
+    case VST_OP_GEMM: return need(4) ? vst_gemm_workspace_bytes(dims[0], dims[1], dims[2], dims[3]) : VST_E_BADARG;
+    case VST_OP_COLSUM: return need(2) ? vst_colsum_workspace_bytes(dims[0], (int)dims[1]) : VST_E_BADARG;
+    case VST_OP_ATTN_BWD:
+      return need(5) ? vst_attn_bwd_workspace_bytes((int)dims[0], (int)dims[1], (int)dims[2], (int)dims[3], (int)dims[4])
+                     : VST_E_BADARG;
+    case VST_OP_LAYERNORM_BWD: return need(2) ? vst_layernorm_bwd_workspace_bytes(dims[0], (int)dims[1]) : VST_E_BADARG;
+    case VST_OP_GROUPNORM5D_BWD:
+      return need(4) ? vst_groupnorm5d_bwd_workspace_bytes((int)dims[0], (int)dims[1], (int)dims[2], (int)dims[3])
+                     : VST_E_BADARG;
+    case VST_OP_REARRANGE: case VST_OP_GROUPNORM5D: case VST_OP_LAYERNORM: case VST_OP_LORA_GEMM:
+    case VST_OP_ATTN_FWD: case VST_OP_TEMPORAL_ATTN_FWD: case VST_OP_TEMPORAL_ATTN_BWD: case VST_OP_GEGLU:
+      return 0;    // these ops take no workspace
+    default:
+      vst_set_error("vst_workspace_bytes: unknown op %d", op);
+      return VST_E_BADARG;
+  }
+}
+
 int vst_sm_count() {
   static int cached = 0;
   if (cached) return cached;
