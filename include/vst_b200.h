@@ -169,6 +169,15 @@ int vst_colsum(const void* x, int64_t ld, int64_t M, int N, float alpha, float* 
 int vst_geglu(const void* hg, void* out, int64_t rows, int inner, int64_t ld_in, int64_t ld_out,
               void* stream);
 
+/* ---- §8f-4 (next): CFG combine + Euler update of the sampler -------------------------------------
+ * inference_animatediff.py:122,131 (EulerDiscreteScheduler.step, epsilon prediction):
+ *   eps = eps_u + g (eps_c - eps_u);  latents_out = latents + (sigma_next - sigma) eps;
+ *   scaled_next (optional) = latents_out / sqrt(sigma_next^2 + 1)  (next scale_model_input).
+ * eps_* / scaled_next in eps_dtype (VST_BF16 | VST_F32), latents in latent_dtype. */
+int vst_cfg_euler_step(const void* eps_uncond, const void* eps_cond, const void* latents,
+                       void* latents_out, void* scaled_next, int64_t n, float guidance, float sigma,
+                       float sigma_next, int eps_dtype, int latent_dtype, void* stream);
+
 /* ---- a2: spatial self / text cross attention (flash, tcgen05) -------------------------------
  * animatediff/attention_processor.py:74-83 (head split, SDPA, head merge) in one kernel.
  * q,o: (Bt, Sq, heads*64) bf16; k,v: (Bk, Sk, heads*64) bf16 where batch b reads k/v batch

@@ -309,3 +309,23 @@ def test_lora_gemm_geglu_epilogue(ops, m, k, inner, bias_dtype):
     # and against the two-kernel path it replaces (bf16-rounded pre-activation)
     two = ops.geglu(ops.lora_gemm(x, w, bias=b))
     assert rel_err(got, two) < REL_TOL
+
+
+# ---- §8f-4: CFG combine + Euler update ----------------------------------------------------------------
+@pytest.mark.parametrize("edt,xdt", [(torch.bfloat16, torch.float32), (torch.bfloat16, torch.bfloat16),
+                                     (torch.float32, torch.float32)])
+def test_cfg_euler_step(ops, edt, xdt):
+    torch.manual_seed(3)
+    shape = (1, 4, 16, 32, 32)
+    eu, ec = torch.randn(shape).to(edt), torch.randn(shape).to(edt)
+    x = torch.randn(shape).to(xdt)
+    g, s, sn = 7.5, 3.1, 2.2
+    out, nxt = ops.cfg_euler_step(eu.cuda(), ec.cuda(), x.cuda(), g, s, sn, want_scaled_next=True)
+    # inference_animatediff.py:122 in the UNet dtype, then EulerDiscreteScheduler.step in fp32
+    noise = eu + g * (ec - eu)
+    want = (x.float() + (sn - s) * noise.float()).to(xdt)
+    assert out.dtype == xdt and nxt.dtype == edt
+    tol = 0 if edt == torch.float32 else 1e-2
+    assert rel_err(out, want) <= max(tol, 1e-6)
+    assert rel_err(nxt, want.float() / (sn * sn + 1) ** 0.5) < 1e-2
+    assert torch.equal(ops.cfg_euler_step(eu.cuda(), ec.cuda(), x.cuda(), g, s, sn), out)

@@ -37,6 +37,7 @@ SIGNATURES = {
     "vst_colsum_workspace_bytes": (_l, [_l, _i]),
     "vst_colsum": (_i, [_p, _l, _l, _i, _f, _p, _p, _l, _p]),
     "vst_geglu": (_i, [_p, _p, _l, _i, _l, _l, _p]),
+    "vst_cfg_euler_step": (_i, [_p, _p, _p, _p, _p, _l, _f, _f, _f, _i, _i, _p]),
     "vst_attn_bwd_workspace_bytes": (_l, [_i, _i, _i, _i, _i]),
     "vst_attn_bwd": (_i, [_p] * 9 + [_i] * 5 + [_l] * 8 + [_i, _f, _p, _l, _l, _l, _p, _l, _p]),
     "vst_temporal_attn_bwd": (_i, [_p] * 7 + [_l, _i, _i, _i] + [_l] * 7 + [_f, _p]),

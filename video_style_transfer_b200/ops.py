@@ -550,6 +550,22 @@ def groupnorm5d_bwd(x_fm: torch.Tensor, dy_fm: torch.Tensor, mean, rstd, gamma, 
     return dx, dg, db
 
 
+def cfg_euler_step(eps_uncond: torch.Tensor, eps_cond: torch.Tensor, latents: torch.Tensor,
+                   guidance: float, sigma: float, sigma_next: float, want_scaled_next: bool = False):
+    """eps = eps_u + g (eps_c - eps_u); latents + (sigma_next - sigma) eps (Euler, epsilon
+    prediction) and, optionally, the next step's scale_model_input in the eps dtype.
+    inference_animatediff.py:122,131."""
+    _cuda(eps_uncond, eps_cond, latents)
+    assert eps_uncond.shape == eps_cond.shape == latents.shape and eps_uncond.dtype == eps_cond.dtype
+    assert eps_uncond.is_contiguous() and eps_cond.is_contiguous() and latents.is_contiguous()
+    out = torch.empty_like(latents)
+    nxt = torch.empty_like(eps_uncond) if want_scaled_next else None
+    check(lib.vst_cfg_euler_step(eps_uncond.data_ptr(), eps_cond.data_ptr(), latents.data_ptr(), out.data_ptr(),
+                                 _ptr(nxt), latents.numel(), float(guidance), float(sigma), float(sigma_next),
+                                 _dt(eps_uncond), _dt(latents), _stream()), "vst_cfg_euler_step")
+    return (out, nxt) if want_scaled_next else out
+
+
 def geglu_raw(hg: torch.Tensor) -> torch.Tensor:
     hg = hg.detach()
     _cuda(hg)
