@@ -362,6 +362,301 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   }
 }
 
+// ---- persistent form ---------------------------------------------------------------------------
+// One CTA walks a strided list of (batch, head, query tile) items, two CTAs per SM.  Per item the
+// fixed costs of the one-shot kernel -- TMEM allocation, barrier set-up, the exposed latency of the
+// Q load and of the O store -- are paid once per CTA or overlapped: Q is double-buffered (the next
+// item's Q and first K / V blocks are in flight while this item finishes), O is staged in the dead
+// Q buffer and leaves by TMA while the next item computes.  It matters where an item is short:
+// L2 self-attention (8 key blocks per item) and text cross-attention (one block).  All barrier
+// phases run on global counters (g: K/V blocks loaded, blk: score blocks), not on the block index.
+constexpr int kSmemBytesP = kTile * (2 + 2 * KST) + 1024 + 256;
+
+template <int kPoly, bool kMask>
+__global__ void __launch_bounds__(192, 2)
+attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                     const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
+                     AttnArgs a, int n_items, int ntile) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  uint8_t* sQ = smem;                       // [2] query tiles (each reused to stage its item's O)
+  uint8_t* sK = sQ + 2 * kTile;             // [KST]
+  uint8_t* sV = sK + KST * kTile;           // [KST]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + KST * kTile);
+  uint64_t* q_full = bars;                  // [2]
+  uint64_t* q_empty = q_full + 2;           // [2]   the O store staged in this buffer has been read
+  uint64_t* k_full = q_empty + 2;           // [KST]
+  uint64_t* k_empty = k_full + KST;         // [KST]
+  uint64_t* v_full = k_empty + KST;         // [KST]
+  uint64_t* v_empty = v_full + KST;         // [KST]
+  uint64_t* s_full = v_empty + KST;         // S_j complete in TMEM
+  uint64_t* s_free = s_full + 1;            // S_j copied to registers by all 128 rows
+  uint64_t* p_full = s_free + 1;            // P_j in TMEM (and O rescaled if needed)
+  uint64_t* o_full = p_full + 1;            // O += P_j V_j complete
+  uint64_t* o_free = o_full + 1;            // the item's O has been read out of TMEM
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_free + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nblk = (a.Sk + BKV - 1) / BKV;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&q_full[i], 1);
+      mbar_init(&q_empty[i], 1);
+    }
+    for (int i = 0; i < KST; ++i) {
+      mbar_init(&k_full[i], 1);
+      mbar_init(&k_empty[i], 1);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&v_empty[i], 1);
+    }
+    mbar_init(s_full, 1);
+    mbar_init(s_free, 128);
+    mbar_init(p_full, 128);
+    mbar_init(o_full, 1);
+    mbar_init(o_free, 128);
+    fence_mbar_init();
+  }
+  if (warp == 4) tmem_alloc(tmem_slot, 256);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 4) {
+    // ================= TMA producer =================
+    if (lane == 0) {
+      tma_prefetch_desc(&tmQ);
+      tma_prefetch_desc(&tmK);
+      tma_prefetch_desc(&tmV);
+      uint32_t g = 0;
+      int i = 0;
+      for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++i) {
+        const int qtile = it % ntile, head = (it / ntile) % a.heads, b = it / (ntile * a.heads);
+        const int bk = b / a.kv_group, buf = i & 1;
+        mbar_wait(&q_empty[buf], ((i >> 1) & 1) ^ 1, 40);
+        mbar_arrive_expect_tx(&q_full[buf], kTile);
+        tma_load_3d(sQ + buf * kTile, &tmQ, &q_full[buf], head * HD, qtile * BQ, b);
+        for (int j = 0; j < nblk; ++j, ++g) {
+          const int st = g % KST;
+          const uint32_t ph = ((g / KST) & 1) ^ 1;
+          mbar_wait(&k_empty[st], ph, 10);
+          mbar_arrive_expect_tx(&k_full[st], kTile);
+          tma_load_3d(sK + st * kTile, &tmK, &k_full[st], head * HD, j * BKV, bk);
+          mbar_wait(&v_empty[st], ph, 11);
+          mbar_arrive_expect_tx(&v_full[st], kTile);
+          tma_load_3d(sV + st * kTile, &tmV, &v_full[st], head * HD, j * BKV, bk);
+        }
+      }
+    }
+  } else if (warp == 5) {
+    // ================= MMA issuer (whole warp in the loop, one elected lane issues) ==========
+    const bool issuer = elect_one();
+    const uint32_t tS = tmem_base;             // S (fp32) columns [0,128)
+    const uint32_t tO = tS + 128;              // O accumulator (fp32), 64 columns
+    const uint32_t tP = tS + 192;              // P (bf16 pairs), 64 columns
+    constexpr uint32_t idesc_s = umma_idesc_bf16(BQ, BKV, 0, 0);
+    constexpr uint32_t idesc_o = umma_idesc_bf16(BQ, HD, 0, 1);  // B (= V) is MN-major
+    uint32_t g = 0, blk = 0;
+    int i = 0;
+    for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++i) {
+      const int buf = i & 1;
+      const uint64_t dq = umma_desc_sw128(smem_u32(sQ + buf * kTile), 1024);
+      mbar_wait(&q_full[buf], (i >> 1) & 1, 20);
+      auto issue_s = [&](uint32_t gg) {
+        const int st = gg % KST;
+        mbar_wait(&k_full[st], (gg / KST) & 1, 21);
+        tc_fence_after();
+        const uint64_t dk = umma_desc_sw128(smem_u32(sK + st * kTile), 1024);
+        if (issuer) {
+#pragma unroll
+          for (int k = 0; k < HD / 16; ++k) umma_bf16_ss(tS, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
+          umma_commit(&k_empty[st]);
+          umma_commit(s_full);
+        }
+        __syncwarp();
+      };
+      if (blk > 0) mbar_wait(s_free, (blk - 1) & 1, 25);   // the previous item's last S is in registers
+      issue_s(g);
+      for (int j = 0; j < nblk; ++j) {
+        if (j + 1 < nblk) {
+          mbar_wait(s_free, (blk + j) & 1, 24);  // S_j is in registers: S_{j+1} overlaps softmax j
+          issue_s(g + j + 1);
+        }
+        const int st = (g + j) % KST;
+        mbar_wait(p_full, (blk + j) & 1, 22);
+        if (j == 0) mbar_wait(o_free, (i & 1) ^ 1, 26);    // the previous item's O has left TMEM
+        mbar_wait(&v_full[st], ((g + j) / KST) & 1, 23);
+        tc_fence_after();
+        const uint64_t dv = umma_desc_sw128(smem_u32(sV + st * kTile), 1024, 8192);
+        if (issuer) {
+#pragma unroll
+          for (int k = 0; k < BKV / 16; ++k)
+            umma_bf16_ts(tO, tP + 8 * k, dv + uint64_t((k * 2048) >> 4), idesc_o, (j | k) != 0);
+          umma_commit(&v_empty[st]);
+          umma_commit(o_full);
+        }
+        __syncwarp();
+      }
+      g += nblk;
+      blk += nblk;
+    }
+  } else {
+    // ================= softmax + output (warps 0..3) =================
+    const int row = warp * 32 + lane;  // query row within the tile == TMEM lane
+    const uint32_t lane_off = uint32_t(warp * 32) << 16;
+    const uint32_t tS = tmem_base + lane_off;
+    const uint32_t tO = tS + 128;
+    const uint32_t tP = tS + 192;
+    const float2 sc2 = kMask ? make_float2(1.f, 1.f) : make_float2(a.scale_log2, a.scale_log2);
+    uint32_t blk = 0;
+    int i = 0;
+    for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++i) {
+      const int qtile = it % ntile, head = (it / ntile) % a.heads, b = it / (ntile * a.heads);
+      const int qt = qtile * BQ, buf = i & 1;
+      float m = -INFINITY;               // running (possibly stale) row max, log2 domain
+      float2 l2 = make_float2(0.f, 0.f);
+      for (int j = 0; j < nblk; ++j) {
+        const int kv0 = j * BKV;
+        const bool tail = kv0 + BKV > a.Sk;
+        mbar_wait(s_full, (blk + j) & 1, 30);
+        tc_fence_after();
+        uint32_t r[BKV];
+#pragma unroll
+        for (int c = 0; c < BKV / 32; ++c) tmem_ld32(tS + c * 32, r + c * 32);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(s_free);             // the tensor pipe may overwrite S now
+        if (tail) {
+#pragma unroll
+          for (int e = 0; e < BKV; ++e)
+            if (kv0 + e >= a.Sk) r[e] = 0xff800000u;  // -inf: excluded from max, exp2 -> 0
+        }
+        if constexpr (kMask) {
+          const int qrow = min(qt + row, a.Sq - 1);
+          const float* mrow = a.mask + (int64_t)b * a.mask_sb + (int64_t)head * a.mask_sh +
+                              (int64_t)qrow * a.mask_sq + kv0;
+          constexpr float kLog2e = 1.4426950408889634f;
+          if (!tail && a.mask_vec4) {
+#pragma unroll
+            for (int e = 0; e < BKV; e += 4) {
+              const float4 mk = __ldg(reinterpret_cast<const float4*>(mrow + e));
+              r[e] = __float_as_uint(fmaf(__uint_as_float(r[e]), a.scale_log2, mk.x * kLog2e));
+              r[e + 1] = __float_as_uint(fmaf(__uint_as_float(r[e + 1]), a.scale_log2, mk.y * kLog2e));
+              r[e + 2] = __float_as_uint(fmaf(__uint_as_float(r[e + 2]), a.scale_log2, mk.z * kLog2e));
+              r[e + 3] = __float_as_uint(fmaf(__uint_as_float(r[e + 3]), a.scale_log2, mk.w * kLog2e));
+            }
+          } else {
+#pragma unroll
+            for (int e = 0; e < BKV; ++e) {
+              const float mk = kv0 + e < a.Sk ? __ldg(mrow + e) : 0.f;
+              r[e] = __float_as_uint(fmaf(__uint_as_float(r[e]), a.scale_log2, mk * kLog2e));
+            }
+          }
+        }
+        const float sl = kMask ? 1.f : a.scale_log2;
+        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+        for (int e = 0; e < BKV; e += 8) {
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
+            mx4[c] = fmaxf(mx4[c], fmaxf(__uint_as_float(r[e + 2 * c]), __uint_as_float(r[e + 2 * c + 1])));
+        }
+        const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+        const float m_cand = fmaxf(m, mx * sl);
+        const bool grow = m_cand - m > kRescaleThreshold;   // true on the first block (m = -inf)
+        const float m_use = grow ? m_cand : m;
+        const float alpha = grow ? ex2(m - m_use) : 1.f;
+        m = m_use;
+        l2 = __fmul2_rn(l2, make_float2(alpha, alpha));
+        const float2 nm2 = make_float2(-m_use, -m_use);
+#pragma unroll
+        for (int e = 0; e < BKV / 2; ++e) {
+          const float2 sv = __ffma2_rn(
+              make_float2(__uint_as_float(r[2 * e]), __uint_as_float(r[2 * e + 1])), sc2, nm2);
+          const bool poly = ((e * kPoly) & 7) + kPoly > 7 && kPoly > 0;
+          const float2 pv = poly ? ex2_poly2(sv) : make_float2(ex2(sv.x), ex2(sv.y));
+          l2 = __fadd2_rn(l2, pv);
+          r[e] = pack_bf16(pv.x, pv.y);
+        }
+        if (j > 0) {
+          mbar_wait(o_full, (blk + j - 1) & 1, 31);   // P V of the previous block is done with P and O
+          tc_fence_after();
+          if (__any_sync(0xffffffffu, grow)) {
+            const float2 al2 = make_float2(alpha, alpha);
+#pragma unroll
+            for (int c = 0; c < HD / 32; ++c) {
+              uint32_t o[32];
+              tmem_ld32(tO + c * 32, o);
+              tmem_ld_wait();
+#pragma unroll
+              for (int e = 0; e < 16; ++e) {
+                const float2 tt = __fmul2_rn(
+                    make_float2(__uint_as_float(o[2 * e]), __uint_as_float(o[2 * e + 1])), al2);
+                o[2 * e] = __float_as_uint(tt.x);
+                o[2 * e + 1] = __float_as_uint(tt.y);
+              }
+              tmem_st32(tO + c * 32, o);
+            }
+          }
+        }
+        tmem_st32(tP, r);
+        tmem_st32(tP + 32, r + 32);
+        tmem_st_wait();
+        tc_fence_before();
+        mbar_arrive(p_full);
+      }
+      // ---- normalise, stage O through this item's (dead) Q buffer, TMA store ----
+      mbar_wait(o_full, (blk + nblk - 1) & 1, 32);
+      tc_fence_after();
+      const float l = l2.x + l2.y;
+      const float inv = 1.f / l;
+      uint8_t* otile = sQ + buf * kTile;
+      uint8_t* orow = otile + row * 128;
+      const int rx = row & 7;
+#pragma unroll
+      for (int c = 0; c < HD / 32; ++c) {
+        uint32_t o[32];
+        tmem_ld32(tO + c * 32, o);
+        tmem_ld_wait();
+        if (c == HD / 32 - 1) {
+          tc_fence_before();
+          mbar_arrive(o_free);           // the next item's first P V may overwrite O
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint4 w;
+          w.x = pack_bf16(__uint_as_float(o[8 * q]) * inv, __uint_as_float(o[8 * q + 1]) * inv);
+          w.y = pack_bf16(__uint_as_float(o[8 * q + 2]) * inv, __uint_as_float(o[8 * q + 3]) * inv);
+          w.z = pack_bf16(__uint_as_float(o[8 * q + 4]) * inv, __uint_as_float(o[8 * q + 5]) * inv);
+          w.w = pack_bf16(__uint_as_float(o[8 * q + 6]) * inv, __uint_as_float(o[8 * q + 7]) * inv);
+          *reinterpret_cast<uint4*>(orow + (((c * 4 + q) ^ rx) * 16)) = w;
+        }
+      }
+      if (a.lse != nullptr && qt + row < a.Sq)
+        a.lse[((int64_t)b * a.heads + head) * a.Sq + qt + row] = (m + log2f(l)) * 0.6931471805599453f;
+      fence_proxy_async_smem();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (threadIdx.x == 0) {
+        tma_store_4d(&tmO, otile, head * HD, qt, b, 0);
+        tma_store_commit();
+        tma_store_wait_read<0>();        // smem read out: the buffer may take the Q of item i + 2
+        mbar_arrive(&q_empty[buf]);
+      }
+      blk += nblk;
+    }
+    if (threadIdx.x == 0) tma_store_wait<0>();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 256);
+  }
+}
+
 int make_qkv_map(CUtensorMap* m, const void* p, int64_t B, int64_t S, int width, int64_t ld,
                  int rank4) {
   const uint64_t dims[4] = {(uint64_t)width, (uint64_t)S, (uint64_t)B, 1};
@@ -409,6 +704,33 @@ extern "C" int vst_attn_fwd(const void* q, const void* k, const void* v, void* o
   AttnArgs a{lse, Sq, Sk, heads, kv_group, scale * 1.4426950408889634f, mask, mask_sb, mask_sh, mask_sq, vec4};
   dim3 grid((Sq + NT * BQ - 1) / (NT * BQ), heads, Bt);
   cudaStream_t st = (cudaStream_t)stream;
+  // persistent form for short key sequences (text cross-attention: one or two key blocks per item,
+  // where the per-CTA fixed costs dominate; r01: 93 -> 74 us at L1, 53 -> 43 us at L2).  For long
+  // sequences the one-shot kernel is faster (808 vs 758 TFLOP/s at Sk = 4096: the persistent loop's
+  // extra live state costs registers in the softmax loop).  VST_ATTN_PERSISTENT=0 / =2 force one
+  // form for every shape.
+  static int persistent = -1;
+  if (persistent < 0) {
+    const char* e = getenv("VST_ATTN_PERSISTENT");
+    persistent = e ? atoi(e) : 1;
+    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_pers_kernel<kDefaultPoly, false>,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesP));
+    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_pers_kernel<kDefaultPoly, true>,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesP));
+  }
+  if (poly == kDefaultPoly && (persistent == 2 || (persistent == 1 && Sk <= 2 * BKV))) {
+    const int ntile = (Sq + BQ - 1) / BQ;
+    const int64_t items = (int64_t)ntile * heads * Bt;
+    VST_REQUIRE(items < (1ll << 31), VST_E_UNSUPPORTED, "attn_fwd: too many tiles");
+    const int slots = 2 * vst_sm_count();
+    const int pgrid = (int)(items < slots ? items : slots);
+    if (mask)
+      attn_fwd_pers_kernel<kDefaultPoly, true><<<pgrid, 192, kSmemBytesP, st>>>(tQ, tK, tV, tO, a, (int)items, ntile);
+    else
+      attn_fwd_pers_kernel<kDefaultPoly, false><<<pgrid, 192, kSmemBytesP, st>>>(tQ, tK, tV, tO, a, (int)items, ntile);
+    VST_LAUNCH_OK();
+    return VST_OK;
+  }
   if (mask) {
     attn_fwd_kernel<kDefaultPoly, true><<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tO, a);
   } else {

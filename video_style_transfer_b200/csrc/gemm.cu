@@ -686,7 +686,8 @@ int launch2(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, 
                                      C::kSmemBytes));
     configured = true;
   }
-  const int m_tiles = (int)((ep.M + 2 * BM - 1) / (2 * BM)), n_tiles = geglu ? ep.N / (BN / 2) : ep.N / BN;
+  // N need not be a multiple of BN: TMA zero-fills the B rows past N and clips the stores
+  const int m_tiles = (int)((ep.M + 2 * BM - 1) / (2 * BM)), n_tiles = geglu ? ep.N / (BN / 2) : (ep.N + BN - 1) / BN;
   const int64_t tiles = (int64_t)m_tiles * n_tiles;
   const int pairs = vst_sm_count() / 2;
   const int grid = 2 * (int)(tiles < pairs ? tiles : pairs);
@@ -759,6 +760,12 @@ extern "C" int vst_lora_gemm(const void* A1, int64_t lda1, const void* B1, int64
   // CTA pairs (256-row tiles) once there is at least one tile per SM pair to keep busy
   if (act == VST_ACT_GEGLU) GO2(256);
   const bool big = M >= 2048 && !vst_force_single_cta();
+  // 256-wide pair tiles move the fewest operand bytes per MAC (64 B/clk/SM against 83 for 160):
+  // worth up to 20 % of padded columns (N = 640, 960, 1920 -> 768, 1024, 2048); r01 launch list:
+  // the BN = 160 family ran at 760 TFLOP/s, the BN = 256 family at 1260
+  if (big && (gn == 0 || gn % 256 == 0) && N > 256 && (int64_t)((N + 255) / 256) * 256 * 5 <= (int64_t)N * 6 &&
+      (M / 256) * ((N + 255) / 256) >= vst_sm_count() / 2)
+    GO2(256);
   if (big && FITS(256) && (M / 256) * (N / 256) >= vst_sm_count() / 2) GO2(256);
   if (big && FITS(160) && (M / 256) * (N / 160) >= vst_sm_count() / 2) GO2(160);
   if (big && FITS(128) && (M / 256) * (N / 128) >= vst_sm_count() / 2) GO2(128);
