@@ -188,7 +188,10 @@ def test_lora_pack_up(ops):
 # ---- a2: spatial / cross attention ------------------------------------------------------------------
 @pytest.mark.parametrize("bt,bk,heads,sq,sk", [(2, 2, 2, 128, 128), (2, 2, 3, 256, 384),
                                                (4, 2, 2, 200, 77), (1, 1, 10, 1024, 1024),
-                                               (3, 1, 1, 100, 300), (1, 1, 2, 64, 1)])
+                                               (3, 1, 1, 100, 300), (1, 1, 2, 64, 1),
+                                               # persistent form, more items than resident CTAs:
+                                               # several items per CTA, one / two key blocks each
+                                               (16, 1, 4, 1024, 77), (16, 16, 5, 512, 200)])
 def test_attn_fwd(ops, hp, bt, bk, heads, sq, sk):
     torch.manual_seed(7)
     c = heads * 64
