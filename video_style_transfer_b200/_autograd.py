@@ -120,6 +120,76 @@ class PackUpFn(torch.autograd.Function):
         return (None, None, None, None, None, like(dbc, b_c), like(dmc, m_c), like(dbs, b_s), like(dms, m_s))
 
 
+def _rows3(t2: torch.Tensor, b: int, s_: int) -> torch.Tensor:
+    """(b*s, n) column view (row stride ld) -> (b, s, n) with the same row stride."""
+    return t2.as_strided((b, s_, t2.shape[1]), (s_ * t2.stride(0), t2.stride(0), 1), t2.storage_offset())
+
+
+def _packed_grads(ts):
+    """If the (B,S,C) tensors `ts` are adjacent column slices of one packed (B*S, len*C) projection
+    output, gradient views with the same packing (one fresh buffer); else None.  The gradient of a
+    packed q|k|v then reaches the projection's backward GEMM without a single copy."""
+    t0 = ts[0]
+    b, s_, c = t0.shape
+    es = t0.element_size()
+    for i, t in enumerate(ts):
+        if t.shape != t0.shape or t.stride() != t0.stride() or t.data_ptr() != t0.data_ptr() + i * c * es:
+            return None
+    if t0.stride(1) != len(ts) * c or t0.stride(0) != s_ * t0.stride(1):
+        return None
+    buf = torch.empty((b * s_, len(ts) * c), dtype=torch.bfloat16, device=t0.device)
+    return [_rows3(buf[:, i * c:(i + 1) * c], b, s_) for i in range(len(ts))]
+
+
+class SplitColsFn(torch.autograd.Function):
+    """y (M, count*n0) -> count column views, 2-D or (b, s, n0).  Backward: when the incoming
+    gradients are already the column slices of one packed buffer (AttnFn / TemporalAttnFn write them
+    that way) it is returned as is; otherwise they are packed with one copy each -- instead of
+    autograd's as_strided / slice backward (a zero fill of the whole packed tensor, a strided copy
+    and an add per slice: 27 % of the Stage-2 training step in the r01 launch list)."""
+
+    @staticmethod
+    def forward(ctx, y, n0, count, b, s_):
+        ctx.cfg = (n0, count, y.shape[0], b, s_)
+        ctx.set_materialize_grads(False)
+        outs = []
+        for i in range(count):
+            v = y[:, i * n0:(i + 1) * n0]
+            outs.append(v if b is None else _rows3(v, b, s_))
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, *gs):
+        n0, count, m, b, s_ = ctx.cfg
+        g0 = next((g for g in gs if g is not None), None)
+        if g0 is None:
+            return None, None, None, None, None
+        es = g0.element_size()
+        ld = g0.stride(-2)
+        packed = all(g is not None and g.dtype == g0.dtype and g.shape == g0.shape and g.stride() == g0.stride()
+                     and g.data_ptr() == g0.data_ptr() + i * n0 * es for i, g in enumerate(gs))
+        packed = packed and g0.stride(-1) == 1 and ld == count * n0 and (g0.dim() == 2 or g0.stride(0) == s_ * ld)
+        if packed:
+            return g0.as_strided((m, count * n0), (ld, 1), g0.storage_offset()), None, None, None, None
+        buf = torch.empty((m, count * n0), dtype=g0.dtype, device=g0.device)
+        for i, g in enumerate(gs):
+            dst = buf[:, i * n0:(i + 1) * n0]
+            if g is None:
+                dst.zero_()
+            else:
+                (dst if b is None else _rows3(dst, b, s_)).copy_(g)
+        return buf, None, None, None, None
+
+
+def split_cols(y: torch.Tensor, n0: int, count: int, batch=None):
+    """Column views of a packed projection output; differentiable without autograd's slice glue."""
+    b, s_ = batch if batch is not None else (None, None)
+    if torch.is_grad_enabled() and y.requires_grad:
+        return list(SplitColsFn.apply(y, n0, count, b, s_))
+    outs = [y[:, i * n0:(i + 1) * n0] for i in range(count)]
+    return outs if b is None else [_rows3(v, b, s_) for v in outs]
+
+
 class AttnFn(torch.autograd.Function):
     """softmax(q k^T * scale) v per head (vst_attn_fwd) with the flash backward (vst_attn_bwd)."""
 
@@ -139,7 +209,15 @@ class AttnFn(torch.autograd.Function):
         if g.dtype != torch.bfloat16 or g.stride(2) != 1 or g.stride(0) != g.shape[1] * g.stride(1) \
                 or g.stride(1) % 8:
             g = g.to(torch.bfloat16).contiguous()
-        dq, dk, dv = ops.attn_bwd(q.detach(), k.detach(), v.detach(), o, g, lse, heads, scale, ctx.mask)
+        out = None
+        if q.shape == k.shape:
+            pk = _packed_grads([q, k, v])                   # self-attention: packed q|k|v
+            out = None if pk is None else tuple(pk)
+        else:
+            pk = _packed_grads([k, v])                      # cross-attention: packed k|v
+            if pk is not None:
+                out = (torch.empty(q.shape, dtype=torch.bfloat16, device=q.device), pk[0], pk[1])
+        dq, dk, dv = ops.attn_bwd(q.detach(), k.detach(), v.detach(), o, g, lse, heads, scale, ctx.mask, out=out)
         return dq, dk, dv, None, None, None
 
 
@@ -159,7 +237,9 @@ class TemporalAttnFn(torch.autograd.Function):
     def backward(ctx, d_o):
         q, k, v = ctx.saved_tensors
         heads, scale = ctx.cfg
-        dq, dk, dv = ops.temporal_attn_bwd(q.detach(), k.detach(), v.detach(), _dense_bf16(d_o), heads, scale)
+        pk = _packed_grads([q, k, v])
+        dq, dk, dv = ops.temporal_attn_bwd(q.detach(), k.detach(), v.detach(), _dense_bf16(d_o), heads, scale,
+                                           out=None if pk is None else tuple(pk))
         return dq, dk, dv, None, None
 
 

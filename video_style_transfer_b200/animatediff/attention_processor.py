@@ -55,24 +55,21 @@ class AnimateDiffAttnProcessor2_0:
         x2 = as_rows_bf16(hidden_states)
         if encoder_hidden_states is None:
             # self-attention: q | k | v read the same tokens -> one GEMM, N = 3C
-            q, k, v = project_fused((attn.to_q, attn.to_k, attn.to_v), x2, lora_scale)
+            q, k, v = project_fused((attn.to_q, attn.to_k, attn.to_v), x2, lora_scale, batch=(batch_size, seq_q))
             kv_batch, seq_k = batch_size, seq_q
         else:
             q = self._proj(attn.to_q, x2, lora_scale)
+            q = q.view(batch_size, seq_q, q.shape[1])
             if attn.norm_cross:
                 encoder_hidden_states = attn.norm_encoder_hidden_states(encoder_hidden_states)
             kv_batch, seq_k = encoder_hidden_states.shape[:2]
             if batch_size % kv_batch != 0:
                 raise ValueError("text batch must divide the B*F batch")
             e2 = as_rows_bf16(encoder_hidden_states)       # NOT repeated: kv_group handles :62-66
-            k, v = project_fused((attn.to_k, attn.to_v), e2, lora_scale)   # one GEMM, N = 2C
+            k, v = project_fused((attn.to_k, attn.to_v), e2, lora_scale, batch=(kv_batch, seq_k))   # N = 2C
         inner = k.shape[-1]
-
-        def rows3(t, b_, s_):      # (b*s, inner) column view -> (b, s, inner) with the same row stride
-            return t.as_strided((b_, s_, inner), (s_ * t.stride(0), t.stride(0), 1), t.storage_offset())
-
-        o = ops.attn_fwd(rows3(q, batch_size, seq_q), rows3(k, kv_batch, seq_k),
-                         rows3(v, kv_batch, seq_k), attn.heads, mask=attention_mask)
+        # q / k / v: (b, s, inner) column views of the packed projection output (packed row stride)
+        o = ops.attn_fwd(q, k, v, attn.heads, mask=attention_mask)
         o2 = o.view(batch_size * seq_q, inner)
 
         fuse_res = (attn.residual_connection and input_ndim == 3 and residual.dtype == torch.bfloat16

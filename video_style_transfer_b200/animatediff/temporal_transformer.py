@@ -65,8 +65,10 @@ class TemporalTransformerBlock(nn.Module):
         sd, bf = x.dtype, torch.bfloat16
         x2 = x.view(n * f, c)
         xn = ops.layernorm(x2, self.norm1.weight, self.norm1.bias, self.norm1.eps, out_dtype=bf)
-        qkv = fused_linear(xn, self.attn.in_proj_weight, self.attn.in_proj_bias).view(n, f, 3 * c)
-        o = ops.temporal_attn(qkv[..., :c], qkv[..., c:2 * c], qkv[..., 2 * c:], self.num_heads)
+        from .._autograd import split_cols
+        qkv = fused_linear(xn, self.attn.in_proj_weight, self.attn.in_proj_bias)        # (N*F, 3C) packed
+        q, k, v = split_cols(qkv, c, 3, (n, f))
+        o = ops.temporal_attn(q, k, v, self.num_heads)
         x2 = fused_linear(o.view(n * f, c), self.attn.out_proj.weight, self.attn.out_proj.bias,
                           residual=x2, out_dtype=sd)
         xn = ops.layernorm(x2, self.norm2.weight, self.norm2.bias, self.norm2.eps, out_dtype=bf)

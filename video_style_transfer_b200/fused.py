@@ -105,9 +105,10 @@ def project_one(layer, x2: torch.Tensor, scale: float = 1.0, residual=None, out_
     return fused_linear(x2, s.site_weight(), s.site_bias(), low, residual, out_scale, act, out_dtype)
 
 
-def project_fused(layers: Sequence, x2: torch.Tensor, scale: float = 1.0) -> List[torch.Tensor]:
+def project_fused(layers: Sequence, x2: torch.Tensor, scale: float = 1.0, batch=None) -> List[torch.Tensor]:
     """[layer(x) for layer in layers] as column views of one (M, sum out) GEMM result when the
-    layers are compatible; otherwise one fused GEMM per layer."""
+    layers are compatible; otherwise one fused GEMM per layer.  batch = (b, s) returns the views as
+    (b, s, out) with the packed row stride (what the attention kernels take)."""
     sites = [_site(l) for l in layers]
     ws = [s.site_weight() for s in sites]
     n0 = ws[0].shape[0]
@@ -118,7 +119,8 @@ def project_fused(layers: Sequence, x2: torch.Tensor, scale: float = 1.0) -> Lis
     same = (len(sites) > 1 and all(w.shape == ws[0].shape for w in ws) and n0 % 64 == 0
             and len(k2s) == 1 and (all(b is None for b in biases) or all(b is not None for b in biases)))
     if not same:
-        return [project_one(l, x2, scale) for l in layers]
+        ys = [project_one(l, x2, scale) for l in layers]
+        return ys if batch is None else [y.view(batch[0], batch[1], y.shape[1]) for y in ys]
     k2_any = next(iter(k2s))
     merge = (k2_any is not None and MERGE_LORA
              and _frozen(list(ws) + [a for d in downs for a in d] + [u for u in ups if u is not None]))
@@ -142,4 +144,5 @@ def project_fused(layers: Sequence, x2: torch.Tensor, scale: float = 1.0) -> Lis
             bp = cached_build(list(ups), "catup", lambda: torch.cat(list(ups), dim=0).contiguous())
         u = ops.lora_gemm(x2, a_cat)                                    # (M, G*K2)
         y = ops.lora_gemm(x2, w, u, bp, bias=bias, k2_group_n=n0)
-    return [y[:, i * n0:(i + 1) * n0] for i in range(len(sites))]
+    from ._autograd import split_cols
+    return split_cols(y, n0, len(sites), batch)

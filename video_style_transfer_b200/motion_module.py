@@ -45,12 +45,9 @@ class TemporalAttention(nn.Module):
     def forward_tokens(self, xn: torch.Tensor, n: int, f: int, residual: torch.Tensor):
         """xn, residual: (N*F, C) bf16 -> residual + to_out(attn(q,k,v))."""
         c = xn.shape[1]
-        q, k, v = project_fused((self.to_q, self.to_k, self.to_v), xn)     # one GEMM, N = 3C
-
-        def seq(t):   # (N*F, C) column view of the packed result -> (N, F, C), same row stride
-            return t.as_strided((n, f, c), (f * t.stride(0), t.stride(0), 1), t.storage_offset())
-
-        o = ops.temporal_attn(seq(q), seq(k), seq(v), self.heads)
+        # one GEMM, N = 3C; q / k / v are (N, F, C) column views with the packed row stride
+        q, k, v = project_fused((self.to_q, self.to_k, self.to_v), xn, batch=(n, f))
+        o = ops.temporal_attn(q, k, v, self.heads)
         return _project(self.to_out[0], o.view(n * f, c), residual=residual)
 
 

@@ -210,17 +210,26 @@ def temporal_attn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int,
     return temporal_attn_raw(q, k, v, heads, scale)
 
 
-def temporal_attn_bwd(q, k, v, d_o, heads: int, scale: Optional[float] = None):
+def temporal_attn_bwd(q, k, v, d_o, heads: int, scale: Optional[float] = None, out=None):
+    """out: optional (dq, dk, dv) bf16 (N,F,C) tensors to write (contiguous C, dense (N,F); e.g.
+    column views of one packed buffer)."""
     _cuda(q, k, v, d_o)
     n, f, c = q.shape
     d = c // heads
     for t in (q, k, v, d_o):
         if t.dtype != torch.bfloat16 or t.stride(2) != 1 or t.stride(0) != f * t.stride(1):
             raise ValueError("temporal_attn_bwd: bf16 (N,F,C) tensors with contiguous C and dense (N,F)")
-    dq, dk, dv = (torch.empty((n, f, c), dtype=torch.bfloat16, device=q.device) for _ in range(3))
+    if out is None:
+        dq, dk, dv = (torch.empty((n, f, c), dtype=torch.bfloat16, device=q.device) for _ in range(3))
+    else:
+        dq, dk, dv = out
+        for t in out:
+            if t.shape != (n, f, c) or t.dtype != torch.bfloat16 or t.stride(2) != 1 or t.stride(0) != f * t.stride(1):
+                raise ValueError("temporal_attn_bwd: out tensors must be bf16 (N,F,C), contiguous C, dense (N,F)")
     check(lib.vst_temporal_attn_bwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), d_o.data_ptr(),
                                     dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), n, f, heads, d,
-                                    q.stride(1), k.stride(1), v.stride(1), d_o.stride(1), c, c, c,
+                                    q.stride(1), k.stride(1), v.stride(1), d_o.stride(1), dq.stride(1),
+                                    dk.stride(1), dv.stride(1),
                                     scale if scale is not None else 1.0 / math.sqrt(d), _stream()),
           "vst_temporal_attn_bwd")
     return dq, dk, dv
@@ -458,8 +467,9 @@ def _bsc(t: torch.Tensor, name: str):
 
 
 def attn_bwd(q, k, v, o, d_o, lse, heads: int, scale: Optional[float] = None,
-             mask: Optional[torch.Tensor] = None):
-    """(dq, dk, dv) of attn_fwd; dk / dv have the (Bk, Sk, C) shape of k / v."""
+             mask: Optional[torch.Tensor] = None, out=None):
+    """(dq, dk, dv) of attn_fwd; dk / dv have the (Bk, Sk, C) shape of k / v.  out: optional
+    (dq, dk, dv) tensors to write (e.g. column views of one packed gradient buffer)."""
     _cuda(q, k, v, o, d_o, lse)
     bt, sq, c = q.shape
     bk, sk, _ = k.shape
@@ -467,9 +477,15 @@ def attn_bwd(q, k, v, o, d_o, lse, heads: int, scale: Optional[float] = None,
     for t, nm in ((q, "q"), (k, "k"), (v, "v"), (o, "o"), (d_o, "d_o")):
         _bsc(t, nm)
     assert lse.dtype == torch.float32 and lse.is_contiguous() and lse.shape == (bt, heads, sq)
-    dq = torch.empty((bt, sq, c), dtype=torch.bfloat16, device=q.device)
-    dk = torch.empty((bk, sk, c), dtype=torch.bfloat16, device=q.device)
-    dv = torch.empty((bk, sk, c), dtype=torch.bfloat16, device=q.device)
+    if out is None:
+        dq = torch.empty((bt, sq, c), dtype=torch.bfloat16, device=q.device)
+        dk = torch.empty((bk, sk, c), dtype=torch.bfloat16, device=q.device)
+        dv = torch.empty((bk, sk, c), dtype=torch.bfloat16, device=q.device)
+    else:
+        dq, dk, dv = out
+        assert dq.shape == (bt, sq, c) and dk.shape == (bk, sk, c) and dv.shape == (bk, sk, c)
+        for t, nm in ((dq, "dq"), (dk, "dk"), (dv, "dv")):
+            _bsc(t, nm)
     wsb = lib.vst_attn_bwd_workspace_bytes(bt, heads, sq, sk, bt // bk)
     ws = torch.empty(wsb + 256, dtype=torch.uint8, device=q.device)
     off = (-ws.data_ptr()) % 256
