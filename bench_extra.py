@@ -5,7 +5,8 @@ warm-up steps, barrier + synchronize on both sides, max over ranks); each prints
   cfg2  UnZipLoRA attention processor fwd+bwd at the SDXL mid-block geometry (C=1280, 20 heads,
         16 x 1024 tokens, text 1 x 77 x 2048, rank-64 content+style), self and cross, Stage-2
         (mergers + dX) and Stage-1 (A, B, mergers + dX) trainable sets.
-  cfg4  one Stage-2 training step of the hot-path stack (fwd + bwd + clip + AdamW), 16 frames.
+  cfg4  one Stage-2 training step of the hot-path stack (fwd + bwd + clip + AdamW), 16 frames; every
+        module output receives a synthetic upstream gradient (the rest of the UNet is out of scope).
   cfg5  one denoising step of ONE 32-frame video, sequence-parallel over --gpus ranks
         (frames <-> positions all-to-alls fused into the layout kernels, peer memory over NVLink).
 """
@@ -173,9 +174,10 @@ def run_cfg4(args, common):
     xs4 = [torch.randn(s, generator=g).to(bf).to(dev) for s in shapes]
     xs3 = [None] + [torch.randn(s[0], s[2] * s[3], s[1], generator=g).to(bf).to(dev) for s in shapes[1:]]
     text = torch.randn(1, 77, 2048, generator=g).to(bf).to(dev)
-    targets = {"motion": [torch.randn(s, generator=g).to(bf).to(dev) for s in shapes],
-               "self": [None] + [torch.randn_like(t) for t in xs3[1:]],
-               "cross": [None] + [torch.randn_like(t) for t in xs3[1:]]}
+    # upstream gradients dL/dy of every module output (what the rest of the UNet would send back)
+    targets = {"motion": [(1e-3 * torch.randn(s, generator=g)).to(bf).to(dev) for s in shapes],
+               "self": [None] + [1e-3 * torch.randn_like(t) for t in xs3[1:]],
+               "cross": [None] + [1e-3 * torch.randn_like(t) for t in xs3[1:]]}
 
     def step_eager():
         return hpth.train_step_hotpath(model, plan, xs4, xs3, text, targets, F, opt, index)
@@ -233,7 +235,7 @@ def run_cfg4(args, common):
                        "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2 ** 30, 1),
                        "step_tflop_fwd_plus_dx": step_fl / 1e12},
             "tflops_fwd_plus_dx": step_fl / (ms * 1e-3) / 1e12,
-            "loss": float(loss), "gpu_launches": launches, "clocks": clk.summary()}
+            "orth_loss": float(loss), "gpu_launches": launches, "clocks": clk.summary()}
     print(json.dumps(line), flush=True)
 
 

@@ -239,17 +239,20 @@ def freeze_for_stage2(model: nn.Module, unfreeze_mergers: bool = True):
     return out
 
 
-def train_step_hotpath(model, plan, xs4, xs3, text, targets, frames: int, optimizer, spatial_index,
+def train_step_hotpath(model, plan, xs4, xs3, text, upstream, frames: int, optimizer, spatial_index,
                        lambda_orth: float = 1e-4, max_grad_norm: float = 1.0):
     """One Stage-2 training step over the hot-path stack (train_animatediff.py:212-317 restricted
-    to SURVEY.md §8): forward of every module with autograd, MSE against `targets` + the temporal /
-    spatial orthogonality loss, backward, gradient clipping, optimizer step.  The inputs require
-    grad (inside the UNet every module has to return dX to the layer before it)."""
+    to SURVEY.md §8): forward of every module with autograd, ONE backward pass in which every
+    module output receives its upstream gradient `upstream[kind][level]` (inside the UNet that
+    gradient comes from the layers behind the module; the reference's MSE sits on the final UNet
+    output, :298-300) together with the temporal / spatial orthogonality loss (:307-308), gradient
+    clipping (:316), optimizer step (:317).  The inputs require grad (every module has to return dX
+    to the layer before it)."""
     from .animatediff.temporal_lora import compute_orth_loss
     optimizer.zero_grad(set_to_none=True)
     x4 = [t.detach().requires_grad_(True) for t in xs4]
     x3 = [None] + [t.detach().requires_grad_(True) for t in xs3[1:]]
-    loss = None
+    outs, grads = [], []
     for kind, lvl, mod in plan:
         if kind == "self":
             y = mod(x3[lvl])
@@ -257,15 +260,17 @@ def train_step_hotpath(model, plan, xs4, xs3, text, targets, frames: int, optimi
             y = mod(x3[lvl], encoder_hidden_states=text)
         else:
             y = mod(x4[lvl], num_frames=frames)
-        term = torch.nn.functional.mse_loss(y.float(), targets[kind][lvl].float())
-        loss = term if loss is None else loss + term
+        outs.append(y)
+        grads.append(upstream[kind][lvl])
     orth = compute_orth_loss(model, spatial_index, lambda_orth)
-    loss = loss + orth.to(loss.device)
-    loss.backward()
+    if orth.requires_grad:
+        outs.append(orth)
+        grads.append(torch.ones_like(orth))
+    torch.autograd.backward(outs, grads)
     params = [p for g in optimizer.param_groups for p in g["params"]]
     torch.nn.utils.clip_grad_norm_(params, max_grad_norm)
     optimizer.step()
-    return loss.detach()
+    return orth.detach()
 
 
 def hotpath_flops(plan, frames: int, latent: int = 128, batch: int = 1, merged: bool = False):
