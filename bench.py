@@ -317,6 +317,13 @@ def run_ours(args):
     step_eager()
     torch.cuda.synchronize()
     apmod.ops.attn_fwd = orig
+    # DRAM traffic of the dominant kernel from the committed `ncu --set full` capture (per launch,
+    # L1 self-attention shape), profiles/ncu_traffic.json
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["attn_fwd_kernel"]
+    except Exception:
+        pass
     attn_ms = sum(s.elapsed_time(e) for s, e, _ in ev)
     attn_fl = sum(f for _, _, f in ev)
     achieved = attn_fl / (attn_ms * 1e-3) / 1e12
@@ -352,7 +359,9 @@ def run_ours(args):
         "tflops_hotpath": step_flops / (ms_step * 1e-3) / 1e12,
         "roofline": {"kernel": "attn_fwd_kernel (spatial self-attention)", "bound": "tensor",
                      "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
-                     "frac": achieved / peak_tf, "traffic": None,
+                     "frac": achieved / peak_tf,
+                     "traffic": None if traffic is None else traffic["dram_bytes_per_launch"],
+                     "traffic_note": None if traffic is None else traffic["note"],
                      "peak_source": f"bf16_tflops_sustained, {pk_src}",
                      "launches_timed": len(ev), "share_of_step": attn_ms / ms_step},
     }

@@ -1,0 +1,154 @@
+#!/usr/bin/env python
+"""Turn one scripts/gpu_round3.sh result set (gpurun_out/) into the tracked files under profiles/.
+
+  python scripts/collect_profiles.py [tag]          # tag defaults to r01_final
+Writes bench lines, the kbench log, the per-kernel launch summary of one bench step, compact
+summaries of the three ncu --set full captures, and profiles/ncu_traffic.json (the DRAM bytes per
+launch bench.py reports as roofline.traffic).
+"""
+import csv
+import gzip
+import json
+import os
+import shutil
+import sys
+from collections import defaultdict
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+OUT = os.path.join(ROOT, "gpurun_out")
+PROF = os.path.join(ROOT, "profiles")
+
+KEEP = [
+    ("gpu__time_duration.sum", "time"),
+    ("sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm_pct"),
+    ("sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed", "tensor_pct"),
+    ("TPC.TriageCompute.sm__pipe_tensor_cycles_active_realtime.avg.pct_of_peak_sustained_elapsed", "tensor_rt_pct"),
+    ("sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active", "xu_pct"),
+    ("dram__bytes_read.sum", "dram_read"),
+    ("dram__bytes_write.sum", "dram_write"),
+    ("dram__throughput.avg.pct_of_peak_sustained_elapsed", "dram_pct"),
+    ("lts__t_bytes.sum", "l2_bytes"),
+    ("lts__throughput.avg.pct_of_peak_sustained_elapsed", "l2_pct"),
+    ("l1tex__throughput.avg.pct_of_peak_sustained_active", "l1_pct"),
+    ("sm__warps_active.avg.pct_of_peak_sustained_active", "occupancy_pct"),
+    ("smsp__issue_active.avg.pct", "issue_pct"),
+    ("launch__registers_per_thread", "regs"),
+    ("launch__shared_mem_per_block_dynamic", "dyn_smem"),
+    ("sm__cycles_elapsed.max", "cycles"),
+]
+
+UNIT = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0, "Tbyte": 1e12,
+        "us": 1.0, "ms": 1e3, "ns": 1e-3, "s": 1e6, "second": 1e6, "usecond": 1.0, "msecond": 1e3, "nsecond": 1e-3}
+
+
+def last_json(path):
+    with open(path) as f:
+        lines = [l for l in f if l.strip().startswith("{")]
+    return json.loads(lines[-1])
+
+
+def raw_rows(path):
+    with open(path, newline="") as f:
+        rows = list(csv.reader(f))
+    start = next(i for i, r in enumerate(rows) if r and r[0] == "ID")
+    head, units = rows[start], rows[start + 1]
+    out = []
+    for r in rows[start + 2:]:
+        if len(r) != len(head):
+            continue
+        d = {}
+        for h, u, v in zip(head, units, r):
+            d[h] = (v, u)
+        out.append(d)
+    return out
+
+
+def num(cell):
+    v, u = cell
+    try:
+        x = float(v.replace(",", ""))
+    except ValueError:
+        return None
+    return x * UNIT.get(u, 1.0)
+
+
+def summarise_raw(name, tag):
+    src = os.path.join(OUT, f"prof_{name}_raw.csv")
+    if not os.path.exists(src):
+        return []
+    rows = raw_rows(src)
+    dst = os.path.join(PROF, f"ncu_{name}_full_{tag}.csv")
+    cols = [(k, s) for k, s in KEEP if rows and k in rows[0]]
+    with open(dst, "w", newline="") as f:
+        w = csv.writer(f)
+        w.writerow(["id", "kernel", "grid", "block"] + [s for _, s in cols])
+        w.writerow(["", "", "", ""] + ["us" if s == "time" else "bytes" if s in ("dram_read", "dram_write", "l2_bytes", "dyn_smem") else "" for _, s in cols])
+        for r in rows:
+            w.writerow([r["ID"][0], r["Kernel Name"][0][:70], r.get("Grid Size", ("", ""))[0], r.get("Block Size", ("", ""))[0]]
+                       + ["%.6g" % num(r[k]) if num(r[k]) is not None else r[k][0] for k, _ in cols])
+    return rows
+
+
+def launch_summary(tag):
+    src = os.path.join(OUT, "launches.csv")
+    if not os.path.exists(src):
+        return
+    with open(src, newline="") as f:
+        rows = list(csv.reader(f))
+    start = next(i for i, r in enumerate(rows) if r and r[0] == "ID")
+    head = rows[start]
+    ki, vi, ui = head.index("Kernel Name"), head.index("Metric Value"), head.index("Metric Unit")
+    tot, cnt = defaultdict(float), defaultdict(int)
+    for r in rows[start + 1:]:
+        if len(r) != len(head):
+            continue
+        k = r[ki].split("(")[0]
+        tot[k] += float(r[vi].replace(",", "")) * UNIT.get(r[ui], 1.0)
+        cnt[k] += 1
+    total = sum(tot.values())
+    with open(os.path.join(PROF, f"launch_summary_{tag}.csv"), "w", newline="") as f:
+        w = csv.writer(f)
+        w.writerow(["kernel", "launches", "total_us", "share"])
+        for k in sorted(tot, key=tot.get, reverse=True):
+            w.writerow([k, cnt[k], "%.1f" % tot[k], "%.3f" % (tot[k] / total)])
+        w.writerow(["TOTAL (serialised, cold cache)", sum(cnt.values()), "%.1f" % total, "1.000"])
+
+
+def main():
+    tag = sys.argv[1] if len(sys.argv) > 1 else "r01_final"
+    for src, dst in [("bench.json", f"bench_{tag}.json"), ("bench_lowrank.json", f"bench_{tag}_lowrank.json"),
+                     ("bench_reference.json", f"bench_{tag}_reference.json"), ("bench_cfg2.json", f"bench_{tag}_cfg2.json"),
+                     ("bench_cfg4.json", f"bench_{tag}_cfg4.json"), ("bench_cfg5_p1.json", f"bench_{tag}_cfg5_sp1.json")]:
+        p = os.path.join(OUT, src)
+        if os.path.exists(p):
+            with open(os.path.join(PROF, dst), "w") as f:
+                f.write(json.dumps(last_json(p)) + "\n")
+    if os.path.exists(os.path.join(OUT, "kbench.log")):
+        shutil.copy(os.path.join(OUT, "kbench.log"), os.path.join(PROF, f"kbench_{tag}.log"))
+    launch_summary(tag)
+    traffic = {}
+    for name in ("attn", "gemm", "attn_bwd"):
+        rows = summarise_raw(name, tag)
+        if name == "attn" and rows:
+            # the dominant launch: L1 spatial self-attention, the longest attn_fwd_kernel captured
+            best = max((r for r in rows if "attn_fwd_kernel" in r["Kernel Name"][0]),
+                       key=lambda r: num(r["gpu__time_duration.sum"]))
+            rd, wr = num(best["dram__bytes_read.sum"]), num(best["dram__bytes_write.sum"])
+            traffic["attn_fwd_kernel"] = {
+                "dram_bytes_per_launch": rd + wr, "dram_read": rd, "dram_write": wr,
+                "duration_us_under_ncu": num(best["gpu__time_duration.sum"]),
+                "note": f"ncu --set full, kbench attn L1 self (B=16 h=10 S=4096 d=64), launch id {best['ID'][0]}; "
+                        f"see profiles/ncu_attn_full_{tag}.csv"}
+    if traffic:
+        with open(os.path.join(PROF, "ncu_traffic.json"), "w") as f:
+            json.dump(traffic, f, indent=1)
+            f.write("\n")
+    for name in ("attn", "attn_bwd"):
+        p = os.path.join(OUT, f"prof_{name}_source.csv.gz")
+        if os.path.exists(p) and os.path.getsize(p) < 1_000_000:
+            shutil.copy(p, os.path.join(PROF, f"ncu_{name}_source_{tag}.csv.gz"))
+    print("profiles/ refreshed with tag", tag)
+
+
+if __name__ == "__main__":
+    main()

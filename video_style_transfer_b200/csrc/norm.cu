@@ -269,6 +269,8 @@ layernorm_flat_kernel(const TI* __restrict__ x, TO* __restrict__ y, const TP* __
   const int lane = threadIdx.x & 31;
   const int64_t row0 = ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * ROWS;
   if (row0 >= rows) return;
+  // frame index of the warp's first row: ONE 64-bit modulo per warp instead of one per vector
+  const int f0 = pe ? (int)(row0 % F) : 0;
   float v[5][8];
   int rr[5], vv[5];
 #pragma unroll
@@ -348,7 +350,9 @@ layernorm_flat_kernel(const TI* __restrict__ x, TO* __restrict__ y, const TP* __
     }
     if (pe) {
       float pr[8];
-      loadp8<float>(pe + (int)(row % F) * C + vv[i] * 8, pr);
+      int fr = f0 + rr[i];             // rr < 4 <= F in every caller; the loop covers tiny F too
+      while (fr >= F) fr -= F;
+      loadp8<float>(pe + fr * C + vv[i] * 8, pr);
 #pragma unroll
       for (int j = 0; j < 8; ++j) o[j] = (float)(TO)o[j] + pr[j];   // two roundings, as in torch
     }
