@@ -50,6 +50,8 @@ const char* vst_last_error(void);
 #define VST_OP_TEMPORAL_ATTN_BWD 10
 #define VST_OP_LAYERNORM_BWD 11     /* dims: rows, C */
 #define VST_OP_GROUPNORM5D_BWD 12   /* dims: B, C, F, groups */
+#define VST_OP_LORA_GEMM_BWD_DX 13
+#define VST_OP_LORA_GEMM_BWD_PARAMS 14   /* dims: M, N, K, Klow, R */
 int64_t vst_workspace_bytes(int op, const int64_t* dims, int ndims);
 /* SM count / compute capability of the current device. */
 int vst_device_info(int* sm_count, int* cc_major, int* cc_minor);
@@ -157,6 +159,36 @@ int vst_lora_pack_up_bwd(const float* dBp, int64_t ld, int rp, const void* Bc, c
                          const uint8_t* maskc, const void* Bs, const void* ms,
                          const uint8_t* masks, float scale, float* dBc, float* dmc, float* dBs,
                          float* dms, int N, int r, int param_dtype, void* stream);
+/* ---- SURVEY.md §8b names of one LoRA linear: forward / dX / parameter gradients -----------------
+ * vst_lora_gemm_fwd is vst_lora_gemm (same arguments).  The two backward calls are the arithmetic
+ * torch autograd derives for lora_linear.py:74-81 + unziplora_linear_layer.py:221-263, 298-346,
+ * lora_unzip.py:66-75 and temporal_lora.py:29-32 (the reference trains through autograd,
+ * train_animatediff.py:314), expressed on the fused operands of the forward:
+ *   y = x W^T + u B'^T,  u = x_low A^T,  A = [A_c ; A_s] (R, Klow),  B' = vst_lora_pack_up (N, R).
+ * vst_lora_gemm_bwd_dx:     dU[M,R] = dY B' (bf16, kept for bwd_params) and
+ *                           dX[M,K] (+)= alpha (dY W + dU A)  -- A is added only when the adapter read
+ *                           the same stream as the base projection (single stream, Klow = K); for the
+ *                           three-stream form pass R = 0 here and get the streams' own gradient
+ *                           dX_low = dU A from vst_gemm.  R = 0: plain dX = alpha dY W.
+ * vst_lora_gemm_bwd_params: dW[N,K] = dY^T X, dA[R,Klow] = dU^T Xlow, dB'[N,R] = dY^T U (fp32, dense
+ *                           row-major, any may be NULL; contraction over the M tokens, deterministic
+ *                           split-K through `workspace`).  dB_c / dB_s / d-merger follow from dB' by
+ *                           vst_lora_pack_up_bwd.  Xlow NULL = X. */
+int vst_lora_gemm_fwd(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1,
+                      const void* A2, int64_t lda2, const void* B2, int64_t ldb2, int K2,
+                      int k2_group_n, const void* bias, int bias_dtype, const void* residual, int64_t ldr,
+                      float out_scale, int act, void* D, int64_t ldd, int64_t M, int N,
+                      int out_dtype, void* stream);
+int vst_lora_gemm_bwd_dx(const void* dY, int64_t lddy, const void* W, int64_t ldw, const void* Bp,
+                         int64_t ldbp, const void* A, int64_t lda, int R, void* dU, int64_t lddu,
+                         void* dX, int64_t lddx, int64_t M, int N, int K, float alpha, int accumulate,
+                         int out_dtype, void* stream);
+int64_t vst_lora_gemm_bwd_params_workspace_bytes(int64_t M, int N, int K, int Klow, int R);
+int vst_lora_gemm_bwd_params(const void* dY, int64_t lddy, const void* X, int64_t ldx,
+                             const void* Xlow, int64_t ldxl, const void* U, int64_t ldu,
+                             const void* dU, int64_t lddu, float* dW, float* dA, float* dBp,
+                             int64_t M, int N, int K, int Klow, int R, int accumulate,
+                             void* workspace, int64_t workspace_bytes, void* stream);
 /* out[n] = alpha * sum_m x[m, n] (bf16 in, fp32 out): the bias gradient.  Deterministic two-stage
  * sum through a caller workspace of vst_colsum_workspace_bytes(M, N) bytes. */
 int64_t vst_colsum_workspace_bytes(int64_t M, int N);

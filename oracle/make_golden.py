@@ -27,8 +27,134 @@ def _close(a, b, tol, what):
     return err
 
 
+def _import_stage1_processor():
+    """unziplora_unet/unzip_attention_processor.py imports diffusers (absent here) for the base
+    class of its ``Attention`` and a few helpers.  ``AttnProcessor2_0.__call__`` (:664-759) itself
+    only touches ``attn.*`` and F.scaled_dot_product_attention, so the import lines are satisfied
+    with empty stand-ins: no diffusers code runs, the processor body that runs is the reference's."""
+    def stub(name, **attrs):
+        m = types.ModuleType(name)
+        m.__dict__.update(attrs)
+        sys.modules.setdefault(name, m)
+
+    class _Log:
+        def __getattr__(self, k):
+            return lambda *a, **kw: None
+
+    stub("diffusers")
+    stub("diffusers.utils", USE_PEFT_BACKEND=False, deprecate=lambda *a, **kw: None,
+         logging=types.SimpleNamespace(get_logger=lambda n: _Log()))
+    stub("diffusers.models")
+    stub("diffusers.models.attention_processor", Attention=torch.nn.Module)
+    stub("diffusers.utils.import_utils", is_xformers_available=lambda: False)
+    stub("diffusers.utils.torch_utils", maybe_allow_in_graph=lambda c: c)
+    import unziplora_unet.unzip_attention_processor as uap
+    return uap.AttnProcessor2_0
+
+
+def stage1_golden(report):
+    """a6: the Stage-1 three-stream processor (unzip_attention_processor.py:664-759) run on
+    lora_unzip.LoRACompatibleLinear + UnZipLoRALinearLayer (train, hard masks).  The processor
+    spells the two extra streams ``hidden_states_content`` / ``hidden_states_style`` while the
+    linear it is wired to spells them ``hidden_states_1`` / ``hidden_states_2`` (lora_unzip.py:66);
+    ``_Kw`` below is that renaming and nothing else."""
+    from unziplora_unet.unziplora_linear_layer import UnZipLoRALinearLayer
+    import unziplora_unet.lora_unzip as lora_unzip
+    from oracle import processor as op
+    Proc = _import_stage1_processor()
+
+    class _Kw(torch.nn.Module):
+        def __init__(self, lin):
+            super().__init__()
+            self.lin = lin
+
+        def forward(self, hidden_states, hidden_states_content=None, hidden_states_style=None):
+            return self.lin(hidden_states, 1.0, hidden_states_content, hidden_states_style)
+
+    C, heads, ctx, rr = 128, 2, 24, 8
+    torch.manual_seed(11)
+
+    def mk(i, o, bias):
+        l = lora_unzip.LoRACompatibleLinear(i, o, bias=bias)
+        ll = UnZipLoRALinearLayer(i, o, rr, ["content", "style"], lora_matrix_num=2)
+        with torch.no_grad():
+            ll.merge_content.uniform_(0, 1)
+            ll.merge_style.uniform_(0, 1)
+        ll.mask_content = torch.rand(o) > 0.3
+        ll.mask_style = torch.rand(o) > 0.3
+        l.set_lora_layer(ll)
+        return l
+
+    def oproj(l, grad=False):
+        ll, d = l.lora_layer, l.lora_layer.lora_matrix_dic
+        f = (lambda t: t.detach().clone().requires_grad_(True)) if grad else (lambda t: t.detach())
+        return op.UnzipProj(l.weight.detach(), None if l.bias is None else l.bias.detach(),
+                            f(d["content_down"].weight), f(d["content_up"].weight),
+                            f(d["style_down"].weight), f(d["style_up"].weight),
+                            f(ll.merge_content), f(ll.merge_style), ll.forward_type,
+                            ll.masked_matrix["content"], ll.masked_matrix["style"], infer=False,
+                            mask_c=ll.mask_content, mask_s=ll.mask_style)
+
+    g = {}
+    proc = Proc()
+    for kind in ("self", "cross"):
+        kv_in = C if kind == "self" else ctx
+        lins = dict(to_q=mk(C, C, False), to_k=mk(kv_in, C, False), to_v=mk(kv_in, C, False),
+                    to_out=mk(C, C, True))
+        attn = types.SimpleNamespace(
+            spatial_norm=None, group_norm=None, norm_cross=False, heads=heads,
+            to_q=_Kw(lins["to_q"]), to_k=_Kw(lins["to_k"]), to_v=_Kw(lins["to_v"]),
+            to_out=torch.nn.ModuleList([_Kw(lins["to_out"]), torch.nn.Dropout(0.0)]),
+            residual_connection=(kind == "self"), rescale_output_factor=1.5 if kind == "self" else 1.0)
+        hs = torch.randn(3, 20, C, requires_grad=True)
+        if kind == "self":
+            e = ec = es = None
+        else:
+            e, ec, es = (torch.randn(3, 11, ctx, requires_grad=True) for _ in range(3))
+        y = proc(attn, hs, encoder_hidden_states=e, encoder_hidden_states_content=ec,
+                 encoder_hidden_states_style=es)
+        dy = torch.randn_like(y)
+        y.backward(dy)
+        # oracle restatement, forward and gradients
+        hs_o = hs.detach().clone().requires_grad_(True)
+        eo = [None if t is None else t.detach().clone().requires_grad_(True) for t in (e, ec, es)]
+        P = op.SpatialAttnParams(heads, oproj(lins["to_q"], True), oproj(lins["to_k"], True),
+                                 oproj(lins["to_v"], True), oproj(lins["to_out"], True),
+                                 attn.residual_connection, attn.rescale_output_factor)
+        yo = op.stage1_attn_processor(P, hs_o, *eo)
+        report[f"stage1_{kind}"] = _close(yo, y.detach(), 2e-5, f"stage-1 processor {kind}")
+        yo.backward(dy)
+        _close(hs_o.grad, hs.grad, 2e-5, f"stage-1 {kind} d hidden_states")
+        g[f"{kind}/hs"], g[f"{kind}/y"], g[f"{kind}/dy"], g[f"{kind}/d_hs"] = hs, y, dy, hs.grad
+        for nm, t, to in (("e", e, eo[0]), ("ec", ec, eo[1]), ("es", es, eo[2])):
+            if t is not None:
+                _close(to.grad, t.grad, 2e-5, f"stage-1 {kind} d {nm}")
+                g[f"{kind}/{nm}"], g[f"{kind}/d_{nm}"] = t, t.grad
+        g[f"{kind}/meta"] = np.array([heads, int(attn.residual_connection)])
+        g[f"{kind}/rescale"] = attn.rescale_output_factor
+        for nm, l in lins.items():
+            ll, d, po = l.lora_layer, l.lora_layer.lora_matrix_dic, getattr(P, nm)
+            g[f"{kind}/{nm}/weight"] = l.weight
+            if l.bias is not None:
+                g[f"{kind}/{nm}/bias"] = l.bias
+            for fld, t, to in (("a_c", d["content_down"].weight, po.a_c), ("b_c", d["content_up"].weight, po.b_c),
+                               ("a_s", d["style_down"].weight, po.a_s), ("b_s", d["style_up"].weight, po.b_s),
+                               ("m_c", ll.merge_content, po.m_c), ("m_s", ll.merge_style, po.m_s)):
+                g[f"{kind}/{nm}/{fld}"] = t
+                _close(to.grad, t.grad, 5e-5, f"stage-1 {kind} d {nm}.{fld}")
+                g[f"{kind}/{nm}/d_{fld}"] = t.grad
+            g[f"{kind}/{nm}/mask_c"], g[f"{kind}/{nm}/mask_s"] = ll.mask_content, ll.mask_style
+    np.savez_compressed(os.path.join(OUT, "stage1_processor.npz"), **_np(g))
+
+
 def main():
     sys.path.insert(0, REF)
+    if sys.argv[1:] == ["stage1"]:          # only the Stage-1 fixture (the others are unchanged)
+        rep = {}
+        os.makedirs(OUT, exist_ok=True)
+        stage1_golden(rep)
+        print(rep)
+        return
     from animatediff.temporal_transformer import TemporalTransformer, PositionalEncoding
     from animatediff.attention_processor import AnimateDiffAttnProcessor2_0
     from animatediff.temporal_lora import TemporalLoRALinear
@@ -353,6 +479,8 @@ def main():
             _close(op.animatediff_attn_processor(P, hs4, None, scale=0.9), y4, 2e-5, "4-D")
             g["self/hs4"], g["self/y4"] = hs4, y4
     np.savez_compressed(os.path.join(OUT, "attn_processor.npz"), **_np(g))
+
+    stage1_golden(report)
 
     for k, v in report.items():
         print(f"{k}: oracle-vs-reference rel err {v:.2e}")

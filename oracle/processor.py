@@ -89,28 +89,37 @@ def animatediff_attn_processor(p: SpatialAttnParams, hidden_states, encoder_hidd
 
 
 def stage1_attn_processor(p: SpatialAttnParams, hidden_states, ehs=None, ehs_content=None,
-                          ehs_style=None, scale: float = 1.0):
+                          ehs_style=None, attention_mask=None):
     """Stage-1 AttnProcessor2_0 with three text streams.
     unziplora_unet/unzip_attention_processor.py:664-759 executed against
     lora_unzip.py:66-75 semantics (hidden_states_content/_style -> hidden_states_1/_2);
-    self-attention aliases all three streams to hidden_states (:711-714)."""
-    residual = hidden_states
-    batch = hidden_states.shape[0]
-    q = p.to_q(hidden_states, scale, hidden_states, hidden_states)
-    if ehs is None:
+    self-attention aliases all three streams to hidden_states (:711-714).  ``scale`` is accepted
+    by the reference (:675) but never forwarded: every projection runs at its default 1.0.
+    (spatial_norm / group_norm / norm_cross are None on the SDXL path and are not restated.)"""
+    residual = hidden_states                                             # :677
+    input_ndim = hidden_states.ndim
+    if input_ndim == 4:                                                  # :683-685
+        bsz, ch, hh, ww = hidden_states.shape
+        hidden_states = hidden_states.view(bsz, ch, hh * ww).transpose(1, 2)
+    batch = hidden_states.shape[0] if ehs is None else ehs.shape[0]      # :687-689
+    q = p.to_q(hidden_states, 1.0, hidden_states, hidden_states)         # :706-708
+    if ehs is None:                                                      # :711-714
         ehs = ehs_content = ehs_style = hidden_states
-    k = p.to_k(ehs, scale, ehs_content, ehs_style)
-    v = p.to_v(ehs, scale, ehs_content, ehs_style)
-    d = k.shape[-1] // p.heads
+    k = p.to_k(ehs, 1.0, ehs_content, ehs_style)                         # :720-725
+    v = p.to_v(ehs, 1.0, ehs_content, ehs_style)
+    d = k.shape[-1] // p.heads                                           # :727-728
 
     def sp(t):
-        return t.reshape(batch, -1, p.heads, d).transpose(1, 2)
+        return t.reshape(batch, -1, p.heads, d).transpose(1, 2)          # :730-733
 
-    o = hp.sdpa(sp(q), sp(k), sp(v)).transpose(1, 2).reshape(batch, -1, p.heads * d)
-    o = p.to_out(o, scale, o, o)
-    if p.residual_connection:
+    o = hp.sdpa(sp(q), sp(k), sp(v), attention_mask)                     # :737-739
+    o = o.transpose(1, 2).reshape(batch, -1, p.heads * d)                # :741
+    o = p.to_out(o, 1.0, o, o)                                           # :745-747
+    if input_ndim == 4:                                                  # :751-752
+        o = o.transpose(-1, -2).reshape(bsz, ch, hh, ww)
+    if p.residual_connection:                                            # :754-755
         o = o + residual
-    return o / p.rescale_output_factor
+    return o / p.rescale_output_factor                                   # :757
 
 
 # --------------------------------------------------------------------------------------

@@ -2,6 +2,7 @@
 _bwd_params, vst_attn_bwd, vst_temporal_attn_bwd, norm / GEGLU gradients), through the C ABI,
 against fp32 torch-CPU autograd of the oracle functions on the same seeded inputs.
 Tolerance: bf16 operands, fp32 accumulation -> max|a-b| / max|b| <= 1e-2 per tensor."""
+import ctypes
 import math
 
 import pytest
@@ -306,6 +307,119 @@ def test_attn_processor_fwd_bwd_midblock_vs_oracle(kind):
 
 
 # ---- a8 / K9 / §8f-1 / a10 backward kernels vs fp32 autograd --------------------------------------------
+
+
+@pytest.mark.parametrize("m,n,k,r", [(300, 136, 72, 16), (1024, 640, 640, 128), (77, 64, 2048, 0)])
+def test_lora_linear_c_abi_fwd_bwd(m, n, k, r):
+    """SURVEY §8b names: vst_lora_gemm_fwd, vst_lora_gemm_bwd_dx, vst_lora_gemm_bwd_params called raw
+    through ctypes, against fp32 autograd of y = x W^T + (x A^T) B'^T on the same bf16 operands."""
+    from video_style_transfer_b200 import _lib
+    lib = _lib.lib
+    torch.manual_seed(0)
+    dev = "cuda"
+    bf = lambda *s_, sc=1.0: (torch.randn(*s_, device=dev) * sc).to(torch.bfloat16)
+    x, w, dy = bf(m, k), bf(n, k, sc=k ** -0.5), bf(m, n)
+    a = bf(r, k, sc=k ** -0.5) if r else None
+    bp = bf(n, r, sc=r ** -0.5) if r else None
+    st = torch.cuda.current_stream().cuda_stream
+    P = lambda t: 0 if t is None else t.data_ptr()
+    # forward: u = x A^T, y = x W^T + u B'^T
+    u = torch.empty(m, r, dtype=torch.bfloat16, device=dev) if r else None
+    if r:
+        _lib.check(lib.vst_lora_gemm_fwd(P(x), k, P(a), k, k, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 1.0, 0, P(u), r, m, r, 1, st),
+                   "u")
+    y = torch.empty(m, n, dtype=torch.bfloat16, device=dev)
+    _lib.check(lib.vst_lora_gemm_fwd(P(x), k, P(w), k, k, P(u), r, P(bp), r, r, 0, 0, 0, 0, 0, 1.0, 0, P(y), n, m, n,
+                                     1, st), "y")
+    # fp32 reference
+    xf, wf = x.float().requires_grad_(True), w.float().requires_grad_(True)
+    af = a.float().requires_grad_(True) if r else None
+    bpf = bp.float().requires_grad_(True) if r else None
+    yf = xf @ wf.t()
+    if r:
+        yf = yf + (xf @ af.t()) @ bpf.t()
+    assert rel_err(y, yf) < 1e-2
+    yf.backward(dy.float())
+    # backward
+    du = torch.empty(m, r, dtype=torch.bfloat16, device=dev) if r else None
+    dx = torch.empty(m, k, dtype=torch.bfloat16, device=dev)
+    _lib.check(lib.vst_lora_gemm_bwd_dx(P(dy), n, P(w), k, P(bp), r, P(a), k, r, P(du), r, P(dx), k, m, n, k, 1.0, 0,
+                                        1, st), "dx")
+    assert rel_err(dx, xf.grad) < 1e-2
+    wsb = lib.vst_lora_gemm_bwd_params_workspace_bytes(m, n, k, k, r)
+    assert wsb >= 0
+    dims = (ctypes.c_int64 * 5)(m, n, k, k, r)
+    assert lib.vst_workspace_bytes(14, dims, 5) == wsb
+    ws = torch.empty(max(wsb, 1), dtype=torch.uint8, device=dev)
+    dw = torch.empty(n, k, dtype=torch.float32, device=dev)
+    da = torch.empty(r, k, dtype=torch.float32, device=dev) if r else None
+    dbp = torch.empty(n, r, dtype=torch.float32, device=dev) if r else None
+    _lib.check(lib.vst_lora_gemm_bwd_params(P(dy), n, P(x), k, 0, 0, P(u), r, P(du), r, P(dw), P(da), P(dbp), m, n, k,
+                                            k, r, 0, P(ws), wsb, st), "params")
+    assert rel_err(dw, wf.grad) < 1e-2
+    if r:
+        assert rel_err(da, af.grad) < 1.5e-2
+        assert rel_err(dbp, bpf.grad) < 1e-2
+    # bad arguments are refused with a message, not executed
+    assert lib.vst_lora_gemm_bwd_dx(0, n, P(w), k, 0, 0, 0, 0, 0, 0, 0, P(dx), k, m, n, k, 1.0, 0, 1, st) != 0
+    assert b"required" in lib.vst_last_error()
+
+
+@pytest.mark.parametrize("kind", ["self", "cross"])
+def test_stage1_processor_golden_fwd_bwd(kind):
+    """a6: the Stage-1 three-stream processor drop-in (unzip_attention_processor.py:664-759) against the
+    fixture made by the reference's own processor: output, d hidden_states, d of the three text streams,
+    and dA / dB / d-merger of every projection (hard column masks on the train layers)."""
+    import types
+    from video_style_transfer_b200.unziplora_unet.unzip_attention_processor import AttnProcessor2_0
+    from video_style_transfer_b200.unziplora_unet.lora_unzip import LoRACompatibleLinear
+    from video_style_transfer_b200.unziplora_unet.unziplora_linear_layer import UnZipLoRALinearLayer
+    g = np.load(os.path.join(GOLD, "stage1_processor.npz"))
+
+    def mk(nm):
+        f = _sub(g, f"{kind}/{nm}/")
+        out_f, in_f = f["weight"].shape
+        lin = LoRACompatibleLinear(in_f, out_f, bias="bias" in f)
+        lay = UnZipLoRALinearLayer(in_f, out_f, f["a_c"].shape[0], ["content", "style"], lora_matrix_num=2)
+        with torch.no_grad():
+            lin.weight.copy_(f["weight"])
+            if "bias" in f:
+                lin.bias.copy_(f["bias"])
+            d = lay.lora_matrix_dic
+            d["content_down"].weight.copy_(f["a_c"]); d["content_up"].weight.copy_(f["b_c"])
+            d["style_down"].weight.copy_(f["a_s"]); d["style_up"].weight.copy_(f["b_s"])
+            lay.merge_content.copy_(f["m_c"]); lay.merge_style.copy_(f["m_s"])
+        lin.set_lora_layer(lay)
+        lin = lin.cuda()
+        lay.mask_content, lay.mask_style = f["mask_c"].cuda(), f["mask_s"].cuda()
+        return lin, f
+
+    lins = {nm: mk(nm) for nm in ("to_q", "to_k", "to_v", "to_out")}
+    heads, res = [int(v) for v in g[f"{kind}/meta"]]
+    attn = types.SimpleNamespace(
+        spatial_norm=None, group_norm=None, norm_cross=False, heads=heads, to_q=lins["to_q"][0],
+        to_k=lins["to_k"][0], to_v=lins["to_v"][0],
+        to_out=torch.nn.ModuleList([lins["to_out"][0], torch.nn.Dropout(0.0)]),
+        residual_connection=bool(res), rescale_output_factor=float(g[f"{kind}/rescale"]))
+    T = lambda k: torch.from_numpy(np.asarray(g[k])).cuda()
+    hs = T(f"{kind}/hs").requires_grad_(True)
+    txt = {n: T(f"cross/{n}").requires_grad_(True) for n in ("e", "ec", "es")} if kind == "cross" else {}
+    y = AttnProcessor2_0()(attn, hs, encoder_hidden_states=txt.get("e"),
+                           encoder_hidden_states_content=txt.get("ec"),
+                           encoder_hidden_states_style=txt.get("es"), scale=0.5)   # scale is ignored (:675)
+    _close(y, T(f"{kind}/y").cpu(), "y")
+    y.backward(T(f"{kind}/dy"))
+    _close(hs.grad, T(f"{kind}/d_hs").cpu(), "d hidden_states", 3e-2)
+    for n, t in txt.items():
+        _close(t.grad, T(f"cross/d_{n}").cpu(), f"d {n}", 3e-2)
+    for nm, (lin, f) in lins.items():
+        d, lay = lin.lora_layer.lora_matrix_dic, lin.lora_layer
+        for fld, t in (("a_c", d["content_down"].weight), ("b_c", d["content_up"].weight),
+                       ("a_s", d["style_down"].weight), ("b_s", d["style_up"].weight),
+                       ("m_c", lay.merge_content), ("m_s", lay.merge_style)):
+            _close(t.grad, f["d_" + fld], f"{nm}.{fld}", 3e-2)
+
+
 @pytest.mark.parametrize("n,f,heads,d", [(64, 16, 8, 40), (33, 16, 8, 80), (9, 32, 8, 160), (17, 5, 2, 16)])
 def test_temporal_attn_bwd_vs_autograd(ops, n, f, heads, d):
     torch.manual_seed(n + f + d)

@@ -108,8 +108,32 @@ def test_oracle_processor_golden(kind):
     close(op.animatediff_attn_processor(p, T(g[f"{kind}/hs"]), ehs, scale=0.9), T(g[f"{kind}/y"]), 2e-5)
     if kind == "self":
         close(op.animatediff_attn_processor(p, T(g["self/hs4"]), None, scale=0.9), T(g["self/y4"]), 2e-5)
-        # Stage-1 three-stream processor degenerates to the same result for self-attention
-        close(op.stage1_attn_processor(p, T(g["self/hs"]), scale=0.9), T(g["self/y"]), 2e-5)
+
+
+@pytest.mark.parametrize("kind", ["self", "cross"])
+def test_oracle_stage1_processor_golden(kind):
+    """a6: oracle vs the fixture made by the reference's own Stage-1 AttnProcessor2_0
+    (unzip_attention_processor.py:664-759) on lora_unzip linears + train-mode UnZipLoRA layers."""
+    from oracle import processor as op
+    g = np.load(os.path.join(GOLD, "stage1_processor.npz"))
+
+    def proj(nm):
+        f = sub(g, f"{kind}/{nm}/")
+        return op.UnzipProj(f["weight"], f.get("bias"), f["a_c"], f["b_c"], f["a_s"], f["b_s"],
+                            f["m_c"], f["m_s"], infer=False, mask_c=f["mask_c"], mask_s=f["mask_s"])
+
+    heads, res = [int(v) for v in g[f"{kind}/meta"]]
+    p = op.SpatialAttnParams(heads, proj("to_q"), proj("to_k"), proj("to_v"), proj("to_out"),
+                             bool(res), float(g[f"{kind}/rescale"]))
+    hs = T(g[f"{kind}/hs"]).requires_grad_(True)
+    txt = [T(g[f"cross/{n}"]).requires_grad_(True) for n in ("e", "ec", "es")] if kind == "cross" else [None] * 3
+    y = op.stage1_attn_processor(p, hs, *txt)
+    close(y, T(g[f"{kind}/y"]), 2e-5)
+    y.backward(T(g[f"{kind}/dy"]))
+    close(hs.grad, T(g[f"{kind}/d_hs"]), 2e-5)
+    if kind == "cross":
+        for t, n in zip(txt, ("e", "ec", "es")):
+            close(t.grad, T(g[f"cross/d_{n}"]), 2e-5)
 
 
 def test_oracle_motion_module_shapes():

@@ -29,6 +29,14 @@ SIGNATURES = {
     "vst_temporal_attn_fwd": (_i, [_p, _p, _p, _p, _l, _i, _i, _i, _l, _l, _l, _l, _f, _p]),
     "vst_lora_gemm": (_i, [_p, _l, _p, _l, _i, _p, _l, _p, _l, _i, _i, _p, _i, _p, _l, _f, _i, _p, _l,
                            _l, _i, _i, _p]),
+    "vst_lora_gemm_fwd": (_i, [_p, _l, _p, _l, _i, _p, _l, _p, _l, _i, _i, _p, _i, _p, _l, _f, _i, _p, _l,
+                               _l, _i, _i, _p]),
+    # dY lddy W ldw Bp ldbp A lda R dU lddu dX lddx M N K alpha accumulate out_dtype stream
+    "vst_lora_gemm_bwd_dx": (_i, [_p, _l, _p, _l, _p, _l, _p, _l, _i, _p, _l, _p, _l, _l, _i, _i, _f, _i, _i, _p]),
+    "vst_lora_gemm_bwd_params_workspace_bytes": (_l, [_l, _i, _i, _i, _i]),
+    # dY lddy X ldx Xlow ldxl U ldu dU lddu dW dA dBp M N K Klow R accumulate workspace bytes stream
+    "vst_lora_gemm_bwd_params": (_i, [_p, _l, _p, _l, _p, _l, _p, _l, _p, _l, _p, _p, _p, _l, _i, _i, _i, _i, _i,
+                                      _p, _l, _p]),
     "vst_lora_pack_up": (_i, [_p, _p, _p, _p, _p, _p, _f, _p, _i, _i, _i, _p]),
     "vst_gemm_workspace_bytes": (_l, [_l, _i, _l, _l]),
     "vst_gemm": (_i, [_p, _l, _p, _l, _l, _p, _l, _p, _l, _l, _i, _i, _p, _l, _l, _i, _f, _i, _i, _p,

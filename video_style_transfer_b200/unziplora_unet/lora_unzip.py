@@ -2,7 +2,12 @@
 ``LoRACompatibleLinear`` of Stage 1 -- the base projection reads ``hidden_states`` while the
 content / style low-rank branches read ``hidden_states_1`` / ``hidden_states_2``.  Still one fused
 GEMM: the up-projections ride as extra K-blocks, only the rank-r down-projections see the other
-two streams."""
+two streams.
+
+The Stage-1 processor of the reference calls these linears with the keywords
+``hidden_states_content=`` / ``hidden_states_style=`` (unzip_attention_processor.py:706-708,
+720-725, 745-747) while this class spells them ``hidden_states_1`` / ``hidden_states_2`` (:66);
+both spellings are accepted here and mean the same streams."""
 from typing import Optional
 
 import torch
@@ -15,7 +20,13 @@ from .lora_linear import LoRALinearLayer  # noqa: F401  (the reference re-export
 class LoRACompatibleLinear(_Base):
     def forward(self, hidden_states: torch.Tensor, scale: float = 1.0,
                 hidden_states_1: torch.Tensor = None,
-                hidden_states_2: torch.Tensor = None) -> torch.Tensor:
+                hidden_states_2: torch.Tensor = None, *,
+                hidden_states_content: torch.Tensor = None,
+                hidden_states_style: torch.Tensor = None) -> torch.Tensor:
+        if hidden_states_1 is None:
+            hidden_states_1 = hidden_states_content
+        if hidden_states_2 is None:
+            hidden_states_2 = hidden_states_style
         x2 = as_rows_bf16(hidden_states)
         if self.lora_layer is None:
             y = self.fused_forward(x2, scale)
