@@ -413,3 +413,110 @@ def test_generic_workspace_entry_matches_per_op_functions():
     assert generic(12, 1, 320, 16, 32) == lib.vst_groupnorm5d_bwd_workspace_bytes(1, 320, 16, 32)
     assert generic(4) == 0 and generic(3, 1, 2, 3) == 0          # ops without a workspace
     assert generic(99) < 0 and generic(7, 1, 2) < 0              # unknown op / too few dims
+
+
+# ---- §8f-3: on-disk formats round-trip through the drop-in wiring (host logic, no GPU) --------------------
+class _ToyAttn(torch.nn.Module):
+    def __init__(self, c, kv):
+        super().__init__()
+        self.to_q = torch.nn.Linear(c, c, bias=False)
+        self.to_k = torch.nn.Linear(kv, c, bias=False)
+        self.to_v = torch.nn.Linear(kv, c, bias=False)
+        self.to_out = torch.nn.ModuleList([torch.nn.Linear(c, c), torch.nn.Dropout(0.0)])
+
+
+class _ToyUNet(torch.nn.Module):
+    def __init__(self, c=16, ctx=24):
+        super().__init__()
+        blk = lambda: torch.nn.ModuleDict({"attn1": _ToyAttn(c, c), "attn2": _ToyAttn(c, ctx)})
+        self.down_blocks = torch.nn.ModuleList([torch.nn.ModuleDict({"transformer_blocks": torch.nn.ModuleList([blk()])})])
+        self.motion_modules = torch.nn.ModuleList([torch.nn.ModuleDict({"attn1": _ToyAttn(c, c)})])
+
+    @property
+    def attn_processors(self):      # diffusers naming: "<attention module>.processor"
+        return {n + ".processor": None for n, m in self.named_modules() if isinstance(m, _ToyAttn)}
+
+
+def test_unziplora_formats_round_trip(tmp_path):
+    """LoRA safetensors (unet.unet.{attn}.{part}.lora.{down,up}.weight) + merger .pth
+    (unet.{attn}.{part}.lora.merge_*) -> insert_unziplora_to_unet -> layers hold exactly those tensors,
+    base Parameters are shared, motion modules are skipped; Stage-2 mergers save in the format the
+    loader reads (reference unziplora_unet/utils.py:324-483, animatediff/utils.py:137-163)."""
+    from safetensors.torch import save_file
+    from video_style_transfer_b200.unziplora_unet import utils as U
+    from video_style_transfer_b200.animatediff import utils as AU
+    torch.manual_seed(0)
+    unet, r = _ToyUNet(), 4
+    names = U.spatial_attention_names(unet)
+    assert len(names) == 2 and all("motion_modules" not in n for n in names)
+    files, mergers = {}, {}
+    for branch in ("content", "style"):
+        sd, md = {}, {}
+        for n in names:
+            attn = unet.get_submodule(n)
+            for part in U.PARTS:
+                lin = attn.get_submodule(part)
+                sd[f"unet.unet.{n}.{part}.lora.down.weight"] = torch.randn(r, lin.in_features)
+                sd[f"unet.unet.{n}.{part}.lora.up.weight"] = torch.randn(lin.out_features, r)
+                md[f"unet.{n}.{part}.lora.merge_{branch}"] = torch.rand(lin.out_features)
+        d = tmp_path / branch
+        d.mkdir()
+        save_file(sd, str(d / U.LORA_WEIGHT_NAME_SAFE))
+        torch.save(md, str(tmp_path / f"merger_{branch}.pth"))
+        files[branch], mergers[branch] = sd, md
+    w_q = unet.down_blocks[0]["transformer_blocks"][0]["attn1"].to_q.weight
+    U.insert_unziplora_to_unet(unet, str(tmp_path / "content"), str(tmp_path / "style"),
+                               str(tmp_path / "merger_content.pth"), str(tmp_path / "merger_style.pth"), rank=r)
+    assert unet.down_blocks[0]["transformer_blocks"][0]["attn1"].to_q.weight is w_q      # Parameters shared
+    assert not hasattr(unet.motion_modules[0]["attn1"].to_q, "lora_layer")               # motion skipped
+    for n in names:
+        for part in U.PARTS:
+            lay = unet.get_submodule(n).get_submodule(part).lora_layer
+            for branch in ("content", "style"):
+                for half in ("down", "up"):
+                    assert torch.equal(lay.lora_matrix_dic[f"{branch}_{half}"].weight,
+                                       files[branch][f"unet.unet.{n}.{part}.lora.{half}.weight"])
+                assert torch.equal(getattr(lay, f"merge_{branch}"), mergers[branch][f"unet.{n}.{part}.lora.merge_{branch}"])
+    U.unziplora_set_forward_type(unet, "style")
+    assert all(l.forward_type == "style" for _, l in U._lora_sites(unet))
+    # Stage-2 merger files: same keys as the files loaded above
+    with torch.no_grad():
+        for _, l in U._lora_sites(unet):
+            l.merge_content.mul_(0.5)
+    counts = AU.freeze_spatial_layers(unet, unfreeze_mergers=True)
+    assert counts["mergers"] == sum(l.merge_content.numel() + l.merge_style.numel() for _, l in U._lora_sites(unet))
+    assert all(p.requires_grad == ("motion_modules" in k or "merge_" in k) for k, p in unet.named_parameters())
+    path = AU.save_checkpoint(unet, str(tmp_path), 7, save_mergers=True)
+    mc = torch.load(os.path.join(path, "merger_content_stage2.pth"))
+    assert set(mc) == set(mergers["content"])
+    k0 = next(iter(mc))
+    assert torch.equal(mc[k0], mergers["content"][k0] * 0.5)
+    motion = torch.load(os.path.join(path, "motion_modules.pth"))
+    assert set(motion) == {k for k in unet.state_dict() if "motion_modules" in k}
+    # and the merger files load straight back through the inference wiring
+    unet2 = _ToyUNet()
+    U.insert_unziplora_to_unet(unet2, files["content"], files["style"], os.path.join(path, "merger_content_stage2.pth"),
+                               os.path.join(path, "merger_style_stage2.pth"), rank=r)
+    lay2 = unet2.get_submodule(names[0]).to_q.lora_layer
+    assert torch.equal(lay2.merge_content, mc[f"unet.{names[0]}.to_q.lora.merge_content"])
+
+
+def test_stage1_export_key_format():
+    """unet_inverse_ziplora_state_dict (reference unziplora_unet/utils.py:288-310): merger-folded up
+    matrices and the merger itself under ``unet.{linear}.lora.*`` keys."""
+    from video_style_transfer_b200.unziplora_unet import utils as U
+    from video_style_transfer_b200.unziplora_unet.unziplora_linear_layer import UnZipLoRALinearLayer
+    torch.manual_seed(1)
+    unet = _ToyUNet()
+    attn = unet.down_blocks[0]["transformer_blocks"][0]["attn2"]
+    U._make_lora_compatible(attn, "to_k")
+    lay = UnZipLoRALinearLayer(24, 16, 4, ["content", "style"], lora_matrix_num=2)
+    with torch.no_grad():
+        lay.merge_style.uniform_(0, 1)
+    attn.to_k.set_lora_layer(lay)
+    lora_sd, mask_sd = U.unet_inverse_ziplora_state_dict(unet, "style")
+    stem = "unet.down_blocks.0.transformer_blocks.0.attn2.to_k.lora"
+    assert set(lora_sd) == {stem + ".up.weight", stem + ".down.weight"} and set(mask_sd) == {stem + ".merge_style"}
+    assert torch.equal(lora_sd[stem + ".down.weight"], lay.lora_matrix_dic["style_down"].weight)
+    assert torch.allclose(lora_sd[stem + ".up.weight"], lay.lora_matrix_dic["style_up"].weight * lay.merge_style[:, None])
+    assert torch.equal(mask_sd[stem + ".merge_style"], lay.merge_style)
