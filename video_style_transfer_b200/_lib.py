@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libvst_b200.so")
+# VST_LIB_PATH: load another build of the same library (A/B timing of two builds in one GPU call)
+LIB_PATH = os.environ.get("VST_LIB_PATH") or os.path.join(_HERE, "libvst_b200.so")
 
 VST_F32, VST_BF16 = 0, 1
 

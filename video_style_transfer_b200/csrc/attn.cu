@@ -3,24 +3,27 @@
 // head merge) -- the head split/merge transposes disappear into the TMA tensor maps, and the
 // text repeat_interleave of :62-66 into the kv batch index (b / kv_group).
 //
-// One CTA = NT x 128 query rows of one (batch, head); NT = 1 ships, with two CTAs resident per SM
-// (256 TMEM columns each: S [0,128) fp32, O [128,192) fp32, P [192,256) bf16 pairs).  Warps:
-//   0..3        softmax: thread t owns query row t (TMEM lane t).  Per 128-key block ONE pass:
-//               S row -> registers (S is released at once, so the next S = Q K^T overlaps this
-//               block's softmax), row max (4 independent chains), P = exp2(s*scale - m) with packed
-//               f32x2 math, kPoly of every 8 pairs on the FMA pipe (ex2_poly2), bf16 P written back
-//               to TMEM.  O accumulates in TMEM across blocks; it is rescaled only when the running
-//               max moves by more than 2^8 (lazy rescale), by the same warps.
-//   4           TMA producer: Q once, K / V tiles [128 x 64] (2 stages each).
-//   5           MMA issuer (whole warp in the loop, one elected lane issues): S = Q K^T
-//               (4 x tcgen05.mma 128x128x16, both operands K-major smem) and O += P V
-//               (8 x 128x64x16, A = P from TMEM, B = V MN-major straight from its row-major tile),
-//               so P never touches shared memory.
-// What bounds it (r01 measurements, scripts/ubench/*.cu, profiles/attn_r01_notes.md): at head dim 64
-// a 128x128 score block is ~530 clk of tensor work but 1024 clk of MUFU.EX2 (16/clk/SM, and
-// ex2.f16x2 is two MUFU ops, no packed rate), so the kernel is XU-bound; NT = 2 (K/V shared by two
-// tiles in one CTA), 8 half-row softmax warps, a per-SM CTA stagger and an exp-phase mutex between
-// tiles were all measured and were slower or equal.
+// A persistent CTA (two per SM) walks a strided list of items = 128 query rows of one (batch, head).
+// TMEM per CTA: 256 columns (S [0,128) fp32, O [128,192) fp32, P [192,256) bf16 pairs).  Warps:
+//   0..3  softmax (warpgroup 0, 208 registers by setmaxnreg): thread t owns query row t (TMEM lane
+//         t).  Per 128-key block ONE pass: S row -> registers (S is released at once, so the next
+//         S = Q K^T overlaps this block's softmax), row max (4 independent chains),
+//         P = exp2(s*scale - m) with packed f32x2 math, kPoly of every 8 pairs on the FMA pipe
+//         (ex2_poly2), bf16 P written back to TMEM.  O accumulates in TMEM across blocks; it is
+//         rescaled only when the running max moves by more than 2^8 (lazy rescale).
+//   4     TMA producer: Q ring of 3 tiles, K / V tiles [128 x 64] (2 stages each).
+//   5     MMA issuer (whole warp in the loop, one elected lane issues): S = Q K^T
+//         (4 x tcgen05.mma 128x128x16, both operands K-major smem) and O += P V
+//         (8 x 128x64x16, A = P from TMEM, B = V MN-major straight from its row-major tile),
+//         so P never touches shared memory.
+//   6     store warp: staged O tiles leave by TMA.   7: idle (warpgroup 1 runs on 48 registers).
+// What bounds it (r01 measurements: scripts/ubench/*.cu, scripts/attn_trace.py,
+// profiles/attn_r01_notes.md): at head dim 64 a 128x128 score block is ~530 clk of tensor work but
+// 1024 clk of MUFU.EX2 (16/clk/SM; ex2.f16x2 is two MUFU ops, no packed rate) plus ~500 issue
+// slots per softmax warp, and with two softmax warps per scheduler the stream is latency-bound at
+// ~2400 clk per block pair (xu pipe 58 %, issue 40 %).  Measured and slower or equal: two query
+// tiles per CTA sharing K / V, 8 half-row softmax warps, a per-SM CTA stagger, an exp-phase
+// mutex, a one-shot (non-persistent) CTA per item (shipped until the item-boundary trace).
 // Roofline: tensor pipe for self-attention (S/2 FLOP/B); FLOPs = 4*Bt*h*Sq*Sk*d.
 #include <stdlib.h>
 #include <type_traits>
@@ -32,14 +35,20 @@ namespace {
 constexpr int BQ = 128;   // query rows per CTA
 constexpr int BKV = 128;  // keys per block
 constexpr int HD = 64;    // head dim
-constexpr int NT = 1;     // query tiles per CTA (they share every K / V tile: halves the L2 traffic)
-constexpr int kTmaWarp = 4 * NT;             // warps [0, 4 NT): softmax; then TMA; then NT MMA warps
-constexpr int kThreads = 32 * (4 * NT + 1 + NT);
-constexpr int KST = NT == 1 ? 2 : 3;    // K and V stages
+constexpr int kThreads = 256;          // warpgroup 0: softmax; warpgroup 1: TMA, MMA, store, idle
+constexpr int kRegsSoftmax = 208;      // setmaxnreg: 128 * 208 + 128 * 48 = half the register file,
+constexpr int kRegsAux = 48;           // so two CTAs stay resident and the softmax loop does not spill
+constexpr int KST = 2;    // K and V stages
 constexpr int kTile = 128 * HD * 2;  // 16 KB
-constexpr int kSmemBytes = kTile * (NT + 2 * KST) + 1024 + 256;
 constexpr int kDefaultPoly = 2;
 constexpr float kRescaleThreshold = 8.f;  // log2 units: P stays below 2^8, safe in bf16 / fp32
+
+template <int N> __device__ __forceinline__ void setmaxnreg_inc() {
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N));
+}
+template <int N> __device__ __forceinline__ void setmaxnreg_dec() {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N));
+}
 
 __device__ __forceinline__ float ex2(float x) {
   float y;
@@ -72,6 +81,15 @@ __device__ __forceinline__ float2 ex2_poly2(float2 x) {
   return p;
 }
 
+// -DVST_ATTN_TRACE: CTA 0 records clock64() stamps of its pipeline events (tuning builds only).
+#ifdef VST_ATTN_TRACE
+__device__ long long g_attn_trace[12 * 1024];
+#define TRACE(slot, idx) do { if (blockIdx.x == 0 && (idx) < 1024 && (threadIdx.x & 31) == 0) \
+    g_attn_trace[(slot) * 1024 + (idx)] = clock64(); } while (0)
+#else
+#define TRACE(slot, idx) do { } while (0)
+#endif
+
 struct AttnArgs {
   float* lse;
   int Sq, Sk, heads, kv_group;
@@ -81,312 +99,38 @@ struct AttnArgs {
   int mask_vec4;                     // base pointer and strides allow 16-byte loads
 };
 
-template <int kPoly, bool kMask>
-__global__ void __launch_bounds__(kThreads, 2 / NT)
-attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
-                const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
-                AttnArgs a) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~uintptr_t(1023));
-  uint8_t* sQ = smem;                       // [NT] query tiles (reused to stage O)
-  uint8_t* sK = sQ + NT * kTile;            // [KST]
-  uint8_t* sV = sK + KST * kTile;           // [KST]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + KST * kTile);
-  uint64_t* q_full = bars;                  // [NT]
-  uint64_t* k_full = q_full + NT;           // [KST]
-  uint64_t* k_empty = k_full + KST;         // [KST]  both tiles' S MMAs have read K_j
-  uint64_t* v_full = k_empty + KST;         // [KST]
-  uint64_t* v_empty = v_full + KST;         // [KST]  both tiles' PV MMAs have read V_j
-  uint64_t* s_full = v_empty + KST;         // [NT] S_j complete in TMEM
-  uint64_t* s_free = s_full + NT;           // [NT] S_j copied to registers by all 128 rows
-  uint64_t* p_full = s_free + NT;           // [NT] P_j in TMEM (and O rescaled if needed)
-  uint64_t* o_full = p_full + NT;           // [NT] O += P_j V_j complete
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + NT);
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int q0 = blockIdx.x * (NT * BQ), head = blockIdx.y, b = blockIdx.z;
-  const int nblk = (a.Sk + BKV - 1) / BKV;
-
-  if (threadIdx.x == 0) {
-    for (int t = 0; t < NT; ++t) {
-      mbar_init(&q_full[t], 1);
-      mbar_init(&s_full[t], 1);
-      mbar_init(&s_free[t], 128);
-      mbar_init(&p_full[t], 128);
-      mbar_init(&o_full[t], 1);
-    }
-    for (int i = 0; i < KST; ++i) {
-      mbar_init(&k_full[i], 1);
-      mbar_init(&k_empty[i], NT);
-      mbar_init(&v_full[i], 1);
-      mbar_init(&v_empty[i], NT);
-    }
-    fence_mbar_init();
-  }
-  if (warp == kTmaWarp) tmem_alloc(tmem_slot, 256 * NT);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
-
-  if (warp == kTmaWarp) {
-    // ================= TMA producer =================
-    if (lane == 0) {
-      tma_prefetch_desc(&tmQ);
-      tma_prefetch_desc(&tmK);
-      tma_prefetch_desc(&tmV);
-      const int bk = b / a.kv_group;
-      mbar_arrive_expect_tx(&q_full[0], kTile);
-      tma_load_3d(sQ, &tmQ, &q_full[0], head * HD, q0, b);
-      mbar_arrive_expect_tx(&k_full[0], kTile);
-      tma_load_3d(sK, &tmK, &k_full[0], head * HD, 0, bk);
-      if (NT > 1) {
-        mbar_arrive_expect_tx(&q_full[NT - 1], kTile);
-        tma_load_3d(sQ + kTile, &tmQ, &q_full[NT - 1], head * HD, q0 + BQ, b);
-      }
-      mbar_arrive_expect_tx(&v_full[0], kTile);
-      tma_load_3d(sV, &tmV, &v_full[0], head * HD, 0, bk);
-      for (int j = 1; j < nblk; ++j) {
-        const int st = j % KST;
-        const uint32_t ph = ((j / KST) & 1) ^ 1;
-        mbar_wait(&k_empty[st], ph, 10);
-        mbar_arrive_expect_tx(&k_full[st], kTile);
-        tma_load_3d(sK + st * kTile, &tmK, &k_full[st], head * HD, j * BKV, bk);
-        mbar_wait(&v_empty[st], ph, 11);
-        mbar_arrive_expect_tx(&v_full[st], kTile);
-        tma_load_3d(sV + st * kTile, &tmV, &v_full[st], head * HD, j * BKV, bk);
-      }
-    }
-  } else if (warp > kTmaWarp) {
-    // ================= MMA issuers: one warp per query tile, sharing the K / V stages ==========
-    // The whole warp runs the loop and one elected lane issues (warp-uniform control flow keeps the
-    // descriptors in uniform registers; see scripts/ubench/mma_rate.cu).
-    const bool issuer = elect_one();
-    const int t = warp - kTmaWarp - 1;
-    const uint32_t tS = tmem_base + t * 256;   // S (fp32) columns [0,128) of this tile's half
-    const uint32_t tO = tS + 128;              // O accumulator (fp32), 64 columns
-    const uint32_t tP = tS + 192;              // P (bf16 pairs, 2 keys per column), 64 columns
-    constexpr uint32_t idesc_s = umma_idesc_bf16(BQ, BKV, 0, 0);
-    constexpr uint32_t idesc_o = umma_idesc_bf16(BQ, HD, 0, 1);  // B (= V) is MN-major
-    const uint64_t dq = umma_desc_sw128(smem_u32(sQ + t * kTile), 1024);
-    mbar_wait(&q_full[t], 0, 20);
-    auto issue_s = [&](int j) {
-      const int st = j % KST;
-      mbar_wait(&k_full[st], (j / KST) & 1, 21);
-      tc_fence_after();
-      const uint64_t dk = umma_desc_sw128(smem_u32(sK + st * kTile), 1024);
-      if (issuer) {
-#pragma unroll
-        for (int k = 0; k < HD / 16; ++k) umma_bf16_ss(tS, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
-        umma_commit(&k_empty[st]);
-        umma_commit(&s_full[t]);
-      }
-      __syncwarp();
-    };
-    issue_s(0);
-    for (int j = 0; j < nblk; ++j) {
-      if (j + 1 < nblk) {
-        mbar_wait(&s_free[t], j & 1, 24);  // S_j is in registers: S_{j+1} overlaps softmax j
-        issue_s(j + 1);
-      }
-      const int st = j % KST;
-      mbar_wait(&p_full[t], j & 1, 22);
-      mbar_wait(&v_full[st], (j / KST) & 1, 23);
-      tc_fence_after();
-      const uint64_t dv = umma_desc_sw128(smem_u32(sV + st * kTile), 1024, 8192);
-      if (issuer) {
-#pragma unroll
-        for (int k = 0; k < BKV / 16; ++k) {
-          // A: 16 keys of P = 8 TMEM columns; B: 16 key rows of V = 16 x 128 B further on
-          umma_bf16_ts(tO, tP + 8 * k, dv + uint64_t((k * 2048) >> 4), idesc_o, (j | k) != 0);
-        }
-        umma_commit(&v_empty[st]);
-        umma_commit(&o_full[t]);
-      }
-      __syncwarp();
-    }
-  } else {
-    // ================= softmax + output: warps 0..3 tile 0, warps 4..7 tile 1 =================
-    // Instruction budget per score (the SM issues 128 lanes/clk; the MMAs need ~512 clk per
-    // 128x128 block): 0.5 FMNMX3 + 0.5 FFMA2 + 1 MUFU.EX2 + 0.5 FADD2 + 0.5 F2FP.
-    const int t = warp >> 2;
-    const int row = (warp & 3) * 32 + lane;  // query row within the tile == TMEM lane
-    const uint32_t lane_off = uint32_t((warp & 3) * 32) << 16;
-    const uint32_t tS = tmem_base + t * 256 + lane_off;
-    const uint32_t tO = tS + 128;
-    const uint32_t tP = tS + 192;
-    const int qt = q0 + t * BQ;
-    float m = -INFINITY;               // running (possibly stale) row max, log2 domain
-    float2 l2 = make_float2(0.f, 0.f);
-    const float2 sc2 = kMask ? make_float2(1.f, 1.f) : make_float2(a.scale_log2, a.scale_log2);
-
-    for (int j = 0; j < nblk; ++j) {
-      const int kv0 = j * BKV;
-      const bool tail = kv0 + BKV > a.Sk;
-      mbar_wait(&s_full[t], j & 1, 30);
-      tc_fence_after();
-      uint32_t r[BKV];
-#pragma unroll
-      for (int c = 0; c < BKV / 32; ++c) tmem_ld32(tS + c * 32, r + c * 32);
-      tmem_ld_wait();
-      tc_fence_before();
-      mbar_arrive(&s_free[t]);         // the tensor pipe may overwrite S now
-      if (tail) {
-#pragma unroll
-        for (int i = 0; i < BKV; ++i)
-          if (kv0 + i >= a.Sk) r[i] = 0xff800000u;  // -inf: excluded from max, exp2 -> 0
-      }
-      if constexpr (kMask) {
-        // additive mask (attention_processor.py:46-48 -> F.scaled_dot_product_attention attn_mask):
-        // s <- s * scale + mask in the log2 domain, then the block proceeds with unit scale
-        const int qrow = min(qt + row, a.Sq - 1);
-        const float* mrow = a.mask + (int64_t)b * a.mask_sb + (int64_t)head * a.mask_sh +
-                            (int64_t)qrow * a.mask_sq + kv0;
-        constexpr float kLog2e = 1.4426950408889634f;
-        if (!tail && a.mask_vec4) {
-#pragma unroll
-          for (int i = 0; i < BKV; i += 4) {
-            const float4 mk = __ldg(reinterpret_cast<const float4*>(mrow + i));
-            r[i] = __float_as_uint(fmaf(__uint_as_float(r[i]), a.scale_log2, mk.x * kLog2e));
-            r[i + 1] = __float_as_uint(fmaf(__uint_as_float(r[i + 1]), a.scale_log2, mk.y * kLog2e));
-            r[i + 2] = __float_as_uint(fmaf(__uint_as_float(r[i + 2]), a.scale_log2, mk.z * kLog2e));
-            r[i + 3] = __float_as_uint(fmaf(__uint_as_float(r[i + 3]), a.scale_log2, mk.w * kLog2e));
-          }
-        } else {
-#pragma unroll
-          for (int i = 0; i < BKV; ++i) {
-            const float mk = kv0 + i < a.Sk ? __ldg(mrow + i) : 0.f;
-            r[i] = __float_as_uint(fmaf(__uint_as_float(r[i]), a.scale_log2, mk * kLog2e));
-          }
-        }
-      }
-      const float sl = kMask ? 1.f : a.scale_log2;
-      // four independent chains: the 3-input max has 4-cycle latency, one chain would serialise
-      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll
-      for (int i = 0; i < BKV; i += 8) {
-#pragma unroll
-        for (int c = 0; c < 4; ++c)
-          mx4[c] = fmaxf(mx4[c], fmaxf(__uint_as_float(r[i + 2 * c]), __uint_as_float(r[i + 2 * c + 1])));
-      }
-      const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
-      // lazy rescale: keep the stale max unless the new one is > 2^8 larger
-      const float m_cand = fmaxf(m, mx * sl);
-      const bool grow = m_cand - m > kRescaleThreshold;   // true on the first block (m = -inf)
-      const float m_use = grow ? m_cand : m;
-      const float alpha = grow ? ex2(m - m_use) : 1.f;
-      m = m_use;
-      l2 = __fmul2_rn(l2, make_float2(alpha, alpha));
-      const float2 nm2 = make_float2(-m_use, -m_use);
-#pragma unroll
-      for (int i = 0; i < BKV / 2; ++i) {
-        const float2 sv = __ffma2_rn(
-            make_float2(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1])), sc2, nm2);
-        // pairs are spread Bresenham-style so MUFU and FMA work interleave in the schedule
-        const bool poly = ((i * kPoly) & 7) + kPoly > 7 && kPoly > 0;
-        const float2 pv = poly ? ex2_poly2(sv) : make_float2(ex2(sv.x), ex2(sv.y));
-        l2 = __fadd2_rn(l2, pv);
-        r[i] = pack_bf16(pv.x, pv.y);   // in place: word i <- keys 2i, 2i+1 (already consumed)
-      }
-      if (j > 0) {
-        // P V of the previous block must have finished reading P (and writing O)
-        mbar_wait(&o_full[t], (j - 1) & 1, 31);
-        tc_fence_after();
-        if (__any_sync(0xffffffffu, grow)) {
-          // O *= alpha for this warp's 32 rows (alpha = 1 for rows that did not grow)
-          const float2 al2 = make_float2(alpha, alpha);
-#pragma unroll
-          for (int c = 0; c < HD / 32; ++c) {
-            uint32_t o[32];
-            tmem_ld32(tO + c * 32, o);
-            tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-              const float2 tt = __fmul2_rn(
-                  make_float2(__uint_as_float(o[2 * i]), __uint_as_float(o[2 * i + 1])), al2);
-              o[2 * i] = __float_as_uint(tt.x);
-              o[2 * i + 1] = __float_as_uint(tt.y);
-            }
-            tmem_st32(tO + c * 32, o);
-          }
-        }
-      }
-      tmem_st32(tP, r);
-      tmem_st32(tP + 32, r + 32);
-      tmem_st_wait();
-      tc_fence_before();
-      mbar_arrive(&p_full[t]);
-    }
-    // ---- normalise, stage O through smem (this tile's Q is dead), TMA store ----
-    mbar_wait(&o_full[t], (nblk - 1) & 1, 32);
-    tc_fence_after();
-    const float l = l2.x + l2.y;
-    const float inv = 1.f / l;
-    uint8_t* otile = sQ + t * kTile;
-    uint8_t* orow = otile + row * 128;
-    const int rx = row & 7;
-#pragma unroll
-    for (int c = 0; c < HD / 32; ++c) {
-      uint32_t o[32];
-      tmem_ld32(tO + c * 32, o);
-      tmem_ld_wait();
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        uint4 w;
-        w.x = pack_bf16(__uint_as_float(o[8 * q]) * inv, __uint_as_float(o[8 * q + 1]) * inv);
-        w.y = pack_bf16(__uint_as_float(o[8 * q + 2]) * inv, __uint_as_float(o[8 * q + 3]) * inv);
-        w.z = pack_bf16(__uint_as_float(o[8 * q + 4]) * inv, __uint_as_float(o[8 * q + 5]) * inv);
-        w.w = pack_bf16(__uint_as_float(o[8 * q + 6]) * inv, __uint_as_float(o[8 * q + 7]) * inv);
-        *reinterpret_cast<uint4*>(orow + (((c * 4 + q) ^ rx) * 16)) = w;
-      }
-    }
-    if (a.lse != nullptr && qt + row < a.Sq)
-      a.lse[((int64_t)b * a.heads + head) * a.Sq + qt + row] =
-          (m + log2f(l)) * 0.6931471805599453f;
-    fence_proxy_async_smem();
-    if (t == 0) asm volatile("bar.sync 1, 128;" ::: "memory");
-    else asm volatile("bar.sync 2, 128;" ::: "memory");
-    if ((threadIdx.x & 127) == 0 && qt < a.Sq) {
-      tma_store_4d(&tmO, otile, head * HD, qt, b, 0);
-      tma_store_commit();
-      tma_store_wait<0>();
-    }
-  }
-
-  tc_fence_before();
-  __syncthreads();
-  if (warp == kTmaWarp) {
-    tc_fence_after();
-    tmem_dealloc(tmem_base, 256 * NT);
-  }
-}
-
 // ---- persistent form ---------------------------------------------------------------------------
-// One CTA walks a strided list of (batch, head, query tile) items, two CTAs per SM.  Per item the
-// fixed costs of the one-shot kernel -- TMEM allocation, barrier set-up, the exposed latency of the
-// Q load and of the O store -- are paid once per CTA or overlapped: Q is double-buffered (the next
-// item's Q and first K / V blocks are in flight while this item finishes), O is staged in the dead
-// Q buffer and leaves by TMA while the next item computes.  It matters where an item is short:
-// L2 self-attention (8 key blocks per item) and text cross-attention (one block).  All barrier
-// phases run on global counters (g: K/V blocks loaded, blk: score blocks), not on the block index.
-constexpr int kSmemBytesP = kTile * (2 + 2 * KST) + 1024 + 256;
+// One CTA walks a strided list of (batch, head, query tile) items, two CTAs per SM.  The stream of
+// score blocks never drains between items (clock64 traces of the first form, scripts/attn_trace.py:
+// an item boundary cost ~3000 clk against a ~2400 clk block period, 11 % at 8 blocks per item):
+//   * TMEM allocation and barrier set-up are paid once per CTA;
+//   * Q lives in a ring of three buffers, so the Q of the next two items is in flight;
+//   * the MMA warp issues the first score block of the NEXT item as soon as the last S of this
+//     item is in registers (S = Q K^T never waits for an epilogue);
+//   * the epilogue of item i is deferred: the softmax warps first run the exponentials of block 0 of
+//     item i+1 -- by then the last P V of item i has long retired -- then read O out of TMEM,
+//     normalise and stage it in item i's dead Q buffer, and only then store P;
+//   * a dedicated store warp (warp 6) sends the staged tile by TMA and recycles the buffer, so the
+//     softmax warps never wait for a bulk store to read shared memory.
+// All barrier phases run on global counters (g: K/V blocks loaded, blk: score blocks, i: items).
+constexpr int NQ = 3;
+constexpr int kSmemBytesP = kTile * (NQ + 2 * KST) + 256;
 
 template <int kPoly, bool kMask>
-__global__ void __launch_bounds__(192, 2)
+__global__ void __launch_bounds__(kThreads, 2)
 attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                      const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
                      AttnArgs a, int n_items, int ntile) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~uintptr_t(1023));
-  uint8_t* sQ = smem;                       // [2] query tiles (each reused to stage its item's O)
-  uint8_t* sK = sQ + 2 * kTile;             // [KST]
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;                 // 128B-swizzled tiles need 1024-byte alignment (checked)
+  uint8_t* sQ = smem;                       // [NQ] query tiles (each reused to stage its item's O)
+  uint8_t* sK = sQ + NQ * kTile;            // [KST]
   uint8_t* sV = sK + KST * kTile;           // [KST]
   uint64_t* bars = reinterpret_cast<uint64_t*>(sV + KST * kTile);
-  uint64_t* q_full = bars;                  // [2]
-  uint64_t* q_empty = q_full + 2;           // [2]   the O store staged in this buffer has been read
-  uint64_t* k_full = q_empty + 2;           // [KST]
+  uint64_t* q_full = bars;                  // [NQ]
+  uint64_t* q_empty = q_full + NQ;          // [NQ]  the O store staged in this buffer has been read
+  uint64_t* o_staged = q_empty + NQ;        // [NQ]  the item's O is normalised and staged (128 rows)
+  uint64_t* k_full = o_staged + NQ;         // [KST]
   uint64_t* k_empty = k_full + KST;         // [KST]
   uint64_t* v_full = k_empty + KST;         // [KST]
   uint64_t* v_empty = v_full + KST;         // [KST]
@@ -401,9 +145,14 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
   const int nblk = (a.Sk + BKV - 1) / BKV;
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < 2; ++i) {
+    if (smem_u32(smem) & 1023u) {
+      printf("vst attn_fwd: dynamic shared memory is not 1024-byte aligned\n");
+      __trap();
+    }
+    for (int i = 0; i < NQ; ++i) {
       mbar_init(&q_full[i], 1);
       mbar_init(&q_empty[i], 1);
+      mbar_init(&o_staged[i], 128);
     }
     for (int i = 0; i < KST; ++i) {
       mbar_init(&k_full[i], 1);
@@ -426,6 +175,7 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
 
   if (warp == 4) {
     // ================= TMA producer =================
+    setmaxnreg_dec<kRegsAux>();
     if (lane == 0) {
       tma_prefetch_desc(&tmQ);
       tma_prefetch_desc(&tmK);
@@ -434,8 +184,8 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       int i = 0;
       for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++i) {
         const int qtile = it % ntile, head = (it / ntile) % a.heads, b = it / (ntile * a.heads);
-        const int bk = b / a.kv_group, buf = i & 1;
-        mbar_wait(&q_empty[buf], ((i >> 1) & 1) ^ 1, 40);
+        const int bk = b / a.kv_group, buf = i % NQ;
+        mbar_wait(&q_empty[buf], ((i / NQ) & 1) ^ 1, 40);
         mbar_arrive_expect_tx(&q_full[buf], kTile);
         tma_load_3d(sQ + buf * kTile, &tmQ, &q_full[buf], head * HD, qtile * BQ, b);
         for (int j = 0; j < nblk; ++j, ++g) {
@@ -452,6 +202,7 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     }
   } else if (warp == 5) {
     // ================= MMA issuer (whole warp in the loop, one elected lane issues) ==========
+    setmaxnreg_dec<kRegsAux>();
     const bool issuer = elect_one();
     const uint32_t tS = tmem_base;             // S (fp32) columns [0,128)
     const uint32_t tO = tS + 128;              // O accumulator (fp32), 64 columns
@@ -460,29 +211,40 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     constexpr uint32_t idesc_o = umma_idesc_bf16(BQ, HD, 0, 1);  // B (= V) is MN-major
     uint32_t g = 0, blk = 0;
     int i = 0;
-    for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++i) {
-      const int buf = i & 1;
-      const uint64_t dq = umma_desc_sw128(smem_u32(sQ + buf * kTile), 1024);
-      mbar_wait(&q_full[buf], (i >> 1) & 1, 20);
-      auto issue_s = [&](uint32_t gg) {
-        const int st = gg % KST;
-        mbar_wait(&k_full[st], (gg / KST) & 1, 21);
-        tc_fence_after();
-        const uint64_t dk = umma_desc_sw128(smem_u32(sK + st * kTile), 1024);
-        if (issuer) {
+    auto issue_s = [&](uint64_t dq, uint32_t gg, uint32_t tr) {
+      const int st = gg % KST;
+      mbar_wait(&k_full[st], (gg / KST) & 1, 21);
+      tc_fence_after();
+      const uint64_t dk = umma_desc_sw128(smem_u32(sK + st * kTile), 1024);
+      TRACE(5, tr);
+      if (issuer) {
 #pragma unroll
-          for (int k = 0; k < HD / 16; ++k) umma_bf16_ss(tS, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
-          umma_commit(&k_empty[st]);
-          umma_commit(s_full);
-        }
-        __syncwarp();
-      };
-      if (blk > 0) mbar_wait(s_free, (blk - 1) & 1, 25);   // the previous item's last S is in registers
-      issue_s(g);
+        for (int k = 0; k < HD / 16; ++k) umma_bf16_ss(tS, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
+        umma_commit(&k_empty[st]);
+        umma_commit(s_full);
+      }
+      __syncwarp();
+    };
+    for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++i) {
+      const int buf = i % NQ;
+      const uint64_t dq = umma_desc_sw128(smem_u32(sQ + buf * kTile), 1024);
+      if (i == 0) {
+        mbar_wait(&q_full[0], 0, 20);
+        issue_s(dq, 0, 0);
+      }
+      const bool has_next = it + (int)gridDim.x < n_items;
       for (int j = 0; j < nblk; ++j) {
+        // The score block that follows block j in this CTA's stream -- the next key block of this
+        // item, or the FIRST block of the next item (its Q sits in the next ring buffer) -- is
+        // issued as soon as S_j is in registers, so it overlaps softmax j also across items.
         if (j + 1 < nblk) {
-          mbar_wait(s_free, (blk + j) & 1, 24);  // S_j is in registers: S_{j+1} overlaps softmax j
-          issue_s(g + j + 1);
+          mbar_wait(s_free, (blk + j) & 1, 24);
+          issue_s(dq, g + j + 1, blk + j + 1);
+        } else if (has_next) {
+          const int nb = (i + 1) % NQ;
+          mbar_wait(&q_full[nb], ((i + 1) / NQ) & 1, 20);
+          mbar_wait(s_free, (blk + j) & 1, 25);
+          issue_s(umma_desc_sw128(smem_u32(sQ + nb * kTile), 1024), g + nblk, blk + nblk);
         }
         const int st = (g + j) % KST;
         mbar_wait(p_full, (blk + j) & 1, 22);
@@ -490,6 +252,7 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         mbar_wait(&v_full[st], ((g + j) / KST) & 1, 23);
         tc_fence_after();
         const uint64_t dv = umma_desc_sw128(smem_u32(sV + st * kTile), 1024, 8192);
+        TRACE(6, blk + j);
         if (issuer) {
 #pragma unroll
           for (int k = 0; k < BKV / 16; ++k)
@@ -502,8 +265,27 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       g += nblk;
       blk += nblk;
     }
+  } else if (warp == 6) {
+    // ================= store warp: staged O tiles leave by TMA, buffers go back to the ring ======
+    setmaxnreg_dec<kRegsAux>();
+    if (lane == 0) {
+      int i = 0;
+      for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++i) {
+        const int qtile = it % ntile, head = (it / ntile) % a.heads, b = it / (ntile * a.heads);
+        const int buf = i % NQ;
+        mbar_wait(&o_staged[buf], (i / NQ) & 1, 41);
+        tma_store_4d(&tmO, sQ + buf * kTile, head * HD, qtile * BQ, b, 0);
+        tma_store_commit();
+        tma_store_wait_read<0>();          // smem read out: the buffer may take the Q of item i + NQ
+        mbar_arrive(&q_empty[buf]);
+      }
+      tma_store_wait<0>();
+    }
+  } else if (warp > 6) {
+    setmaxnreg_dec<kRegsAux>();          // idle warp of the auxiliary warpgroup
   } else {
     // ================= softmax + output (warps 0..3) =================
+    setmaxnreg_inc<kRegsSoftmax>();
     const int row = warp * 32 + lane;  // query row within the tile == TMEM lane
     const uint32_t lane_off = uint32_t(warp * 32) << 16;
     const uint32_t tS = tmem_base + lane_off;
@@ -512,20 +294,60 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     const float2 sc2 = kMask ? make_float2(1.f, 1.f) : make_float2(a.scale_log2, a.scale_log2);
     uint32_t blk = 0;
     int i = 0;
+    // deferred epilogue of the previous item
+    int pend_it = -1;
+    float pend_inv = 0.f, pend_lse = 0.f;
+    auto epilogue = [&](int pit, int pi, float inv, float lse, uint32_t last_blk) {
+      // O of item pit (ring slot pi % NQ): TMEM -> normalise -> its dead Q buffer -> store warp
+      mbar_wait(o_full, last_blk & 1, 32);
+      if (warp == 0) TRACE(7, pi);
+      tc_fence_after();
+      uint8_t* orow = sQ + (pi % NQ) * kTile + row * 128;
+      const int rx = row & 7;
+#pragma unroll
+      for (int c = 0; c < HD / 32; ++c) {
+        uint32_t o[32];
+        tmem_ld32(tO + c * 32, o);
+        tmem_ld_wait();
+        if (c == HD / 32 - 1) {
+          tc_fence_before();
+          mbar_arrive(o_free);           // the next item's first P V may overwrite O
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint4 w;
+          w.x = pack_bf16(__uint_as_float(o[8 * q]) * inv, __uint_as_float(o[8 * q + 1]) * inv);
+          w.y = pack_bf16(__uint_as_float(o[8 * q + 2]) * inv, __uint_as_float(o[8 * q + 3]) * inv);
+          w.z = pack_bf16(__uint_as_float(o[8 * q + 4]) * inv, __uint_as_float(o[8 * q + 5]) * inv);
+          w.w = pack_bf16(__uint_as_float(o[8 * q + 6]) * inv, __uint_as_float(o[8 * q + 7]) * inv);
+          *reinterpret_cast<uint4*>(orow + (((c * 4 + q) ^ rx) * 16)) = w;
+        }
+      }
+      fence_proxy_async_smem();
+      mbar_arrive(&o_staged[pi % NQ]);
+      if (warp == 0) TRACE(8, pi);
+      if (a.lse != nullptr) {
+        const int qt = (pit % ntile) * BQ;
+        if (qt + row < a.Sq) {
+          const int head = (pit / ntile) % a.heads, b = pit / (ntile * a.heads);
+          a.lse[((int64_t)b * a.heads + head) * a.Sq + qt + row] = lse;
+        }
+      }
+    };
     for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++i) {
-      const int qtile = it % ntile, head = (it / ntile) % a.heads, b = it / (ntile * a.heads);
-      const int qt = qtile * BQ, buf = i & 1;
       float m = -INFINITY;               // running (possibly stale) row max, log2 domain
       float2 l2 = make_float2(0.f, 0.f);
       for (int j = 0; j < nblk; ++j) {
         const int kv0 = j * BKV;
         const bool tail = kv0 + BKV > a.Sk;
         mbar_wait(s_full, (blk + j) & 1, 30);
+        if (warp == 0) TRACE(0, blk + j);
         tc_fence_after();
         uint32_t r[BKV];
 #pragma unroll
         for (int c = 0; c < BKV / 32; ++c) tmem_ld32(tS + c * 32, r + c * 32);
         tmem_ld_wait();
+        if (warp == 0) TRACE(1, blk + j);
         tc_fence_before();
         mbar_arrive(s_free);             // the tensor pipe may overwrite S now
         if (tail) {
@@ -534,7 +356,8 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
             if (kv0 + e >= a.Sk) r[e] = 0xff800000u;  // -inf: excluded from max, exp2 -> 0
         }
         if constexpr (kMask) {
-          const int qrow = min(qt + row, a.Sq - 1);
+          const int qtile = it % ntile, head = (it / ntile) % a.heads, b = it / (ntile * a.heads);
+          const int qrow = min(qtile * BQ + row, a.Sq - 1);
           const float* mrow = a.mask + (int64_t)b * a.mask_sb + (int64_t)head * a.mask_sh +
                               (int64_t)qrow * a.mask_sq + kv0;
           constexpr float kLog2e = 1.4426950408889634f;
@@ -580,8 +403,10 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
           l2 = __fadd2_rn(l2, pv);
           r[e] = pack_bf16(pv.x, pv.y);
         }
+        if (warp == 0) TRACE(2, blk + j);
         if (j > 0) {
           mbar_wait(o_full, (blk + j - 1) & 1, 31);   // P V of the previous block is done with P and O
+          if (warp == 0) TRACE(3, blk + j);
           tc_fence_after();
           if (__any_sync(0xffffffffu, grow)) {
             const float2 al2 = make_float2(alpha, alpha);
@@ -600,53 +425,25 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
               tmem_st32(tO + c * 32, o);
             }
           }
+        } else if (pend_it >= 0) {
+          // the previous item's last P V retired while this block's exponentials ran: its O leaves
+          // TMEM now, before this item's first P V (gated by o_free) overwrites it
+          epilogue(pend_it, i - 1, pend_inv, pend_lse, blk - 1);
         }
         tmem_st32(tP, r);
         tmem_st32(tP + 32, r + 32);
         tmem_st_wait();
         tc_fence_before();
         mbar_arrive(p_full);
+        if (warp == 0) TRACE(4, blk + j);
       }
-      // ---- normalise, stage O through this item's (dead) Q buffer, TMA store ----
-      mbar_wait(o_full, (blk + nblk - 1) & 1, 32);
-      tc_fence_after();
       const float l = l2.x + l2.y;
-      const float inv = 1.f / l;
-      uint8_t* otile = sQ + buf * kTile;
-      uint8_t* orow = otile + row * 128;
-      const int rx = row & 7;
-#pragma unroll
-      for (int c = 0; c < HD / 32; ++c) {
-        uint32_t o[32];
-        tmem_ld32(tO + c * 32, o);
-        tmem_ld_wait();
-        if (c == HD / 32 - 1) {
-          tc_fence_before();
-          mbar_arrive(o_free);           // the next item's first P V may overwrite O
-        }
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          uint4 w;
-          w.x = pack_bf16(__uint_as_float(o[8 * q]) * inv, __uint_as_float(o[8 * q + 1]) * inv);
-          w.y = pack_bf16(__uint_as_float(o[8 * q + 2]) * inv, __uint_as_float(o[8 * q + 3]) * inv);
-          w.z = pack_bf16(__uint_as_float(o[8 * q + 4]) * inv, __uint_as_float(o[8 * q + 5]) * inv);
-          w.w = pack_bf16(__uint_as_float(o[8 * q + 6]) * inv, __uint_as_float(o[8 * q + 7]) * inv);
-          *reinterpret_cast<uint4*>(orow + (((c * 4 + q) ^ rx) * 16)) = w;
-        }
-      }
-      if (a.lse != nullptr && qt + row < a.Sq)
-        a.lse[((int64_t)b * a.heads + head) * a.Sq + qt + row] = (m + log2f(l)) * 0.6931471805599453f;
-      fence_proxy_async_smem();
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (threadIdx.x == 0) {
-        tma_store_4d(&tmO, otile, head * HD, qt, b, 0);
-        tma_store_commit();
-        tma_store_wait_read<0>();        // smem read out: the buffer may take the Q of item i + 2
-        mbar_arrive(&q_empty[buf]);
-      }
+      pend_it = it;
+      pend_inv = 1.f / l;
+      pend_lse = (m + log2f(l)) * 0.6931471805599453f;
       blk += nblk;
     }
-    if (threadIdx.x == 0) tma_store_wait<0>();
+    if (pend_it >= 0) epilogue(pend_it, i - 1, pend_inv, pend_lse, blk - 1);
   }
 
   tc_fence_before();
@@ -668,6 +465,12 @@ int make_qkv_map(CUtensorMap* m, const void* p, int64_t B, int64_t S, int width,
 
 }  // namespace
 
+#ifdef VST_ATTN_TRACE
+extern "C" int vst_attn_debug_trace(long long* host_dst) {
+  return (int)cudaMemcpyFromSymbol(host_dst, g_attn_trace, sizeof(long long) * 12 * 1024);
+}
+#endif
+
 extern "C" int vst_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse,
                             int Bt, int heads, int Sq, int Sk, int d, int64_t ldq, int64_t ldk,
                             int64_t ldv, int64_t ldo, int kv_group, float scale, const float* mask,
@@ -687,58 +490,38 @@ extern "C" int vst_attn_fwd(const void* q, const void* k, const void* v, void* o
   if ((rc = make_qkv_map(&tK, k, Bt / kv_group, Sk, width, ldk, 0))) return rc;
   if ((rc = make_qkv_map(&tV, v, Bt / kv_group, Sk, width, ldv, 0))) return rc;
   if ((rc = make_qkv_map(&tO, o, Bt, Sq, width, ldo, 1))) return rc;
-  // kPoly: how many of every 8 exp2 pairs run on the FMA pipe.  VST_ATTN_POLY overrides the
-  // default (tuning only).
-  static int poly = -1;
+  // kPoly: how many of every 8 exp2 pairs run on the FMA pipe.  VST_ATTN_POLY (0..3) overrides the
+  // default, VST_ATTN_CTAS_PER_SM the persistent grid (tuning only).
+  static int poly = -1, per_sm = 2;
   if (poly < 0) {
     const char* e = getenv("VST_ATTN_POLY");
     poly = e ? atoi(e) : kDefaultPoly;
-    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<kDefaultPoly, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    if (poly < 0 || poly > 3) poly = kDefaultPoly;
+    if ((e = getenv("VST_ATTN_CTAS_PER_SM")) && atoi(e) > 0) per_sm = atoi(e);
+    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_pers_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesP));
+    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_pers_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesP));
+    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_pers_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesP));
+    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_pers_kernel<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesP));
+    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_pers_kernel<kDefaultPoly, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesP));
   }
   const int vec4 = mask && (reinterpret_cast<uintptr_t>(mask) & 15) == 0 && mask_sb % 4 == 0 &&
                    mask_sh % 4 == 0 && mask_sq % 4 == 0;
   AttnArgs a{lse, Sq, Sk, heads, kv_group, scale * 1.4426950408889634f, mask, mask_sb, mask_sh, mask_sq, vec4};
-  dim3 grid((Sq + NT * BQ - 1) / (NT * BQ), heads, Bt);
   cudaStream_t st = (cudaStream_t)stream;
-  // persistent form for short key sequences (text cross-attention: one or two key blocks per item,
-  // where the per-CTA fixed costs dominate; r01: 93 -> 74 us at L1, 53 -> 43 us at L2).  For long
-  // sequences the one-shot kernel is faster (808 vs 758 TFLOP/s at Sk = 4096: the persistent loop's
-  // extra live state costs registers in the softmax loop).  VST_ATTN_PERSISTENT=0 / =2 force one
-  // form for every shape.
-  static int persistent = -1;
-  if (persistent < 0) {
-    const char* e = getenv("VST_ATTN_PERSISTENT");
-    persistent = e ? atoi(e) : 1;
-    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_pers_kernel<kDefaultPoly, false>,
-                                     cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesP));
-    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_pers_kernel<kDefaultPoly, true>,
-                                     cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesP));
-  }
-  if (poly == kDefaultPoly && (persistent == 2 || (persistent == 1 && Sk <= 2 * BKV))) {
-    const int ntile = (Sq + BQ - 1) / BQ;
-    const int64_t items = (int64_t)ntile * heads * Bt;
-    VST_REQUIRE(items < (1ll << 31), VST_E_UNSUPPORTED, "attn_fwd: too many tiles");
-    const int slots = 2 * vst_sm_count();
-    const int pgrid = (int)(items < slots ? items : slots);
-    if (mask)
-      attn_fwd_pers_kernel<kDefaultPoly, true><<<pgrid, 192, kSmemBytesP, st>>>(tQ, tK, tV, tO, a, (int)items, ntile);
-    else
-      attn_fwd_pers_kernel<kDefaultPoly, false><<<pgrid, 192, kSmemBytesP, st>>>(tQ, tK, tV, tO, a, (int)items, ntile);
-    VST_LAUNCH_OK();
-    return VST_OK;
-  }
+  const int ntile = (Sq + BQ - 1) / BQ;
+  const int64_t items = (int64_t)ntile * heads * Bt;
+  VST_REQUIRE(items < (1ll << 31), VST_E_UNSUPPORTED, "attn_fwd: too many tiles");
+  const int slots = per_sm * vst_sm_count();
+  const int pgrid = (int)(items < slots ? items : slots);
+  const int n = (int)items;
   if (mask) {
-    attn_fwd_kernel<kDefaultPoly, true><<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tO, a);
+    attn_fwd_pers_kernel<kDefaultPoly, true><<<pgrid, kThreads, kSmemBytesP, st>>>(tQ, tK, tV, tO, a, n, ntile);
   } else {
     switch (poly) {
-      case 0: attn_fwd_kernel<0, false><<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tO, a); break;
-      case 3: attn_fwd_kernel<3, false><<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tO, a); break;
-      case 4: attn_fwd_kernel<4, false><<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tO, a); break;
-      default: attn_fwd_kernel<2, false><<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tO, a); break;
+      case 0: attn_fwd_pers_kernel<0, false><<<pgrid, kThreads, kSmemBytesP, st>>>(tQ, tK, tV, tO, a, n, ntile); break;
+      case 1: attn_fwd_pers_kernel<1, false><<<pgrid, kThreads, kSmemBytesP, st>>>(tQ, tK, tV, tO, a, n, ntile); break;
+      case 3: attn_fwd_pers_kernel<3, false><<<pgrid, kThreads, kSmemBytesP, st>>>(tQ, tK, tV, tO, a, n, ntile); break;
+      default: attn_fwd_pers_kernel<2, false><<<pgrid, kThreads, kSmemBytesP, st>>>(tQ, tK, tV, tO, a, n, ntile); break;
     }
   }
   VST_LAUNCH_OK();
