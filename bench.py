@@ -242,6 +242,7 @@ def run_ours(args):
     # the product's step: the same launches captured once in a CUDA graph and replayed
     graphed = None if (args.no_graph or args.ncu_step) else hpth.GraphedDenoiseStep(plan, d_x4, d_x3, d_text, F)
     step_device = step_eager if graphed is None else graphed.replay
+    streamed = None if graphed is None else hpth.StreamedDenoiseStep(graphed)
 
     def step_e2e():
         if graphed is None:
@@ -252,9 +253,9 @@ def run_ours(args):
             for text in texts:
                 outs = hpth.run_unet_hotpath(plan, x4, x3, text, F)
         else:
-            for dst, src in zip(graphed.x4 + graphed.x3[1:] + graphed.texts, h_x4 + h_x3[1:] + h_text):
-                dst.copy_(src, non_blocking=True)
-            outs = graphed.replay()
+            # the product's host-fed path: copies of step n+1 / n-1 overlap the replay of step n
+            streamed.submit(h_x4 + h_x3[1:] + h_text, h_out)
+            return
         for lvl in range(3):                                   # the step's result back on the host
             o = outs[lvl]
             if o.dim() == 3:                                   # last call at L1/L2 may be a token tensor
@@ -268,12 +269,14 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps):
+    def timed(fn, steps, after=None):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(steps):
             fn()
+        if after is not None:
+            after()                                            # e.g. wait for the last D2H copy
         e1.record()
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
@@ -295,7 +298,7 @@ def run_ours(args):
         ms_dev = timed(step_device, args.steps)
     launches = (_lib.launch_count - launches0) if graphed is None else graphed.launches * args.steps
     step_e2e()
-    ms_e2e = timed(step_e2e, args.steps)
+    ms_e2e = timed(step_e2e, args.steps, after=None if streamed is None else streamed.drain)
 
     # ---- roofline of the dominant kernel (spatial self-attention, tcgen05 flash): one extra
     #      step with CUDA events around every self-attention launch on the launching stream ----

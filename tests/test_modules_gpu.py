@@ -439,3 +439,51 @@ def test_denoise_25_steps_latent_cosine_vs_oracle():
             worst = min(worst, cos)
             assert cos >= 0.999, (i, cos)
     assert worst >= 0.999
+
+
+def test_streamed_denoise_step_matches_eager():
+    """The graph replay and the host-fed pipeline around it (StreamedDenoiseStep: H2D / D2H of
+    neighbouring steps overlapped with the replay) return, for every submitted step, exactly what
+    the eager launch sequence returns for that step's inputs (bit-exact: same kernels, same order)."""
+    from video_style_transfer_b200 import sdxl_hotpath as hpth
+    torch.manual_seed(11)
+    F_, S = 4, 16
+    with torch.device("cuda"):
+        model = hpth.SDXLHotPath(temporal_rank=8, depth_scale=0.1)
+    model = model.to(torch.bfloat16).eval()
+    plan = model.forward_plan()
+    shapes = hpth.level_shapes(F_, S)
+    bf = torch.bfloat16
+
+    def host_inputs(seed):
+        g = torch.Generator().manual_seed(seed)
+        x4 = [torch.randn(s, generator=g).to(bf).pin_memory() for s in shapes]
+        x3 = [torch.randn(s[0], s[2] * s[3], s[1], generator=g).to(bf).pin_memory() for s in shapes[1:]]
+        texts = [torch.randn(1, 77, 2048, generator=g).to(bf).pin_memory() for _ in range(2)]
+        return x4, x3, texts
+
+    def eager(x4, x3, texts):
+        d4 = [t.cuda() for t in x4]
+        d3 = [None] + [t.cuda() for t in x3]
+        outs = None
+        for t in texts:
+            outs = hpth.run_unet_hotpath(plan, d4, d3, t.cuda(), F_)
+        return [o.float().cpu() for o in outs]
+
+    steps = [host_inputs(100 + i) for i in range(5)]
+    want = [eager(*s) for s in steps]
+    x4, x3, texts = steps[0]
+    graphed = hpth.GraphedDenoiseStep(plan, [t.cuda() for t in x4], [None] + [t.cuda() for t in x3],
+                                      [t.cuda() for t in texts], F_)
+    got0 = [o.float().cpu() for o in graphed.replay()]
+    for a, b in zip(got0, want[0]):
+        assert torch.equal(a, b)
+    pipe = hpth.StreamedDenoiseStep(graphed)
+    host_outs = [[torch.empty(o.shape, dtype=bf).pin_memory() for o in graphed.outs] for _ in steps]
+    for (x4, x3, texts), ho in zip(steps, host_outs):
+        pipe.submit(x4 + x3 + texts, ho)
+    pipe.drain()
+    torch.cuda.synchronize()
+    for ho, w in zip(host_outs, want):
+        for a, b in zip(ho, w):
+            assert torch.equal(a.float(), b)
