@@ -324,7 +324,7 @@ def run_ours(args):
     # L1 self-attention shape), profiles/ncu_traffic.json
     traffic = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["attn_fwd_kernel"]
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["attn_fwd_pers_kernel"]
     except Exception:
         pass
     attn_ms = sum(s.elapsed_time(e) for s, e, _ in ev)
@@ -360,7 +360,7 @@ def run_ours(args):
         "gpu_launches": launches,
         "clocks": clk.summary(),
         "tflops_hotpath": step_flops / (ms_step * 1e-3) / 1e12,
-        "roofline": {"kernel": "attn_fwd_kernel (spatial self-attention)", "bound": "tensor",
+        "roofline": {"kernel": "attn_fwd_pers_kernel (spatial self-attention)", "bound": "tensor",
                      "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
                      "frac": achieved / peak_tf,
                      "traffic": None if traffic is None else traffic["dram_bytes_per_launch"],

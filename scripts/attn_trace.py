@@ -29,9 +29,20 @@ def run(sq=1024, heads=20, bt=16):
                               c, c, c, c, 1, 0.125, None, 0, 0, 0, None)
         assert rc == 0
         torch.cuda.synchronize()
-    buf = np.zeros(12 * 1024, dtype=np.int64)
+    buf = np.zeros(4 * 12 * 1024, dtype=np.int64)
     assert lib.vst_attn_debug_trace(buf.ctypes.data_as(ctypes.c_void_p)) == 0
-    t = buf.reshape(12, 1024)
+    full = buf.reshape(4, 12, 1024)
+    # the MMA warp (warp 5) and the TMA warp land in banks 1 and 0: fold the MMA stamps into bank 0's view
+    w = int(os.environ.get("TRACE_WARP", "0"))
+    t = full[w].copy()
+    t[5], t[6] = full[1][5], full[1][6]     # the MMA warp (warp 5) stamps into bank 1
+    nb = sq // 128
+    print("math phase per softmax warp (mean over item 2):",
+          [float(np.mean([full[x][2][i] - full[x][1][i] for i in range(nb + 1, 2 * nb)])) for x in range(4)])
+    print("block period per softmax warp:",
+          [float(np.mean([full[x][4][i + 1] - full[x][4][i] for i in range(nb + 1, 2 * nb - 1)])) for x in range(4)])
+    print("P_stored skew vs warp 0 (mean):",
+          [float(np.mean([full[x][4][i] - full[0][4][i] for i in range(nb + 1, 2 * nb)])) for x in range(4)])
     nblk = sq // 128
     n = min(3 * nblk, 1024)
     t0 = t[5, 0]

@@ -130,11 +130,11 @@ def main():
     for name in ("attn", "gemm", "attn_bwd"):
         rows = summarise_raw(name, tag)
         if name == "attn" and rows:
-            # the dominant launch: L1 spatial self-attention, the longest attn_fwd_kernel captured
-            best = max((r for r in rows if "attn_fwd_kernel" in r["Kernel Name"][0]),
+            # the dominant launch: L1 spatial self-attention, the longest attn_fwd_pers_kernel captured
+            best = max((r for r in rows if "attn_fwd_pers_kernel" in r["Kernel Name"][0]),
                        key=lambda r: num(r["gpu__time_duration.sum"]))
             rd, wr = num(best["dram__bytes_read.sum"]), num(best["dram__bytes_write.sum"])
-            traffic["attn_fwd_kernel"] = {
+            traffic["attn_fwd_pers_kernel"] = {
                 "dram_bytes_per_launch": rd + wr, "dram_read": rd, "dram_write": wr,
                 "duration_us_under_ncu": num(best["gpu__time_duration.sum"]),
                 "note": f"ncu --set full, kbench attn L1 self (B=16 h=10 S=4096 d=64), launch id {best['ID'][0]}; "

@@ -83,9 +83,9 @@ __device__ __forceinline__ float2 ex2_poly2(float2 x) {
 
 // -DVST_ATTN_TRACE: CTA 0 records clock64() stamps of its pipeline events (tuning builds only).
 #ifdef VST_ATTN_TRACE
-__device__ long long g_attn_trace[12 * 1024];
+__device__ long long g_attn_trace[4 * 12 * 1024];   // [warp & 3][slot][index]
 #define TRACE(slot, idx) do { if (blockIdx.x == 0 && (idx) < 1024 && (threadIdx.x & 31) == 0) \
-    g_attn_trace[(slot) * 1024 + (idx)] = clock64(); } while (0)
+    g_attn_trace[((threadIdx.x >> 5) & 3) * 12 * 1024 + (slot) * 1024 + (idx)] = clock64(); } while (0)
 #else
 #define TRACE(slot, idx) do { } while (0)
 #endif
@@ -297,10 +297,11 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     // deferred epilogue of the previous item
     int pend_it = -1;
     float pend_inv = 0.f, pend_lse = 0.f;
+    bool p_pending = false;              // a P store is in flight, p_full not yet signalled
     auto epilogue = [&](int pit, int pi, float inv, float lse, uint32_t last_blk) {
       // O of item pit (ring slot pi % NQ): TMEM -> normalise -> its dead Q buffer -> store warp
       mbar_wait(o_full, last_blk & 1, 32);
-      if (warp == 0) TRACE(7, pi);
+      TRACE(7, pi);
       tc_fence_after();
       uint8_t* orow = sQ + (pi % NQ) * kTile + row * 128;
       const int rx = row & 7;
@@ -325,7 +326,7 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       }
       fence_proxy_async_smem();
       mbar_arrive(&o_staged[pi % NQ]);
-      if (warp == 0) TRACE(8, pi);
+      TRACE(8, pi);
       if (a.lse != nullptr) {
         const int qt = (pit % ntile) * BQ;
         if (qt + row < a.Sq) {
@@ -341,13 +342,22 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         const int kv0 = j * BKV;
         const bool tail = kv0 + BKV > a.Sk;
         mbar_wait(s_full, (blk + j) & 1, 30);
-        if (warp == 0) TRACE(0, blk + j);
+        TRACE(0, blk + j);
         tc_fence_after();
         uint32_t r[BKV];
 #pragma unroll
         for (int c = 0; c < BKV / 32; ++c) tmem_ld32(tS + c * 32, r + c * 32);
+        if (p_pending) {
+          // the previous block's P store completes under this block's S load (traces: the
+          // tcgen05.wait::st + fence + arrive chain cost ~200 clk per block when it sat behind
+          // the store itself)
+          tmem_st_wait();
+          tc_fence_before();
+          mbar_arrive(p_full);
+          p_pending = false;
+        }
         tmem_ld_wait();
-        if (warp == 0) TRACE(1, blk + j);
+        TRACE(1, blk + j);
         tc_fence_before();
         mbar_arrive(s_free);             // the tensor pipe may overwrite S now
         if (tail) {
@@ -403,10 +413,10 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
           l2 = __fadd2_rn(l2, pv);
           r[e] = pack_bf16(pv.x, pv.y);
         }
-        if (warp == 0) TRACE(2, blk + j);
+        TRACE(2, blk + j);
         if (j > 0) {
           mbar_wait(o_full, (blk + j - 1) & 1, 31);   // P V of the previous block is done with P and O
-          if (warp == 0) TRACE(3, blk + j);
+          TRACE(3, blk + j);
           tc_fence_after();
           if (__any_sync(0xffffffffu, grow)) {
             const float2 al2 = make_float2(alpha, alpha);
@@ -432,16 +442,19 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         }
         tmem_st32(tP, r);
         tmem_st32(tP + 32, r + 32);
-        tmem_st_wait();
-        tc_fence_before();
-        mbar_arrive(p_full);
-        if (warp == 0) TRACE(4, blk + j);
+        p_pending = true;                // completion + p_full arrive: under the next S load
+        TRACE(4, blk + j);
       }
       const float l = l2.x + l2.y;
       pend_it = it;
       pend_inv = 1.f / l;
       pend_lse = (m + log2f(l)) * 0.6931471805599453f;
       blk += nblk;
+    }
+    if (p_pending) {
+      tmem_st_wait();
+      tc_fence_before();
+      mbar_arrive(p_full);
     }
     if (pend_it >= 0) epilogue(pend_it, i - 1, pend_inv, pend_lse, blk - 1);
   }
@@ -467,7 +480,7 @@ int make_qkv_map(CUtensorMap* m, const void* p, int64_t B, int64_t S, int width,
 
 #ifdef VST_ATTN_TRACE
 extern "C" int vst_attn_debug_trace(long long* host_dst) {
-  return (int)cudaMemcpyFromSymbol(host_dst, g_attn_trace, sizeof(long long) * 12 * 1024);
+  return (int)cudaMemcpyFromSymbol(host_dst, g_attn_trace, sizeof(long long) * 4 * 12 * 1024);
 }
 #endif
 
