@@ -101,6 +101,8 @@ def main():
                  ("L2 self proj M=16384 C=1280 r=64x2", 16384, 1280, 1280, 128),
                  ("L1 u = x A^T  N=128", 65536, 128, 640, 0),
                  ("L2 cross kv M=1232 K=2048 N=1280", 1232, 1280, 2048, 128),
+                 ("L2 text k|v folded M=77 K=2048 N=2560", 77, 2560, 2048, 0),
+                 ("L1 text k|v folded M=77 K=2048 N=1280", 77, 1280, 2048, 0),
                  ("L0 temporal proj M=262144 C=320 r=32", 262144, 320, 320, 32),
                  ("L2 ff M=16384 1280->10240", 16384, 10240, 1280, 0)]
         for tag, m, n, k1, k2 in cases:

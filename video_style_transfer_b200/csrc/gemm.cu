@@ -760,6 +760,11 @@ extern "C" int vst_lora_gemm(const void* A1, int64_t lda1, const void* B1, int64
   // CTA pairs (256-row tiles) once there is at least one tile per SM pair to keep busy
   if (act == VST_ACT_GEGLU) GO2(256);
   const bool big = M >= 2048 && !vst_force_single_cta();
+  static int force_bn = -1;
+  if (force_bn < 0) { const char* e = getenv("VST_GEMM_BN"); force_bn = e ? atoi(e) : 0; }   // tuning only
+  if (big && force_bn == 160 && FITS(160)) GO2(160);
+  if (big && force_bn == 128 && FITS(128)) GO2(128);
+  if (force_bn == 256 && FITS(256)) GO(256);
   // 256-wide pair tiles move the fewest operand bytes per MAC (64 B/clk/SM against 83 for 160):
   // worth up to 20 % of padded columns (N = 640, 960, 1920 -> 768, 1024, 2048); r01 launch list:
   // the BN = 160 family ran at 760 TFLOP/s, the BN = 256 family at 1260
@@ -769,6 +774,9 @@ extern "C" int vst_lora_gemm(const void* A1, int64_t lda1, const void* B1, int64
   if (big && FITS(256) && (M / 256) * (N / 256) >= vst_sm_count() / 2) GO2(256);
   if (big && FITS(160) && (M / 256) * (N / 160) >= vst_sm_count() / 2) GO2(160);
   if (big && FITS(128) && (M / 256) * (N / 128) >= vst_sm_count() / 2) GO2(128);
+  // one row tile (the text K / V projections: M = 77 per prompt, K = 2048): the run time is the
+  // weight read, and one SM pulls only ~0.15 TB/s -- narrow tiles spread it over 4x the SMs
+  if (M <= 128 && (force_bn == 0 || force_bn == 64) && FITS(64) && N / 64 >= 16) GO(64);
   if (FITS(256)) GO(256);
   if (FITS(160)) GO(160);
   if (FITS(192)) GO(192);
