@@ -260,8 +260,11 @@ layernorm_kernel(const TI* __restrict__ x, TO* __restrict__ y, const TP* __restr
 // flat span of 160 16-byte vectors = exactly 5 per lane, so no lane idles (the per-row mapping
 // leaves 24 of 32 lanes idle on the second vector of a 40-vector row) and 5 loads are in flight
 // per lane before the first reduction.
+#ifndef LN_MIN_BLOCKS
+#define LN_MIN_BLOCKS 4
+#endif
 template <typename TI, typename TO, typename TP, int NVEC>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, LN_MIN_BLOCKS)
 layernorm_flat_kernel(const TI* __restrict__ x, TO* __restrict__ y, const TP* __restrict__ gamma,
                       const TP* __restrict__ beta, const float* __restrict__ pe, int64_t rows, int F,
                       float eps) {
