@@ -40,74 +40,119 @@ __device__ __forceinline__ void load8<float>(const float* p, float* v) {
   v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
 }
 
-// grid = B*groups*F*slabs; block (b,g,f,s) reduces elements [s*kSlabElems, ...) of the cg*HW chunk
-// (32-bit index arithmetic: the host checks cg*HW < 2^31).
+// One work item (b,g,f,s) = elements [s*kSlabElems, ...) of the cg*HW chunk of one (group, frame)
+// (32-bit index arithmetic: the host checks cg*HW < 2^31).  Blocks are persistent over a strided
+// list of items and keep the NEXT item's 16-byte loads in flight (raw, in registers) while the
+// current one goes through its two block reductions: one-shot blocks spent most of their life
+// in the reductions with nothing outstanding (r01: 1.8 TB/s at L0).
+template <typename T> struct Raw8;
+template <> struct Raw8<__nv_bfloat16> {
+  uint4 r;
+  __device__ __forceinline__ void load(const __nv_bfloat16* p) { r = ld_stream16(p); }
+  __device__ __forceinline__ void zero() { r = make_uint4(0, 0, 0, 0); }
+  __device__ __forceinline__ void get(float* v) const {
+    float2 e;
+    e = unpack_bf16(r.x); v[0] = e.x; v[1] = e.y;
+    e = unpack_bf16(r.y); v[2] = e.x; v[3] = e.y;
+    e = unpack_bf16(r.z); v[4] = e.x; v[5] = e.y;
+    e = unpack_bf16(r.w); v[6] = e.x; v[7] = e.y;
+  }
+};
+template <> struct Raw8<float> {
+  float4 a, b;
+  __device__ __forceinline__ void load(const float* p) {
+    a = *reinterpret_cast<const float4*>(p);
+    b = *reinterpret_cast<const float4*>(p + 4);
+  }
+  __device__ __forceinline__ void zero() { a = b = make_float4(0.f, 0.f, 0.f, 0.f); }
+  __device__ __forceinline__ void get(float* v) const {
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  }
+};
+
 template <typename T, bool VEC>
-__global__ void __launch_bounds__(kSlabThreads)
+__global__ void __launch_bounds__(kSlabThreads, 4)
 gn_stats_kernel(const T* __restrict__ x, float* __restrict__ partials, int C, int F, int HW,
-                int64_t sB, int64_t sC, int64_t sF, int groups, int slabs) {
+                int64_t sB, int64_t sC, int64_t sF, int groups, int slabs, int total) {
   __shared__ float red[32];
-  int t = blockIdx.x;
-  const int s = t % slabs; t /= slabs;
-  const int f = t % F; t /= F;
-  const int g = t % groups;
-  const int b = t / groups;
   const int cg = C / groups;
   const int chunk = cg * HW;
-  const int e0 = s * kSlabElems;
-  const T* base = x + (int64_t)b * sB + (int64_t)f * sF + (int64_t)g * cg * sC;
-
-  float v[kVecPerThread][8];
-  float sum = 0.f;
-  int cnt = 0;
+  auto item_base = [&](int t, int& s) -> const T* {
+    s = t % slabs; t /= slabs;
+    const int f = t % F; t /= F;
+    const int g = t % groups;
+    const int b = t / groups;
+    return x + (int64_t)b * sB + (int64_t)f * sF + (int64_t)g * cg * sC;
+  };
+  Raw8<T> nxt[kVecPerThread];
+  auto fetch = [&](int t) {
+    int s;
+    const T* base = item_base(t, s);
+    const int e0 = s * kSlabElems;
 #pragma unroll
-  for (int i = 0; i < kVecPerThread; ++i) {
-    const int e = e0 + (i * kSlabThreads + (int)threadIdx.x) * 8;
-    if (VEC) {
+    for (int i = 0; i < kVecPerThread; ++i) {
+      const int e = e0 + (i * kSlabThreads + (int)threadIdx.x) * 8;
       if (e < chunk) {
         const int c = e / HW, hw = e - c * HW;
-        load8<T>(base + (int64_t)c * sC + hw, v[i]);
-        cnt += 8;
+        nxt[i].load(base + (int64_t)c * sC + hw);
       } else {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[i][j] = 0.f;
+        nxt[i].zero();
       }
+    }
+  };
+  int t = blockIdx.x;
+  if (VEC && t < total) fetch(t);
+  for (; t < total; t += gridDim.x) {
+    int s;
+    const T* base = item_base(t, s);
+    const int e0 = s * kSlabElems;
+    float v[kVecPerThread][8];
+    if (VEC) {
+#pragma unroll
+      for (int i = 0; i < kVecPerThread; ++i) nxt[i].get(v[i]);
+      if (t + (int)gridDim.x < total) fetch(t + gridDim.x);      // in flight under the reductions
     } else {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int ej = e + j;
-        if (ej < chunk) {
-          const int c = ej / HW, hw = ej - c * HW;
-          v[i][j] = (float)base[(int64_t)c * sC + hw];
-          ++cnt;
-        } else {
-          v[i][j] = 0.f;
+      for (int i = 0; i < kVecPerThread; ++i) {
+        const int e = e0 + (i * kSlabThreads + (int)threadIdx.x) * 8;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int ej = e + j;
+          if (ej < chunk) {
+            const int c = ej / HW, hw = ej - c * HW;
+            v[i][j] = (float)base[(int64_t)c * sC + hw];
+          } else {
+            v[i][j] = 0.f;
+          }
         }
       }
     }
+    float sum = 0.f;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) sum += v[i][j];
-  }
-  const int rem = chunk - e0;
-  const float n = (float)(rem < kSlabElems ? rem : kSlabElems);
-  const float mean = block_sum(sum, red) / n;
-  float m2 = 0.f;
+    for (int i = 0; i < kVecPerThread; ++i)
 #pragma unroll
-  for (int i = 0; i < kVecPerThread; ++i) {
-    const int e = e0 + (i * kSlabThreads + (int)threadIdx.x) * 8;
+      for (int j = 0; j < 8; ++j) sum += v[i][j];
+    const int rem = chunk - e0;
+    const float n = (float)(rem < kSlabElems ? rem : kSlabElems);
+    const float mean = block_sum(sum, red) / n;
+    float m2 = 0.f;
 #pragma unroll
-    for (int j = 0; j < 8; ++j)
-      if (e + j < chunk) {
-        const float d = v[i][j] - mean;
-        m2 = fmaf(d, d, m2);
-      }
+    for (int i = 0; i < kVecPerThread; ++i) {
+      const int e = e0 + (i * kSlabThreads + (int)threadIdx.x) * 8;
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (e + j < chunk) {
+          const float d = v[i][j] - mean;
+          m2 = fmaf(d, d, m2);
+        }
+    }
+    m2 = block_sum(m2, red);
+    if (threadIdx.x == 0) {
+      // item t = ((b*groups + g)*F + f)*slabs + s: the partials are laid out in item order
+      float* out = partials + (int64_t)t * 3;
+      out[0] = n; out[1] = mean; out[2] = m2;
+    }
   }
-  m2 = block_sum(m2, red);
-  if (threadIdx.x == 0) {
-    float* out = partials + ((int64_t)(b * groups + g) * (F * slabs) + (f * slabs + s)) * 3;
-    out[0] = n; out[1] = mean; out[2] = m2;
-  }
-  (void)cnt;
 }
 
 __device__ __forceinline__ void chan(float& n, float& mu, float& m2, float nb, float mub,
@@ -433,9 +478,11 @@ extern "C" int vst_groupnorm5d_stats(const void* x, float* partials, int B, int 
   const bool vec = HW % 8 == 0 && sB % 8 == 0 && sC % 8 == 0 && sF % 8 == 0 &&
                    (reinterpret_cast<uintptr_t>(x) & 31) == 0;
   cudaStream_t st = (cudaStream_t)stream;
+  const int64_t resident = (int64_t)vst_sm_count() * 4;     // 4 x 256 threads per SM (64 registers)
+  const unsigned pgrid = (unsigned)(grid < resident ? grid : resident);
 #define GN_LAUNCH(T, V)                                                                         \
-  gn_stats_kernel<T, V><<<(unsigned)grid, kSlabThreads, 0, st>>>((const T*)x, partials, C, F, HW, \
-                                                                 sB, sC, sF, groups, slabs)
+  gn_stats_kernel<T, V><<<pgrid, kSlabThreads, 0, st>>>((const T*)x, partials, C, F, HW, sB, sC, \
+                                                        sF, groups, slabs, (int)grid)
   if (dtype == VST_BF16) { if (vec) GN_LAUNCH(__nv_bfloat16, true); else GN_LAUNCH(__nv_bfloat16, false); }
   else { if (vec) GN_LAUNCH(float, true); else GN_LAUNCH(float, false); }
 #undef GN_LAUNCH
