@@ -213,6 +213,36 @@ def test_attn_fwd(ops, hp, bt, bk, heads, sq, sk):
     assert torch.allclose(lse.cpu(), want_lse, atol=2e-2, rtol=1e-3)
 
 
+@pytest.mark.parametrize("bt,bk,heads,sq,sk", [(16, 16, 20, 1024, 1024), (16, 1, 20, 1024, 77),
+                                               (16, 16, 10, 4096, 4096)])
+def test_attn_fwd_full_size_schedule_independence(ops, bt, bk, heads, sq, sk):
+    """Config-3 shapes, where the oracle is too slow: size-independent properties of the persistent
+    kernel.  (1) An item's result does not depend on which CTA walked it or on what that CTA did
+    before (Q ring slot, deferred epilogue, barrier phases): one (batch, head) slice computed alone
+    is BIT-identical to the same slice of the full launch.  (2) Attention is invariant under a
+    joint permutation of keys and values (different block composition, same softmax): the outputs
+    agree to bf16 rounding.  (3) Rows of P sum to one: with V = 1 the output is exactly 1."""
+    torch.manual_seed(17)
+    c = heads * 64
+    q = torch.randn(bt, sq, c).to(torch.bfloat16).cuda()
+    k = torch.randn(bk, sk, c).to(torch.bfloat16).cuda()
+    v = torch.randn(bk, sk, c).to(torch.bfloat16).cuda()
+    o, lse = ops.attn_fwd(q, k, v, heads, return_lse=True)
+    b, h = bt - 3, heads - 2
+    kb = b // (bt // bk)
+    cols = slice(h * 64, (h + 1) * 64)
+    o1, lse1 = ops.attn_fwd(q[b:b + 1, :, cols].contiguous(), k[kb:kb + 1, :, cols].contiguous(),
+                            v[kb:kb + 1, :, cols].contiguous(), 1, return_lse=True)
+    assert torch.equal(o1[0], o[b, :, cols])
+    assert torch.equal(lse1.reshape(-1), lse[b, h].reshape(-1))
+    perm = torch.randperm(sk, device="cuda")
+    o2 = ops.attn_fwd(q, k[:, perm].contiguous(), v[:, perm].contiguous(), heads)
+    assert rel_err(o2, o.float().cpu()) < REL_TOL
+    ones = torch.ones_like(v)
+    o3 = ops.attn_fwd(q, k, ones, heads)
+    assert (o3.float() - 1.0).abs().max().item() <= 2 ** -7
+
+
 @pytest.mark.parametrize("m,c,k1,k2,groups", [(300, 128, 64, 16, 3), (1000, 640, 640, 128, 3),
                                               (6400, 1280, 1280, 128, 3), (16384, 640, 640, 128, 3),
                                               (77, 1280, 2048, 128, 2), (513, 320, 320, 32, 3)])
