@@ -74,21 +74,27 @@ __device__ __forceinline__ int64_t tok_offset(const ShardArgs& sh, int b, int hw
 // MODE 0: forward (x[b,c,f,hw] -> y[(b,hw),f,c] + pe[f,c])
 // MODE 1: backward (y[(b,hw),f,c] -> out[b,c,f,hw] + residual[b,c,f,hw])
 // MODE 2: forward with the GroupNorm affine applied on the way in
+// One CTA moves kNT 64 x 64 tiles that follow each other along hw, with the global loads of all of
+// them issued before the first shared-memory pass: a one-tile CTA had 32 B per thread in flight and
+// ran at 60-75 % of a plain copy (r01 kbench); kNT = 4 keeps 128 B (forward) / 256 B (backward +
+// residual) per thread outstanding.
+constexpr int kNT = 4;
+
 template <int MODE>
 __global__ void __launch_bounds__(kThreads)
 rearrange_bf16_kernel(const __nv_bfloat16* __restrict__ src, __nv_bfloat16* __restrict__ dst,
                       const float* __restrict__ pe, const __nv_bfloat16* __restrict__ residual,
                       int C, int F, int HW, int64_t sB, int64_t sC, int64_t sF, int tilesHW,
                       int tilesC, NormArgs na, ShardArgs sh) {
-  __shared__ __align__(16) uint32_t tile[kTileHW * kTileWords];
+  __shared__ __align__(16) uint32_t tiles[kNT][kTileHW * kTileWords];
   int t = blockIdx.x;
-  const int thw = t % tilesHW;
+  const int thw = t % tilesHW;          // tilesHW counts GROUPS of kNT tiles
   t /= tilesHW;
   const int tc = t % tilesC;
   t /= tilesC;
   const int f = t % F;
   const int b = t / F;
-  const int hw0 = thw * kTileHW, c0 = tc * 64;
+  const int hwg = thw * (kNT * kTileHW), c0 = tc * 64;
   const int tid = threadIdx.x;
 
   // "planar" tensor P[b,c,f,hw] (strided) and "token" tensor T[(b,hw),f,c]
@@ -97,94 +103,140 @@ rearrange_bf16_kernel(const __nv_bfloat16* __restrict__ src, __nv_bfloat16* __re
   if (MODE == 0 || MODE == 2) {
     // load: thread = (channel pair cp, hw chunk hc); 16 B along hw from rows c, c+1
     const int hc = tid & 7, cp = tid >> 3;
-    const int c = c0 + 2 * cp, hw = hw0 + 8 * hc;
-    uint4 r0 = make_uint4(0, 0, 0, 0), r1 = r0;
-    if (hw < HW && c < C) {
-      r0 = ld_stream16(src + pbase + (int64_t)c * sC + hw);
-      if (c + 1 < C) r1 = ld_stream16(src + pbase + (int64_t)(c + 1) * sC + hw);
-    }
-    uint32_t a[4] = {r0.x, r0.y, r0.z, r0.w}, bb[4] = {r1.x, r1.y, r1.z, r1.w};
-    if (MODE == 2 && hw < HW && c < C) {
-      const float2 k0 = norm_coeffs(na, b, c, C);
-      const float2 k1 = c + 1 < C ? norm_coeffs(na, b, c + 1, C) : k0;
+    const int c = c0 + 2 * cp;
+    uint4 r0[kNT], r1[kNT];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        a[j] = norm_word(a[j], k0);
-        bb[j] = norm_word(bb[j], k1);
+    for (int k = 0; k < kNT; ++k) {
+      const int hw = hwg + k * kTileHW + 8 * hc;
+      r0[k] = make_uint4(0, 0, 0, 0);
+      r1[k] = r0[k];
+      if (hw < HW && c < C) {
+        r0[k] = ld_stream16(src + pbase + (int64_t)c * sC + hw);
+        if (c + 1 < C) r1[k] = ld_stream16(src + pbase + (int64_t)(c + 1) * sC + hw);
       }
     }
+    float2 k0 = make_float2(1.f, 0.f), k1 = k0;
+    if (MODE == 2 && c < C) {
+      k0 = norm_coeffs(na, b, c, C);
+      k1 = c + 1 < C ? norm_coeffs(na, b, c + 1, C) : k0;
+    }
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      tile[swz(8 * hc + 2 * j, cp)] = __byte_perm(a[j], bb[j], 0x5410);      // (c,hw) (c+1,hw)
-      tile[swz(8 * hc + 2 * j + 1, cp)] = __byte_perm(a[j], bb[j], 0x7632);  // hw+1
+    for (int k = 0; k < kNT; ++k) {
+      const int hw = hwg + k * kTileHW + 8 * hc;
+      uint32_t a[4] = {r0[k].x, r0[k].y, r0[k].z, r0[k].w}, bb[4] = {r1[k].x, r1[k].y, r1[k].z, r1[k].w};
+      if (MODE == 2 && hw < HW && c < C) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          a[j] = norm_word(a[j], k0);
+          bb[j] = norm_word(bb[j], k1);
+        }
+      }
+      uint32_t* tile = tiles[k];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        tile[swz(8 * hc + 2 * j, cp)] = __byte_perm(a[j], bb[j], 0x5410);      // (c,hw) (c+1,hw)
+        tile[swz(8 * hc + 2 * j + 1, cp)] = __byte_perm(a[j], bb[j], 0x7632);  // hw+1
+      }
     }
     __syncthreads();
     // store: item = (hw row, 16-B chunk of 8 channels)
 #pragma unroll
-    for (int it = 0; it < 2; ++it) {
-      const int item = tid + it * kThreads;
-      const int row = item >> 3, ch = item & 7;
-      const int hwr = hw0 + row, cc = c0 + 8 * ch;
-      if (hwr < HW && cc < C) {
-        uint4 v = *reinterpret_cast<const uint4*>(&tile[swz(row, 4 * ch)]);
-        if (pe != nullptr) {
-          const float4 p0 = __ldg(reinterpret_cast<const float4*>(pe + (int64_t)f * C + cc));
-          const float4 p1 = __ldg(reinterpret_cast<const float4*>(pe + (int64_t)f * C + cc + 4));
-          float2 e;
-          e = unpack_bf16(v.x); v.x = pack_bf16(e.x + p0.x, e.y + p0.y);
-          e = unpack_bf16(v.y); v.y = pack_bf16(e.x + p0.z, e.y + p0.w);
-          e = unpack_bf16(v.z); v.z = pack_bf16(e.x + p1.x, e.y + p1.y);
-          e = unpack_bf16(v.w); v.w = pack_bf16(e.x + p1.z, e.y + p1.w);
+    for (int k = 0; k < kNT; ++k) {
+      const uint32_t* tile = tiles[k];
+#pragma unroll
+      for (int it = 0; it < 2; ++it) {
+        const int item = tid + it * kThreads;
+        const int row = item >> 3, ch = item & 7;
+        const int hwr = hwg + k * kTileHW + row, cc = c0 + 8 * ch;
+        if (hwr < HW && cc < C) {
+          uint4 v = *reinterpret_cast<const uint4*>(&tile[swz(row, 4 * ch)]);
+          if (pe != nullptr) {
+            const float4 p0 = __ldg(reinterpret_cast<const float4*>(pe + (int64_t)f * C + cc));
+            const float4 p1 = __ldg(reinterpret_cast<const float4*>(pe + (int64_t)f * C + cc + 4));
+            float2 e;
+            e = unpack_bf16(v.x); v.x = pack_bf16(e.x + p0.x, e.y + p0.y);
+            e = unpack_bf16(v.y); v.y = pack_bf16(e.x + p0.z, e.y + p0.w);
+            e = unpack_bf16(v.z); v.z = pack_bf16(e.x + p1.x, e.y + p1.y);
+            e = unpack_bf16(v.w); v.w = pack_bf16(e.x + p1.z, e.y + p1.w);
+          }
+          int rk;
+          const int64_t toff = tok_offset(sh, b, hwr, f, F, HW, C, &rk);
+          __nv_bfloat16* tdst = rk < 0 ? dst : reinterpret_cast<__nv_bfloat16*>(sh.peer[rk]);
+          st_stream16(tdst + toff + cc, v);
         }
-        int rk;
-        const int64_t toff = tok_offset(sh, b, hwr, f, F, HW, C, &rk);
-        __nv_bfloat16* tdst = rk < 0 ? dst : reinterpret_cast<__nv_bfloat16*>(sh.peer[rk]);
-        st_stream16(tdst + toff + cc, v);
       }
     }
   } else {
     // load: item = (hw row, 16-B chunk of 8 channels) from the token tensor
+    uint4 v[kNT][2];
 #pragma unroll
-    for (int it = 0; it < 2; ++it) {
-      const int item = tid + it * kThreads;
-      const int row = item >> 3, ch = item & 7;
-      const int hwr = hw0 + row, cc = c0 + 8 * ch;
-      uint4 v = make_uint4(0, 0, 0, 0);
-      if (hwr < HW && cc < C) {
-        int rk;
-        const int64_t toff = tok_offset(sh, b, hwr, f, F, HW, C, &rk);
-        const __nv_bfloat16* tsrc = rk < 0 ? src : reinterpret_cast<const __nv_bfloat16*>(sh.peer[rk]);
-        v = ld_stream16(tsrc + toff + cc);
+    for (int k = 0; k < kNT; ++k) {
+#pragma unroll
+      for (int it = 0; it < 2; ++it) {
+        const int item = tid + it * kThreads;
+        const int row = item >> 3, ch = item & 7;
+        const int hwr = hwg + k * kTileHW + row, cc = c0 + 8 * ch;
+        v[k][it] = make_uint4(0, 0, 0, 0);
+        if (hwr < HW && cc < C) {
+          int rk;
+          const int64_t toff = tok_offset(sh, b, hwr, f, F, HW, C, &rk);
+          const __nv_bfloat16* tsrc = rk < 0 ? src : reinterpret_cast<const __nv_bfloat16*>(sh.peer[rk]);
+          v[k][it] = ld_stream16(tsrc + toff + cc);
+        }
       }
-      *reinterpret_cast<uint4*>(&tile[swz(row, 4 * ch)]) = v;
     }
-    __syncthreads();
+    // the residual rows this thread will add: in flight under the shared-memory pass
     const int hc = tid & 7, cp = tid >> 3;
-    const int c = c0 + 2 * cp, hw = hw0 + 8 * hc;
-    if (hw < HW && c < C) {
-      uint32_t lo[4], hi[4];
+    const int c = c0 + 2 * cp;
+    uint4 rr[kNT][2];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const uint32_t w0 = tile[swz(8 * hc + 2 * j, cp)];      // (c,hw)   (c+1,hw)
-        const uint32_t w1 = tile[swz(8 * hc + 2 * j + 1, cp)];  // (c,hw+1) (c+1,hw+1)
-        lo[j] = __byte_perm(w0, w1, 0x5410);                    // row c  : hw, hw+1
-        hi[j] = __byte_perm(w0, w1, 0x7632);                    // row c+1
-      }
+    for (int k = 0; k < kNT; ++k) {
+      const int hw = hwg + k * kTileHW + 8 * hc;
 #pragma unroll
       for (int r = 0; r < 2; ++r) {
-        if (c + r >= C) break;
-        uint32_t* w = r == 0 ? lo : hi;
-        const int64_t off = pbase + (int64_t)(c + r) * sC + hw;
-        if (residual != nullptr) {
-          const uint4 rr = ld_stream16(residual + off);
-          const uint32_t rv[4] = {rr.x, rr.y, rr.z, rr.w};
+        rr[k][r] = make_uint4(0, 0, 0, 0);
+        if (residual != nullptr && hw < HW && c + r < C)
+          rr[k][r] = ld_stream16(residual + pbase + (int64_t)(c + r) * sC + hw);
+      }
+    }
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const float2 e = unpack_bf16(w[j]), q = unpack_bf16(rv[j]);
-            w[j] = pack_bf16(e.x + q.x, e.y + q.y);
-          }
+    for (int k = 0; k < kNT; ++k) {
+#pragma unroll
+      for (int it = 0; it < 2; ++it) {
+        const int item = tid + it * kThreads;
+        const int row = item >> 3, ch = item & 7;
+        *reinterpret_cast<uint4*>(&tiles[k][swz(row, 4 * ch)]) = v[k][it];
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < kNT; ++k) {
+      const int hw = hwg + k * kTileHW + 8 * hc;
+      if (hw < HW && c < C) {
+        const uint32_t* tile = tiles[k];
+        uint32_t lo[4], hi[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t w0 = tile[swz(8 * hc + 2 * j, cp)];      // (c,hw)   (c+1,hw)
+          const uint32_t w1 = tile[swz(8 * hc + 2 * j + 1, cp)];  // (c,hw+1) (c+1,hw+1)
+          lo[j] = __byte_perm(w0, w1, 0x5410);                    // row c  : hw, hw+1
+          hi[j] = __byte_perm(w0, w1, 0x7632);                    // row c+1
         }
-        st_stream16(dst + off, make_uint4(w[0], w[1], w[2], w[3]));
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+          if (c + r >= C) break;
+          uint32_t* w = r == 0 ? lo : hi;
+          const int64_t off = pbase + (int64_t)(c + r) * sC + hw;
+          if (residual != nullptr) {
+            const uint32_t rv[4] = {rr[k][r].x, rr[k][r].y, rr[k][r].z, rr[k][r].w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float2 e = unpack_bf16(w[j]), q = unpack_bf16(rv[j]);
+              w[j] = pack_bf16(e.x + q.x, e.y + q.y);
+            }
+          }
+          st_stream16(dst + off, make_uint4(w[0], w[1], w[2], w[3]));
+        }
       }
     }
   }
@@ -279,7 +331,7 @@ int launch(const void* src, void* dst, const float* pe, const void* residual, in
   VST_REQUIRE(fast || shard == nullptr, VST_E_UNSUPPORTED,
               "sequence-parallel rearrange needs bf16 and 16-byte friendly shapes / pointers");
   if (fast) {
-    const int tilesHW = (HW + kTileHW - 1) / kTileHW, tilesC = (C + 63) / 64;
+    const int tilesHW = (HW + kNT * kTileHW - 1) / (kNT * kTileHW), tilesC = (C + 63) / 64;   // groups of kNT tiles
     const int64_t grid = (int64_t)B * F * tilesHW * tilesC;
     VST_REQUIRE(grid < (1ll << 31), VST_E_UNSUPPORTED, "rearrange: grid too large");
     rearrange_bf16_kernel<MODE><<<(unsigned)grid, kThreads, 0, st>>>(
