@@ -116,6 +116,23 @@ def main():
             report(f"lora_gemm {tag}", ms, b, None, 2 * m * n * (k1 + k2))
             ms, b = timeit(lambda: torch.nn.functional.linear(a1, b1, bias))
             report(f"  (cuBLAS F.linear, K1 only) {tag}", ms, b, None, 2 * m * n * k1)
+    if "gemmres" in which:
+        # memory-bound GEMMs with a fused residual add (motion-module to_out / FF2, spatial to_out)
+        for tag, m, n, k in [("L0 to_out +res M=262144 320x320", 262144, 320, 320),
+                             ("L0 ff2 +res M=262144 N=320 K=1280", 262144, 320, 1280),
+                             ("L1 to_out +res M=65536 640x640", 65536, 640, 640),
+                             ("L1 ff2 +res M=65536 N=640 K=2560", 65536, 640, 2560),
+                             ("L2 to_out +res M=16384 1280x1280", 16384, 1280, 1280)]:
+            a1 = torch.randn(m, k, device="cuda").to(bf)
+            b1 = (torch.randn(n, k, device="cuda") / k ** 0.5).to(bf)
+            bias = torch.randn(n, device="cuda").to(bf)
+            res = torch.randn(m, n, device="cuda").to(bf)
+            out = torch.empty(m, n, device="cuda", dtype=bf)
+            nb = (a1.numel() + b1.numel() + 2 * res.numel()) * 2
+            ms, b = timeit(lambda: ops.lora_gemm(a1, b1, bias=bias, residual=res, out=out))
+            report(f"lora_gemm {tag}", ms, b, nb, 2 * m * n * k)
+            ms, b = timeit(lambda: ops.lora_gemm(a1, b1, bias=bias, out=out))
+            report(f"  (same without residual) {tag}", ms, b, nb - res.numel() * 2, 2 * m * n * k)
     if "attn" in which:
         for tag, bt, h, sq, sk in [("L1 self", 16, 10, 4096, 4096), ("L2 self", 16, 20, 1024, 1024),
                                    ("L1 cross", 16, 10, 4096, 77), ("L2 cross", 16, 20, 1024, 77)]:

@@ -119,9 +119,10 @@ __device__ __forceinline__ void epilogue_chunk(const EpiArgs& ep, const uint32_t
   }
 }
 
-// bias / activation / scale of one 32-column chunk, packed to bf16 (TMA-store path: no residual)
+// bias / activation / residual / scale of one 32-column chunk, packed to bf16 (TMA-store path).
+// res: the 32 residual values of this row chunk (bf16 pairs, zero where there is none).
 __device__ __forceinline__ void epilogue_pack(const EpiArgs& ep, const uint32_t* r, float bl,
-                                              uint32_t* w) {
+                                              const uint4* res, uint32_t* w) {
 #pragma unroll
   for (int v8 = 0; v8 < 4; ++v8) {
     float o[8];
@@ -134,6 +135,15 @@ __device__ __forceinline__ void epilogue_pack(const EpiArgs& ep, const uint32_t*
     if (ep.act == 1) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) o[j] = 0.5f * o[j] * (1.f + erff(o[j] * 0.70710678118654752f));
+    }
+    if (res != nullptr) {
+      const uint32_t rw[4] = {res[v8].x, res[v8].y, res[v8].z, res[v8].w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 e = unpack_bf16(rw[j]);
+        o[2 * j] += e.x;
+        o[2 * j + 1] += e.y;
+      }
     }
 #pragma unroll
     for (int j = 0; j < 4; ++j)
@@ -164,7 +174,7 @@ __device__ __forceinline__ void epilogue_bias(const EpiArgs& ep, int n0, int ewa
   for (int i = 0; i < EpiBias<BN>::kMax; ++i) b.v[i] = bias_lane(ep, n0 + half * 32 + i * 64 + lane, ep.N);
 }
 
-template <int BN, typename Release>
+template <int BN, bool RES, typename Release>
 __device__ __forceinline__ void epilogue_tile(const EpiArgs& ep, const CUtensorMap* tmD,
                                               uint32_t tacc, int m0, int n0, int ewarp, int lane,
                                               uint8_t* stage_out, int& buf, const EpiBias<BN>& bias,
@@ -174,7 +184,10 @@ __device__ __forceinline__ void epilogue_tile(const EpiArgs& ep, const CUtensorM
   const int64_t row = (int64_t)m0 + quarter * 32 + lane;
   const bool row_ok = row < ep.M;
   const uint32_t taddr = tacc + (uint32_t(quarter * 32) << 16);
-  const bool via_tma = ep.residual == nullptr && !ep.out_f32 && !(ep.debug & 16);   // 16: direct stores
+  // bf16 output always leaves through the staged TMA store; a residual is read per row chunk and
+  // added before the pack (r01 launch list: the direct row stores made the memory-bound residual
+  // GEMMs 3x slower than their twins without residual -- L0 to_out 230 us against 76 us)
+  const bool via_tma = !ep.out_f32 && !(ep.debug & 16);   // 16: direct stores
   constexpr int kMax = EpiBias<BN>::kMax;
   const int nch = (BN - half * 32 + 63) / 64;          // chunks of this warp: c0 = half*32 + 64 i
   uint32_t r[2][32];
@@ -183,6 +196,17 @@ __device__ __forceinline__ void epilogue_tile(const EpiArgs& ep, const CUtensorM
   for (int i = 0; i < kMax; ++i) {
     if (i >= nch) break;
     const int c0 = half * 32 + i * 64;
+    // RES (a kernel instantiation of its own, so the plain kernel's epilogue keeps its registers):
+    // bf16 output + residual.  The residual row chunk is requested before the accumulator wait;
+    // 16-byte loads, column groups past N and rows past M read as zero.
+    uint4 res[4];
+    if (RES) {
+      const __nv_bfloat16* rp = reinterpret_cast<const __nv_bfloat16*>(ep.residual) + row * ep.ldr + n0 + c0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        res[q] = (row_ok && n0 + c0 + q * 8 < ep.N) ? __ldg(reinterpret_cast<const uint4*>(rp + q * 8))
+                                                    : make_uint4(0, 0, 0, 0);
+    }
     tmem_ld_wait();
     if (i + 1 < nch) {
       tmem_ld32(taddr + c0 + 64, r[(i + 1) & 1]);
@@ -196,7 +220,7 @@ __device__ __forceinline__ void epilogue_tile(const EpiArgs& ep, const CUtensorM
     if (ep.debug & 2) continue;
     if (via_tma) {
       uint32_t w[16];
-      epilogue_pack(ep, rc, bias.v[i], w);
+      epilogue_pack(ep, rc, bias.v[i], RES ? res : nullptr, w);
       uint8_t* sbuf = stage_out + buf * kStageOutBytes;
       if (lane == 0) tma_store_wait_read<1>();      // the store that last used this buffer is done
       __syncwarp();
@@ -296,7 +320,7 @@ __device__ __forceinline__ void epilogue_tile_geglu(const EpiArgs& ep, const CUt
   }
 }
 
-template <int BN>
+template <int BN, bool RES>
 __global__ void __launch_bounds__(kThreads, 1)
 lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
                  const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
@@ -409,8 +433,8 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
       mbar_wait(&acc_full[acc], acc_phase, 4);
       tc_fence_after();
       uint64_t* done = &acc_empty[acc];
-      epilogue_tile<BN>(ep, &tmD, tmem_base + acc * C::kAccStride, m0, n0, ewarp, lane, my_out, buf, bias,
-                        [&]() { if (lane == 0) mbar_arrive(done); });
+      epilogue_tile<BN, RES>(ep, &tmD, tmem_base + acc * C::kAccStride, m0, n0, ewarp, lane, my_out, buf, bias,
+                             [&]() { if (lane == 0) mbar_arrive(done); });
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
     if (lane == 0) tma_store_wait<0>();
@@ -445,7 +469,7 @@ struct Cfg2 {
   static constexpr int kSmemBytes = kStages * kStageBytes + kOutBytes + 1024 + 256;
 };
 
-template <int BN>
+template <int BN, bool RES>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 lora_gemm2_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
                   const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
@@ -589,7 +613,7 @@ lora_gemm2_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constan
       epilogue_bias<BN>(ep, n0, ewarp, lane, bias);
       mbar_wait(&acc_full[acc], acc_phase, 4);
       tc_fence_after();
-      epilogue_tile<BN>(ep, &tmD, tmem_base + acc * C::kAccStride, m0, n0, ewarp, lane, my_out, buf, bias, release);
+      epilogue_tile<BN, RES>(ep, &tmD, tmem_base + acc * C::kAccStride, m0, n0, ewarp, lane, my_out, buf, bias, release);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
     if (lane == 0) tma_store_wait<0>();
@@ -611,7 +635,7 @@ int make_operand_map(CUtensorMap* m, const void* p, int64_t rows, int K, int64_t
 }
 
 int make_out_map(CUtensorMap* m, const EpiArgs& ep) {
-  if (ep.out_f32 || ep.residual != nullptr) {      // direct-store path: the map is never used
+  if (ep.out_f32) {      // direct-store path: the map is never used
     memset(m, 0, sizeof(*m));
     return VST_OK;
   }
@@ -640,10 +664,13 @@ int launch(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, c
   }
   CUtensorMap tD;
   if ((rc = make_out_map(&tD, ep))) return rc;
-  auto kern = lora_gemm_kernel<BN>;
+  const bool res = ep.residual != nullptr && !ep.out_f32;    // bf16 + residual: staged-store epilogue
+  auto kern = res ? lora_gemm_kernel<BN, true> : lora_gemm_kernel<BN, false>;
   static bool configured = false;
   if (!configured) {
-    VST_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    VST_CUDA_OK(cudaFuncSetAttribute(lora_gemm_kernel<BN, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     C::kSmemBytes));
+    VST_CUDA_OK(cudaFuncSetAttribute(lora_gemm_kernel<BN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      C::kSmemBytes));
     configured = true;
   }
@@ -679,10 +706,13 @@ int launch2(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, 
   }
   CUtensorMap tD;
   if ((rc = make_out_map(&tD, ep))) return rc;
-  auto kern = lora_gemm2_kernel<BN>;
+  const bool res = ep.residual != nullptr && !ep.out_f32;    // bf16 + residual: staged-store epilogue
+  auto kern = res ? lora_gemm2_kernel<BN, true> : lora_gemm2_kernel<BN, false>;
   static bool configured = false;
   if (!configured) {
-    VST_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    VST_CUDA_OK(cudaFuncSetAttribute(lora_gemm2_kernel<BN, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     C::kSmemBytes));
+    VST_CUDA_OK(cudaFuncSetAttribute(lora_gemm2_kernel<BN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      C::kSmemBytes));
     configured = true;
   }
