@@ -174,6 +174,20 @@ __device__ __forceinline__ void epilogue_bias(const EpiArgs& ep, int n0, int ewa
   for (int i = 0; i < EpiBias<BN>::kMax; ++i) b.v[i] = bias_lane(ep, n0 + half * 32 + i * 64 + lane, ep.N);
 }
 
+// RES kernels: the residual rows of the coming tile are pulled towards L2 while its mainloop still
+// runs (the epilogue's own 16-byte loads then find them there; no registers held across the wait).
+// Measured and dropped: carrying the residual chunk one chunk ahead in registers (L0 157 -> 171 us).
+template <int BN>
+__device__ __forceinline__ void epilogue_prefetch_res(const EpiArgs& ep, int m0, int n0, int ewarp, int lane) {
+  const int quarter = (ewarp + 2) & 3, half = ewarp >> 2;
+  const int64_t row = (int64_t)m0 + quarter * 32 + lane;
+  if (row >= ep.M) return;
+  const __nv_bfloat16* rp = reinterpret_cast<const __nv_bfloat16*>(ep.residual) + row * ep.ldr + n0;
+#pragma unroll
+  for (int c0 = half * 32; c0 < BN; c0 += 64)
+    if (n0 + c0 < ep.N) asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + c0));
+}
+
 template <int BN, bool RES, typename Release>
 __device__ __forceinline__ void epilogue_tile(const EpiArgs& ep, const CUtensorMap* tmD,
                                               uint32_t tacc, int m0, int n0, int ewarp, int lane,
@@ -198,7 +212,8 @@ __device__ __forceinline__ void epilogue_tile(const EpiArgs& ep, const CUtensorM
     const int c0 = half * 32 + i * 64;
     // RES (a kernel instantiation of its own, so the plain kernel's epilogue keeps its registers):
     // bf16 output + residual.  The residual row chunk is requested before the accumulator wait;
-    // 16-byte loads, column groups past N and rows past M read as zero.
+    // 16-byte loads, column groups past N and rows past M read as zero.  Measured and dropped:
+    // coalesced loads bounced through the staging buffer (L0 157 -> 175 us).
     uint4 res[4];
     if (RES) {
       const __nv_bfloat16* rp = reinterpret_cast<const __nv_bfloat16*>(ep.residual) + row * ep.ldr + n0 + c0;
@@ -430,6 +445,7 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
       const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
       EpiBias<BN> bias;
       epilogue_bias<BN>(ep, n0, ewarp, lane, bias);
+      if (RES) epilogue_prefetch_res<BN>(ep, m0, n0, ewarp, lane);
       mbar_wait(&acc_full[acc], acc_phase, 4);
       tc_fence_after();
       uint64_t* done = &acc_empty[acc];
@@ -611,6 +627,7 @@ lora_gemm2_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constan
       const int n0 = (tile % n_tiles) * BN;
       EpiBias<BN> bias;
       epilogue_bias<BN>(ep, n0, ewarp, lane, bias);
+      if (RES) epilogue_prefetch_res<BN>(ep, m0, n0, ewarp, lane);
       mbar_wait(&acc_full[acc], acc_phase, 4);
       tc_fence_after();
       epilogue_tile<BN, RES>(ep, &tmD, tmem_base + acc * C::kAccStride, m0, n0, ewarp, lane, my_out, buf, bias, release);
