@@ -11,7 +11,7 @@ python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_referen
 python bench.py --workload cfg2 --steps 10 > gpurun_out/bench_cfg2.json 2> gpurun_out/bench_cfg2.err; echo "cfg2 rc=$?"
 python bench.py --workload cfg4 --steps 3 > gpurun_out/bench_cfg4.json 2> gpurun_out/bench_cfg4.err; echo "cfg4 rc=$?"
 python bench.py --workload cfg5 --steps 3 > gpurun_out/bench_cfg5_p1.json 2> gpurun_out/bench_cfg5_p1.err; echo "cfg5 p1 rc=$?"
-python scripts/kbench.py layout norm tattn gemm attn bwd > gpurun_out/kbench.log 2>&1; echo "kbench rc=$?"
+python scripts/kbench.py layout norm tattn gemm gemmres attn bwd > gpurun_out/kbench.log 2>&1; echo "kbench rc=$?"
 python bench.py --ncu-step --no-cpu-baseline > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file gpurun_out/launches.csv python bench.py --ncu-step --no-cpu-baseline > gpurun_out/ncu_launch.log 2>&1
 echo "ncu launches rc=$?"
