@@ -18,3 +18,8 @@ $(LIB): $(OBJS)
 
 clean:
 	rm -f $(OBJS) $(LIB)
+
+# microbenchmarks behind the notes in profiles/ (MMA issue rate, MUFU rate); not part of the library
+ubench: scripts/ubench/mma_rate.bin scripts/ubench/mufu_rate.bin
+scripts/ubench/%.bin: scripts/ubench/%.cu
+	$(NVCC) $(ARCH) -O3 -std=c++17 -o $@ $<

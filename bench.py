@@ -43,6 +43,9 @@ def parse():
     ap.add_argument("--workload", default="cfg3", choices=["cfg3", "cfg2", "cfg4", "cfg5"],
                     help="cfg3 = the judged headline line; the others are the secondary BASELINE "
                          "configs (bench_extra.py)")
+    ap.add_argument("--cfg-mode", default="batched", choices=["batched", "two-pass"],
+                    help="batched: uncond|cond as one B=2 pass (default); two-pass: the reference's two B=1 calls")
+    ap.add_argument("--no-sp", action="store_true", help="skip the sequence-parallel probe at N>1")
     ap.add_argument("--ncu-step", action="store_true",
                     help="warm up, then run ONE step between cudaProfilerStart/Stop and exit "
                          "(for `ncu --profile-from-start off`; prints no bench line)")
@@ -98,103 +101,266 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------------------------------
-# CPU baseline: the oracle port of the reference path on the host cores (bounded sample)
+# workload description shared by both arms (the driver compares the two `config` objects)
 # --------------------------------------------------------------------------------------------------
-def cpu_sample(frames, latent):
-    """Times one oracle call per (kind, level) and scales to a full step.  L2 modules run at full
-    shape; L1 / L0 modules are down-batched 8x (frames for the spatial processors, spatial
-    positions for the motion modules) and scaled linearly -- BASELINE.md §4 allows exactly this."""
-    from oracle import processor as op
-    from oracle import hotpath as hp
-    torch.set_num_threads(os.cpu_count() or 1)
-    g = torch.Generator().manual_seed(0)
-    rn = lambda *s: torch.randn(*s, generator=g)
-
-    def proj(i, o, bias):
-        r = 64
-        return op.UnzipProj(rn(o, i) / i ** 0.5, rn(o) if bias else None, rn(r, i) / r, rn(o, r) / r,
-                            rn(r, i) / r, rn(o, r) / r, torch.rand(o, generator=g), torch.rand(o, generator=g))
-
-    def attn(c, heads, kv):
-        return op.SpatialAttnParams(heads, proj(c, c, False), proj(kv, c, False), proj(kv, c, False),
-                                    proj(c, c, True))
-
-    def motion_w(c):
-        w = {"norm.weight": torch.ones(c), "norm.bias": torch.zeros(c), "pos_embed.pe": hp.positional_table(c)}
-        for n in ("proj_in", "proj_out"):
-            w[n + ".weight"], w[n + ".bias"] = rn(c, c) / c ** 0.5, rn(c)
-        tb = "transformer_blocks.0."
-        for n in ("norm1", "norm2", "norm3"):
-            w[tb + n + ".weight"], w[tb + n + ".bias"] = torch.ones(c), torch.zeros(c)
-        for a in ("attn1", "attn2"):
-            for p in ("to_q", "to_k", "to_v", "to_out.0"):
-                w[tb + f"{a}.{p}.base.weight"] = rn(c, c) / c ** 0.5
-                w[tb + f"{a}.{p}.lora_A"], w[tb + f"{a}.{p}.lora_B"] = rn(32, c) * 0.01, rn(c, 32) / 32
-            w[tb + f"{a}.to_out.0.base.bias"] = rn(c)
-        w[tb + "ff.net.0.proj.weight"], w[tb + "ff.net.0.proj.bias"] = rn(8 * c, c) / c ** 0.5, rn(8 * c)
-        w[tb + "ff.net.2.weight"], w[tb + "ff.net.2.bias"] = rn(c, 4 * c) / (4 * c) ** 0.5, rn(c)
-        return w
-
-    s1, s2 = latent // 2, latent // 4
-    text = rn(1, 77, 2048)
-    t = {}
-    with torch.no_grad():
-        def clock(fn):
-            t0 = time.perf_counter()
-            fn()
-            return time.perf_counter() - t0
-        fs = max(1, frames // 8)
-        p2s, p2c = attn(1280, 20, 1280), attn(1280, 20, 2048)
-        x = rn(frames, s2 * s2, 1280)
-        t["L2_self"] = clock(lambda: op.animatediff_attn_processor(p2s, x))
-        t["L2_cross"] = clock(lambda: op.animatediff_attn_processor(p2c, x, text))
-        w2 = motion_w(1280)
-        xm = rn(frames, 1280, s2, s2)
-        t["L2_motion"] = clock(lambda: op.motion_module(xm, w2, frames, lora={"scale": 1 / 32}))
-        p1s, p1c = attn(640, 10, 640), attn(640, 10, 2048)
-        x = rn(fs, s1 * s1, 640)
-        t["L1_self"] = clock(lambda: op.animatediff_attn_processor(p1s, x)) * (frames / fs)
-        t["L1_cross"] = clock(lambda: op.animatediff_attn_processor(p1c, x, text)) * (frames / fs)
-        w1 = motion_w(640)
-        xm = rn(frames, 640, s1, max(1, s1 // 8))
-        t["L1_motion"] = clock(lambda: op.motion_module(xm, w1, frames, lora={"scale": 1 / 32})) * 8
-        w0 = motion_w(320)
-        xm = rn(frames, 320, latent, max(1, latent // 8))
-        t["L0_motion"] = clock(lambda: op.motion_module(xm, w0, frames, lora={"scale": 1 / 32})) * 8
-    unet = (60 * (t["L2_self"] + t["L2_cross"]) + 10 * (t["L1_self"] + t["L1_cross"]) +
-            5 * (t["L2_motion"] + t["L1_motion"] + t["L0_motion"]))
-    return 2.0 * unet, t
+def common_config(frames, latent, world):
+    return {"workload": "cfg3-hotpath", "frames": frames, "latent": latent, "cfg_passes": 2,
+            "modules_per_unet_call": {"self_attn": 70, "cross_attn": 70, "motion": 15},
+            "unziplora_rank": 64, "temporal_lora_rank": 32, "parallelism": f"dp{world} (videos)",
+            "l2": "per-step working set (2.4 GB of weights + >0.4 GB activations) exceeds the 126 MB L2"}
 
 
-SAMPLE_TEXT = ("oracle port (torch CPU fp32, reference's dense 3-GEMM UnZipLoRA form): one call per "
-               "(kind, level); L2 self/cross/motion at full shape, L1 self/cross on frames/8 and "
-               "L1/L0 motion on 1/8 of the positions, scaled x8; step = 2 CFG x (60 L2 + 10 L1 "
-               "self+cross, 5 motion per level)")
+# --------------------------------------------------------------------------------------------------
+# CPU arm: the reference's own modules (oracle/_ref) on the host cores, bounded sample
+# --------------------------------------------------------------------------------------------------
+def cpu_arm_line(arm, walls, med, best):
+    sec = arm.step_seconds(med)
+    return {"value": 1.0 / sec, "unit": "steps/s", "cores": arm.cores, "kind": arm.kind,
+            "sample": arm.sample_text,
+            "extrapolation": {"kind": "module_sum", "cfg_passes": 2,
+                              "calls_x_downbatch_factor": {k: round(v, 3) for k, v in arm.factors().items()},
+                              "unit_seconds_median": {k: round(v, 4) for k, v in med.items()},
+                              "unit_seconds_best": {k: round(v, 4) for k, v in best.items()},
+                              "step_seconds_median": round(sec, 2),
+                              "step_seconds_best": round(arm.step_seconds(best), 2)},
+            "timed_passes": len(walls), "seconds_per_pass": round(sum(walls) / len(walls), 3)}
 
 
 def run_reference(args):
+    """`--impl reference`: K timed passes (after W untimed ones) over the bounded sample of the cfg3
+    hot-path step through the reference's own modules on all host threads.  `ms_per_step` is what one
+    timed pass took (steps x ms_per_step is the timed region); `value` is the full step's rate by the
+    module-sum extrapolation spelled out under cpu_baseline.extrapolation."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    for _ in range(max(0, min(args.warmup, 1))):
-        cpu_sample(max(8, args.frames // 2), max(32, args.latent // 4))     # touch the code paths
-    times = []
-    for _ in range(args.steps):
-        s, _ = cpu_sample(args.frames, args.latent)
-        times.append(s)
-    sec = sum(times) / len(times)
-    val = args.gpus / sec if False else 1.0 / sec
-    cores = os.cpu_count() or 1
+    from oracle.ref_cpu import CpuArm
+    arm = CpuArm(args.frames, args.latent)
+    walls, med, best = arm.run(max(1, args.steps), max(0, args.warmup))
+    cb = cpu_arm_line(arm, walls, med, best)
+    val = cb["value"]
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "steps/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
+            "ms_per_step": 1e3 * sum(walls) / len(walls), "ms_per_full_step_extrapolated": 1e3 / val,
+            "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "cfg3-hotpath", "frames": args.frames, "latent": args.latent,
-                       "cfg_passes": 2, "unet_calls_per_step": 2},
-            "cpu_baseline": {"value": val, "unit": "steps/s", "cores": cores, "kind": "port",
-                             "sample": SAMPLE_TEXT},
+            "config": common_config(args.frames, args.latent, args.gpus),
+            "cpu_baseline": cb,
             "e2e": {"value": val, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------------
+# per-kernel event timing of one eager step (roofline of the dominant kernel)
+# --------------------------------------------------------------------------------------------------
+class KernelTimer:
+    """Wraps ops.lora_gemm_raw / ops.attn_fwd_raw with CUDA events on the launching stream and groups
+    the launches by the kernel instantiation they run on (vst_lora_gemm_plan)."""
+
+    def __init__(self, ops, lib):
+        self.ops, self.lib, self.rows = ops, lib, []
+        self._gemm, self._attn = ops.lora_gemm_raw, ops.attn_fwd_raw
+
+    def __enter__(self):
+        ops, lib = self.ops, self.lib
+
+        def gemm(a1, b1, a2=None, b2=None, bias=None, residual=None, out_scale=1.0, act="none",
+                 k2_group_n=0, out=None, out_dtype=torch.bfloat16):
+            m, k1 = a1.shape
+            n = b1.shape[0]
+            k2 = 0 if b2 is None else b2.shape[1]
+            nn = n // 2 if act == "geglu" else n
+            code = lib.vst_lora_gemm_plan(m, nn, k2, k2_group_n if a2 is not None else 0,
+                                          {"none": 0, "gelu": 1, "geglu": 2}[act])
+            name = ("lora_gemm2_kernel" if code >= 1000 else "lora_gemm_kernel") + \
+                f"<{code % 1000},{1 if (residual is not None and out_dtype == torch.bfloat16) else 0}>" + \
+                (" geglu" if act == "geglu" else "")
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            r = self._gemm(a1, b1, a2, b2, bias, residual, out_scale, act, k2_group_n, out, out_dtype)
+            e.record()
+            byts = 2.0 * (m * k1 + n * k1 + m * nn * (2 if residual is not None else 1) + (m + n) * k2)
+            self.rows.append((name, s, e, 2.0 * m * n * (k1 + k2), byts))
+            return r
+
+        def attn(q, k, v, heads, scale=None, return_lse=False, mask=None):
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            r = self._attn(q, k, v, heads, scale, return_lse, mask)
+            e.record()
+            name = "attn_fwd_pers_kernel " + ("self" if k.shape[1] == q.shape[1] else "text-cross")
+            fl = 4.0 * q.shape[0] * q.shape[1] * k.shape[1] * q.shape[2]
+            byts = 2.0 * (2 * q.numel() + k.shape[0] * k.shape[1] * q.shape[2] * 2)
+            self.rows.append((name, s, e, fl, byts))
+            return r
+
+        ops.lora_gemm_raw, ops.attn_fwd_raw = gemm, attn
+        return self
+
+    def __exit__(self, *a):
+        self.ops.lora_gemm_raw, self.ops.attn_fwd_raw = self._gemm, self._attn
+
+    def table(self):
+        torch.cuda.synchronize()
+        out = {}
+        for name, s, e, fl, by in self.rows:
+            t = out.setdefault(name, {"ms": 0.0, "flop": 0.0, "bytes": 0.0, "launches": 0})
+            t["ms"] += s.elapsed_time(e)
+            t["flop"] += fl
+            t["bytes"] += by
+            t["launches"] += 1
+        return out
+
+
+# --------------------------------------------------------------------------------------------------
+# sequence-parallel probe (WORLD_SIZE > 1): BASELINE config 5 on the driver's clock
+# --------------------------------------------------------------------------------------------------
+def sp_probe(args, world, rank, dev, steps):
+    """One 32-frame video sharded over the ranks (frames for the spatial processors, positions for
+    the motion-module bodies; the two all-to-alls per motion module are the layout kernels writing
+    to / reading from peer memory over NVLink).  Returns the `sp` object of the bench line."""
+    import torch.distributed as dist
+    from video_style_transfer_b200 import sdxl_hotpath as hpth, sequence_parallel as spm
+    from video_style_transfer_b200 import fused as fusedmod
+    bf = torch.bfloat16
+    F, S = 32, args.latent
+    fl_ = F // world
+    torch.manual_seed(4321)                      # every rank holds the same weights: ONE video
+    with torch.device(dev):
+        model = hpth.SDXLHotPath(temporal_rank=32, depth_scale=args.depth_scale)
+    model = model.to(bf).eval()
+    plan = model.forward_plan()
+    full_shapes = hpth.level_shapes(F, S)
+    g = torch.Generator().manual_seed(777)       # the same full video on every rank; each keeps its frames
+    full4 = [torch.randn(s, generator=g).to(bf) for s in full_shapes]
+    full3 = [None] + [torch.randn(s[0], s[2] * s[3], s[1], generator=g).to(bf) for s in full_shapes[1:]]
+    texts = [torch.randn(1, 77, 2048, generator=g).to(bf).to(dev) for _ in range(2)]
+    sl = slice(rank * fl_, (rank + 1) * fl_)
+    xs4 = [t[sl].contiguous().to(dev) for t in full4]
+    xs3 = [None] + [t[sl].contiguous().to(dev) for t in full3[1:]]
+    nbytes = max(spm.SPMotionStep.buffer_bytes(1, s[1], s[2] * s[3], F, world) for s in full_shapes)
+    comm = spm.SPComm.from_process_group(nbytes)
+
+    def barrier():
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, n):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return ms.item() / n
+
+    # ---- parity: this rank's slice of the unsharded modules' outputs (same kernels, one GPU) ------
+    with torch.no_grad():
+        want = hpth.run_unet_hotpath(plan, [t.to(dev) for t in full4], [None] + [t.to(dev) for t in full3[1:]],
+                                     texts[1], F)
+        got = hpth.run_unet_hotpath_sp(plan, xs4, xs3, texts[1], F, comm)
+    errs = []
+    for w_, g_ in zip(want, got):
+        w_ = w_[sl].float()
+        errs.append(((g_.float() - w_).abs().max() / w_.abs().max().clamp_min(1e-30)).item())
+    perr = torch.tensor([max(errs)], device=dev)
+    dist.all_reduce(perr, op=dist.ReduceOp.MAX)
+    del want, got
+
+    # ---- the sharded step, graph replay, max over ranks -------------------------------------------
+    graphed = hpth.GraphedSPDenoiseStep(plan, xs4, xs3, texts, F, comm)
+    for _ in range(3):
+        graphed.replay()
+    ms_sp = timed(graphed.replay, steps)
+
+    # ---- per-phase device time of one eager step (events on the launching stream) -----------------
+    phases = {k: [] for k in ("gn_partials_share", "push", "compute", "pull", "barrier_wait", "spatial")}
+
+    def ev():
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        return e
+
+    def motion_sp_timed(module, x_local):
+        st = spm.SPMotionStep(module, comm, x_local, F)
+        t = [ev()]
+        st.share_partials(); t.append(ev())
+        comm.barrier(); t.append(ev())
+        st.push(); t.append(ev())
+        comm.barrier(); t.append(ev())
+        st.compute(); t.append(ev())
+        comm.barrier(); t.append(ev())
+        out = st.pull(); t.append(ev())
+        comm.barrier(); t.append(ev())
+        for name, i in (("gn_partials_share", 0), ("push", 2), ("compute", 4), ("pull", 6)):
+            phases[name].append((t[i], t[i + 1]))
+        for i in (1, 3, 5, 7):
+            phases["barrier_wait"].append((t[i], t[i + 1]))
+        return out
+
+    barrier()
+    with torch.no_grad():
+        for text in texts:
+            t_prev = ev()
+            for kind, lvl, mod in plan:
+                if kind == "motion":
+                    phases["spatial"].append((t_prev, ev()))
+                    motion_sp_timed(mod, xs4[lvl])
+                    t_prev = ev()
+                elif kind == "self":
+                    mod(xs3[lvl])
+                else:
+                    mod(xs3[lvl], encoder_hidden_states=text)
+            phases["spatial"].append((t_prev, ev()))
+    torch.cuda.synchronize()
+    ph = torch.tensor([sum(a.elapsed_time(b) for a, b in phases[k]) for k in phases], device=dev)
+    dist.all_reduce(ph, op=dist.ReduceOp.MAX)
+    phase_ms = {k: round(v, 3) for k, v in zip(phases, ph.tolist())}
+
+    # ---- the same video on ONE GPU (rank 0 alone, same process, same clocks window) --------------
+    ms_sp1 = torch.zeros(1, device=dev)
+    barrier()
+    if rank == 0:
+        g1 = hpth.GraphedDenoiseStep(plan, [t.to(dev) for t in full4], [None] + [t.to(dev) for t in full3[1:]],
+                                     texts, F)
+        for _ in range(3):
+            g1.replay()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            g1.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        ms_sp1[0] = e0.elapsed_time(e1) / steps
+        del g1
+    dist.all_reduce(ms_sp1, op=dist.ReduceOp.MAX)
+    ms_sp1 = ms_sp1.item()
+    egress = 0
+    for kind, lvl, _ in plan:
+        if kind == "motion":
+            s = full_shapes[lvl]
+            egress += 2 * (s[0] * s[1] * s[2] * s[3] * 2 // world) * (world - 1) // world   # push + pull
+    egress *= 2                                                                             # x2 CFG passes
+    barrier()
+    del graphed
+    comm.close()
+    return {"workload": "cfg5-sequence-parallel: ONE 32-frame 1024^2 video, hot path, x2 CFG (two passes)",
+            "n_gpus": world, "frames": F, "frames_per_rank": fl_, "steps": steps,
+            "ms_per_step": ms_sp, "ms_sp1": ms_sp1, "speedup": ms_sp1 / ms_sp,
+            "efficiency": ms_sp1 / (world * ms_sp), "scaling": "strong",
+            "nvlink_bytes_per_rank": egress, "parity_rel_err": perr.item(),
+            "parity_note": "rank-sliced output of the sharded step vs the unsharded modules on one GPU, "
+                           "max |a-b| / max |b| over the per-level outputs, max over ranks",
+            "phase_ms": phase_ms,
+            "phase_note": "one eager step, CUDA events on the launching stream, summed over the 30 motion-module "
+                          "calls, max over ranks; barrier_wait = 4 flag barriers per motion module (includes peer "
+                          "skew and, in eager mode, launch skew); the timed ms_per_step is the graph replay",
+            "launch": "CUDA graph replay (one graph per rank, no NCCL and no host sync on the data path)",
+            "adapters": "folded" if fusedmod.MERGE_LORA else "low-rank"}
 
 
 # --------------------------------------------------------------------------------------------------
@@ -203,6 +369,7 @@ def run_reference(args):
 def run_ours(args):
     import torch.distributed as dist
     from video_style_transfer_b200 import _lib, ops, sdxl_hotpath as hpth
+    from video_style_transfer_b200 import fused as fusedmod
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -213,29 +380,31 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     bf = torch.bfloat16
     F, S = args.frames, args.latent
+    batched = args.cfg_mode == "batched"
+    nb = 2 if batched else 1                                   # CFG halves stacked along the batch
 
     torch.manual_seed(1234 + rank)
     with torch.device(dev):
         model = hpth.SDXLHotPath(temporal_rank=32, depth_scale=args.depth_scale)
     model = model.to(bf).eval()
     plan = model.forward_plan()
-    shapes = hpth.level_shapes(F, S)
+    shapes = hpth.level_shapes(F, S, batch=nb)
 
     # host (pinned) copies of one step's inputs, and device-resident copies for `value`
     g = torch.Generator().manual_seed(rank)
     h_x4 = [torch.randn(s, generator=g).to(bf).pin_memory() for s in shapes]
     h_x3 = [None] + [torch.randn(s[0], s[2] * s[3], s[1], generator=g).to(bf).pin_memory() for s in shapes[1:]]
-    h_text = [torch.randn(1, 77, 2048, generator=g).to(bf).pin_memory() for _ in range(2)]
+    h_text = [torch.randn(1, 77, 2048, generator=g).to(bf) for _ in range(2)]     # uncond, cond: per PROMPT
     d_x4 = [t.to(dev) for t in h_x4]
     d_x3 = [None] + [t.to(dev) for t in h_x3[1:]]
-    d_text = [t.to(dev) for t in h_text]
+    d_text = [torch.cat(h_text).to(dev)] if batched else [t.to(dev) for t in h_text]
     h_out = [torch.empty(s, dtype=bf).pin_memory() for s in shapes]
-    h2d = sum(t.numel() * 2 for t in h_x4 + h_x3[1:] + h_text)
+    h2d = sum(t.numel() * 2 for t in h_x4 + h_x3[1:])
     d2h = sum(t.numel() * 2 for t in h_out)
 
     def step_eager():
         outs = None
-        for text in d_text:                                    # uncond, cond: two B=1 UNet calls
+        for text in d_text:           # two-pass: uncond, cond B=1 calls; batched: one B=2 call
             outs = hpth.run_unet_hotpath(plan, d_x4, d_x3, text, F)
         return outs
 
@@ -243,18 +412,18 @@ def run_ours(args):
     graphed = None if (args.no_graph or args.ncu_step) else hpth.GraphedDenoiseStep(plan, d_x4, d_x3, d_text, F)
     step_device = step_eager if graphed is None else graphed.replay
     streamed = None if graphed is None else hpth.StreamedDenoiseStep(graphed)
+    used_graph = graphed is not None
 
     def step_e2e():
         if graphed is None:
             x4 = [t.to(dev, non_blocking=True) for t in h_x4]
             x3 = [None] + [t.to(dev, non_blocking=True) for t in h_x3[1:]]
-            texts = [t.to(dev, non_blocking=True) for t in h_text]
             outs = None
-            for text in texts:
+            for text in d_text:
                 outs = hpth.run_unet_hotpath(plan, x4, x3, text, F)
         else:
             # the product's host-fed path: copies of step n+1 / n-1 overlap the replay of step n
-            streamed.submit(h_x4 + h_x3[1:] + h_text, h_out)
+            streamed.submit(h_x4 + h_x3[1:], h_out)
             return
         for lvl in range(3):                                   # the step's result back on the host
             o = outs[lvl]
@@ -300,82 +469,88 @@ def run_ours(args):
     step_e2e()
     ms_e2e = timed(step_e2e, args.steps, after=None if streamed is None else streamed.drain)
 
-    # ---- roofline of the dominant kernel (spatial self-attention, tcgen05 flash): one extra
-    #      step with CUDA events around every self-attention launch on the launching stream ----
+    # ---- rooflines: one extra eager step with CUDA events around every GEMM / attention launch ----
     pk, pk_src = peaks()
-    ev, orig = [], ops.attn_fwd
-
-    def traced(q, k, v, heads, *a, **kw):
-        if k.shape[1] != q.shape[1]:
-            return orig(q, k, v, heads, *a, **kw)
-        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s.record()
-        out = orig(q, k, v, heads, *a, **kw)
-        e.record()
-        ev.append((s, e, 4.0 * q.shape[0] * q.shape[1] * k.shape[1] * q.shape[2]))
-        return out
-
-    import video_style_transfer_b200.animatediff.attention_processor as apmod
-    apmod.ops.attn_fwd = traced
-    step_eager()
-    torch.cuda.synchronize()
-    apmod.ops.attn_fwd = orig
-    # DRAM traffic of the dominant kernel from the committed `ncu --set full` capture (per launch,
-    # L1 self-attention shape), profiles/ncu_traffic.json
-    traffic = None
+    with KernelTimer(ops, _lib.lib) as kt:
+        step_eager()
+    table = kt.table()
+    peak_tf = pk.get("bf16_tflops_sustained", pk["bf16_tflops"])
+    traffic_db = {}
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["attn_fwd_pers_kernel"]
+        traffic_db = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
     except Exception:
         pass
-    attn_ms = sum(s.elapsed_time(e) for s, e, _ in ev)
-    attn_fl = sum(f for _, _, f in ev)
-    achieved = attn_fl / (attn_ms * 1e-3) / 1e12
-    peak_tf = pk.get("bf16_tflops_sustained", pk["bf16_tflops"])
-    from video_style_transfer_b200 import fused as fusedmod
-    fl = hpth.hotpath_flops(plan, F, S, merged=fusedmod.MERGE_LORA)        # FLOPs executed
+    ms_step = ms_dev / args.steps
+
+    def roof(name):
+        t = table[name]
+        ach = t["flop"] / (t["ms"] * 1e-3) / 1e12
+        tr = traffic_db.get(name.split(" ")[0])
+        return {"kernel": name, "bound": "tensor", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s",
+                "frac": ach / peak_tf,
+                "traffic": None if tr is None else tr["dram_bytes_per_launch"],
+                "traffic_note": None if tr is None else tr["note"],
+                "algorithmic_bytes_per_launch": t["bytes"] / t["launches"],
+                "algorithmic_flop_per_launch": t["flop"] / t["launches"],
+                "us_per_launch": 1e3 * t["ms"] / t["launches"],
+                "peak_source": f"bf16_tflops_sustained, {pk_src}",
+                "launches_timed": t["launches"], "share_of_step": t["ms"] / ms_step,
+                "timing": "CUDA events around every launch of one eager step (adds ~2 us of event overhead per launch)"}
+
+    gemm_names = [n for n in table if n.startswith("lora_gemm")]
+    dominant = max(gemm_names, key=lambda n: table[n]["ms"])
+    by_kernel = {n: {"ms": round(t["ms"], 3), "launches": t["launches"],
+                     "tflops": round(t["flop"] / (t["ms"] * 1e-3) / 1e12, 1),
+                     "frac": round(t["flop"] / (t["ms"] * 1e-3) / 1e12 / peak_tf, 3)}
+                 for n, t in sorted(table.items(), key=lambda kv: -kv[1]["ms"])}
+    fl = hpth.hotpath_flops(plan, F, S, merged=fusedmod.MERGE_LORA, text_kv_cached=True)   # FLOPs executed
     step_flops = 2.0 * sum(fl.values())
     step_flops_lowrank = 2.0 * sum(hpth.hotpath_flops(plan, F, S).values())  # SURVEY §8d low-rank form
 
+    sp = None
+    if world > 1 and not args.no_sp and 32 % world == 0:
+        if graphed is not None:
+            del streamed, graphed
+            streamed = graphed = None
+        torch.cuda.empty_cache()
+        sp = sp_probe(args, world, rank, dev, max(3, min(args.steps, 10)))
+
     if rank != 0:
         return
-    ms_step = ms_dev / args.steps
+    cfg = common_config(F, S, world)
     line = {
         "metric": METRIC, "value": world * 1e3 / ms_step, "unit": "steps/s", "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
-        "data": "synthetic",
-        "config": {"workload": "cfg3-hotpath", "frames": F, "latent": S, "cfg_passes": 2,
-                   "modules_per_unet_call": {"self_attn": sum(k == "self" for k, _, _ in plan),
-                                             "cross_attn": sum(k == "cross" for k, _, _ in plan),
-                                             "motion": sum(k == "motion" for k, _, _ in plan)},
-                   "unziplora_rank": 64, "temporal_lora_rank": 32, "parallelism": f"dp{world} (videos)",
-                   "launch": "eager (one Python call per kernel)" if graphed is None else "CUDA graph replay",
-                   "l2": "per-step working set (2.4 GB of weights + 0.4 GB activations) exceeds the 126 MB L2",
-                   "adapters": ("folded into the weights once per parameter version (W + B'A), one GEMM per "
-                                "projection" if fusedmod.MERGE_LORA else
-                                "low-rank form: u = x A^T pre-pass + extra K blocks in the fused GEMM"),
-                   "step_tflop": step_flops / 1e12, "step_tflop_lowrank_form": step_flops_lowrank / 1e12},
+        "data": "synthetic", "config": cfg,
+        "execution": {"cfg": ("batched: uncond | cond stacked along the batch, ONE B=2 pass per step "
+                              "(pipeline_animatediff_xl.py:353,373-375)" if batched else
+                              "two B=1 passes per step (inference_animatediff.py:110-121)"),
+                      "launch": "CUDA graph replay" if used_graph else "eager (one Python call per kernel)",
+                      "text_kv": "to_k | to_v of the text computed once per prompt (constant over the denoise loop), "
+                                 "outside the step",
+                      "adapters": ("folded into the weights once per parameter version (W + B'A), one GEMM per "
+                                   "projection" if fusedmod.MERGE_LORA else
+                                   "low-rank form: u = x A^T pre-pass + extra K blocks in the fused GEMM"),
+                      "step_tflop": step_flops / 1e12, "step_tflop_lowrank_form": step_flops_lowrank / 1e12},
         "e2e": {"value": world * 1e3 / (ms_e2e / args.steps), "unit": "steps/s",
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": launches,
         "clocks": clk.summary(),
         "tflops_hotpath": step_flops / (ms_step * 1e-3) / 1e12,
-        "roofline": {"kernel": "attn_fwd_pers_kernel (spatial self-attention)", "bound": "tensor",
-                     "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
-                     "frac": achieved / peak_tf,
-                     "traffic": None if traffic is None else traffic["dram_bytes_per_launch"],
-                     "traffic_note": None if traffic is None else traffic["note"],
-                     "peak_source": f"bf16_tflops_sustained, {pk_src}",
-                     "launches_timed": len(ev), "share_of_step": attn_ms / ms_step},
+        "frac_step": step_flops / (ms_step * 1e-3) / 1e12 / peak_tf,
+        "roofline": roof(dominant),
+        "roofline_attn": roof("attn_fwd_pers_kernel self"),
+        "by_kernel": by_kernel,
     }
+    if sp is not None:
+        line["sp"] = sp
     if world == 1 and not args.no_cpu_baseline:
-        sec, parts = cpu_sample(F, S)
-        line["cpu_baseline"] = {"value": 1.0 / sec, "unit": "steps/s", "cores": os.cpu_count() or 1,
-                                "kind": "port", "sample": SAMPLE_TEXT,
-                                "seconds_by_module": {k: round(v, 3) for k, v in parts.items()}}
+        from oracle.ref_cpu import CpuArm
+        arm = CpuArm(F, S)
+        walls, med, best = arm.run(3, 1)
+        line["cpu_baseline"] = cpu_arm_line(arm, walls, med, best)
     print(json.dumps(line), flush=True)
-    if world > 1:
-        pass
 
 
 def main():

@@ -127,6 +127,10 @@ int vst_lora_gemm(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, in
                   int k2_group_n, const void* bias, int bias_dtype, const void* residual, int64_t ldr,
                   float out_scale, int act, void* D, int64_t ldd, int64_t M, int N,
                   int out_dtype, void* stream);
+/* Which kernel instantiation vst_lora_gemm runs a shape on: 1000 * pair + BN (pair = 1: the CTA-pair
+ * kernel with 256 x BN tiles, 0: 128 x BN tiles), or VST_E_UNSUPPORTED.  Host-only, launches nothing;
+ * bench.py uses it to attribute event-timed launches to the dominant kernel. */
+int vst_lora_gemm_plan(int64_t M, int N, int K2, int k2_group_n, int act);
 /* B2'[n, j] = scale * m[n] * mask[n] * B[n, j] for up to two branches packed side by side
  * (columns [0,r) content, [r,2r) style); m/mask may be NULL (=1).  unziplora_linear_layer.py
  * :313,:321 (merger), :236-237 (hard mask), lora_linear.py:81 (scale). */

@@ -196,3 +196,25 @@ def temporal_lora_linear(x, weight, bias, lora_a, lora_b, scale: float):
     if bias is not None:
         out = out + bias
     return out + ((x @ lora_a.t()) @ lora_b.t()) * scale
+
+
+# --------------------------------------------------------------------------------------
+# §8f-2: temporal / spatial orthogonality loss
+# --------------------------------------------------------------------------------------
+
+
+def orth_loss_dense(pairs, lambda_orth: float):
+    """lambda / N * sum_l ||D_t^T D_c||_F^2 + ||D_t^T D_s||_F^2 in the reference's dense form.
+    animatediff/temporal_lora.py:126-166.  ``pairs``: [(A_t (r,in), B_t (out,r), scale_t,
+    A_c, B_c, A_s, B_s)] per paired layer; D_t = scale_t * B_t A_t carries the gradient (:147),
+    the spatial deltas are constants (:148-155)."""
+    if lambda_orth == 0.0 or not pairs:
+        return torch.tensor(0.0)
+    total = None
+    for a_t, b_t, scale_t, a_c, b_c, a_s, b_s in pairs:
+        w = (b_t @ a_t) * scale_t                                   # (out, in)   :147
+        d_c = (b_c @ a_c).detach()                                  # :153
+        d_s = (b_s @ a_s).detach()                                  # :154
+        contrib = torch.sum((w.T @ d_c) ** 2) + torch.sum((w.T @ d_s) ** 2)   # :156-158
+        total = contrib if total is None else total + contrib
+    return lambda_orth * total / len(pairs)                         # :164

@@ -343,102 +343,7 @@ def test_attn_processor_low_rank_form_matches_folded_weights(kind, monkeypatch):
     assert rel(y2, y_fold.float().cpu()) > 1e-3          # the output did change
 
 
-def test_denoise_25_steps_latent_cosine_vs_oracle():
-    """BASELINE config 3's acceptance bar on a reduced stack: a 25-step CFG + Euler denoise
-    (inference_animatediff.py:105-131: eps = eps_u + g (eps_c - eps_u); EulerDiscrete
-    x <- x + (sigma_next - sigma) eps) whose noise predictor is the hot path itself -- spatial
-    self-attention, text cross-attention (UnZipLoRA rank 16 content + style, residual connections)
-    and a motion module with temporal LoRA -- run in bf16 on the sm_100a path and in fp32 through
-    the oracle from the same initial latent.  Per-step latent cosine similarity >= 0.999."""
-    from oracle import processor as op
-    from video_style_transfer_b200.animatediff.attention_processor import AnimateDiffAttnProcessor2_0
-    from video_style_transfer_b200.animatediff.temporal_lora import inject_temporal_lora, TemporalLoRALinear
-    from video_style_transfer_b200.motion_module import MotionModule
-    from video_style_transfer_b200.unziplora_unet.lora_linear import LoRACompatibleLinear
-    from video_style_transfer_b200.unziplora_unet.unziplora_linear_layer import UnZipLoRALinearLayerInfer
-    torch.manual_seed(5)
-    C, heads, ctx, r, F_, hw = 128, 2, 96, 16, 8, 8
-    steps, guidance = 25, 7.5
-
-    def mk(i, o, bias):
-        lin = LoRACompatibleLinear(i, o, bias=bias)
-        lay = UnZipLoRALinearLayerInfer(i, o, r, ["content", "style"])
-        with torch.no_grad():
-            lay.merge_content.uniform_(0, 1)
-            lay.merge_style.uniform_(0, 1)
-        lin.set_lora_layer(lay)
-        return lin
-
-    def oproj(l):
-        ll, d = l.lora_layer, l.lora_layer.lora_matrix_dic
-        f = lambda t: None if t is None else t.detach().float().cpu()
-        return op.UnzipProj(f(l.weight), f(l.bias), f(d["content_down"].weight), f(d["content_up"].weight),
-                            f(d["style_down"].weight), f(d["style_up"].weight), f(ll.merge_content),
-                            f(ll.merge_style))
-
-    def mk_attn(kv):
-        return types.SimpleNamespace(
-            spatial_norm=None, group_norm=None, norm_cross=False, heads=heads,
-            to_q=mk(C, C, False), to_k=mk(kv, C, False), to_v=mk(kv, C, False),
-            to_out=torch.nn.ModuleList([mk(C, C, True), torch.nn.Dropout(0.0)]),
-            residual_connection=True, rescale_output_factor=1.0)
-
-    a_self, a_cross = mk_attn(C), mk_attn(ctx)
-    P_self, P_cross = (op.SpatialAttnParams(heads, oproj(a.to_q), oproj(a.to_k), oproj(a.to_v), oproj(a.to_out[0]),
-                                            residual_connection=True) for a in (a_self, a_cross))
-    holder = torch.nn.Module()
-    holder.motion_modules = torch.nn.ModuleList([MotionModule(C, 8)])
-    inject_temporal_lora(holder, rank=32, alpha=1.0)
-    with torch.no_grad():
-        for m in holder.modules():
-            if isinstance(m, TemporalLoRALinear):
-                m.lora_B.normal_(0, 0.1)
-    mm = holder.motion_modules[0]
-    w = {k: v.float() for k, v in mm.temporal_transformer.state_dict().items()}
-    w["pos_embed.pe"] = w["transformer_blocks.0.pos_embed.pe"]
-    text_u, text_c = torch.randn(1, 77, ctx), torch.randn(1, 77, ctx)
-    x0 = torch.randn(F_, C, hw, hw)
-    sig = torch.linspace(1.0, 0.0, steps + 1) ** 2 * 14.6        # Karras-like decreasing sigmas
-    sig_in = lambda s: 1.0 / (s * s + 1.0) ** 0.5                 # scheduler.scale_model_input
-
-    def tok(x4):
-        return x4.flatten(2).transpose(1, 2)
-
-    def untok(x3):
-        return x3.transpose(1, 2).reshape(F_, C, hw, hw)
-
-    def eps_oracle(x4, text):
-        h = op.animatediff_attn_processor(P_self, tok(x4))
-        h = op.animatediff_attn_processor(P_cross, h, text)
-        return op.motion_module(untok(h), w, F_, 8, 32, {"rank": 32, "scale": 1.0 / 32})
-
-    for m in (a_self, a_cross):
-        for l in (m.to_q, m.to_k, m.to_v, m.to_out):
-            l.cuda().to(torch.bfloat16)
-    mm.cuda().to(torch.bfloat16)
-    proc = AnimateDiffAttnProcessor2_0()
-
-    def eps_ours(x4, text):
-        h = proc(a_self, tok(x4).contiguous())
-        h = proc(a_cross, h, text)
-        return mm(untok(h).contiguous(), num_frames=F_)
-
-    xo, xg = x0.clone(), x0.clone().cuda()
-    tu, tc = text_u.cuda().to(torch.bfloat16), text_c.cuda().to(torch.bfloat16)
-    worst = 1.0
-    with torch.no_grad():
-        for i in range(steps):
-            s, sn = float(sig[i]), float(sig[i + 1])
-            xin = xo * sig_in(s)
-            eu, ec = eps_oracle(xin, text_u), eps_oracle(xin, text_c)
-            xo = xo + (sn - s) * (eu + guidance * (ec - eu)) * 0.02
-            gin = (xg * sig_in(s)).to(torch.bfloat16)
-            gu, gc = eps_ours(gin, tu).float(), eps_ours(gin, tc).float()
-            xg = xg + (sn - s) * (gu + guidance * (gc - gu)) * 0.02
-            cos = torch.nn.functional.cosine_similarity(xg.cpu().flatten(), xo.flatten(), dim=0).item()
-            worst = min(worst, cos)
-            assert cos >= 0.999, (i, cos)
-    assert worst >= 0.999
+# (the 25-step CFG + Euler acceptance test lives in tests/test_parity_full_gpu.py, at the L2 geometry)
 
 
 def test_streamed_denoise_step_matches_eager():
@@ -481,7 +386,8 @@ def test_streamed_denoise_step_matches_eager():
     pipe = hpth.StreamedDenoiseStep(graphed)
     host_outs = [[torch.empty(o.shape, dtype=bf).pin_memory() for o in graphed.outs] for _ in steps]
     for (x4, x3, texts), ho in zip(steps, host_outs):
-        pipe.submit(x4 + x3 + texts, ho)
+        graphed.set_text(texts)                     # the text is per prompt, not a per-step input
+        pipe.submit(x4 + x3, ho)
     pipe.drain()
     torch.cuda.synchronize()
     for ho, w in zip(host_outs, want):

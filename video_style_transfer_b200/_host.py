@@ -8,10 +8,46 @@ import torch
 from . import ops
 
 _cache: Dict[Tuple, Tuple] = {}
+_inserts = 0
 
 
 def _alive(refs):
     return all(r() is not None for r in refs)
+
+
+def _ident(t: torch.Tensor):
+    """Cache identity of an operand.  A tensor DERIVED by cached_build (packed up-projection, folded
+    weight ...) carries the key it was built under: when its sources change it is rebuilt as a new
+    tensor object, and anything derived from it in turn must overwrite its own entry instead of
+    leaving the old one behind (round-1 advisor finding: one folded W_eff leaked per rebuild)."""
+    return getattr(t, "_vst_key", None) or id(t)
+
+
+def _stamp(t: torch.Tensor):
+    return getattr(t, "_vst_stamp", None) or (t._version, t.data_ptr())
+
+
+def _store(key, tensors, stamp, val):
+    global _inserts
+    _inserts += 1
+    if _inserts % 256 == 0:                      # drop entries whose sources are gone or replaced
+        for k in [k for k, v in _cache.items() if not _alive(v[0])]:
+            del _cache[k]
+    _cache[key] = (tuple(weakref.ref(t) for t in tensors), stamp, val)
+
+
+def invalidate_caches():
+    """Forget every cached operand (bf16 copies, packed B', folded W_eff, transposes).  Call after
+    writing parameters through ``.data`` on the device (diffusers ``EMAModel.copy_to/restore``,
+    ``p.data.copy_()``): such writes do not bump ``tensor._version``, which is what the caches key
+    on.  ``load_state_dict``, optimiser steps and in-place ops under ``no_grad`` need no call."""
+    _cache.clear()
+
+
+def cache_stats():
+    return {"entries": len(_cache),
+            "bytes": sum(v[2].numel() * v[2].element_size() for v in _cache.values()
+                         if isinstance(v[2], torch.Tensor))}
 
 
 def pad8(n: int) -> int:
@@ -42,8 +78,8 @@ def bf16_cached(*tensors: torch.Tensor, pad_rows: bool = False) -> torch.Tensor:
         with torch.no_grad():
             val = bf16_cached(*tensors, pad_rows=pad_rows)
         return CastCatFn.apply(pad_rows, val, *tensors)
-    key = tuple(id(t) for t in tensors) + (pad_rows,)
-    stamp = tuple((t._version, t.data_ptr()) for t in tensors)
+    key = ("bf16",) + tuple(_ident(t) for t in tensors) + (pad_rows,)
+    stamp = tuple(_stamp(t) for t in tensors)
     hit = _cache.get(key)
     if hit is not None and hit[1] == stamp and _alive(hit[0]):
         return hit[2]
@@ -52,10 +88,9 @@ def bf16_cached(*tensors: torch.Tensor, pad_rows: bool = False) -> torch.Tensor:
         if pad_rows:
             parts = [torch.nn.functional.pad(q, (0, 0, 0, pad8(q.shape[0]) - q.shape[0])) for q in parts]
         val = parts[0].contiguous() if len(parts) == 1 else torch.cat(parts, dim=0).contiguous()
-    if len(_cache) > 4096:
-        for k in [k for k, v in _cache.items() if not _alive(v[0])]:
-            del _cache[k]
-    _cache[key] = (tuple(weakref.ref(t) for t in tensors), stamp, val)
+    if len(tensors) > 1 or pad_rows or tensors[0].dtype != torch.bfloat16:
+        val._vst_key, val._vst_stamp = key, stamp
+    _store(key, tensors, stamp, val)
     return val
 
 
@@ -89,14 +124,16 @@ def fused_linear(x2: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Te
 def cached_build(tensors: Sequence[torch.Tensor], extra, builder):
     """Memoise ``builder()`` (a derived operand such as the packed, merger-scaled up-projection)
     on the identity + in-place version of ``tensors`` and on ``extra`` (scale, forward type ...)."""
-    key = ("build",) + tuple(id(t) for t in tensors) + (extra,)
-    stamp = tuple((t._version, t.data_ptr()) for t in tensors)
+    key = ("build",) + tuple(_ident(t) for t in tensors) + (extra,)
+    stamp = tuple(_stamp(t) for t in tensors)
     hit = _cache.get(key)
     if hit is not None and hit[1] == stamp and _alive(hit[0]):
         return hit[2]
     with torch.no_grad():
         val = builder()
-    _cache[key] = (tuple(weakref.ref(t) for t in tensors), stamp, val)
+    if isinstance(val, torch.Tensor):
+        val._vst_key, val._vst_stamp = key, stamp      # identity for operands derived from this one
+    _store(key, tensors, stamp, val)
     return val
 
 

@@ -30,6 +30,7 @@ SIGNATURES = {
     "vst_temporal_attn_fwd": (_i, [_p, _p, _p, _p, _l, _i, _i, _i, _l, _l, _l, _l, _f, _p]),
     "vst_lora_gemm": (_i, [_p, _l, _p, _l, _i, _p, _l, _p, _l, _i, _i, _p, _i, _p, _l, _f, _i, _p, _l,
                            _l, _i, _i, _p]),
+    "vst_lora_gemm_plan": (_i, [_l, _i, _i, _i, _i]),
     "vst_lora_gemm_fwd": (_i, [_p, _l, _p, _l, _i, _p, _l, _p, _l, _i, _i, _p, _i, _p, _l, _f, _i, _p, _l,
                                _l, _i, _i, _p]),
     # dY lddy W ldw Bp ldbp A lda R dU lddu dX lddx M N K alpha accumulate out_dtype stream

@@ -18,6 +18,64 @@ from .._host import as_rows_bf16
 from ..fused import project_fused
 
 
+# ---- step-invariant text K / V ------------------------------------------------------------------
+# The text embedding is constant over the denoise loop (inference_animatediff.py:105-121 passes the
+# same `encoder_hidden_states` to every UNet call), so to_k | to_v of a cross-attention need
+# computing once per prompt, not once per step: 140 M = 77 GEMM launches per UNet call at ~3 % of
+# peak leave the step.  One entry per (to_k, to_v, text buffer); it is recomputed when the text
+# tensor is written (in-place version), re-allocated, or when any weight / adapter / merger /
+# mask / scale behind the projection changes.  A refresh writes INTO the cached buffers, so a CUDA
+# graph that captured them sees the new prompt (GraphedDenoiseStep.set_text).
+_text_kv_cache = {}
+TEXT_KV_CACHE = True
+
+
+def _kv_deps(attn, scale):
+    from ..fused import _site
+    deps = []
+    for lin in (attn.to_k, attn.to_v):
+        s = _site(lin)
+        deps.append(s.site_weight())
+        if s.site_bias() is not None:
+            deps.append(s.site_bias())
+        downs = s.site_downs()
+        deps.extend(downs)
+        if downs:
+            up = s.site_up(scale)
+            if up is not None:
+                deps.append(up)
+    return deps
+
+
+def text_kv(attn, text: torch.Tensor, scale: float):
+    """(k, v) = to_k(text), to_v(text) as (B_text, S_text, C) column views of one packed GEMM output."""
+    from .._host import _alive, _ident, _stamp
+    from ..fused import MERGE_LORA  # noqa: F401  (folding is decided inside project_fused)
+    kv_batch, seq_k = text.shape[:2]
+    run = lambda: project_fused((attn.to_k, attn.to_v), as_rows_bf16(text), scale, batch=(kv_batch, seq_k))
+    deps = [text] + _kv_deps(attn, scale)
+    if not TEXT_KV_CACHE or (torch.is_grad_enabled() and any(t.requires_grad for t in deps)):
+        return run()
+    key = (id(attn.to_k), id(attn.to_v), text.data_ptr(), tuple(text.shape), text.dtype)
+    stamp = (float(scale),) + tuple((_ident(t), _stamp(t)) for t in deps)
+    hit = _text_kv_cache.get(key)
+    if hit is not None and hit[0] == stamp and _alive(hit[1]):
+        return hit[2], hit[3]
+    if torch.cuda.is_current_stream_capturing():
+        return run()                    # never park graph-pool memory in a cache that outlives the graph
+    k, v = run()
+    if hit is not None and _alive(hit[1]) and hit[2].shape == k.shape and hit[2].stride() == k.stride():
+        hit[2].copy_(k)                 # refresh in place: graphs holding these buffers stay valid
+        hit[3].copy_(v)
+        k, v = hit[2], hit[3]
+    if len(_text_kv_cache) > 4096:
+        for kk in [kk for kk, vv in _text_kv_cache.items() if not _alive(vv[1])]:
+            del _text_kv_cache[kk]
+    import weakref
+    _text_kv_cache[key] = (stamp, tuple(weakref.ref(t) for t in deps), k, v)
+    return k, v
+
+
 class AnimateDiffAttnProcessor2_0:
     def __init__(self):
         if not torch.cuda.is_available():
@@ -65,23 +123,29 @@ class AnimateDiffAttnProcessor2_0:
             kv_batch, seq_k = encoder_hidden_states.shape[:2]
             if batch_size % kv_batch != 0:
                 raise ValueError("text batch must divide the B*F batch")
-            e2 = as_rows_bf16(encoder_hidden_states)       # NOT repeated: kv_group handles :62-66
-            k, v = project_fused((attn.to_k, attn.to_v), e2, lora_scale, batch=(kv_batch, seq_k))   # N = 2C
+            # NOT repeated: kv_group handles :62-66; constant over the denoise loop: once per prompt
+            k, v = text_kv(attn, encoder_hidden_states, lora_scale)                                 # N = 2C
         inner = k.shape[-1]
         # q / k / v: (b, s, inner) column views of the packed projection output (packed row stride)
         o = ops.attn_fwd(q, k, v, attn.heads, mask=attention_mask)
         o2 = o.view(batch_size * seq_q, inner)
 
+        # dropout sits between to_out[0] and the residual add (reference :85-92): the epilogue may
+        # only carry the residual / rescale when that dropout is the identity
+        drop = attn.to_out[1]
+        drop_id = not (getattr(drop, "training", False) and getattr(drop, "p", 0.0) > 0.0)
         fuse_res = (attn.residual_connection and input_ndim == 3 and residual.dtype == torch.bfloat16
-                    and residual.is_contiguous())
+                    and residual.is_contiguous() and drop_id)
         res2 = residual.view(batch_size * seq_q, -1) if fuse_res else None
         post = 1.0 / float(attn.rescale_output_factor)
         y = self._proj(attn.to_out[0], o2, lora_scale, residual=res2,
-                       out_scale=post if (fuse_res or not attn.residual_connection) else 1.0)
+                       out_scale=post if (fuse_res or (not attn.residual_connection and drop_id)) else 1.0)
         y = attn.to_out[1](y)                                             # dropout (p = 0)
         y = y.view(batch_size, seq_q, -1).to(in_dtype)
         if input_ndim == 4:
             y = y.transpose(-1, -2).reshape(bsz, channel, height, width)
         if attn.residual_connection and not fuse_res:
             y = (y + residual) * post
+        elif not attn.residual_connection and not drop_id:
+            y = y * post
         return y

@@ -769,6 +769,52 @@ __global__ void pack_up_kernel(const T* __restrict__ Bc, const T* __restrict__ m
 
 }  // namespace
 
+// Tile selection of vst_lora_gemm (also exported as vst_lora_gemm_plan so a caller -- bench.py's
+// per-kernel roofline -- can name the kernel instantiation a shape runs on).  Returns BN and sets
+// *pair = 1 for the CTA-pair kernel (lora_gemm2_kernel, 256-row tiles); 0 = unsupported grouping.
+static int vst_lora_gemm_select(int64_t M, int N, int gn, int act, int* pair) {
+  *pair = 0;
+#define FITS(BNV) (N % BNV == 0 && (gn == 0 || gn % BNV == 0))
+  if (act == VST_ACT_GEGLU) { *pair = 1; return 256; }
+  // CTA pairs (256-row tiles) once there is at least one tile per SM pair to keep busy
+  const bool big = M >= 2048 && !vst_force_single_cta();
+  static int force_bn = -1;
+  if (force_bn < 0) { const char* e = getenv("VST_GEMM_BN"); force_bn = e ? atoi(e) : 0; }   // tuning only
+  const int half_sms = vst_sm_count() / 2;
+  if (big && force_bn == 160 && FITS(160)) { *pair = 1; return 160; }
+  if (big && force_bn == 128 && FITS(128)) { *pair = 1; return 128; }
+  if (force_bn == 256 && FITS(256)) return 256;
+  // 256-wide pair tiles move the fewest operand bytes per MAC (64 B/clk/SM against 83 for 160):
+  // worth up to 20 % of padded columns (N = 640, 960, 1920 -> 768, 1024, 2048); r01 launch list:
+  // the BN = 160 family ran at 760 TFLOP/s, the BN = 256 family at 1260
+  if (big && (gn == 0 || gn % 256 == 0) && N > 256 && (int64_t)((N + 255) / 256) * 256 * 5 <= (int64_t)N * 6 &&
+      (M / 256) * ((N + 255) / 256) >= half_sms) { *pair = 1; return 256; }
+  if (big && FITS(256) && (M / 256) * (N / 256) >= half_sms) { *pair = 1; return 256; }
+  if (big && FITS(160) && (M / 256) * (N / 160) >= half_sms) { *pair = 1; return 160; }
+  if (big && FITS(128) && (M / 256) * (N / 128) >= half_sms) { *pair = 1; return 128; }
+  // one row tile (the text K / V projections: M = 77 per prompt, K = 2048): the run time is the
+  // weight read, and one SM pulls only ~0.15 TB/s -- narrow tiles spread it over 4x the SMs
+  if (M <= 128 && (force_bn == 0 || force_bn == 64) && FITS(64) && N / 64 >= 16) return 64;
+  if (FITS(256)) return 256;
+  if (FITS(160)) return 160;
+  if (FITS(192)) return 192;
+  if (FITS(128)) return 128;
+  if (FITS(64)) return 64;
+#undef FITS
+  if (gn != 0) return 0;
+  if (N <= 64) return 64;
+  if (N <= 128) return 128;
+  if (N <= 160) return 160;
+  return 256;
+}
+
+extern "C" int vst_lora_gemm_plan(int64_t M, int N, int K2, int k2_group_n, int act) {
+  int pair = 0;
+  const int gn = (K2 > 0 && k2_group_n > 0) ? k2_group_n : 0;
+  const int bn = vst_lora_gemm_select(M, N, gn, act, &pair);
+  return bn <= 0 ? VST_E_UNSUPPORTED : pair * 1000 + bn;
+}
+
 extern "C" int vst_lora_gemm(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1,
                              const void* A2, int64_t lda2, const void* B2, int64_t ldb2, int K2,
                              int k2_group_n, const void* bias, int bias_dtype, const void* residual, int64_t ldr,
@@ -801,41 +847,27 @@ extern "C" int vst_lora_gemm(const void* A1, int64_t lda1, const void* B1, int64
   cudaStream_t st = (cudaStream_t)stream;
   VST_REQUIRE(k2_group_n >= 0 && (k2_group_n == 0 || K2 > 0), VST_E_BADARG, "lora_gemm: bad k2_group_n");
   const int gn = (K2 > 0 && k2_group_n > 0) ? k2_group_n : 0;
-#define GO(BNV) return launch<BNV>(A1, lda1, B1, ldb1, K1, A2, lda2, B2, ldb2, K2, gn, ep, st)
-#define FITS(BNV) (N % BNV == 0 && (gn == 0 || gn % BNV == 0))
-#define GO2(BNV) return launch2<BNV>(A1, lda1, B1, ldb1, K1, A2, lda2, B2, ldb2, K2, gn, ep, st)
-  // CTA pairs (256-row tiles) once there is at least one tile per SM pair to keep busy
-  if (act == VST_ACT_GEGLU) GO2(256);
-  const bool big = M >= 2048 && !vst_force_single_cta();
-  static int force_bn = -1;
-  if (force_bn < 0) { const char* e = getenv("VST_GEMM_BN"); force_bn = e ? atoi(e) : 0; }   // tuning only
-  if (big && force_bn == 160 && FITS(160)) GO2(160);
-  if (big && force_bn == 128 && FITS(128)) GO2(128);
-  if (force_bn == 256 && FITS(256)) GO(256);
-  // 256-wide pair tiles move the fewest operand bytes per MAC (64 B/clk/SM against 83 for 160):
-  // worth up to 20 % of padded columns (N = 640, 960, 1920 -> 768, 1024, 2048); r01 launch list:
-  // the BN = 160 family ran at 760 TFLOP/s, the BN = 256 family at 1260
-  if (big && (gn == 0 || gn % 256 == 0) && N > 256 && (int64_t)((N + 255) / 256) * 256 * 5 <= (int64_t)N * 6 &&
-      (M / 256) * ((N + 255) / 256) >= vst_sm_count() / 2)
-    GO2(256);
-  if (big && FITS(256) && (M / 256) * (N / 256) >= vst_sm_count() / 2) GO2(256);
-  if (big && FITS(160) && (M / 256) * (N / 160) >= vst_sm_count() / 2) GO2(160);
-  if (big && FITS(128) && (M / 256) * (N / 128) >= vst_sm_count() / 2) GO2(128);
-  // one row tile (the text K / V projections: M = 77 per prompt, K = 2048): the run time is the
-  // weight read, and one SM pulls only ~0.15 TB/s -- narrow tiles spread it over 4x the SMs
-  if (M <= 128 && (force_bn == 0 || force_bn == 64) && FITS(64) && N / 64 >= 16) GO(64);
-  if (FITS(256)) GO(256);
-  if (FITS(160)) GO(160);
-  if (FITS(192)) GO(192);
-  if (FITS(128)) GO(128);
-  if (FITS(64)) GO(64);
-  VST_REQUIRE(gn == 0, VST_E_UNSUPPORTED,
+  int pair = 0;
+  const int bn = vst_lora_gemm_select(M, N, gn, act, &pair);
+  VST_REQUIRE(bn > 0, VST_E_UNSUPPORTED,
               "lora_gemm: k2_group_n=%d must be a multiple of 64 that tiles N=%d", gn, N);
-  if (N <= 64) GO(64);
-  if (N <= 128) GO(128);
-  if (N <= 160) GO(160);
-  GO(256);
-#undef FITS
+#define GO(BNV) return launch<BNV>(A1, lda1, B1, ldb1, K1, A2, lda2, B2, ldb2, K2, gn, ep, st)
+#define GO2(BNV) return launch2<BNV>(A1, lda1, B1, ldb1, K1, A2, lda2, B2, ldb2, K2, gn, ep, st)
+  if (pair) {
+    switch (bn) {
+      case 256: GO2(256);
+      case 160: GO2(160);
+      default: GO2(128);
+    }
+  }
+  switch (bn) {
+    case 256: GO(256);
+    case 192: GO(192);
+    case 160: GO(160);
+    case 128: GO(128);
+    default: GO(64);
+  }
+#undef GO2
 #undef GO
 }
 

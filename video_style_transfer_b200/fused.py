@@ -48,16 +48,19 @@ def merged_weight(ws: Sequence[torch.Tensor], downs: Sequence[Sequence[torch.Ten
     deps = list(ws) + flat + [u for u in ups if u is not None]
 
     def build():
-        w = bf16_cached(*ws).clone()
+        # W + B'A is accumulated in fp32 from the parameters themselves and rounded to bf16 ONCE
+        # (a delta below one bf16 ulp of W still moves the rounding the right way on average;
+        # folding onto an already-rounded bf16 W would round twice)
+        w32 = torch.cat([w_.detach().float() for w_ in ws], dim=0)
         row = 0
         for wg, dg, ug in zip(ws, downs, ups):
             n = wg.shape[0]
             if ug is not None and dg:
                 a = bf16_cached(*dg, pad_rows=True)                     # (K2, in)
                 assert a.shape[0] == ug.shape[1]
-                ops.gemm(ug.detach(), a, trans_b=True, out=w[row:row + n], accumulate=True)
+                ops.gemm(ug.detach(), a, trans_b=True, out=w32[row:row + n], accumulate=True)
             row += n
-        return w
+        return w32.to(torch.bfloat16)
 
     return cached_build(deps, "merged_weight", build)
 

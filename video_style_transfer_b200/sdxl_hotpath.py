@@ -148,11 +148,19 @@ def run_unet_hotpath(plan, xs4, xs3, text, frames: int):
 
 
 class GraphedDenoiseStep:
-    """One denoising step's worth of hot-path work (one run_unet_hotpath per text embedding: uncond
-    + cond) captured ONCE into a CUDA graph and replayed: the step is ~2,300 kernel launches of
-    10-800 us each, and the Python + launch overhead between them (~10 % of the step at 16 frames)
-    disappears on replay.  Inputs live in static device buffers (`x4`, `x3`, `texts`); copy new
-    data into them (e.g. ``step.x4[0].copy_(host, non_blocking=True)``) before ``replay()``.
+    """One denoising step's worth of hot-path work captured ONCE into a CUDA graph and replayed: the
+    step is ~1,200-2,300 kernel launches of 10-800 us each, and the Python + launch overhead between
+    them (~10 % of the step at 16 frames) disappears on replay.
+
+    `texts` lists the text embeddings of the step, one run_unet_hotpath per entry:
+      * two-pass CFG (inference_animatediff.py:110-121): texts = [uncond (1,77,2048), cond], xs hold
+        the F frames of the video and both passes read them;
+      * batched CFG (pipeline_animatediff_xl.py:353,373-375): texts = [cat(uncond, cond) (2,77,2048)],
+        xs hold 2F frames (uncond half, cond half): every weight is read once per step and every
+        GEMM runs at twice the M.
+    Inputs live in static device buffers (`x4`, `x3`); copy new data into them before ``replay()``.
+    The text is per PROMPT, not per step: ``set_text`` copies it and refreshes the cached text K / V
+    of every cross-attention (attention_processor.text_kv) outside the graph.
     Everything the C ABI needs is graph-safe: no host synchronisation, workspaces come from the
     caching allocator's graph pool, tensor maps travel as kernel parameters."""
 
@@ -164,7 +172,7 @@ class GraphedDenoiseStep:
         self.texts = [t.clone() for t in texts]
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.stream(side):                   # bf16 caches, smem attributes, allocator warm-up
+        with torch.cuda.stream(side):                   # bf16 caches, text K/V, smem attributes, allocator
             for _ in range(warmup):
                 self._run()
         torch.cuda.current_stream().wait_stream(side)
@@ -181,6 +189,18 @@ class GraphedDenoiseStep:
             outs = run_unet_hotpath(self.plan, self.x4, self.x3, text, self.frames)
         return outs
 
+    @torch.no_grad()
+    def set_text(self, texts):
+        """New prompt: copy the embeddings into the static buffers and recompute the text K / V the
+        captured graph reads (in place, eagerly, on the current stream)."""
+        from .animatediff.attention_processor import text_kv
+        for dst, src in zip(self.texts, texts):
+            dst.copy_(src, non_blocking=True)
+        for kind, _, mod in self.plan:
+            if kind == "cross":
+                for t in self.texts:
+                    text_kv(mod, t, 1.0)
+
     def replay(self):
         self.graph.replay()
         return self.outs
@@ -189,7 +209,8 @@ class GraphedDenoiseStep:
 class StreamedDenoiseStep:
     """Host-fed pipeline around a GraphedDenoiseStep: every step's inputs come from (pinned) host
     tensors and its outputs go back to host tensors, with the PCIe traffic of step n+1 / n-1 hidden
-    behind the graph replay of step n.  Three streams: `h2d` fills one of two device staging sets,
+    behind the graph replay of step n (the prompt's text embedding is not a per-step input: it is
+    set once with GraphedDenoiseStep.set_text).  Three streams: `h2d` fills one of two device staging sets,
     the compute stream moves it into the graph's static inputs (device-to-device, ~0.3 ms for the
     420 MB of a 16-frame step), replays, and parks the outputs in one of two output staging sets,
     `d2h` drains those to the host.  submit() never blocks the host; drain() makes the calling
@@ -197,7 +218,7 @@ class StreamedDenoiseStep:
 
     def __init__(self, graphed: "GraphedDenoiseStep"):
         self.g = graphed
-        self.dst = graphed.x4 + graphed.x3[1:] + graphed.texts
+        self.dst = graphed.x4 + graphed.x3[1:]        # the text is per prompt: GraphedDenoiseStep.set_text
         self.h2d, self.d2h = torch.cuda.Stream(), torch.cuda.Stream()
         self.stage_in = [[torch.empty_like(t) for t in self.dst] for _ in range(2)]
         self.stage_out = [[torch.empty_like(t) for t in graphed.outs] for _ in range(2)]
@@ -206,7 +227,7 @@ class StreamedDenoiseStep:
         self.n = 0
 
     def submit(self, host_inputs, host_outs):
-        """host_inputs: tensors matching x4 + x3[1:] + texts of the wrapped step; host_outs: one
+        """host_inputs: tensors matching x4 + x3[1:] of the wrapped step; host_outs: one
         host tensor per level output (same numel).  Enqueues one step and returns at once."""
         k, first = self.n & 1, self.n < 2
         cur = torch.cuda.current_stream()
@@ -325,7 +346,8 @@ def train_step_hotpath(model, plan, xs4, xs3, text, upstream, frames: int, optim
     return orth.detach()
 
 
-def hotpath_flops(plan, frames: int, latent: int = 128, batch: int = 1, merged: bool = False):
+def hotpath_flops(plan, frames: int, latent: int = 128, batch: int = 1, merged: bool = False,
+                  text_kv_cached: bool = False):
     """Algorithmic FLOPs of one UNet forward of the plan (SURVEY.md §8d formulas), by kernel family.
     merged=True: the FLOPs actually executed when the frozen adapters are folded into the weights
     (fused.merged_weight): the low-rank terms cost nothing per call."""
@@ -344,7 +366,8 @@ def hotpath_flops(plan, frames: int, latent: int = 128, batch: int = 1, merged: 
             fl["attn_cross"] += 4.0 * batch * frames * hw * TEXT_LEN * c
             mt = batch * TEXT_LEN
             fl["proj"] += 2 * (2.0 * m * c * c + 2.0 * m * r2 * 2 * c)
-            fl["proj"] += 2 * (2.0 * mt * TEXT_DIM * c + 2.0 * mt * r2 * (TEXT_DIM + c))
+            if not text_kv_cached:       # once per prompt, not per step (attention_processor.text_kv)
+                fl["proj"] += 2 * (2.0 * mt * TEXT_DIM * c + 2.0 * mt * r2 * (TEXT_DIM + c))
         else:
             n = batch * hw
             fl["temporal_attn"] += 2 * 4.0 * n * frames * frames * c

@@ -86,16 +86,20 @@ class AttnProcessor2_0:
         o = ops.attn_fwd(q, k, v, attn.heads, mask=attention_mask)           # :737-741
         o2 = o.view(batch_size * seq_q, inner)
 
+        drop = attn.to_out[1]        # dropout precedes the residual add (:749-755): fuse only if identity
+        drop_id = not (getattr(drop, "training", False) and getattr(drop, "p", 0.0) > 0.0)
         fuse_res = (attn.residual_connection and input_ndim == 3 and residual.dtype == torch.bfloat16
-                    and residual.is_contiguous())
+                    and residual.is_contiguous() and drop_id)
         res2 = residual.view(batch_size * seq_q, -1) if fuse_res else None
         post = 1.0 / float(attn.rescale_output_factor)
         y = self._proj(attn.to_out[0], o2, residual=res2,                     # :745-747
-                       out_scale=post if (fuse_res or not attn.residual_connection) else 1.0)
+                       out_scale=post if (fuse_res or (not attn.residual_connection and drop_id)) else 1.0)
         y = attn.to_out[1](y)                                                # dropout :749
         y = y.view(batch_size, seq_q, -1).to(in_dtype)
         if input_ndim == 4:                                                  # :751-752
             y = y.transpose(-1, -2).reshape(bsz, channel, height, width)
         if attn.residual_connection and not fuse_res:                        # :754-757
             y = (y + residual) * post
+        elif not attn.residual_connection and not drop_id:
+            y = y * post
         return y
