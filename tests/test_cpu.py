@@ -520,3 +520,96 @@ def test_stage1_export_key_format():
     assert torch.equal(lora_sd[stem + ".down.weight"], lay.lora_matrix_dic["style_down"].weight)
     assert torch.allclose(lora_sd[stem + ".up.weight"], lay.lora_matrix_dic["style_up"].weight * lay.merge_style[:, None])
     assert torch.equal(mask_sd[stem + ".merge_style"], lay.merge_style)
+
+
+# ---- the oracle's library-shaped pieces against torch.nn.functional -------------------
+def test_oracle_pieces_match_torch_functional():
+    """GroupNorm5D / LayerNorm / GELU / sdpa of oracle/hotpath.py are the pieces the (unpinned) motion
+    block restatement is assembled from; each is checked against the torch library op diffusers calls
+    at that point (F.group_norm on the (B,C,F,H,W) view, F.layer_norm, F.gelu, F.scaled_dot_product_attention)."""
+    import torch.nn.functional as F
+    from oracle import hotpath as hp
+    torch.manual_seed(0)
+    x5 = torch.randn(2, 64, 5, 6, 7) * 3 + 1
+    w, b = torch.randn(64), torch.randn(64)
+    close(hp.groupnorm5d(x5, w, b, 32, 1e-6), F.group_norm(x5, 32, w, b, 1e-6), 2e-6)
+    x = torch.randn(37, 11, 96)
+    w, b = torch.randn(96), torch.randn(96)
+    close(hp.layernorm(x, w, b, 1e-5), F.layer_norm(x, (96,), w, b, 1e-5), 2e-6)
+    close(hp.gelu(x), F.gelu(x), 1e-6)
+    q, k, v = torch.randn(3, 4, 50, 24), torch.randn(3, 4, 77, 24), torch.randn(3, 4, 77, 24)
+    close(hp.sdpa(q, k, v), F.scaled_dot_product_attention(q, k, v), 2e-6)
+    m = torch.zeros(3, 1, 1, 77)
+    m[..., 40:] = -1e4
+    close(hp.sdpa(q, k, v, m), F.scaled_dot_product_attention(q, k, v, attn_mask=m), 2e-6)
+    hg = torch.randn(9, 64)
+    hid, gate = hg.chunk(2, dim=-1)
+    close(hid * hp.gelu(gate), hid * F.gelu(gate), 1e-6)                 # diffusers GEGLU
+
+
+def test_oracle_orth_loss_dense_matches_reference_golden():
+    """oracle.hotpath.orth_loss_dense restates animatediff/temporal_lora.py:126-166; the fixture value was
+    produced by the reference's own compute_orth_loss (oracle/make_golden.py)."""
+    from oracle import hotpath as hp
+    from video_style_transfer_b200.animatediff import temporal_lora as tl
+    g = np.load(os.path.join(GOLD, "lora_linear.npz"))
+    unet = _toy_unet(g)
+    tl.inject_temporal_lora(unet, rank=4, alpha=2.0)
+    lora = sub(g, "toy/lora/")
+    with torch.no_grad():
+        for n, m in unet.named_modules():
+            if isinstance(m, tl.TemporalLoRALinear):
+                m.lora_A.copy_(lora[n + ".lora_A"])
+                m.lora_B.copy_(lora[n + ".lora_B"])
+    idx = tl.build_spatial_lora_index(unet)
+    pairs = []
+    for n, m in unet.named_modules():
+        if n in idx and isinstance(m, tl.TemporalLoRALinear):
+            d = idx[n].lora_matrix_dic
+            pairs.append((m.lora_A, m.lora_B, m.scale, d["content_down"].weight, d["content_up"].weight,
+                          d["style_down"].weight, d["style_up"].weight))
+    close(hp.orth_loss_dense(pairs, 1e-2).detach(), T(g["toy/orth_loss"]), 1e-5)
+
+
+def test_cpu_arm_uses_reference_modules_when_placed():
+    """oracle/ref_cpu.py: with oracle/_ref in place (oracle/build_ref.py) the timed CPU arm is the
+    reference's own code; its spatial path agrees with the oracle restatement on the same weights."""
+    from oracle import build_ref, ref_cpu, processor as op
+    have = build_ref.build()
+    ns = ref_cpu.load_reference()
+    if not have:
+        assert ns is None
+        pytest.skip("no /root/reference and no oracle/_ref on this machine")
+    assert ns is not None
+    torch.manual_seed(0)
+    attn, proc = ref_cpu.ref_spatial_attn(ns, 64, 2, 96, rank=8)
+    x, text = torch.randn(4, 10, 64), torch.randn(1, 77, 96)
+
+    def oproj(l):
+        ll, d = l.lora_layer, l.lora_layer.lora_matrix_dic
+        f = lambda t: None if t is None else t.detach()
+        return op.UnzipProj(f(l.weight), f(l.bias), f(d["content_down"].weight), f(d["content_up"].weight),
+                            f(d["style_down"].weight), f(d["style_up"].weight), f(ll.merge_content), f(ll.merge_style))
+    P = op.SpatialAttnParams(2, oproj(attn.to_q), oproj(attn.to_k), oproj(attn.to_v), oproj(attn.to_out[0]))
+    with torch.no_grad():
+        close(op.animatediff_attn_processor(P, x, text), proc(attn, x, encoder_hidden_states=text, scale=1.0), 1e-5)
+        mm = ref_cpu.RefMotionModule(ns, 64).eval()
+        xm = torch.randn(8, 64, 3, 3)
+        w = {"norm.weight": mm.norm.weight, "norm.bias": mm.norm.bias, "pos_embed.pe": mm.pe,
+             "proj_in.weight": mm.proj_in.weight, "proj_in.bias": mm.proj_in.bias,
+             "proj_out.weight": mm.proj_out.weight, "proj_out.bias": mm.proj_out.bias}
+        tb = "transformer_blocks.0."
+        for i, nm in enumerate(("norm1", "norm2", "norm3")):
+            w[tb + nm + ".weight"], w[tb + nm + ".bias"] = mm.norms[i].weight, mm.norms[i].bias
+        for ai, a in enumerate(("attn1", "attn2")):
+            for pi, p_ in enumerate(("to_q", "to_k", "to_v", "to_out.0")):
+                lin = mm.attns[ai][pi]
+                w[tb + f"{a}.{p_}.base.weight"] = lin.base.weight
+                if lin.base.bias is not None:
+                    w[tb + f"{a}.{p_}.base.bias"] = lin.base.bias
+                w[tb + f"{a}.{p_}.lora_A"], w[tb + f"{a}.{p_}.lora_B"] = lin.lora_A, lin.lora_B
+        w[tb + "ff.net.0.proj.weight"], w[tb + "ff.net.0.proj.bias"] = mm.ff_in.weight, mm.ff_in.bias
+        w[tb + "ff.net.2.weight"], w[tb + "ff.net.2.bias"] = mm.ff_out.weight, mm.ff_out.bias
+        close(op.motion_module(xm, w, 8, 8, 32, {"scale": 1.0 / 32}), mm(xm, 8), 2e-5)
+    arm = ref_cpu.CpuArm(8, 32)
+    assert arm.kind == "reference" and set(arm.units) == set(arm.CALLS)
