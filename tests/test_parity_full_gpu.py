@@ -161,7 +161,8 @@ def test_denoise_25_steps_l2_geometry_undamped():
 def test_gradient_checkpointing_bit_exact(what):
     """The reference trains with gradient checkpointing on (train_animatediff.py:100-101): autograd
     re-enters the forward during backward.  Every op is deterministic (no atomics in the forward,
-    fixed-order reductions), so the recomputed forward must give bit-identical gradients."""
+    fixed-order reductions), so the recomputed forward is bit-identical and so are the gradients
+    wherever the backward is deterministic too (the whole motion module)."""
     from torch.utils.checkpoint import checkpoint
     from video_style_transfer_b200.animatediff.attention_processor import AnimateDiffAttnProcessor2_0
     torch.manual_seed(3)
@@ -193,16 +194,26 @@ def test_gradient_checkpointing_bit_exact(what):
 
     y0, dx0, g0 = grads(False)
     y1, dx1, g1 = grads(True)
-    assert torch.equal(y0, y1) and torch.equal(dx0, dx1)
+    assert torch.equal(y0, y1), "recomputed forward differs"
     assert len(g0) == len(g1) > 0
-    for a, b in zip(g0, g1):
-        assert torch.equal(a, b)
+    if what == "motion":
+        assert torch.equal(dx0, dx1)
+        for a, b in zip(g0, g1):
+            assert torch.equal(a, b)
+    else:
+        # the spatial attention backward adds its per-key-tile dQ contributions with fp32 atomics
+        # (csrc/attn_bwd.cu), so gradients downstream of dQ are reproducible only up to fp32
+        # summation order, with or without checkpointing: the bound asserted is that order noise
+        # (1e-5 of the tensor's max), three orders of magnitude below the bf16 tolerance.
+        assert rel(dx1, dx0) < 1e-5
+        for a, b in zip(g0, g1):
+            assert rel(b, a) < 1e-5
     # reentrant flavour (what diffusers' _gradient_checkpointing_func uses on older versions)
     xi = x.detach().clone().requires_grad_(True)
     for p in params:
         p.grad = None
     checkpoint(fn, xi, use_reentrant=True).backward(dy)
-    assert torch.equal(xi.grad, dx0)
+    assert torch.equal(xi.grad, dx0) if what == "motion" else rel(xi.grad, dx0) < 1e-5
 
 
 # ---- config 4: one Stage-2 optimiser step ----------------------------------------------------------------
@@ -490,13 +501,16 @@ def test_batched_cfg_equals_two_pass_and_graph_set_text():
                                     [None] + [t[sl].contiguous() for t in x3[1:]], text, F_)
         for a, b in zip(both, one):
             assert torch.equal(a[sl], b), "batched CFG differs from the two-pass form"
-    graphed = hpth.GraphedDenoiseStep(plan, x4, x3, [torch.cat([tu, tc])], F_)
+    # a plan whose last module per level is a text cross-attention, so the outputs depend on the prompt
+    plan_t = plan + [next(p for p in plan if p[0] == "cross" and p[1] == lvl) for lvl in (1, 2)]
+    both = hpth.run_unet_hotpath(plan_t, x4, x3, torch.cat([tu, tc]), F_)
+    graphed = hpth.GraphedDenoiseStep(plan_t, x4, x3, [torch.cat([tu, tc])], F_)
     for a, b in zip(graphed.replay(), both):
         assert torch.equal(a, b)
     tu2, tc2 = (torch.randn(1, 77, 2048, generator=g).to(bf).cuda() for _ in range(2))
-    want = hpth.run_unet_hotpath(plan, x4, x3, torch.cat([tu2, tc2]), F_)
+    want = hpth.run_unet_hotpath(plan_t, x4, x3, torch.cat([tu2, tc2]), F_)
     graphed.set_text([torch.cat([tu2, tc2])])
     got = graphed.replay()
-    assert not torch.equal(got[2], both[2])
+    assert not torch.equal(got[2], both[2]) and not torch.equal(got[1], both[1])
     for a, b in zip(got, want):
         assert torch.equal(a, b)
