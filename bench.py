@@ -230,15 +230,20 @@ def sp_probe(args, world, rank, dev, steps):
         model = hpth.SDXLHotPath(temporal_rank=32, depth_scale=args.depth_scale)
     model = model.to(bf).eval()
     plan = model.forward_plan()
-    full_shapes = hpth.level_shapes(F, S)
+    nb = 2                                       # batched CFG: uncond | cond stacked along the batch
+    full_shapes = hpth.level_shapes(F, S, batch=nb)
     g = torch.Generator().manual_seed(777)       # the same full video on every rank; each keeps its frames
     full4 = [torch.randn(s, generator=g).to(bf) for s in full_shapes]
     full3 = [None] + [torch.randn(s[0], s[2] * s[3], s[1], generator=g).to(bf) for s in full_shapes[1:]]
-    texts = [torch.randn(1, 77, 2048, generator=g).to(bf).to(dev) for _ in range(2)]
+    texts = [torch.randn(nb, 77, 2048, generator=g).to(bf).to(dev)]
     sl = slice(rank * fl_, (rank + 1) * fl_)
-    xs4 = [t[sl].contiguous().to(dev) for t in full4]
-    xs3 = [None] + [t[sl].contiguous().to(dev) for t in full3[1:]]
-    nbytes = max(spm.SPMotionStep.buffer_bytes(1, s[1], s[2] * s[3], F, world) for s in full_shapes)
+
+    def mine(t):                                 # (nb * F, ...) -> this rank's frames of both CFG halves
+        return t.view(nb, F, *t.shape[1:])[:, sl].reshape(nb * fl_, *t.shape[1:]).contiguous()
+
+    xs4 = [mine(t).to(dev) for t in full4]
+    xs3 = [None] + [mine(t).to(dev) for t in full3[1:]]
+    nbytes = max(spm.SPMotionStep.buffer_bytes(nb, s[1], s[2] * s[3], F, world) for s in full_shapes)
     comm = spm.SPComm.from_process_group(nbytes)
 
     def barrier():
@@ -260,11 +265,11 @@ def sp_probe(args, world, rank, dev, steps):
     # ---- parity: this rank's slice of the unsharded modules' outputs (same kernels, one GPU) ------
     with torch.no_grad():
         want = hpth.run_unet_hotpath(plan, [t.to(dev) for t in full4], [None] + [t.to(dev) for t in full3[1:]],
-                                     texts[1], F)
-        got = hpth.run_unet_hotpath_sp(plan, xs4, xs3, texts[1], F, comm)
+                                     texts[0], F)
+        got = hpth.run_unet_hotpath_sp(plan, xs4, xs3, texts[0], F, comm)
     errs = []
     for w_, g_ in zip(want, got):
-        w_ = w_[sl].float()
+        w_ = mine(w_).float()
         errs.append(((g_.float() - w_).abs().max() / w_.abs().max().clamp_min(1e-30)).item())
     perr = torch.tensor([max(errs)], device=dev)
     dist.all_reduce(perr, op=dist.ReduceOp.MAX)
@@ -277,7 +282,7 @@ def sp_probe(args, world, rank, dev, steps):
     ms_sp = timed(graphed.replay, steps)
 
     # ---- per-phase device time of one eager step (events on the launching stream) -----------------
-    phases = {k: [] for k in ("gn_partials_share", "push", "compute", "pull", "barrier_wait", "spatial")}
+    phases = {k: [] for k in ("gn_partials_share", "push", "normalize", "compute", "pull", "barrier_wait", "spatial")}
 
     def ev():
         e = torch.cuda.Event(enable_timing=True)
@@ -288,16 +293,15 @@ def sp_probe(args, world, rank, dev, steps):
         st = spm.SPMotionStep(module, comm, x_local, F)
         t = [ev()]
         st.share_partials(); t.append(ev())
+        st.push_raw(); t.append(ev())
         comm.barrier(); t.append(ev())
-        st.push(); t.append(ev())
-        comm.barrier(); t.append(ev())
+        st.normalize(); t.append(ev())
         st.compute(); t.append(ev())
         comm.barrier(); t.append(ev())
         out = st.pull(); t.append(ev())
-        comm.barrier(); t.append(ev())
-        for name, i in (("gn_partials_share", 0), ("push", 2), ("compute", 4), ("pull", 6)):
+        for name, i in (("gn_partials_share", 0), ("push", 1), ("normalize", 3), ("compute", 4), ("pull", 6)):
             phases[name].append((t[i], t[i + 1]))
-        for i in (1, 3, 5, 7):
+        for i in (2, 5):
             phases["barrier_wait"].append((t[i], t[i + 1]))
         return out
 
@@ -344,11 +348,11 @@ def sp_probe(args, world, rank, dev, steps):
         if kind == "motion":
             s = full_shapes[lvl]
             egress += 2 * (s[0] * s[1] * s[2] * s[3] * 2 // world) * (world - 1) // world   # push + pull
-    egress *= 2                                                                             # x2 CFG passes
+    # (full_shapes already carry both CFG halves)
     barrier()
     del graphed
     comm.close()
-    return {"workload": "cfg5-sequence-parallel: ONE 32-frame 1024^2 video, hot path, x2 CFG (two passes)",
+    return {"workload": "cfg5-sequence-parallel: ONE 32-frame 1024^2 video, hot path, x2 CFG (batched B=2)",
             "n_gpus": world, "frames": F, "frames_per_rank": fl_, "steps": steps,
             "ms_per_step": ms_sp, "ms_sp1": ms_sp1, "speedup": ms_sp1 / ms_sp,
             "efficiency": ms_sp1 / (world * ms_sp), "scaling": "strong",
@@ -357,7 +361,7 @@ def sp_probe(args, world, rank, dev, steps):
                            "max |a-b| / max |b| over the per-level outputs, max over ranks",
             "phase_ms": phase_ms,
             "phase_note": "one eager step, CUDA events on the launching stream, summed over the 30 motion-module "
-                          "calls, max over ranks; barrier_wait = 4 flag barriers per motion module (includes peer "
+                          "calls, max over ranks; barrier_wait = 2 flag barriers per motion module (includes peer "
                           "skew and, in eager mode, launch skew); the timed ms_per_step is the graph replay",
             "launch": "CUDA graph replay (one graph per rank, no NCCL and no host sync on the data path)",
             "adapters": "folded" if fusedmod.MERGE_LORA else "low-rank"}

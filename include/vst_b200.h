@@ -313,6 +313,12 @@ int vst_a2a_frames_to_hw(void* comm, const void* x, int64_t dst_offset_bytes, co
 int vst_a2a_hw_to_frames(void* comm, int64_t src_offset_bytes, void* out, const void* residual, int B,
                          int C, int F_local, int F_total, int HW, int64_t sB, int64_t sC, int64_t sF,
                          void* stream);
+/* GroupNorm affine applied IN PLACE on a token tensor (B, rows_per_batch, C) bf16: the same fp32
+ * coefficients and single fma + rounding as vst_groupnorm5d_apply_rearrange.  Used by the sequence-
+ * parallel path, whose push sends raw activations and partial statistics under ONE barrier. */
+int vst_groupnorm_tokens_apply(void* tok, const float* mean, const float* rstd, const void* gamma,
+                               const void* beta, int B, int64_t rows_per_batch, int C, int groups,
+                               int param_dtype, void* stream);
 
 #ifdef __cplusplus
 }

@@ -158,6 +158,24 @@ def test_lora_gemm(ops, m, n, k1, k2, out_dtype):
         REL_TOL if out_dtype == torch.bfloat16 else 1e-4)
 
 
+@pytest.mark.parametrize("m,n,k", [(262144, 320, 320), (65536, 640, 640), (16384, 1280, 1280), (4100, 200, 72)])
+def test_lora_gemm_residual_tma_epilogue(ops, m, n, k):
+    """bf16 output + residual (to_out / ff.net.2 / proj_out of every module): the residual tile is
+    TMA-loaded into the output staging buffers and added in place.  Full config-3 shapes, a strided
+    residual view (row stride != N), and the exact identity D = 0 * A + R == R."""
+    torch.manual_seed(m % 97)
+    a = torch.randn(m, k).to(torch.bfloat16).cuda()
+    w = (torch.randn(n, k) / math.sqrt(k)).to(torch.bfloat16).cuda()
+    wide = torch.randn(m, n + 64).to(torch.bfloat16).cuda()
+    res = wide[:, 8:8 + n]                                      # row stride n + 64, 16-byte aligned
+    bias = torch.randn(n).cuda()
+    out = ops.lora_gemm(a, w, bias=bias, residual=res, out_scale=0.25)
+    want = (a.float() @ w.float().t() + bias + res.float()) * 0.25
+    assert rel_err(out, want.cpu()) < REL_TOL
+    zero = torch.zeros_like(a)
+    assert torch.equal(ops.lora_gemm(zero, w, residual=res), res)
+
+
 def test_lora_gemm_linearity(ops):
     """Size-independent property at a full config-3 shape (M=16384, C=1280): exact identity
     columns of B pick out columns of A, and doubling A doubles D (power-of-two scaling is exact)."""

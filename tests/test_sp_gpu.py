@@ -47,7 +47,14 @@ def test_sp_motion_module_emulated_ranks_match_unsharded(world, c, hw, f):
         for s in steps:
             # the gathered block is the unsharded partial order: statistics are bit-identical
             assert torch.equal(s.comm.view(s.part_off, s._part_shape, torch.float32), parts)
-            s.push()
+            s.push()                           # round-1 form: GroupNorm applied on the way out
+        toks_fused = [s.comm.view(0, (s.n_local * f, c)).clone() for s in steps]
+        # the shipped form: raw push + partials under ONE barrier, GroupNorm applied by the owner
+        for s in steps:
+            s.push_raw()
+        for s, t in zip(steps, toks_fused):
+            s.normalize()
+            assert torch.equal(s.comm.view(0, (s.n_local * f, c)), t)     # bit-identical tokens
         for s in steps:
             s.compute()
         got = torch.cat([s.pull() for s in steps], dim=0)

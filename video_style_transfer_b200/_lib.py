@@ -69,6 +69,7 @@ SIGNATURES = {
     "vst_comm_allgather_partials": (_i, [_p, _p, _i, _i, _l, _p]),
     "vst_a2a_frames_to_hw": (_i, [_p, _p, _l, _p, _p, _p, _p, _i, _i, _i, _i, _i, _l, _l, _l, _i, _i, _p]),
     "vst_a2a_hw_to_frames": (_i, [_p, _l, _p, _p, _i, _i, _i, _i, _i, _l, _l, _l, _p]),
+    "vst_groupnorm_tokens_apply": (_i, [_p, _p, _p, _p, _p, _i, _l, _i, _i, _i, _p]),
     "vst_attn_fwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _l, _l, _l, _l, _i, _f, _p, _l, _l, _l, _p]),
 }
 

@@ -32,16 +32,27 @@ constexpr int BK = 64;  // one 128-byte swizzle atom of bf16
 constexpr int kEpiWarps = 8;                 // 2 per TMEM lane quarter, interleaved over column chunks
 constexpr int kThreads = 64 + 32 * kEpiWarps;
 constexpr int kStageOutBytes = 32 * 32 * 2;  // one 32-row x 32-col bf16 chunk per TMA store
-constexpr int kOutBytes = kEpiWarps * 2 * kStageOutBytes;
-constexpr int kSmemBudget = 198400;          // operand ring; + kOutBytes staging + barriers <= 227 KB
+// RES kernels (bf16 output + residual): the residual chunk is brought in by TMA into the chunk's own
+// staging buffer kResAhead chunks ahead, added in place and sent back out by the TMA store.
+#ifndef VST_RES_BUFS
+#define VST_RES_BUFS 4
+#define VST_RES_AHEAD 2
+#endif
+constexpr int kResBufs = VST_RES_BUFS, kResAhead = VST_RES_AHEAD;
+constexpr int kSmemTotal = 227 * 1024;       // per-CTA limit; 1024 alignment slack + 512 B of barriers
+constexpr int kBarBytes = 512;
 
-template <int BN>
+constexpr int out_bytes(bool res) { return kEpiWarps * (res ? kResBufs : 2) * kStageOutBytes; }
+constexpr int ring_budget(bool res) { return kSmemTotal - 1024 - kBarBytes - out_bytes(res); }
+
+template <int BN, bool RES = false>
 struct Cfg {
   static constexpr int kStageBytes = (BM + BN) * BK * 2;
-  static constexpr int kStages = (kSmemBudget / kStageBytes) > 8 ? 8 : (kSmemBudget / kStageBytes);
+  static constexpr int kOutBytes = out_bytes(RES);
+  static constexpr int kStages = (ring_budget(RES) / kStageBytes) > 8 ? 8 : (ring_budget(RES) / kStageBytes);
   static constexpr int kAccStride = BN <= 64 ? 64 : (BN <= 128 ? 128 : 256);
   static constexpr int kTmemCols = 2 * kAccStride;  // power of two >= 32
-  static constexpr int kSmemBytes = kStages * kStageBytes + kOutBytes + 1024 /*align*/ + 256;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kOutBytes + 1024 /*align*/ + kBarBytes;
 };
 
 struct EpiArgs {
@@ -174,21 +185,7 @@ __device__ __forceinline__ void epilogue_bias(const EpiArgs& ep, int n0, int ewa
   for (int i = 0; i < EpiBias<BN>::kMax; ++i) b.v[i] = bias_lane(ep, n0 + half * 32 + i * 64 + lane, ep.N);
 }
 
-// RES kernels: the residual rows of the coming tile are pulled towards L2 while its mainloop still
-// runs (the epilogue's own 16-byte loads then find them there; no registers held across the wait).
-// Measured and dropped: carrying the residual chunk one chunk ahead in registers (L0 157 -> 171 us).
-template <int BN>
-__device__ __forceinline__ void epilogue_prefetch_res(const EpiArgs& ep, int m0, int n0, int ewarp, int lane) {
-  const int quarter = (ewarp + 2) & 3, half = ewarp >> 2;
-  const int64_t row = (int64_t)m0 + quarter * 32 + lane;
-  if (row >= ep.M) return;
-  const __nv_bfloat16* rp = reinterpret_cast<const __nv_bfloat16*>(ep.residual) + row * ep.ldr + n0;
-#pragma unroll
-  for (int c0 = half * 32; c0 < BN; c0 += 64)
-    if (n0 + c0 < ep.N) asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + c0));
-}
-
-template <int BN, bool RES, typename Release>
+template <int BN, typename Release>
 __device__ __forceinline__ void epilogue_tile(const EpiArgs& ep, const CUtensorMap* tmD,
                                               uint32_t tacc, int m0, int n0, int ewarp, int lane,
                                               uint8_t* stage_out, int& buf, const EpiBias<BN>& bias,
@@ -198,9 +195,8 @@ __device__ __forceinline__ void epilogue_tile(const EpiArgs& ep, const CUtensorM
   const int64_t row = (int64_t)m0 + quarter * 32 + lane;
   const bool row_ok = row < ep.M;
   const uint32_t taddr = tacc + (uint32_t(quarter * 32) << 16);
-  // bf16 output always leaves through the staged TMA store; a residual is read per row chunk and
-  // added before the pack (r01 launch list: the direct row stores made the memory-bound residual
-  // GEMMs 3x slower than their twins without residual -- L0 to_out 230 us against 76 us)
+  // bf16 output always leaves through the staged TMA store (bf16 + residual: epilogue_res_loop);
+  // fp32 output (parameter-gradient GEMMs, config-1 fp32 activations) is written row by row
   const bool via_tma = !ep.out_f32 && !(ep.debug & 16);   // 16: direct stores
   constexpr int kMax = EpiBias<BN>::kMax;
   const int nch = (BN - half * 32 + 63) / 64;          // chunks of this warp: c0 = half*32 + 64 i
@@ -210,18 +206,6 @@ __device__ __forceinline__ void epilogue_tile(const EpiArgs& ep, const CUtensorM
   for (int i = 0; i < kMax; ++i) {
     if (i >= nch) break;
     const int c0 = half * 32 + i * 64;
-    // RES (a kernel instantiation of its own, so the plain kernel's epilogue keeps its registers):
-    // bf16 output + residual.  The residual row chunk is requested before the accumulator wait;
-    // 16-byte loads, column groups past N and rows past M read as zero.  Measured and dropped:
-    // coalesced loads bounced through the staging buffer (L0 157 -> 175 us).
-    uint4 res[4];
-    if (RES) {
-      const __nv_bfloat16* rp = reinterpret_cast<const __nv_bfloat16*>(ep.residual) + row * ep.ldr + n0 + c0;
-#pragma unroll
-      for (int q = 0; q < 4; ++q)
-        res[q] = (row_ok && n0 + c0 + q * 8 < ep.N) ? __ldg(reinterpret_cast<const uint4*>(rp + q * 8))
-                                                    : make_uint4(0, 0, 0, 0);
-    }
     tmem_ld_wait();
     if (i + 1 < nch) {
       tmem_ld32(taddr + c0 + 64, r[(i + 1) & 1]);
@@ -235,7 +219,7 @@ __device__ __forceinline__ void epilogue_tile(const EpiArgs& ep, const CUtensorM
     if (ep.debug & 2) continue;
     if (via_tma) {
       uint32_t w[16];
-      epilogue_pack(ep, rc, bias.v[i], RES ? res : nullptr, w);
+      epilogue_pack(ep, rc, bias.v[i], nullptr, w);
       uint8_t* sbuf = stage_out + buf * kStageOutBytes;
       if (lane == 0) tma_store_wait_read<1>();      // the store that last used this buffer is done
       __syncwarp();
@@ -256,6 +240,99 @@ __device__ __forceinline__ void epilogue_tile(const EpiArgs& ep, const CUtensorM
       epilogue_chunk(ep, rc, row, row_ok, n0, c0, bias.v[i]);
     }
   }
+}
+
+// ---- RES epilogue: bf16 output + residual, the whole persistent loop of one epilogue warp -----------
+// The residual tile never goes through the register-addressed row loads of the first version (each
+// lane fetching its own 64-byte row segment: 8 warps x 2 KB in flight per SM, L0 to_out + residual
+// 154.7 us against 74.8 us without residual, r01).  Each 32 x 32 chunk of the residual is fetched by
+// ONE TMA load (64B swizzle, the layout of the output staging buffer) into the buffer the chunk
+// will be stored from, kResAhead chunks ahead of its use and across tile boundaries, so while the
+// warp waits for an accumulator the residual of the coming chunks is already in flight.  The
+// epilogue then reads its row's 64 bytes from shared memory, adds, packs, writes the result IN
+// PLACE and sends the buffer out by TMA store.  A buffer is refilled once the store issued from it
+// kResBufs - kResAhead chunks ago has finished reading (cp.async.bulk.wait_group.read).
+// coords(tile, m0, n0) maps a tile index of this CTA's walk to its origin; release(acc) hands the
+// accumulator stage back to the MMA issuer.
+template <int BN, typename Coords, typename Release>
+__device__ __forceinline__ void epilogue_res_loop(const EpiArgs& ep, const CUtensorMap* tmD,
+                                                  const CUtensorMap* tmR, uint32_t tmem_base, int acc_stride,
+                                                  uint64_t* acc_full, uint8_t* my_out, uint64_t* my_bar,
+                                                  int ewarp, int lane, int first, int stride, int total,
+                                                  Coords coords, Release release) {
+  constexpr int kMax = EpiBias<BN>::kMax;
+  const int quarter = (ewarp + 2) & 3, half = ewarp >> 2;
+  const int nch = (BN - half * 32 + 63) / 64;             // chunks of this warp per tile
+  const int my_tiles = first < total ? (total - first + stride - 1) / stride : 0;
+  const int nseq = my_tiles * nch;
+  auto issue = [&](int seq) {                             // lane 0: residual chunk `seq` -> its buffer
+    const int tk = seq / nch, i = seq - tk * nch;
+    int m0, n0;
+    coords(first + tk * stride, m0, n0);
+    const int b = seq % kResBufs;
+    mbar_arrive_expect_tx(&my_bar[b], kStageOutBytes);
+    tma_load_2d(my_out + b * kStageOutBytes, tmR, &my_bar[b], n0 + half * 32 + i * 64, m0 + quarter * 32);
+  };
+  if (lane == 0) {
+    tma_prefetch_desc(tmD);
+    tma_prefetch_desc(tmR);
+#pragma unroll
+    for (int a = 0; a < kResAhead; ++a)
+      if (a < nseq) issue(a);
+  }
+  int seq = 0, acc = 0;
+  uint32_t acc_phase = 0;
+  for (int tk = 0; tk < my_tiles; ++tk) {
+    int m0, n0;
+    coords(first + tk * stride, m0, n0);
+    EpiBias<BN> bias;
+    epilogue_bias<BN>(ep, n0, ewarp, lane, bias);
+    mbar_wait(&acc_full[acc], acc_phase, 4);
+    tc_fence_after();
+    const uint32_t taddr = tmem_base + acc * acc_stride + (uint32_t(quarter * 32) << 16);
+    uint32_t r[2][32];
+    tmem_ld32(taddr + half * 32, r[0]);
+#pragma unroll
+    for (int i = 0; i < kMax; ++i) {
+      if (i >= nch) break;
+      const int c0 = half * 32 + i * 64;
+      const int b = seq % kResBufs;
+      uint8_t* sbuf = my_out + b * kStageOutBytes;
+      tmem_ld_wait();
+      if (i + 1 < nch) {
+        tmem_ld32(taddr + c0 + 64, r[(i + 1) & 1]);
+      } else {
+        tc_fence_before();
+        __syncwarp();
+        release(acc);
+      }
+      mbar_wait(&my_bar[b], (seq / kResBufs) & 1, 5);     // the residual chunk has landed
+      uint8_t* srow = sbuf + lane * 64;
+      const int sx = (lane >> 1) & 3;                    // SWIZZLE_64B: 16-B chunk ^= (row >> 1) & 3
+      uint4 res[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) res[q] = *reinterpret_cast<const uint4*>(srow + ((q ^ sx) * 16));
+      uint32_t w[16];
+      epilogue_pack(ep, r[i & 1], bias.v[i], res, w);
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        *reinterpret_cast<uint4*>(srow + ((q ^ sx) * 16)) =
+            make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        if (n0 + c0 < ep.N) tma_store_2d(tmD, sbuf, n0 + c0, m0 + quarter * 32);
+        tma_store_commit();                               // (an empty group keeps the count uniform)
+        if (seq + kResAhead < nseq) {
+          tma_store_wait_read<kResBufs - kResAhead>();    // the store that last used that buffer is out
+          issue(seq + kResAhead);
+        }
+      }
+      ++seq;
+    }
+    if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+  }
+  if (lane == 0) tma_store_wait<0>();
 }
 
 // ---- VST_ACT_GEGLU: D[:, j] = (acc[:, j] + bias[j]) * gelu(acc[:, BN/2 + j] + bias[N + j]) ----------
@@ -339,18 +416,20 @@ template <int BN, bool RES>
 __global__ void __launch_bounds__(kThreads, 1)
 lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
                  const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
-                 const __grid_constant__ CUtensorMap tmD, int nk1, int nk2, int m_tiles, int n_tiles, int k2_group_n, int k2_cols,
+                 const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmR,
+                 int nk1, int nk2, int m_tiles, int n_tiles, int k2_group_n, int k2_cols,
                  EpiArgs ep) {
-  using C = Cfg<BN>;
+  using C = Cfg<BN, RES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
   uint8_t* stage_out = smem + C::kStages * C::kStageBytes;   // 1024-aligned: stage sizes are k*1024
-  uint64_t* full = reinterpret_cast<uint64_t*>(stage_out + kOutBytes);
+  uint64_t* full = reinterpret_cast<uint64_t*>(stage_out + C::kOutBytes);
   uint64_t* empty = full + C::kStages;
   uint64_t* acc_full = empty + C::kStages;
   uint64_t* acc_empty = acc_full + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  uint64_t* res_bar = acc_empty + 2;                       // [kEpiWarps][kResBufs] (RES kernels)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + kEpiWarps * kResBufs);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nk = nk1 + nk2;
@@ -371,6 +450,8 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
       mbar_init(&acc_full[i], 1);
       mbar_init(&acc_empty[i], kEpiWarps);
     }
+    if (RES)
+      for (int i = 0; i < kEpiWarps * kResBufs; ++i) mbar_init(&res_bar[i], 1);
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, C::kTmemCols);
@@ -436,24 +517,31 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
   } else {
     // ================= epilogue (warps 2..9) =================
     const int ewarp = warp - 2;
-    uint8_t* my_out = stage_out + ewarp * 2 * kStageOutBytes;
-    int buf = 0;
-    int acc = 0;
-    uint32_t acc_phase = 0;
-    if (lane == 0) tma_prefetch_desc(&tmD);
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
-      EpiBias<BN> bias;
-      epilogue_bias<BN>(ep, n0, ewarp, lane, bias);
-      if (RES) epilogue_prefetch_res<BN>(ep, m0, n0, ewarp, lane);
-      mbar_wait(&acc_full[acc], acc_phase, 4);
-      tc_fence_after();
-      uint64_t* done = &acc_empty[acc];
-      epilogue_tile<BN, RES>(ep, &tmD, tmem_base + acc * C::kAccStride, m0, n0, ewarp, lane, my_out, buf, bias,
-                             [&]() { if (lane == 0) mbar_arrive(done); });
-      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    if constexpr (RES) {
+      epilogue_res_loop<BN>(
+          ep, &tmD, &tmR, tmem_base, C::kAccStride, acc_full, stage_out + ewarp * kResBufs * kStageOutBytes,
+          res_bar + ewarp * kResBufs, ewarp, lane, blockIdx.x, gridDim.x, total_tiles,
+          [&](int tile, int& m0, int& n0) { m0 = (tile / n_tiles) * BM; n0 = (tile % n_tiles) * BN; },
+          [&](int acc) { if (lane == 0) mbar_arrive(&acc_empty[acc]); });
+    } else {
+      uint8_t* my_out = stage_out + ewarp * 2 * kStageOutBytes;
+      int buf = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      if (lane == 0) tma_prefetch_desc(&tmD);
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
+        EpiBias<BN> bias;
+        epilogue_bias<BN>(ep, n0, ewarp, lane, bias);
+        mbar_wait(&acc_full[acc], acc_phase, 4);
+        tc_fence_after();
+        uint64_t* done = &acc_empty[acc];
+        epilogue_tile<BN>(ep, &tmD, tmem_base + acc * C::kAccStride, m0, n0, ewarp, lane, my_out, buf, bias,
+                          [&]() { if (lane == 0) mbar_arrive(done); });
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+      if (lane == 0) tma_store_wait<0>();
     }
-    if (lane == 0) tma_store_wait<0>();
   }
 
   tc_fence_before();
@@ -475,32 +563,35 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
 //   empty[s]     in both CTAs, released by a multicast tcgen05.commit
 //   acc_full[a]  in both CTAs (multicast commit); acc_empty[a] in the leader, 8 warp arrivals
 // ------------------------------------------------------------------------------------------------
-template <int BN>
+template <int BN, bool RES = false>
 struct Cfg2 {
   static constexpr int kBRows = BN / 2;
   static constexpr int kStageBytes = (BM + kBRows) * BK * 2;
-  static constexpr int kStages = (kSmemBudget / kStageBytes) > 8 ? 8 : (kSmemBudget / kStageBytes);
+  static constexpr int kOutBytes = out_bytes(RES);
+  static constexpr int kStages = (ring_budget(RES) / kStageBytes) > 8 ? 8 : (ring_budget(RES) / kStageBytes);
   static constexpr int kAccStride = BN <= 64 ? 64 : (BN <= 128 ? 128 : 256);
   static constexpr int kTmemCols = 2 * kAccStride;
-  static constexpr int kSmemBytes = kStages * kStageBytes + kOutBytes + 1024 + 256;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kOutBytes + 1024 + kBarBytes;
 };
 
 template <int BN, bool RES>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 lora_gemm2_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
                   const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
-                  const __grid_constant__ CUtensorMap tmD, int nk1, int nk2, int m_tiles, int n_tiles, int k2_group_n, int k2_cols,
+                  const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmR,
+                  int nk1, int nk2, int m_tiles, int n_tiles, int k2_group_n, int k2_cols,
                   EpiArgs ep) {
-  using C = Cfg2<BN>;
+  using C = Cfg2<BN, RES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
   uint8_t* stage_out = smem + C::kStages * C::kStageBytes;   // 1024-aligned: stage sizes are k*1024
-  uint64_t* full = reinterpret_cast<uint64_t*>(stage_out + kOutBytes);
+  uint64_t* full = reinterpret_cast<uint64_t*>(stage_out + C::kOutBytes);
   uint64_t* empty = full + C::kStages;
   uint64_t* acc_full = empty + C::kStages;
   uint64_t* acc_empty = acc_full + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  uint64_t* res_bar = acc_empty + 2;                       // [kEpiWarps][kResBufs] (RES kernels)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + kEpiWarps * kResBufs);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
@@ -524,6 +615,8 @@ lora_gemm2_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constan
       mbar_init(&acc_full[i], 1);
       mbar_init(&acc_empty[i], 2 * kEpiWarps);
     }
+    if (RES)
+      for (int i = 0; i < kEpiWarps * kResBufs; ++i) mbar_init(&res_bar[i], 1);
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc_2sm(tmem_slot, C::kTmemCols);
@@ -599,41 +692,48 @@ lora_gemm2_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constan
   } else {
     // ================= epilogue (warps 2..9 of both CTAs; own 128 rows) =================
     const int ewarp = warp - 2;
-    uint8_t* my_out = stage_out + ewarp * 2 * kStageOutBytes;
-    int buf = 0;
-    int acc = 0;
-    uint32_t acc_phase = 0;
-    if (lane == 0) tma_prefetch_desc(&tmD);
-    for (int tile = cluster_id; tile < total_tiles; tile += n_clusters) {
-      const int m0 = (tile / n_tiles) * (2 * BM) + rank * BM;
-      uint64_t* done = &acc_empty[acc];
-      auto release = [&]() { if (lane == 0) mbar_arrive_cluster(done, 0); };
-      if (ep.act == 2) {
-        const int n0 = (tile % n_tiles) * (BN / 2);
-        float bh[(BN / 2 + 63) / 64], bg[(BN / 2 + 63) / 64];
+    if constexpr (RES) {
+      epilogue_res_loop<BN>(
+          ep, &tmD, &tmR, tmem_base, C::kAccStride, acc_full, stage_out + ewarp * kResBufs * kStageOutBytes,
+          res_bar + ewarp * kResBufs, ewarp, lane, cluster_id, n_clusters, total_tiles,
+          [&](int tile, int& m0, int& n0) { m0 = (tile / n_tiles) * (2 * BM) + rank * BM; n0 = (tile % n_tiles) * BN; },
+          [&](int acc) { if (lane == 0) mbar_arrive_cluster(&acc_empty[acc], 0); });
+    } else {
+      uint8_t* my_out = stage_out + ewarp * 2 * kStageOutBytes;
+      int buf = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      if (lane == 0) tma_prefetch_desc(&tmD);
+      for (int tile = cluster_id; tile < total_tiles; tile += n_clusters) {
+        const int m0 = (tile / n_tiles) * (2 * BM) + rank * BM;
+        uint64_t* done = &acc_empty[acc];
+        auto release = [&]() { if (lane == 0) mbar_arrive_cluster(done, 0); };
+        if (ep.act == 2) {
+          const int n0 = (tile % n_tiles) * (BN / 2);
+          float bh[(BN / 2 + 63) / 64], bg[(BN / 2 + 63) / 64];
 #pragma unroll
-        for (int i = 0; i < (BN / 2 + 63) / 64; ++i) {
-          const int col = n0 + (ewarp >> 2) * 32 + i * 64 + lane;
-          bh[i] = bias_lane(ep, col, ep.N);
-          bg[i] = bias_lane(ep, col < ep.N ? ep.N + col : 2 * ep.N, 2 * ep.N);
+          for (int i = 0; i < (BN / 2 + 63) / 64; ++i) {
+            const int col = n0 + (ewarp >> 2) * 32 + i * 64 + lane;
+            bh[i] = bias_lane(ep, col, ep.N);
+            bg[i] = bias_lane(ep, col < ep.N ? ep.N + col : 2 * ep.N, 2 * ep.N);
+          }
+          mbar_wait(&acc_full[acc], acc_phase, 4);
+          tc_fence_after();
+          epilogue_tile_geglu<BN>(ep, &tmD, tmem_base + acc * C::kAccStride, m0, n0, ewarp, lane, my_out, buf,
+                                  bh, bg, release);
+          if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+          continue;
         }
+        const int n0 = (tile % n_tiles) * BN;
+        EpiBias<BN> bias;
+        epilogue_bias<BN>(ep, n0, ewarp, lane, bias);
         mbar_wait(&acc_full[acc], acc_phase, 4);
         tc_fence_after();
-        epilogue_tile_geglu<BN>(ep, &tmD, tmem_base + acc * C::kAccStride, m0, n0, ewarp, lane, my_out, buf,
-                                bh, bg, release);
+        epilogue_tile<BN>(ep, &tmD, tmem_base + acc * C::kAccStride, m0, n0, ewarp, lane, my_out, buf, bias, release);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
-        continue;
       }
-      const int n0 = (tile % n_tiles) * BN;
-      EpiBias<BN> bias;
-      epilogue_bias<BN>(ep, n0, ewarp, lane, bias);
-      if (RES) epilogue_prefetch_res<BN>(ep, m0, n0, ewarp, lane);
-      mbar_wait(&acc_full[acc], acc_phase, 4);
-      tc_fence_after();
-      epilogue_tile<BN, RES>(ep, &tmD, tmem_base + acc * C::kAccStride, m0, n0, ewarp, lane, my_out, buf, bias, release);
-      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      if (lane == 0) tma_store_wait<0>();
     }
-    if (lane == 0) tma_store_wait<0>();
   }
 
   tc_fence_before();
@@ -651,22 +751,28 @@ int make_operand_map(CUtensorMap* m, const void* p, int64_t rows, int K, int64_t
   return vst_make_tmap(m, p, 2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
+int make_row_map(CUtensorMap* m, const void* p, int64_t ld, int64_t M, int N);
+
 int make_out_map(CUtensorMap* m, const EpiArgs& ep) {
   if (ep.out_f32) {      // direct-store path: the map is never used
     memset(m, 0, sizeof(*m));
     return VST_OK;
   }
-  const uint64_t dims[2] = {(uint64_t)ep.N, (uint64_t)ep.M};
-  const uint64_t strides[2] = {2, (uint64_t)ep.ldd * 2};
-  const uint32_t box[2] = {32, 32};
-  return vst_make_tmap(m, ep.D, 2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_64B);
+  return make_row_map(m, ep.D, ep.ldd, ep.M, ep.N);
 }
 
-template <int BN>
-int launch(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, const void* A2,
-           int64_t lda2, const void* B2, int64_t ldb2, int K2, int k2_group_n, const EpiArgs& ep,
-           cudaStream_t st) {
-  using C = Cfg<BN>;
+int make_row_map(CUtensorMap* m, const void* p, int64_t ld, int64_t M, int N) {
+  const uint64_t dims[2] = {(uint64_t)N, (uint64_t)M};
+  const uint64_t strides[2] = {2, (uint64_t)ld * 2};
+  const uint32_t box[2] = {32, 32};
+  return vst_make_tmap(m, p, 2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_64B);
+}
+
+template <int BN, bool RES>
+int launch_t(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, const void* A2,
+             int64_t lda2, const void* B2, int64_t ldb2, int K2, int k2_group_n, const EpiArgs& ep,
+             cudaStream_t st) {
+  using C = Cfg<BN, RES>;
   CUtensorMap tA1, tB1, tA2, tB2;
   int rc;
   if ((rc = make_operand_map(&tA1, A1, ep.M, K1, lda1, BM))) return rc;
@@ -679,15 +785,13 @@ int launch(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, c
     tA2 = tA1;
     tB2 = tB1;
   }
-  CUtensorMap tD;
+  CUtensorMap tD, tR;
   if ((rc = make_out_map(&tD, ep))) return rc;
-  const bool res = ep.residual != nullptr && !ep.out_f32;    // bf16 + residual: staged-store epilogue
-  auto kern = res ? lora_gemm_kernel<BN, true> : lora_gemm_kernel<BN, false>;
+  tR = tD;
+  if (RES && (rc = make_row_map(&tR, ep.residual, ep.ldr, ep.M, ep.N))) return rc;
   static bool configured = false;
   if (!configured) {
-    VST_CUDA_OK(cudaFuncSetAttribute(lora_gemm_kernel<BN, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     C::kSmemBytes));
-    VST_CUDA_OK(cudaFuncSetAttribute(lora_gemm_kernel<BN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    VST_CUDA_OK(cudaFuncSetAttribute(lora_gemm_kernel<BN, RES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      C::kSmemBytes));
     configured = true;
   }
@@ -695,19 +799,27 @@ int launch(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, c
   const int64_t tiles = (int64_t)m_tiles * n_tiles;
   VST_REQUIRE(tiles < (1ll << 31), VST_E_UNSUPPORTED, "lora_gemm: too many tiles");
   const int grid = (int)(tiles < vst_sm_count() ? tiles : vst_sm_count());
-  kern<<<grid, kThreads, C::kSmemBytes, st>>>(tA1, tB1, tA2, tB2, tD, (K1 + BK - 1) / BK,
-                                               (K2 + BK - 1) / BK, m_tiles, n_tiles, k2_group_n, K2,
-                                               ep);
+  lora_gemm_kernel<BN, RES><<<grid, kThreads, C::kSmemBytes, st>>>(tA1, tB1, tA2, tB2, tD, tR, (K1 + BK - 1) / BK,
+                                                                   (K2 + BK - 1) / BK, m_tiles, n_tiles,
+                                                                   k2_group_n, K2, ep);
   VST_LAUNCH_OK();
   return VST_OK;
 }
 
-
 template <int BN>
-int launch2(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, const void* A2,
-            int64_t lda2, const void* B2, int64_t ldb2, int K2, int k2_group_n, const EpiArgs& ep,
-            cudaStream_t st) {
-  using C = Cfg2<BN>;
+int launch(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, const void* A2,
+           int64_t lda2, const void* B2, int64_t ldb2, int K2, int k2_group_n, const EpiArgs& ep,
+           cudaStream_t st) {
+  const bool res = ep.residual != nullptr && !ep.out_f32;    // bf16 + residual: TMA-fed residual epilogue
+  return res ? launch_t<BN, true>(A1, lda1, B1, ldb1, K1, A2, lda2, B2, ldb2, K2, k2_group_n, ep, st)
+             : launch_t<BN, false>(A1, lda1, B1, ldb1, K1, A2, lda2, B2, ldb2, K2, k2_group_n, ep, st);
+}
+
+template <int BN, bool RES>
+int launch2_t(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, const void* A2,
+              int64_t lda2, const void* B2, int64_t ldb2, int K2, int k2_group_n, const EpiArgs& ep,
+              cudaStream_t st) {
+  using C = Cfg2<BN, RES>;
   CUtensorMap tA1, tB1, tA2, tB2;
   int rc;
   const bool geglu = ep.act == 2;     // B1 = [W_hidden ; W_gate]: 2N rows
@@ -721,28 +833,36 @@ int launch2(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, 
     tA2 = tA1;
     tB2 = tB1;
   }
-  CUtensorMap tD;
+  CUtensorMap tD, tR;
   if ((rc = make_out_map(&tD, ep))) return rc;
-  const bool res = ep.residual != nullptr && !ep.out_f32;    // bf16 + residual: staged-store epilogue
-  auto kern = res ? lora_gemm2_kernel<BN, true> : lora_gemm2_kernel<BN, false>;
+  tR = tD;
+  if (RES && (rc = make_row_map(&tR, ep.residual, ep.ldr, ep.M, ep.N))) return rc;
   static bool configured = false;
   if (!configured) {
-    VST_CUDA_OK(cudaFuncSetAttribute(lora_gemm2_kernel<BN, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     C::kSmemBytes));
-    VST_CUDA_OK(cudaFuncSetAttribute(lora_gemm2_kernel<BN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    VST_CUDA_OK(cudaFuncSetAttribute(lora_gemm2_kernel<BN, RES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      C::kSmemBytes));
     configured = true;
   }
   // N need not be a multiple of BN: TMA zero-fills the B rows past N and clips the stores
   const int m_tiles = (int)((ep.M + 2 * BM - 1) / (2 * BM)), n_tiles = geglu ? ep.N / (BN / 2) : (ep.N + BN - 1) / BN;
   const int64_t tiles = (int64_t)m_tiles * n_tiles;
+  VST_REQUIRE(tiles < (1ll << 31), VST_E_UNSUPPORTED, "lora_gemm: too many tiles");
   const int pairs = vst_sm_count() / 2;
   const int grid = 2 * (int)(tiles < pairs ? tiles : pairs);
-  kern<<<grid, kThreads, C::kSmemBytes, st>>>(tA1, tB1, tA2, tB2, tD, (K1 + BK - 1) / BK,
-                                               (K2 + BK - 1) / BK, m_tiles, n_tiles, k2_group_n, K2,
-                                               ep);
+  lora_gemm2_kernel<BN, RES><<<grid, kThreads, C::kSmemBytes, st>>>(tA1, tB1, tA2, tB2, tD, tR, (K1 + BK - 1) / BK,
+                                                                    (K2 + BK - 1) / BK, m_tiles, n_tiles,
+                                                                    k2_group_n, K2, ep);
   VST_LAUNCH_OK();
   return VST_OK;
+}
+
+template <int BN>
+int launch2(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, const void* A2,
+            int64_t lda2, const void* B2, int64_t ldb2, int K2, int k2_group_n, const EpiArgs& ep,
+            cudaStream_t st) {
+  const bool res = ep.residual != nullptr && !ep.out_f32;
+  return res ? launch2_t<BN, true>(A1, lda1, B1, ldb1, K1, A2, lda2, B2, ldb2, K2, k2_group_n, ep, st)
+             : launch2_t<BN, false>(A1, lda1, B1, ldb1, K1, A2, lda2, B2, ldb2, K2, k2_group_n, ep, st);
 }
 
 // ---- vst_lora_pack_up: B2'[n, br*r + j] = scale * m_br[n] * mask_br[n] * B_br[n, j] ------------

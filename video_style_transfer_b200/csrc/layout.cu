@@ -447,3 +447,54 @@ extern "C" int vst_a2a_hw_to_frames(void* comm, int64_t src_offset_bytes, void* 
   return launch<1>(local, out, nullptr, residual, B, C, F_local, HW, sB, sC, sF, VST_BF16, (cudaStream_t)stream,
                    NormArgs{nullptr, nullptr, nullptr, nullptr, 1, 0}, &sh);
 }
+
+
+// ---- GroupNorm affine on the TOKEN layout ((B, rows_per_batch, C) bf16, in place) -----------------------
+// Sequence parallelism (comm.cu): the frames -> positions push sends RAW activations together with the
+// GroupNorm partials, so ONE flag barrier covers both; the owner of the positions then applies
+// y = x * a_c + b_c here, with exactly the coefficients and the single fp32 fma + rounding of the
+// fused apply+rearrange above (bit-identical tokens).
+namespace {
+__global__ void gn_tokens_apply_kernel(__nv_bfloat16* __restrict__ tok, int64_t rows_per_batch, int C,
+                                       NormArgs na) {
+  extern __shared__ float2 coef[];                 // [C] (a_c, b_c) of this block's batch
+  const int b = blockIdx.y;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) coef[c] = norm_coeffs(na, b, c, C);
+  __syncthreads();
+  const int vec_per_row = C >> 3;
+  const int64_t total = rows_per_batch * vec_per_row;
+  uint4* base = reinterpret_cast<uint4*>(tok + (int64_t)b * rows_per_batch * C);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % vec_per_row) * 8;
+    uint4 w = base[i];
+    uint32_t* ww = reinterpret_cast<uint32_t*>(&w);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 e = unpack_bf16(ww[j]);
+      const float2 k0 = coef[c0 + 2 * j], k1 = coef[c0 + 2 * j + 1];
+      ww[j] = pack_bf16(fmaf(e.x, k0.x, k0.y), fmaf(e.y, k1.x, k1.y));
+    }
+    base[i] = w;
+  }
+}
+}  // namespace
+
+extern "C" int vst_groupnorm_tokens_apply(void* tok, const float* mean, const float* rstd, const void* gamma,
+                                          const void* beta, int B, int64_t rows_per_batch, int C, int groups,
+                                          int param_dtype, void* stream) {
+  VST_REQUIRE(tok && mean && rstd && gamma && beta && B > 0 && rows_per_batch >= 0 && C > 0, VST_E_BADARG,
+              "groupnorm_tokens_apply: bad argument");
+  VST_REQUIRE(groups > 0 && C % groups == 0 && C % 8 == 0, VST_E_UNSUPPORTED,
+              "groupnorm_tokens_apply: C=%d must be a multiple of 8 and of groups=%d", C, groups);
+  if (rows_per_batch == 0) return VST_OK;
+  NormArgs na{mean, rstd, gamma, beta, groups, param_dtype == VST_BF16};
+  const int64_t vecs = rows_per_batch * (C / 8);
+  int gx = (int)((vecs + 256 * 8 - 1) / (256 * 8));
+  const int cap = 8 * vst_sm_count();
+  if (gx > cap) gx = cap;
+  if (gx < 1) gx = 1;
+  gn_tokens_apply_kernel<<<dim3(gx, B), 256, C * sizeof(float2), (cudaStream_t)stream>>>(
+      reinterpret_cast<__nv_bfloat16*>(tok), rows_per_batch, C, na);
+  VST_LAUNCH_OK();
+  return VST_OK;
+}

@@ -6,9 +6,11 @@ The two transposes per motion module are done by the module's own layout kernels
 reading from peer memory over NVLink (csrc/layout.cu ShardArgs, csrc/comm.cu):
 
     frames-sharded x --GroupNorm partials stored into every peer (vst_comm_allgather_partials)
-        --barrier--> vst_a2a_frames_to_hw (push, GroupNorm applied on the way)
-        --barrier--> proj_in .. proj_out on N/P sequences
-        --barrier--> vst_a2a_hw_to_frames (pull, + residual) --barrier--> frames-sharded output
+                     --vst_a2a_frames_to_hw (push of the RAW tokens to the position owners)
+        --barrier--> GroupNorm on the received tokens (vst_groupnorm_tokens_apply, same rounding as the
+                     fused apply), proj_in .. proj_out on N/P sequences
+        --barrier--> vst_a2a_hw_to_frames (pull, + residual) --> frames-sharded output
+    (two flag barriers per motion module; round 1 used four)
 
 torch.distributed (NCCL) is plumbing only: it carries the IPC handles at start-up.  No NCCL call
 and no host synchronisation sits on the data path, so a whole sequence-parallel denoising step is
@@ -188,13 +190,34 @@ class SPMotionStep:
         self.comm.allgather_partials(part, self.part_off)
 
     def push(self, partials_all: Optional[torch.Tensor] = None):
-        """partials_all: the ranks' partials concatenated along dim 1 (rank order); None = the
-        block `share_partials` of all ranks filled in this rank's buffer."""
+        """Fused form (GroupNorm applied on the way out): needs the ranks' partials first.
+        partials_all: the ranks' partials concatenated along dim 1 (rank order); None = the block
+        `share_partials` of all ranks filled in this rank's buffer."""
         if partials_all is None:
             partials_all = self.comm.view(self.part_off, self._part_shape, torch.float32)
         mean, rstd = ops.groupnorm5d_finalize(partials_all, self.tt.norm.eps)
         n = self.tt.norm
         self.comm.frames_to_hw(self.x5, self.f_total, 0, (mean, rstd, n.weight.detach(), n.bias.detach(), self.tt.groups))
+
+    def push_raw(self):
+        """This rank's frames, un-normalised, into the token buffers of the position owners (peer
+        stores).  Together with share_partials it needs ONE barrier before normalize()."""
+        self.comm.frames_to_hw(self.x5, self.f_total, 0, None)
+
+    def normalize(self, partials_all: Optional[torch.Tensor] = None):
+        """GroupNorm on the received tokens, in place (same coefficients / rounding as the fused
+        apply + rearrange: bit-identical tokens)."""
+        if partials_all is None:
+            partials_all = self.comm.view(self.part_off, self._part_shape, torch.float32)
+        mean, rstd = ops.groupnorm5d_finalize(partials_all, self.tt.norm.eps)
+        n = self.tt.norm
+        c = self.geom[0]
+        tok = self.comm.view(0, (self.n_local * self.f_total, c))
+        gamma, beta = n.weight.detach(), n.bias.detach()
+        check(lib.vst_groupnorm_tokens_apply(tok.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gamma.data_ptr(),
+                                             beta.data_ptr(), self.b, (self.n_local // self.b) * self.f_total, c,
+                                             self.tt.groups, ops._dt(gamma), torch.cuda.current_stream().cuda_stream),
+              "vst_groupnorm_tokens_apply")
 
     def compute(self):
         from ._host import bf16_cached
@@ -225,12 +248,14 @@ def motion_module_sp(module, comm: SPComm, x_local: torch.Tensor, f_total: int, 
     """Inference forward of one motion module with the video's frames sharded over the ranks of
     `comm`.  Graph-capturable: only kernels of this library, on the current stream."""
     step = SPMotionStep(module, comm, x_local, f_total)
-    step.share_partials()                                          # (B*groups, nparts, 3) fp32 -> peers
-    comm.barrier()
-    step.push()
-    comm.barrier()
+    step.share_partials()          # (B*groups, nparts, 3) fp32 -> every peer
+    step.push_raw()                # raw tokens -> position owners (peer stores over NVLink)
+    comm.barrier()                 # 1: partials and tokens of every rank have landed here
+    step.normalize()
     step.compute()
-    comm.barrier()
-    out = step.pull()
-    comm.barrier()        # peers are done reading our send region before the next module overwrites it
-    return out
+    comm.barrier()                 # 2: every rank's send region is complete
+    return step.pull()
+    # No trailing barrier: a rank next writes its send region (or a peer's token / partial region) only
+    # after barrier 1 of the NEXT module, which every rank reaches only after this pull has finished on
+    # its own stream; and no rank passes barrier 2 before all have finished compute(), so the token
+    # buffer is never overwritten while its owner still reads it.
