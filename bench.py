@@ -46,6 +46,9 @@ def parse():
     ap.add_argument("--cfg-mode", default="batched", choices=["batched", "two-pass"],
                     help="batched: uncond|cond as one B=2 pass (default); two-pass: the reference's two B=1 calls")
     ap.add_argument("--no-sp", action="store_true", help="skip the sequence-parallel probe at N>1")
+    ap.add_argument("--with-spatial-ff", action="store_true",
+                    help="secondary line: every spatial transformer block in full (LayerNorms + GEGLU feed-forward "
+                         "around the two attentions, SURVEY.md §8f-1) instead of the attention processors alone")
     ap.add_argument("--ncu-step", action="store_true",
                     help="warm up, then run ONE step between cudaProfilerStart/Stop and exit "
                          "(for `ncu --profile-from-start off`; prints no bench line)")
@@ -389,7 +392,7 @@ def run_ours(args):
 
     torch.manual_seed(1234 + rank)
     with torch.device(dev):
-        model = hpth.SDXLHotPath(temporal_rank=32, depth_scale=args.depth_scale)
+        model = hpth.SDXLHotPath(temporal_rank=32, depth_scale=args.depth_scale, spatial_ff=args.with_spatial_ff)
     model = model.to(bf).eval()
     plan = model.forward_plan()
     shapes = hpth.level_shapes(F, S, batch=nb)
@@ -528,6 +531,10 @@ def run_ours(args):
     if rank != 0:
         return
     cfg = common_config(F, S, world)
+    if args.with_spatial_ff:
+        cfg["workload"] = "cfg3-hotpath+spatial-ff"
+        cfg["modules_per_unet_call"] = {"spatial_transformer_block (LN, self-attn, LN, cross-attn, LN, GEGLU FF)": 70,
+                                        "motion": 15}
     line = {
         "metric": METRIC, "value": world * 1e3 / ms_step, "unit": "steps/s", "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,

@@ -122,6 +122,25 @@ def stage1_attn_processor(p: SpatialAttnParams, hidden_states, ehs=None, ehs_con
     return o / p.rescale_output_factor                                   # :757
 
 
+def basic_transformer_block(p1: SpatialAttnParams, p2: SpatialAttnParams, w: Dict[str, torch.Tensor],
+                            hidden_states, encoder_hidden_states=None, scale: float = 1.0):
+    """Spatial BasicTransformerBlock.forward for SDXL (norm_type "layer_norm", GEGLU feed-forward).
+    unziplora_unet/unzip_attention.py:113-239: h = attn1(norm1(h)) + h (:128-166);
+    h = attn2(norm2(h), text) + h (:176-203); h = ff(norm3(h)) + h (:206-235).  The class subclasses
+    diffusers' block (un-vendored), so the wrapper itself cannot be imported here: PARITY UNPINNED for
+    the composition, every piece is pinned (processor: tests/golden/attn_processor.npz; LayerNorm / GELU:
+    tests/test_cpu.py against torch.nn.functional; GEGLU = hidden * gelu(gate), diffusers recalled).
+    ``w``: norm{1,2,3}.{weight,bias}, ff.net.0.proj.{weight,bias}, ff.net.2.{weight,bias}."""
+    h = hidden_states
+    h = animatediff_attn_processor(p1, hp.layernorm(h, w["norm1.weight"], w["norm1.bias"]), None, scale=scale) + h
+    h = animatediff_attn_processor(p2, hp.layernorm(h, w["norm2.weight"], w["norm2.bias"]),
+                                   encoder_hidden_states, scale=scale) + h
+    hn = hp.layernorm(h, w["norm3.weight"], w["norm3.bias"])
+    hg = hn @ w["ff.net.0.proj.weight"].t() + w["ff.net.0.proj.bias"]
+    hid, gate = hg.chunk(2, dim=-1)
+    return (hid * hp.gelu(gate)) @ w["ff.net.2.weight"].t() + w["ff.net.2.bias"] + h
+
+
 # --------------------------------------------------------------------------------------
 # Motion block (diffusers TransformerTemporalModel, un-vendored: recalled, PARITY UNPINNED)
 # --------------------------------------------------------------------------------------

@@ -514,3 +514,85 @@ def test_batched_cfg_equals_two_pass_and_graph_set_text():
     assert not torch.equal(got[2], both[2]) and not torch.equal(got[1], both[1])
     for a, b in zip(got, want):
         assert torch.equal(a, b)
+
+
+# ---- §8f-1, spatial half: the full BasicTransformerBlock ----------------------------------------------------
+def _block_and_oracle(c, heads, ctx, rank, train=False):
+    from video_style_transfer_b200.unziplora_unet.unzip_attention import BasicTransformerBlock
+    from video_style_transfer_b200 import sdxl_hotpath as hpth
+
+    class _A(torch.nn.Module):                       # diffusers-protocol Attention duck type as an nn.Module
+        def __init__(self, ns):
+            super().__init__()
+            self.__dict__.update({k: v for k, v in vars(ns).items() if not isinstance(v, torch.nn.Module)})
+            self.to_q, self.to_k, self.to_v, self.to_out = ns.to_q, ns.to_k, ns.to_v, ns.to_out
+            self.processor = None
+
+        def forward(self, x, encoder_hidden_states=None, **kw):
+            from video_style_transfer_b200.animatediff.attention_processor import AnimateDiffAttnProcessor2_0
+            if self.processor is None:
+                self.processor = AnimateDiffAttnProcessor2_0()
+            return self.processor(self, x, encoder_hidden_states=encoder_hidden_states, **kw)
+
+    a1, a2 = make_attn(c, heads, c, rank, train=train), make_attn(c, heads, ctx, rank, train=train)
+    blk = BasicTransformerBlock(c, heads, 64, cross_attention_dim=ctx, attn1=_A(a1), attn2=_A(a2))
+    with torch.no_grad():
+        for n, p in blk.named_parameters():
+            if n.startswith("norm") or (n.startswith("ff") and n.endswith("bias")):
+                p.add_(0.1 * torch.randn_like(p))
+    return blk, a1, a2
+
+
+def _block_weights(blk, grad=False):
+    return {k: v.detach().float().cpu().clone().requires_grad_(grad)
+            for k, v in blk.named_parameters() if k.startswith(("norm", "ff."))}
+
+
+def test_spatial_transformer_block_vs_oracle_l2_geometry():
+    """SDXL L2 spatial BasicTransformerBlock (unzip_attention.py:113-239: LN -> self-attn -> +h; LN ->
+    text cross-attn -> +h; LN -> GEGLU FF -> +h) at C=1280, 20 heads, 1024 tokens, 4 frames, text
+    (1, 77, 2048), UnZipLoRA rank 64, against the fp32 oracle."""
+    from oracle import processor as op
+    torch.manual_seed(21)
+    C, heads, ctx = 1280, 20, 2048
+    blk, a1, a2 = _block_and_oracle(C, heads, ctx, 64)
+    x, text = torch.randn(4, 1024, C), torch.randn(1, 77, ctx)
+    want = op.basic_transformer_block(oracle_attn(a1), oracle_attn(a2), _block_weights(blk), x, text)
+    blk = blk.cuda().to(bf)
+    with torch.no_grad():
+        y = blk(x.cuda().to(bf), encoder_hidden_states=text.cuda().to(bf))
+    assert y.shape == x.shape and y.dtype == bf
+    assert rel(y, want) < 2e-2
+    assert torch.nn.functional.cosine_similarity(y.float().cpu().flatten(), want.flatten(), dim=0) > 0.9999
+
+
+def test_spatial_transformer_block_backward_vs_oracle():
+    """Gradients of the full block (input, text, LayerNorm / FF parameters, UnZipLoRA A / B / mergers) against
+    fp32 autograd of the oracle at a size the CPU differentiates in seconds."""
+    from oracle import processor as op
+    torch.manual_seed(22)
+    C, heads, ctx = 320, 5, 256
+    blk, a1, a2 = _block_and_oracle(C, heads, ctx, 16, train=True)
+    x, text = torch.randn(3, 200, C).to(bf), torch.randn(1, 77, ctx).to(bf)
+    dy = (torch.randn(3, 200, C) * 0.1).to(bf)
+    P1, P2 = oracle_attn(a1, grad=True, infer=False), oracle_attn(a2, grad=True, infer=False)
+    w = _block_weights(blk, grad=True)
+    xr, tr = x.float().requires_grad_(True), text.float().requires_grad_(True)
+    want = op.basic_transformer_block(P1, P2, w, xr, tr)
+    want.backward(dy.float())
+    blk = blk.cuda()
+    xd, td = x.cuda().requires_grad_(True), text.cuda().requires_grad_(True)
+    y = blk(xd, encoder_hidden_states=td)
+    assert rel(y, want.detach()) < 2e-2
+    y.backward(dy.cuda())
+    assert rel(xd.grad, xr.grad) < 3e-2 and rel(td.grad, tr.grad) < 3e-2
+    got = dict(blk.named_parameters())
+    for k, v in w.items():
+        if v.requires_grad:
+            assert rel(got[k].grad, v.grad) < 3e-2, k
+    for attn, P in ((a1, P1), (a2, P2)):
+        for n, pr in zip(("to_q", "to_k", "to_v", "to_out"), (P.to_q, P.to_k, P.to_v, P.to_out)):
+            lay = attn_linears(attn)[n].lora_layer
+            assert rel(lay.merge_content.grad, pr.m_c.grad) < 3e-2, n
+            assert rel(lay.lora_matrix_dic["style_up"].weight.grad, pr.b_s.grad) < 3e-2, n
+            assert rel(lay.lora_matrix_dic["content_down"].weight.grad, pr.a_c.grad) < 3e-2, n

@@ -77,6 +77,8 @@ def text_kv(attn, text: torch.Tensor, scale: float):
 
 
 class AnimateDiffAttnProcessor2_0:
+    fuses_residual = True        # honours the `fused_residual` kwarg (see __call__)
+
     def __init__(self):
         if not torch.cuda.is_available():
             raise ImportError("AnimateDiffAttnProcessor2_0 (B200) requires a CUDA device; "
@@ -93,6 +95,11 @@ class AnimateDiffAttnProcessor2_0:
                  encoder_hidden_states: Optional[torch.Tensor] = None,
                  attention_mask: Optional[torch.Tensor] = None,
                  temb: Optional[torch.Tensor] = None, scale: float = 1.0, **kwargs) -> torch.Tensor:
+        # Extension of the reference protocol (unknown kwargs are swallowed there, :26): a caller that
+        # adds its own residual right after the attention (BasicTransformerBlock: `attn(norm(h)) + h`,
+        # unzip_attention.py:166,203) may hand it over as `fused_residual`; it rides in the to_out
+        # GEMM's epilogue instead of costing a pass of its own.
+        fused_residual = kwargs.pop("fused_residual", None)
         residual = hidden_states
         in_dtype = hidden_states.dtype
         if attn.spatial_norm is not None:
@@ -137,6 +144,15 @@ class AnimateDiffAttnProcessor2_0:
         fuse_res = (attn.residual_connection and input_ndim == 3 and residual.dtype == torch.bfloat16
                     and residual.is_contiguous() and drop_id)
         res2 = residual.view(batch_size * seq_q, -1) if fuse_res else None
+        extra = None
+        if fused_residual is not None:
+            ok = (input_ndim == 3 and not attn.residual_connection and drop_id and attn.rescale_output_factor == 1.0
+                  and fused_residual.dtype == torch.bfloat16 and fused_residual.is_contiguous()
+                  and fused_residual.shape == hidden_states.shape)
+            if ok:
+                res2 = fused_residual.view(batch_size * seq_q, -1)
+            else:
+                extra = fused_residual
         post = 1.0 / float(attn.rescale_output_factor)
         y = self._proj(attn.to_out[0], o2, lora_scale, residual=res2,
                        out_scale=post if (fuse_res or (not attn.residual_connection and drop_id)) else 1.0)
@@ -148,4 +164,6 @@ class AnimateDiffAttnProcessor2_0:
             y = (y + residual) * post
         elif not attn.residual_connection and not drop_id:
             y = y * post
+        if extra is not None:
+            y = y + extra.to(y.dtype)
         return y

@@ -68,18 +68,27 @@ class _Block(nn.Module):
         self.attn2 = SpatialAttention(dim, heads, TEXT_DIM)
 
 
+def _full_block(dim, heads):
+    """The whole spatial BasicTransformerBlock (LayerNorms + GEGLU feed-forward around the two
+    attentions; unziplora_unet/unzip_attention.py:113-239)."""
+    from .unziplora_unet.unzip_attention import BasicTransformerBlock
+    return BasicTransformerBlock(dim, heads, 64, cross_attention_dim=TEXT_DIM,
+                                 attn1=SpatialAttention(dim, heads), attn2=SpatialAttention(dim, heads, TEXT_DIM))
+
+
 class _Transformer2D(nn.Module):
-    def __init__(self, dim, heads, depth):
+    def __init__(self, dim, heads, depth, spatial_ff=False):
         super().__init__()
-        self.transformer_blocks = nn.ModuleList([_Block(dim, heads) for _ in range(depth)])
+        mk = _full_block if spatial_ff else _Block
+        self.transformer_blocks = nn.ModuleList([mk(dim, heads) for _ in range(depth)])
 
 
 class _UNetBlock(nn.Module):
-    def __init__(self, dim, n_attn, depth, n_motion):
+    def __init__(self, dim, n_attn, depth, n_motion, spatial_ff=False):
         super().__init__()
         self.dim = dim
         if n_attn:
-            self.attentions = nn.ModuleList([_Transformer2D(dim, dim // 64, depth)
+            self.attentions = nn.ModuleList([_Transformer2D(dim, dim // 64, depth, spatial_ff)
                                              for _ in range(n_attn)])
         if n_motion:
             self.motion_modules = nn.ModuleList([MotionModule(dim, 8) for _ in range(n_motion)])
@@ -88,14 +97,16 @@ class _UNetBlock(nn.Module):
 class SDXLHotPath(nn.Module):
     """levels: (C, latent-side divisor).  ``forward_plan()`` lists the modules in UNet order."""
 
-    def __init__(self, temporal_rank: int = 32, depth_scale: float = 1.0):
+    def __init__(self, temporal_rank: int = 32, depth_scale: float = 1.0, spatial_ff: bool = False):
+        """spatial_ff: build every spatial transformer block in full (norm1/2/3 + GEGLU ff around the two
+        attentions); the plan then lists ("block", level, module) entries."""
         super().__init__()
+        self.spatial_ff = spatial_ff
         d2, d10 = max(1, round(2 * depth_scale)), max(1, round(10 * depth_scale))
-        self.down_blocks = nn.ModuleList([_UNetBlock(320, 0, 0, 2), _UNetBlock(640, 2, d2, 2),
-                                          _UNetBlock(1280, 2, d10, 2)])
-        self.mid_block = _UNetBlock(1280, 1, d10, 0)
-        self.up_blocks = nn.ModuleList([_UNetBlock(1280, 3, d10, 3), _UNetBlock(640, 3, d2, 3),
-                                        _UNetBlock(320, 0, 0, 3)])
+        U = lambda *a: _UNetBlock(*a, spatial_ff=spatial_ff)
+        self.down_blocks = nn.ModuleList([U(320, 0, 0, 2), U(640, 2, d2, 2), U(1280, 2, d10, 2)])
+        self.mid_block = U(1280, 1, d10, 0)
+        self.up_blocks = nn.ModuleList([U(1280, 3, d10, 3), U(640, 3, d2, 3), U(320, 0, 0, 3)])
         self.n_temporal_lora = inject_temporal_lora(self, rank=temporal_rank, alpha=1.0)
         with torch.no_grad():      # B = 0 at init would make the low-rank update a no-op
             for n, p in self.named_parameters():
@@ -117,8 +128,11 @@ class SDXLHotPath(nn.Module):
             for i in range(max(len(attns), len(motions))):
                 if i < len(attns):
                     for tb in attns[i].transformer_blocks:
-                        plan.append(("self", lvl, tb.attn1))
-                        plan.append(("cross", lvl, tb.attn2))
+                        if self.spatial_ff:
+                            plan.append(("block", lvl, tb))
+                        else:
+                            plan.append(("self", lvl, tb.attn1))
+                            plan.append(("cross", lvl, tb.attn2))
                 if i < len(motions):
                     plan.append(("motion", lvl, motions[i]))
         return plan
@@ -140,7 +154,7 @@ def run_unet_hotpath(plan, xs4, xs3, text, frames: int):
     for kind, lvl, mod in plan:
         if kind == "self":
             outs[lvl] = mod(xs3[lvl])
-        elif kind == "cross":
+        elif kind in ("cross", "block"):
             outs[lvl] = mod(xs3[lvl], encoder_hidden_states=text)
         else:
             outs[lvl] = mod(xs4[lvl], num_frames=frames)
@@ -197,9 +211,9 @@ class GraphedDenoiseStep:
         for dst, src in zip(self.texts, texts):
             dst.copy_(src, non_blocking=True)
         for kind, _, mod in self.plan:
-            if kind == "cross":
+            if kind in ("cross", "block"):
                 for t in self.texts:
-                    text_kv(mod, t, 1.0)
+                    text_kv(mod.attn2 if kind == "block" else mod, t, 1.0)
 
     def replay(self):
         self.graph.replay()
@@ -288,7 +302,7 @@ def run_unet_hotpath_sp(plan, xs4_local, xs3_local, text, f_total: int, comm, gr
     for kind, lvl, mod in plan:
         if kind == "self":
             outs[lvl] = mod(xs3_local[lvl])
-        elif kind == "cross":
+        elif kind in ("cross", "block"):
             outs[lvl] = mod(xs3_local[lvl], encoder_hidden_states=text)
         else:
             outs[lvl] = motion_module_sp(mod, comm, xs4_local[lvl], f_total, group)
@@ -329,7 +343,7 @@ def train_step_hotpath(model, plan, xs4, xs3, text, upstream, frames: int, optim
     for kind, lvl, mod in plan:
         if kind == "self":
             y = mod(x3[lvl])
-        elif kind == "cross":
+        elif kind in ("cross", "block"):
             y = mod(x3[lvl], encoder_hidden_states=text)
         else:
             y = mod(x4[lvl], num_frames=frames)
@@ -359,16 +373,19 @@ def hotpath_flops(plan, frames: int, latent: int = 128, batch: int = 1, merged: 
         m = batch * frames * hw
         r2 = 0 if merged else 128
         rt = 0 if merged else 32
-        if kind == "self":
+        if kind == "block":                  # self + cross + LN/FF of one spatial transformer block
+            fl.setdefault("spatial_ff", 0.0)
+            fl["spatial_ff"] += 2.0 * m * c * 8 * c + 2.0 * m * 4 * c * c
+        if kind in ("self", "block"):
             fl["attn_self"] += 4.0 * batch * frames * hw * hw * c
             fl["proj"] += 4 * (2.0 * m * c * c + 2.0 * m * r2 * (c + c))
-        elif kind == "cross":
+        if kind in ("cross", "block"):
             fl["attn_cross"] += 4.0 * batch * frames * hw * TEXT_LEN * c
             mt = batch * TEXT_LEN
             fl["proj"] += 2 * (2.0 * m * c * c + 2.0 * m * r2 * 2 * c)
             if not text_kv_cached:       # once per prompt, not per step (attention_processor.text_kv)
                 fl["proj"] += 2 * (2.0 * mt * TEXT_DIM * c + 2.0 * mt * r2 * (TEXT_DIM + c))
-        else:
+        if kind == "motion":
             n = batch * hw
             fl["temporal_attn"] += 2 * 4.0 * n * frames * frames * c
             fl["motion_gemm"] += 2.0 * m * c * c * 2                       # proj_in, proj_out
