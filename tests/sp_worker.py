@@ -17,7 +17,9 @@ def main():
     from tests.test_sp_gpu import _module
     from video_style_transfer_b200.sequence_parallel import SPComm, SPMotionStep, motion_module_sp
     worst = 0.0
-    for c, hw, f in ((320, 32, 16), (640, 16, 32)):
+    # the fused all-to-all kernels move 64-position tiles: HW must be a multiple of world x 64 (SDXL levels:
+    # 16384 / 4096 / 1024 positions, fine up to 8 ranks)
+    for c, hw, f in ((320, 32, 16), (640, 32 if world > 4 else 16, 32)):
         mm = _module(c)
         g = torch.Generator(device="cuda").manual_seed(1234)
         x = torch.randn(f, c, hw, hw, device="cuda", generator=g).to(torch.bfloat16)

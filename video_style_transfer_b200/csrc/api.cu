@@ -175,6 +175,13 @@ int vst_make_tmap(CUtensorMap* out, const void* base, int rank, const uint64_t* 
   CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base),
                    d, s, b, es, CU_TENSOR_MAP_INTERLEAVE_NONE, swz, l2,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r == CUDA_ERROR_INVALID_CONTEXT) {
+    // a thread that has made no runtime call yet (torch's autograd worker entering a backward whose first
+    // device action is this driver call) has no current context: bind the primary one and retry
+    cudaFree(0);
+    r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), d, s, b, es,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, swz, l2, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
   VST_REQUIRE(r == CUDA_SUCCESS, VST_E_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d",
               (int)r);
   return VST_OK;
