@@ -131,6 +131,25 @@ int vst_lora_gemm(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, in
  * kernel with 256 x BN tiles, 0: 128 x BN tiles), or VST_E_UNSUPPORTED.  Host-only, launches nothing;
  * bench.py uses it to attribute event-timed launches to the dominant kernel. */
 int vst_lora_gemm_plan(int64_t M, int N, int K2, int k2_group_n, int act);
+/* ---- the single-launch fused LoRA projection (north_star: "ONE fused GEMM") ---------------------------
+ * D[M,N] = act(X[M,K1] W[N,K1]^T + (X A_down^T) Bp^T + bias) * out_scale with u = X A_down^T computed INSIDE the
+ * kernel, once per (256-row tile, projection group): a leading tcgen05 MMA into a spare accumulator stage, bf16
+ * into shared memory as the A operand of the K2 extra k-blocks.  No second launch, no u round trip through HBM.
+ * unziplora_linear_layer.py:221-263, 298-346 + lora_linear.py:74-81 (A_down = [A_c ; A_s] (K2, K1), Bp = packed
+ * scale * [m_c.mask_c.B_c | m_s.mask_s.B_s] (N, K2)); temporal_lora.py:29-32; grouped along N (k2_group_n) for
+ * q|k|v: A_down is then (G*K2, K1) and output columns of group g use rows [g*K2, (g+1)*K2).
+ * U_out (optional, bf16 [M, G*K2], row stride ldu): u is also written out for the backward.
+ * Shapes: vst_lora_gemm_fused_supported(...) != 0 (M >= 2048, K2 in {64, 128}, group width a multiple of the tile
+ * width it returns); otherwise VST_E_UNSUPPORTED and the caller uses vst_lora_gemm twice.  bf16 output. */
+int vst_lora_gemm_fused_supported(int64_t M, int N, int K1, int K2, int k2_group_n);
+int vst_lora_gemm_fused(const void* X, int64_t ldx, const void* W, int64_t ldw, int K1, const void* A_down,
+                        int64_t lda, const void* Bp, int64_t ldbp, int K2, int k2_group_n, const void* bias,
+                        int bias_dtype, float out_scale, int act, void* U_out, int64_t ldu, void* D, int64_t ldd,
+                        int64_t M, int N, void* stream);
+/* A'[br * rp + j, :] = A_br[j, :] as bf16 (rows j in [r, rp) zero): the down-projections of up to two branches
+ * stacked for vst_lora_gemm_fused / the u = x A^T pre-pass.  unziplora_linear_layer.py:311,319 ({key}_down). */
+int vst_lora_pack_down(const void* Ac, const void* As, void* out, int r, int rp, int K, int param_dtype,
+                       void* stream);
 /* B2'[n, j] = scale * m[n] * mask[n] * B[n, j] for up to two branches packed side by side
  * (columns [0,r) content, [r,2r) style); m/mask may be NULL (=1).  unziplora_linear_layer.py
  * :313,:321 (merger), :236-237 (hard mask), lora_linear.py:81 (scale). */
@@ -163,11 +182,19 @@ int vst_lora_pack_up_bwd(const float* dBp, int64_t ld, int rp, const void* Bc, c
                          const uint8_t* maskc, const void* Bs, const void* ms,
                          const uint8_t* masks, float scale, float* dBc, float* dmc, float* dBs,
                          float* dms, int N, int r, int param_dtype, void* stream);
-/* ---- SURVEY.md §8b names of one LoRA linear: forward / dX / parameter gradients -----------------
- * vst_lora_gemm_fwd is vst_lora_gemm (same arguments).  The two backward calls are the arithmetic
- * torch autograd derives for lora_linear.py:74-81 + unziplora_linear_layer.py:221-263, 298-346,
- * lora_unzip.py:66-75 and temporal_lora.py:29-32 (the reference trains through autograd,
- * train_animatediff.py:314), expressed on the fused operands of the forward:
+/* ---- one LoRA linear at MODULE level (raw parameters in): forward / dX / parameter gradients ----
+ * vst_lora_gemm_fwd:  y = (x W^T + bias + u B'^T + residual) * out_scale,  u = [x_c A_c^T | x_s A_s^T],
+ *   B' = scale * [m_c.mask_c.B_c | m_s.mask_s.B_s]  (lora_linear.py:74-81, lora_unzip.py:66-75,
+ *   unziplora_linear_layer.py:221-263, 298-346).  x_c / x_s NULL = x (single stream); a block-masked branch
+ *   (:308,:316) is passed as A = NULL; mask_* are the hard column masks of the training layer (:236-237) or
+ *   NULL; mode VST_LORA_CONTENT / _STYLE run one branch without its merger (:324-345).  A_* (rank, Klow),
+ *   B_* (N, rank), m_* (N) in param_dtype; rank a multiple of 8.  u is computed INSIDE the main kernel
+ *   (vst_lora_gemm_fused) when the streams coincide and the shape is a fused one, by a pre-pass otherwise, and
+ *   written to u_out (bf16 [M, branches*rank]) when given -- vst_lora_gemm_bwd_params needs it.
+ *   workspace: vst_lora_gemm_fwd_workspace_bytes(M, N, Klow, rank, branches, u_out != NULL), 256-byte aligned
+ *   (packed bf16 A', B' and, without u_out, u).
+ * The two backward calls are the arithmetic torch autograd derives for the same modules (the reference
+ * trains through autograd, train_animatediff.py:314), expressed on the fused operands of the forward:
  *   y = x W^T + u B'^T,  u = x_low A^T,  A = [A_c ; A_s] (R, Klow),  B' = vst_lora_pack_up (N, R).
  * vst_lora_gemm_bwd_dx:     dU[M,R] = dY B' (bf16, kept for bwd_params) and
  *                           dX[M,K] (+)= alpha (dY W + dU A)  -- A is added only when the adapter read
@@ -178,11 +205,17 @@ int vst_lora_pack_up_bwd(const float* dBp, int64_t ld, int rp, const void* Bc, c
  *                           row-major, any may be NULL; contraction over the M tokens, deterministic
  *                           split-K through `workspace`).  dB_c / dB_s / d-merger follow from dB' by
  *                           vst_lora_pack_up_bwd.  Xlow NULL = X. */
-int vst_lora_gemm_fwd(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1,
-                      const void* A2, int64_t lda2, const void* B2, int64_t ldb2, int K2,
-                      int k2_group_n, const void* bias, int bias_dtype, const void* residual, int64_t ldr,
-                      float out_scale, int act, void* D, int64_t ldd, int64_t M, int N,
-                      int out_dtype, void* stream);
+#define VST_LORA_BOTH 0
+#define VST_LORA_CONTENT 1
+#define VST_LORA_STYLE 2
+int64_t vst_lora_gemm_fwd_workspace_bytes(int64_t M, int N, int Klow, int rank, int branches, int have_u_out);
+int vst_lora_gemm_fwd(const void* x, int64_t ldx, const void* x_c, int64_t ldxc, const void* x_s, int64_t ldxs,
+                      const void* W, int64_t ldw, const void* bias, int bias_dtype, const void* A_c,
+                      const void* B_c, const void* m_c, const uint8_t* mask_c, const void* A_s, const void* B_s,
+                      const void* m_s, const uint8_t* mask_s, int rank, int param_dtype, float scale, int mode,
+                      const void* residual, int64_t ldr, float out_scale, void* u_out, int64_t ldu, void* D,
+                      int64_t ldd, int64_t M, int N, int K, int Klow, int out_dtype, void* workspace,
+                      int64_t workspace_bytes, void* stream);
 int vst_lora_gemm_bwd_dx(const void* dY, int64_t lddy, const void* W, int64_t ldw, const void* Bp,
                          int64_t ldbp, const void* A, int64_t lda, int R, void* dU, int64_t lddu,
                          void* dX, int64_t lddx, int64_t M, int N, int K, float alpha, int accumulate,

@@ -116,6 +116,26 @@ def main():
             report(f"lora_gemm {tag}", ms, b, None, 2 * m * n * (k1 + k2))
             ms, b = timeit(lambda: torch.nn.functional.linear(a1, b1, bias))
             report(f"  (cuBLAS F.linear, K1 only) {tag}", ms, b, None, 2 * m * n * k1)
+    if "fused" in which:
+        # single-launch fused LoRA projection against the two-launch form (u = x A^T pre-pass + extra K blocks)
+        # and against the plain GEMM with the adapters folded into W
+        for tag, m, n, k1, k2, gn in [("L2 q|k|v M=32768 C=1280 r=64x2", 32768, 3840, 1280, 128, 1280),
+                                      ("L2 to_q   M=32768 C=1280 r=64x2", 32768, 1280, 1280, 128, 0),
+                                      ("L1 q|k|v M=131072 C=640 r=64x2", 131072, 1920, 640, 128, 640),
+                                      ("L1 to_q   M=131072 C=640 r=64x2", 131072, 640, 640, 128, 0),
+                                      ("L2 q|k|v M=16384 (two-pass CFG)", 16384, 3840, 1280, 128, 1280)]:
+            g = n // gn if gn else 1
+            x = torch.randn(m, k1, device="cuda").to(torch.bfloat16)
+            w = (torch.randn(n, k1, device="cuda") / math.sqrt(k1)).to(torch.bfloat16)
+            a = (torch.randn(g * k2, k1, device="cuda") / math.sqrt(k1)).to(torch.bfloat16)
+            bp = (torch.randn(n, k2, device="cuda") / math.sqrt(k2)).to(torch.bfloat16)
+            fl = 2 * m * n * (k1 + k2) + 2 * m * g * k2 * k1
+            ms, b = timeit(lambda: ops.lora_gemm_fused(x, w, a, bp, None, 1.0, gn))
+            report(f"lora_gemm_fused {tag}", ms, b, None, fl)
+            ms, b = timeit(lambda: ops.lora_gemm(x, w, ops.lora_gemm(x, a), bp, k2_group_n=gn))
+            report(f"  (two launches) {tag}", ms, b, None, fl)
+            ms, b = timeit(lambda: ops.lora_gemm(x, w))
+            report(f"  (folded: plain GEMM) {tag}", ms, b, None, 2 * m * n * k1)
     if "gemmres" in which:
         # memory-bound GEMMs with a fused residual add (motion-module to_out / FF2, spatial to_out)
         for tag, m, n, k in [("L0 to_out +res M=262144 320x320", 262144, 320, 320),

@@ -239,7 +239,7 @@ def test_attn_bwd_packed_qkv_views(ops):
 # ---- a8 / K9 / §8f-1 / a10 backward kernels vs fp32 autograd --------------------------------------------
 
 
-@pytest.mark.parametrize("m,n,k,r", [(300, 136, 72, 16), (1024, 640, 640, 128), (77, 64, 2048, 0)])
+@pytest.mark.parametrize("m,n,k,r", [(300, 136, 72, 16), (1024, 640, 640, 128), (77, 64, 2048, 0), (4096, 640, 640, 64)])
 def test_lora_linear_c_abi_fwd_bwd(m, n, k, r):
     """SURVEY §8b names: vst_lora_gemm_fwd, vst_lora_gemm_bwd_dx, vst_lora_gemm_bwd_params called raw
     through ctypes, against fp32 autograd of y = x W^T + (x A^T) B'^T on the same bf16 operands."""
@@ -253,14 +253,15 @@ def test_lora_linear_c_abi_fwd_bwd(m, n, k, r):
     bp = bf(n, r, sc=r ** -0.5) if r else None
     st = torch.cuda.current_stream().cuda_stream
     P = lambda t: 0 if t is None else t.data_ptr()
-    # forward: u = x A^T, y = x W^T + u B'^T
+    # forward through the MODULE-level entry: raw A / B in, u saved for the backward (one branch, no merger,
+    # bf16 parameters so the packed operands are A and B themselves)
     u = torch.empty(m, r, dtype=torch.bfloat16, device=dev) if r else None
-    if r:
-        _lib.check(lib.vst_lora_gemm_fwd(P(x), k, P(a), k, k, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 1.0, 0, P(u), r, m, r, 1, st),
-                   "u")
     y = torch.empty(m, n, dtype=torch.bfloat16, device=dev)
-    _lib.check(lib.vst_lora_gemm_fwd(P(x), k, P(w), k, k, P(u), r, P(bp), r, r, 0, 0, 0, 0, 0, 1.0, 0, P(y), n, m, n,
-                                     1, st), "y")
+    wsb = lib.vst_lora_gemm_fwd_workspace_bytes(m, n, k, max(r, 8), 1, 1)
+    wsf = torch.empty(wsb + 256, dtype=torch.uint8, device=dev)
+    wsp = wsf.data_ptr() + (-wsf.data_ptr()) % 256
+    _lib.check(lib.vst_lora_gemm_fwd(P(x), k, 0, 0, 0, 0, P(w), k, 0, 0, P(a), P(bp), 0, 0, 0, 0, 0, 0, r, 1, 1.0, 0,
+                                     0, 0, 1.0, P(u), r, P(y), n, m, n, k, k, 1, wsp, wsb, st), "vst_lora_gemm_fwd")
     # fp32 reference
     xf, wf = x.float().requires_grad_(True), w.float().requires_grad_(True)
     af = a.float().requires_grad_(True) if r else None
@@ -512,3 +513,54 @@ def test_temporal_transformer_fwd_bwd_vs_reference_golden_weights():
     _close(xd.grad, xr.grad, "dx", 3e-2)
     for k, p in m.named_parameters():
         _close(p.grad, ref_grads[k], k, 3e-2)
+
+
+@pytest.mark.parametrize("m", [200, 4096])
+@pytest.mark.parametrize("mode,three", [(0, False), (0, True), (1, False), (2, True)])
+def test_lora_gemm_fwd_module_level_vs_oracle(m, mode, three):
+    """vst_lora_gemm_fwd from RAW parameters (fp32 A / B / mergers, hard column masks, scale, forward type,
+    one or three activation streams) against the oracle's UnZipLoRALinearLayer + LoRACompatibleLinear
+    (unziplora_linear_layer.py:221-263, lora_unzip.py:66-75).  m = 4096 single-stream takes the single-launch
+    kernel, the rest the pre-pass form; u_out is what the backward consumes."""
+    from oracle import hotpath as hp
+    from video_style_transfer_b200 import _lib
+    lib = _lib.lib
+    torch.manual_seed(m + 10 * mode + three)
+    n, k, r = 640, 640, 64
+    f32 = lambda *s_, sc=1.0: (torch.randn(*s_) * sc)
+    x, x1, x2 = (f32(m, k).to(torch.bfloat16) for _ in range(3))
+    w, bias = f32(n, k, sc=k ** -0.5).to(torch.bfloat16), f32(n)
+    a_c, b_c, a_s, b_s = f32(r, k, sc=1 / r), f32(n, r, sc=1 / r), f32(r, k, sc=1 / r), f32(n, r, sc=1 / r)
+    m_c, m_s = torch.rand(n), torch.rand(n)
+    mk_c, mk_s = torch.rand(n) > 0.3, torch.rand(n) > 0.3
+    ft = ("both", "content", "style")[mode]
+    xc, xs = (x1, x2) if three else (x, x)
+    delta = hp.unziplora_delta(xc.float(), xs.float(), a_c, b_c, a_s, b_s, m_c, m_s, ft, True, True, infer=False,
+                               mask_c=mk_c, mask_s=mk_s)
+    want = hp.lora_compatible_linear(x.float(), w.float(), bias, delta, 0.7)
+    d = lambda t: t.cuda().contiguous()
+    X, X1, X2, W, Bi = d(x), d(x1), d(x2), d(w), d(bias)
+    Ac, Bc, As, Bs, Mc, Ms = d(a_c), d(b_c), d(a_s), d(b_s), d(m_c), d(m_s)
+    Kc, Ks = d(mk_c.to(torch.uint8)), d(mk_s.to(torch.uint8))
+    nbr = 2 if mode == 0 else 1
+    y = torch.empty(m, n, dtype=torch.bfloat16, device="cuda")
+    u = torch.empty(m, nbr * r, dtype=torch.bfloat16, device="cuda")
+    wsb = lib.vst_lora_gemm_fwd_workspace_bytes(m, n, k, r, nbr, 1)
+    ws = torch.empty(wsb + 256, dtype=torch.uint8, device="cuda")
+    wsp = ws.data_ptr() + (-ws.data_ptr()) % 256
+    P = lambda t: t.data_ptr()
+    st = torch.cuda.current_stream().cuda_stream
+    _lib.check(lib.vst_lora_gemm_fwd(P(X), k, P(X1) if three else 0, k, P(X2) if three else 0, k, P(W), k, P(Bi), 0,
+                                     P(Ac), P(Bc), P(Mc), P(Kc), P(As), P(Bs), P(Ms), P(Ks), r, 0, 0.7, mode,
+                                     0, 0, 1.0, P(u), nbr * r, P(y), n, m, n, k, k, 1, wsp, wsb, st), "vst_lora_gemm_fwd")
+    assert rel_err(y, want) < 1e-2
+    u_want = []
+    if mode != 2:
+        u_want.append(xc.float() @ a_c.to(torch.bfloat16).float().t())
+    if mode != 1:
+        u_want.append(xs.float() @ a_s.to(torch.bfloat16).float().t())
+    assert rel_err(u, torch.cat(u_want, dim=1)) < 1e-2
+    # every branch block-masked (inference layer): A = NULL -> the plain linear
+    _lib.check(lib.vst_lora_gemm_fwd(P(X), k, 0, 0, 0, 0, P(W), k, P(Bi), 0, 0, 0, 0, 0, 0, 0, 0, 0, r, 0, 0.7, mode,
+                                     0, 0, 1.0, 0, 0, P(y), n, m, n, k, k, 1, 0, 0, st), "vst_lora_gemm_fwd plain")
+    assert rel_err(y, x.float() @ w.float().t() + bias) < 1e-2

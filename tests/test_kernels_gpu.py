@@ -176,6 +176,73 @@ def test_lora_gemm_residual_tma_epilogue(ops, m, n, k):
     assert torch.equal(ops.lora_gemm(zero, w, residual=res), res)
 
 
+@pytest.mark.parametrize("m,n,k1,k2,gn", [(4096, 1280, 1280, 128, 0), (4100, 3840, 1280, 128, 1280),
+                                          (8192, 1920, 640, 128, 640), (2048, 640, 640, 64, 0),
+                                          (16384, 960, 320, 64, 320), (32768, 1280, 1280, 128, 0)])
+def test_lora_gemm_fused_single_launch(ops, m, n, k1, k2, gn):
+    """vst_lora_gemm_fused (u = x A^T computed inside the main kernel) against the two-launch form it replaces
+    (bit-identical: same bf16 u, same accumulation order), against fp32, and its u_out against the u GEMM."""
+    torch.manual_seed(m + n + k2)
+    groups = n // gn if gn else 1
+    x = torch.randn(m, k1).to(torch.bfloat16).cuda()
+    w = (torch.randn(n, k1) / math.sqrt(k1)).to(torch.bfloat16).cuda()
+    a = (torch.randn(groups * k2, k1) / math.sqrt(k1)).to(torch.bfloat16).cuda()
+    bp = (torch.randn(n, k2) / math.sqrt(k2)).to(torch.bfloat16).cuda()
+    bias = torch.randn(n).cuda()
+    assert ops.lora_gemm_fused_supported(m, n, k1, k2, gn)
+    y, u = ops.lora_gemm_fused_raw(x, w, a, bp, bias, 0.5, gn, save_u=True)
+    u_ref = ops.lora_gemm(x, a)
+    y_ref = ops.lora_gemm(x, w, u_ref, bp, bias=bias, out_scale=0.5, k2_group_n=gn)
+    assert torch.equal(u, u_ref)
+    assert torch.equal(y, y_ref)
+    y_nou = ops.lora_gemm_fused(x, w, a, bp, bias, 0.5, gn)
+    assert torch.equal(y_nou, y)
+    sel = slice(0, 512)                                          # fp32 check on a slab
+    uf = (x[sel].float() @ a.float().t()).to(torch.bfloat16).float()
+    want = x[sel].float() @ w.float().t() + bias
+    for g_ in range(groups):
+        cols = slice(g_ * gn, (g_ + 1) * gn) if gn else slice(0, n)
+        want[:, cols] += uf[:, g_ * k2:(g_ + 1) * k2] @ bp[cols].float().t()
+    assert rel_err(y[sel], (want * 0.5).cpu()) < REL_TOL
+    assert not ops.lora_gemm_fused_supported(1000, n, k1, k2, gn)       # small M: the two-launch form stays
+
+
+def test_lora_gemm_fused_autograd_matches_two_launch_form(ops):
+    """FusedLoraFn (one forward launch, u saved by the kernel) gives the gradients of the two-launch autograd
+    graph (LoraGemmFn twice) and of fp32 autograd."""
+    torch.manual_seed(8)
+    m, n, k1, k2, gn = 4096, 1920, 640, 128, 640
+    mk = lambda *s_, sc=1.0: (torch.randn(*s_) * sc).to(torch.bfloat16).cuda()
+    x0, w0, a0, bp0 = mk(m, k1), mk(n, k1, sc=k1 ** -0.5), mk(3 * k2, k1, sc=k1 ** -0.5), mk(n, k2, sc=k2 ** -0.5)
+    b0 = torch.randn(n).cuda()
+    dy = mk(m, n, sc=0.1)
+
+    def run(fused):
+        ts = [t.clone().requires_grad_(True) for t in (x0, w0, a0, bp0, b0)]
+        x, w, a, bp, b = ts
+        if fused:
+            y = ops.lora_gemm_fused(x, w, a, bp, b, 1.0, gn)
+        else:
+            y = ops.lora_gemm(x, w, ops.lora_gemm(x, a), bp, bias=b, k2_group_n=gn)
+        y.backward(dy)
+        return y.detach(), [t.grad for t in ts]
+
+    y1, g1 = run(True)
+    y2, g2 = run(False)
+    assert torch.equal(y1, y2)
+    for a_, b_, nm in zip(g1, g2, ("dx", "dw", "da", "dbp", "dbias")):
+        # (the two-launch graph sums dy W and du A as two bf16 tensors; the fused backward accumulates both
+        # operand pairs in one fp32 accumulator: they differ by bf16 rounding)
+        assert rel_err(a_, b_.float().cpu()) < 1.5e-2, nm
+    xf, wf, af, bpf = (t.float().cpu().requires_grad_(True) for t in (x0, w0, a0, bp0))
+    uf = xf @ af.t()
+    yf = xf @ wf.t() + b0.cpu()
+    yf = yf + torch.cat([uf[:, i * k2:(i + 1) * k2] @ bpf[i * gn:(i + 1) * gn].t() for i in range(3)], dim=1)
+    yf.backward(dy.float().cpu())
+    for got, ref, nm in zip(g1[:4], (xf.grad, wf.grad, af.grad, bpf.grad), ("dx", "dw", "da", "dbp")):
+        assert rel_err(got, ref) < 1.5e-2, nm
+
+
 def test_lora_gemm_linearity(ops):
     """Size-independent property at a full config-3 shape (M=16384, C=1280): exact identity
     columns of B pick out columns of A, and doubling A doubles D (power-of-two scaling is exact)."""

@@ -88,6 +88,60 @@ class LoraGemmFn(torch.autograd.Function):
         return da1, db1, da2, db2, dbias, dres, None, None, None, None
 
 
+class FusedLoraFn(torch.autograd.Function):
+    """y = (x w^T + (x a^T) bp^T [grouped] + bias) * out_scale through the single-launch kernel; u = x a^T comes
+    back from the same launch for the backward, which is the arithmetic of LoraGemmFn applied to
+    y = x w^T + u bp^T and u = x a^T:  du = dy bp, dx = dy w + du a, dw = dy^T x, da = du^T x, dbp = dy^T u."""
+
+    @staticmethod
+    def forward(ctx, x, w, a, bp, bias, out_scale, k2_group_n):
+        y, u = ops.lora_gemm_fused_raw(x, w, a, bp, bias, out_scale, k2_group_n, True)
+        ctx.save_for_backward(x, w, a, bp, u)
+        ctx.cfg = (out_scale, k2_group_n, None if bias is None else bias.dtype)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w, a, bp, u = ctx.saved_tensors
+        out_scale, gn, bias_dtype = ctx.cfg
+        need = ctx.needs_input_grad
+        g = _rows_bf16(dy)
+        m, n = g.shape
+        k2 = bp.shape[1]
+        groups = (n // gn) if gn else 1
+        dx = dw = da = dbp = dbias = None
+        du = None
+        if need[0] or need[2]:                       # du = dy bp   (per projection group)
+            if groups == 1:
+                du = ops.gemm(g, bp, trans_b=True, alpha=out_scale)
+            else:
+                du = torch.empty((m, groups * k2), dtype=torch.bfloat16, device=g.device)
+                for i in range(groups):
+                    ops.gemm(g[:, i * gn:(i + 1) * gn], bp[i * gn:(i + 1) * gn], trans_b=True, alpha=out_scale,
+                             out=du[:, i * k2:(i + 1) * k2])
+        if need[0]:                                  # dx = dy w + du a   (two operand pairs, one GEMM)
+            if out_scale == 1.0:
+                dx = ops.gemm(g, w, du, a, trans_b=True)
+            else:
+                dx = ops.gemm(g, w, trans_b=True, alpha=out_scale)
+                ops.gemm(du, a, trans_b=True, out=dx, accumulate=True)
+        if need[1]:
+            dw = ops.gemm(g, x, trans_a=True, trans_b=True, alpha=out_scale)
+        if need[2]:
+            da = ops.gemm(du, x, trans_a=True, trans_b=True)
+        if need[3]:
+            if groups == 1:
+                dbp = ops.gemm(g, u, trans_a=True, trans_b=True, alpha=out_scale)
+            else:
+                dbp = torch.empty((n, k2), dtype=torch.bfloat16, device=g.device)
+                for i in range(groups):
+                    ops.gemm(g[:, i * gn:(i + 1) * gn], u[:, i * k2:(i + 1) * k2], trans_a=True, trans_b=True,
+                             alpha=out_scale, out=dbp[i * gn:(i + 1) * gn])
+        if need[4]:
+            dbias = ops.colsum(g, out_scale).to(bias_dtype)
+        return dx, dw, da, dbp, dbias, None, None
+
+
 class CastCatFn(torch.autograd.Function):
     """bf16, row-concatenated (optionally row-padded to 8) GEMM operand of one or more parameters;
     the value itself comes from the version-keyed cache of _host.bf16_cached."""

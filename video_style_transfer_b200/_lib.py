@@ -31,8 +31,14 @@ SIGNATURES = {
     "vst_lora_gemm": (_i, [_p, _l, _p, _l, _i, _p, _l, _p, _l, _i, _i, _p, _i, _p, _l, _f, _i, _p, _l,
                            _l, _i, _i, _p]),
     "vst_lora_gemm_plan": (_i, [_l, _i, _i, _i, _i]),
-    "vst_lora_gemm_fwd": (_i, [_p, _l, _p, _l, _i, _p, _l, _p, _l, _i, _i, _p, _i, _p, _l, _f, _i, _p, _l,
-                               _l, _i, _i, _p]),
+    "vst_lora_gemm_fused_supported": (_i, [_l, _i, _i, _i, _i]),
+    "vst_lora_gemm_fused": (_i, [_p, _l, _p, _l, _i, _p, _l, _p, _l, _i, _i, _p, _i, _f, _i, _p, _l, _p, _l, _l, _i, _p]),
+    "vst_lora_pack_down": (_i, [_p, _p, _p, _i, _i, _i, _i, _p]),
+    "vst_lora_gemm_fwd_workspace_bytes": (_l, [_l, _i, _i, _i, _i, _i]),
+    # x ldx x_c ldxc x_s ldxs W ldw bias bias_dtype A_c B_c m_c mask_c A_s B_s m_s mask_s rank param_dtype scale mode
+    # residual ldr out_scale u_out ldu D ldd M N K Klow out_dtype workspace bytes stream
+    "vst_lora_gemm_fwd": (_i, [_p, _l, _p, _l, _p, _l, _p, _l, _p, _i] + [_p] * 8 + [_i, _i, _f, _i, _p, _l, _f, _p, _l,
+                               _p, _l, _l, _i, _i, _i, _i, _p, _l, _p]),
     # dY lddy W ldw Bp ldbp A lda R dU lddu dX lddx M N K alpha accumulate out_dtype stream
     "vst_lora_gemm_bwd_dx": (_i, [_p, _l, _p, _l, _p, _l, _p, _l, _i, _p, _l, _p, _l, _l, _i, _i, _f, _i, _i, _p]),
     "vst_lora_gemm_bwd_params_workspace_bytes": (_l, [_l, _i, _i, _i, _i]),

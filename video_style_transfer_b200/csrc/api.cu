@@ -51,15 +51,89 @@ extern "C" int64_t vst_workspace_bytes(int op, const int64_t* dims, int ndims) {
 }
 
 // ---- SURVEY.md §8b entry points of the fused LoRA linear: forward, dX, parameter gradients ------
-// Thin compositions of vst_lora_gemm / vst_gemm so a C caller can run one LoRA linear's forward and
-// backward without the Python autograd glue (video_style_transfer_b200/_autograd.py does the same).
-extern "C" int vst_lora_gemm_fwd(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1,
-                                 const void* A2, int64_t lda2, const void* B2, int64_t ldb2, int K2,
-                                 int k2_group_n, const void* bias, int bias_dtype, const void* residual,
-                                 int64_t ldr, float out_scale, int act, void* D, int64_t ldd, int64_t M,
-                                 int N, int out_dtype, void* stream) {
-  return vst_lora_gemm(A1, lda1, B1, ldb1, K1, A2, lda2, B2, ldb2, K2, k2_group_n, bias, bias_dtype, residual,
-                       ldr, out_scale, act, D, ldd, M, N, out_dtype, stream);
+// Module-level calls: a C caller runs one LoRA linear's forward and backward from the RAW parameters
+// (A, B, mergers, masks), without the Python glue (video_style_transfer_b200/_autograd.py, fused.py).
+static int64_t al256(int64_t x) { return (x + 255) / 256 * 256; }
+
+extern "C" int64_t vst_lora_gemm_fwd_workspace_bytes(int64_t M, int N, int Klow, int rank, int branches,
+                                                     int have_u_out) {
+  if (M < 0 || N <= 0 || Klow <= 0 || rank <= 0 || branches < 1 || branches > 2) return VST_E_BADARG;
+  const int64_t k2 = (int64_t)branches * ((rank + 7) / 8 * 8);
+  return al256(k2 * Klow * 2) + al256((int64_t)N * k2 * 2) + (have_u_out ? 0 : al256(M * k2 * 2));
+}
+
+// y = (x W^T + bias + [(x_c A_c^T)(scale m_c.mask_c.B_c)^T + (x_s A_s^T)(scale m_s.mask_s.B_s)^T] + residual) * out_scale
+//   lora_linear.py:74-81 (x_c = x_s = x), lora_unzip.py:66-75 (three streams), unziplora_linear_layer.py:221-263
+//   (hard masks multiply), :298-346 (a block-masked branch is absent: pass its A = NULL), :324-345 (modes
+//   content / style: one branch, no merger).  u = [x_c A_c^T | x_s A_s^T] is computed INSIDE the main kernel
+//   (vst_lora_gemm_fused) when the streams coincide and the shape allows, else by a pre-pass; it is written to
+//   u_out when given (the backward needs it).
+extern "C" int vst_lora_gemm_fwd(const void* x, int64_t ldx, const void* x_c, int64_t ldxc, const void* x_s,
+                                 int64_t ldxs, const void* W, int64_t ldw, const void* bias, int bias_dtype,
+                                 const void* A_c, const void* B_c, const void* m_c, const uint8_t* mask_c,
+                                 const void* A_s, const void* B_s, const void* m_s, const uint8_t* mask_s,
+                                 int rank, int param_dtype, float scale, int mode, const void* residual,
+                                 int64_t ldr, float out_scale, void* u_out, int64_t ldu, void* D, int64_t ldd,
+                                 int64_t M, int N, int K, int Klow, int out_dtype, void* workspace,
+                                 int64_t workspace_bytes, void* stream) {
+  VST_REQUIRE(x && W && D && M >= 0 && N > 0 && K > 0, VST_E_BADARG, "vst_lora_gemm_fwd: x, W and D are required");
+  VST_REQUIRE(mode >= VST_LORA_BOTH && mode <= VST_LORA_STYLE, VST_E_BADARG, "vst_lora_gemm_fwd: bad mode %d", mode);
+  if (M == 0) return VST_OK;
+  const bool use_c = mode != VST_LORA_STYLE && A_c != nullptr && B_c != nullptr;
+  const bool use_s = mode != VST_LORA_CONTENT && A_s != nullptr && B_s != nullptr;
+  const int nbr = (use_c ? 1 : 0) + (use_s ? 1 : 0);
+  if (nbr == 0)      // every branch block-masked: the plain linear (unziplora_linear_layer.py:308-309,316-317)
+    return vst_lora_gemm(x, ldx, W, ldw, K, nullptr, 0, nullptr, 0, 0, 0, bias, bias_dtype, residual, ldr, out_scale,
+                         VST_ACT_NONE, D, ldd, M, N, out_dtype, stream);
+  VST_REQUIRE(rank > 0 && rank % 8 == 0, VST_E_UNSUPPORTED, "vst_lora_gemm_fwd: rank=%d must be a multiple of 8", rank);
+  if (Klow <= 0) Klow = K;
+  if (x_c == nullptr) { x_c = x; ldxc = ldx; VST_REQUIRE(Klow == K, VST_E_BADARG, "vst_lora_gemm_fwd: Klow != K needs x_c"); }
+  if (x_s == nullptr) { x_s = x_c; ldxs = ldxc; }
+  const int k2 = nbr * rank;
+  const int64_t need = vst_lora_gemm_fwd_workspace_bytes(M, N, Klow, rank, nbr, u_out != nullptr);
+  VST_REQUIRE(workspace && workspace_bytes >= need && (reinterpret_cast<uintptr_t>(workspace) & 255) == 0, VST_E_BADARG,
+              "vst_lora_gemm_fwd: a 256-byte aligned workspace of %lld bytes is required", (long long)need);
+  uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
+  void* a_pack = ws;
+  ws += al256((int64_t)k2 * Klow * 2);
+  void* b_pack = ws;
+  ws += al256((int64_t)N * k2 * 2);
+  void* u = u_out ? u_out : (void*)ws;
+  const int64_t ldu_ = u_out ? ldu : k2;
+  const bool merger = mode == VST_LORA_BOTH;                       // :331,:343: single-branch modes skip the merger
+  int rc = vst_lora_pack_down(use_c ? A_c : nullptr, use_s ? A_s : nullptr, a_pack, rank, rank, Klow, param_dtype, stream);
+  if (rc) return rc;
+  rc = vst_lora_pack_up(use_c ? B_c : nullptr, use_c && merger ? m_c : nullptr, use_c ? mask_c : nullptr,
+                        use_s ? B_s : nullptr, use_s && merger ? m_s : nullptr, use_s ? mask_s : nullptr, scale, b_pack,
+                        N, rank, param_dtype, stream);
+  if (rc) return rc;
+  const bool one_stream = (!use_c || x_c == x) && (!use_s || x_s == x) && Klow == K;
+  if (one_stream && residual == nullptr && out_dtype == VST_BF16 && vst_lora_gemm_fused_supported(M, N, K, k2, 0))
+    return vst_lora_gemm_fused(x, ldx, W, ldw, K, a_pack, Klow, b_pack, k2, k2, 0, bias, bias_dtype, out_scale,
+                               VST_ACT_NONE, u_out, ldu, D, ldd, M, N, stream);
+  // pre-pass: u[:, branch] = x_branch A_branch^T (one GEMM when both branches read the same stream)
+  const uint8_t* ap = reinterpret_cast<const uint8_t*>(a_pack);
+  uint8_t* up = reinterpret_cast<uint8_t*>(u);
+  if (nbr == 2 && x_s == x_c) {
+    rc = vst_lora_gemm(x_c, ldxc, a_pack, Klow, Klow, nullptr, 0, nullptr, 0, 0, 0, nullptr, VST_F32, nullptr, 0, 1.0f,
+                       VST_ACT_NONE, u, ldu_, M, k2, VST_BF16, stream);
+    if (rc) return rc;
+  } else {
+    int col = 0;
+    if (use_c) {
+      rc = vst_lora_gemm(x_c, ldxc, ap, Klow, Klow, nullptr, 0, nullptr, 0, 0, 0, nullptr, VST_F32, nullptr, 0, 1.0f,
+                         VST_ACT_NONE, up, ldu_, M, rank, VST_BF16, stream);
+      if (rc) return rc;
+      col = rank;
+    }
+    if (use_s) {
+      rc = vst_lora_gemm(x_s, ldxs, ap + (int64_t)col * Klow * 2, Klow, Klow, nullptr, 0, nullptr, 0, 0, 0, nullptr, VST_F32,
+                         nullptr, 0, 1.0f, VST_ACT_NONE, up + (int64_t)col * 2, ldu_, M, rank, VST_BF16, stream);
+      if (rc) return rc;
+    }
+  }
+  return vst_lora_gemm(x, ldx, W, ldw, K, u, ldu_, b_pack, k2, k2, 0, bias, bias_dtype, residual, ldr, out_scale,
+                       VST_ACT_NONE, D, ldd, M, N, out_dtype, stream);
 }
 
 extern "C" int vst_lora_gemm_bwd_dx(const void* dY, int64_t lddy, const void* W, int64_t ldw, const void* Bp,

@@ -172,6 +172,28 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int ta
   }
 }
 
+// wait whose acquire is cluster-scoped: pairs with a peer CTA's mbarrier.arrive.release.cluster when DATA
+// (shared-memory writes of the peer, read next by this CTA's tcgen05 ops) rides on the barrier
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity, int tag = 0) {
+  const uint32_t addr = smem_u32(bar);
+  const uint64_t t0 = globaltimer_ns();
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(addr), "r"(parity), "r"(1000000u)
+        : "memory");
+    if (!done && globaltimer_ns() - t0 > VST_WATCHDOG_NS) {
+      printf("vst watchdog: cluster mbarrier wait timed out (tag %d, block %d thread %d)\n", tag, blockIdx.x,
+             threadIdx.x);
+      __trap();
+    }
+  }
+}
+
 // ---- TMA ----------------------------------------------------------------------------------------
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(m) : "memory");

@@ -744,6 +744,284 @@ lora_gemm2_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constan
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Single-launch fused LoRA GEMM (CTA pairs):  D = act(x W^T + (x A^T) B'^T + bias) * out_scale  with the
+// down-projection u = x A^T computed INSIDE this kernel, once per (256-row tile, projection group):
+//
+//   unit (m, g)   U item      u[256 x K2] = x[256 x K1] A_g^T     (leading MMA, N = K2, into an accumulator stage)
+//                             epilogue warps: TMEM -> bf16 -> THIS CTA's shared memory, laid out as the K-major,
+//                             128B-swizzled A operand of K2/64 extra k-blocks (and, when the backward needs it,
+//                             sent to u_out by TMA store from that very tile)
+//                 TILE items  n-tiles of group g:  K1/64 k-blocks from the TMA ring, then the K2 k-blocks whose A
+//                             operand is the resident u tile and whose B operand (B' rows of the tile) comes
+//                             through the ring
+//
+// so the low-rank path costs its own FLOPs (2 M K1 K2 + 2 M K2 N) and nothing else: no second launch, no u
+// round trip through HBM.  Reference arithmetic: unziplora_linear_layer.py:221-263,298-346 + lora_linear.py
+// :74-81 (single stream), temporal_lora.py:29-32; grouped along N for q|k|v.  Tiles are dealt to the CTA pairs
+// in CONTIGUOUS ranges of the (m, n) order (n fastest), so a pair recomputes u only when it enters a new (m, g)
+// unit.  Barriers on top of lora_gemm2_kernel's: u_ready (leader CTA, 16 warp arrivals: both CTAs' u tiles
+// are in shared memory and visible to the async proxy), u_free (both CTAs, multicast commit: the low-rank MMAs
+// of the unit have read the tile).
+// ------------------------------------------------------------------------------------------------
+struct FusedSched {
+  int t, t_end, n_tiles, tiles_per_group, prev_unit;
+  __device__ FusedSched(int cluster, int n_clusters, int total, int n_tiles_, int tpg)
+      : n_tiles(n_tiles_), tiles_per_group(tpg), prev_unit(-1) {
+    t = (int)((int64_t)total * cluster / n_clusters);
+    t_end = (int)((int64_t)total * (cluster + 1) / n_clusters);
+  }
+  __device__ bool done() const { return t >= t_end; }
+  __device__ int unit_of(int tt) const { return (tt / n_tiles) * (n_tiles / tiles_per_group) + (tt % n_tiles) / tiles_per_group; }
+  __device__ bool opens_unit() const { return unit_of(t) != prev_unit; }      // a U item precedes this tile
+  __device__ bool closes_unit() const { return t + 1 >= t_end || unit_of(t + 1) != unit_of(t); }
+  __device__ void advance() { prev_unit = unit_of(t); ++t; }
+};
+
+template <int BN>
+struct CfgF {
+  using C = Cfg2<BN, false>;
+  static constexpr int kUBytes = 2 * BM * BK * 2;       // resident u tile: two k-blocks of [128 x 64] bf16
+  static constexpr int kStages = (ring_budget(false) - kUBytes) / C::kStageBytes > 8
+                                     ? 8 : (ring_budget(false) - kUBytes) / C::kStageBytes;
+  static constexpr int kSmemBytes = kStages * C::kStageBytes + kUBytes + C::kOutBytes + 1024 + kBarBytes;
+};
+
+template <int BN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+lora_gemm2_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
+                        const __grid_constant__ CUtensorMap tmAd, const __grid_constant__ CUtensorMap tmBp,
+                        const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmU,
+                        int nk1, int K2, int m_tiles, int n_tiles, int k2_group_n, int store_u, EpiArgs ep) {
+  using C = Cfg2<BN, false>;
+  constexpr int kUBytes = CfgF<BN>::kUBytes;
+  constexpr int kStagesF = CfgF<BN>::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* u_smem = smem + kStagesF * C::kStageBytes;       // 1024-aligned (stage sizes are k * 1024)
+  uint8_t* stage_out = u_smem + kUBytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(stage_out + C::kOutBytes);
+  uint64_t* empty = full + kStagesF;
+  uint64_t* acc_full = empty + kStagesF;
+  uint64_t* acc_empty = acc_full + 2;
+  uint64_t* u_ready = acc_empty + 2;
+  uint64_t* u_free = u_ready + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(u_free + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int total_tiles = m_tiles * n_tiles;
+  const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+  const int tpg = k2_group_n > 0 ? k2_group_n / BN : n_tiles;          // n-tiles per projection group
+  const int nk2 = K2 / BK;
+  const int ubrows = K2 / 2;                                           // A_g rows each CTA stages for the U item
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmX);
+    tma_prefetch_desc(&tmW);
+    tma_prefetch_desc(&tmAd);
+    tma_prefetch_desc(&tmBp);
+    for (int i = 0; i < kStagesF; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_empty[i], 2 * kEpiWarps);
+    }
+    mbar_init(u_ready, 2 * kEpiWarps);
+    mbar_init(u_free, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc_2sm(tmem_slot, C::kTmemCols);
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================= TMA producer (both CTAs) =================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      auto next = [&]() { if (++stage == kStagesF) { stage = 0; phase ^= 1; } };
+      for (FusedSched sc(cluster_id, n_clusters, total_tiles, n_tiles, tpg); !sc.done(); sc.advance()) {
+        const int m0 = (sc.t / n_tiles) * (2 * BM) + rank * BM;
+        const int n0 = (sc.t % n_tiles) * BN;
+        const int g = (sc.t % n_tiles) / tpg;
+        if (sc.opens_unit()) {                           // U item: x k-blocks + this CTA's half of A_g
+          const uint32_t bytes = BM * BK * 2 + ubrows * BK * 2;
+          for (int kb = 0; kb < nk1; ++kb) {
+            mbar_wait(&empty[stage], phase ^ 1, 1);
+            uint8_t* sa = smem + stage * C::kStageBytes;
+            if (leader) mbar_arrive_expect_tx(&full[stage], 2 * bytes);
+            tma_load_2d_2sm(sa, &tmX, &full[stage], kb * BK, m0);
+            tma_load_2d_2sm(sa + BM * BK * 2, &tmAd, &full[stage], kb * BK, g * K2 + rank * ubrows);
+            next();
+          }
+        }
+        const int nb = n0 + rank * C::kBRows;
+        for (int kb = 0; kb < nk1; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1, 1);
+          uint8_t* sa = smem + stage * C::kStageBytes;
+          if (leader) mbar_arrive_expect_tx(&full[stage], 2 * C::kStageBytes);
+          tma_load_2d_2sm(sa, &tmX, &full[stage], kb * BK, m0);
+          tma_load_2d_2sm(sa + BM * BK * 2, &tmW, &full[stage], kb * BK, nb);
+          next();
+        }
+        for (int kb = 0; kb < nk2; ++kb) {               // low-rank k-blocks: only B' travels, u is resident
+          mbar_wait(&empty[stage], phase ^ 1, 1);
+          uint8_t* sa = smem + stage * C::kStageBytes;
+          if (leader) mbar_arrive_expect_tx(&full[stage], 2 * C::kBRows * BK * 2);
+          tma_load_2d_2sm(sa + BM * BK * 2, &tmBp, &full[stage], kb * BK, nb);
+          next();
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer (leader CTA only) =================
+    if (leader && lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(2 * BM, BN);
+      const uint32_t idesc_u = umma_idesc_bf16(2 * BM, K2);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0, unit_phase = 0;
+      auto next = [&]() { if (++stage == kStagesF) { stage = 0; phase ^= 1; } };
+      auto next_acc = [&]() { if (++acc == 2) { acc = 0; acc_phase ^= 1; } };
+      for (FusedSched sc(cluster_id, n_clusters, total_tiles, n_tiles, tpg); !sc.done(); sc.advance()) {
+        if (sc.opens_unit()) {
+          mbar_wait(&acc_empty[acc], acc_phase ^ 1, 2);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + acc * C::kAccStride;
+          for (int kb = 0; kb < nk1; ++kb) {
+            mbar_wait(&full[stage], phase, 3);
+            tc_fence_after();
+            const uint32_t sa = smem_u32(smem + stage * C::kStageBytes);
+            const uint64_t da = umma_desc_sw128(sa, 1024);
+            const uint64_t db = umma_desc_sw128(sa + BM * BK * 2, 1024);
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k)
+              umma_bf16_ss_2sm(d_tmem, da + 2 * k, db + 2 * k, idesc_u, (kb | k) != 0);
+            umma_commit_2sm(&empty[stage]);
+            next();
+          }
+          umma_commit_2sm(&acc_full[acc]);
+          next_acc();
+        }
+        mbar_wait(&acc_empty[acc], acc_phase ^ 1, 2);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * C::kAccStride;
+        for (int kb = 0; kb < nk1; ++kb) {
+          mbar_wait(&full[stage], phase, 3);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * C::kStageBytes);
+          const uint64_t da = umma_desc_sw128(sa, 1024);
+          const uint64_t db = umma_desc_sw128(sa + BM * BK * 2, 1024);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k)
+            umma_bf16_ss_2sm(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+          umma_commit_2sm(&empty[stage]);
+          next();
+        }
+        mbar_wait_cluster(u_ready, unit_phase, 6);       // both CTAs' u tiles of this unit are in place
+        tc_fence_after();
+        for (int kb = 0; kb < nk2; ++kb) {
+          mbar_wait(&full[stage], phase, 3);
+          tc_fence_after();
+          const uint64_t da = umma_desc_sw128(smem_u32(u_smem + kb * BM * BK * 2), 1024);
+          const uint64_t db = umma_desc_sw128(smem_u32(smem + stage * C::kStageBytes + BM * BK * 2), 1024);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) umma_bf16_ss_2sm(d_tmem, da + 2 * k, db + 2 * k, idesc, 1);
+          umma_commit_2sm(&empty[stage]);
+          next();
+        }
+        umma_commit_2sm(&acc_full[acc]);
+        next_acc();
+        if (sc.closes_unit()) {
+          umma_commit_2sm(u_free);                       // the unit's low-rank MMAs have read the u tiles
+          unit_phase ^= 1;
+        }
+      }
+    }
+  } else {
+    // ================= epilogue (warps 2..9 of both CTAs; own 128 rows) =================
+    const int ewarp = warp - 2;
+    const int quarter = (ewarp + 2) & 3, half = ewarp >> 2;
+    uint8_t* my_out = stage_out + ewarp * 2 * kStageOutBytes;
+    int buf = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0, unit_phase = 0;
+    if (lane == 0) tma_prefetch_desc(&tmD);
+    auto next_acc = [&]() { if (++acc == 2) { acc = 0; acc_phase ^= 1; } };
+    for (FusedSched sc(cluster_id, n_clusters, total_tiles, n_tiles, tpg); !sc.done(); sc.advance()) {
+      const int m0 = (sc.t / n_tiles) * (2 * BM) + rank * BM;
+      if (sc.opens_unit()) {
+        // ---- U item: this CTA's 128 rows of u -> bf16 -> shared memory (K-major, 128B swizzle) ----
+        const int g = (sc.t % n_tiles) / tpg;
+        if (ewarp == 0 && lane == 0) tma_store_wait_read<0>();        // the previous unit's u_out store has left
+        asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
+        mbar_wait(u_free, unit_phase ^ 1, 7);                          // ... and its MMAs have read the tile
+        mbar_wait(&acc_full[acc], acc_phase, 4);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + acc * C::kAccStride + (uint32_t(quarter * 32) << 16);
+        const int row = quarter * 32 + lane;
+        for (int c0 = half * 32; c0 < K2; c0 += 64) {
+          uint32_t r[32];
+          tmem_ld32(taddr + c0, r);
+          tmem_ld_wait();
+          uint8_t* dst = u_smem + (c0 >> 6) * (BM * BK * 2) + row * 128;
+          const int cbase = (c0 & 32) ? 4 : 0;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            uint4 w;
+            w.x = pack_bf16(__uint_as_float(r[8 * q]), __uint_as_float(r[8 * q + 1]));
+            w.y = pack_bf16(__uint_as_float(r[8 * q + 2]), __uint_as_float(r[8 * q + 3]));
+            w.z = pack_bf16(__uint_as_float(r[8 * q + 4]), __uint_as_float(r[8 * q + 5]));
+            w.w = pack_bf16(__uint_as_float(r[8 * q + 6]), __uint_as_float(r[8 * q + 7]));
+            *reinterpret_cast<uint4*>(dst + (((cbase + q) ^ (row & 7)) * 16)) = w;
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(&acc_empty[acc], 0);
+        next_acc();
+        fence_proxy_async_smem();                                      // u tile -> visible to tcgen05 / TMA
+        asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
+        if (ewarp == 0 && lane == 0 && store_u) {
+          for (int kb = 0; kb < nk2; ++kb)
+            tma_store_2d(&tmU, u_smem + kb * BM * BK * 2, g * K2 + kb * BK, m0);
+          tma_store_commit();
+        }
+        if (lane == 0) {                                                // release: the peer SM's tensor core reads it
+          uint32_t remote;
+          asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(u_ready)), "r"(0));
+          asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+        }
+        unit_phase ^= 1;
+      }
+      const int n0 = (sc.t % n_tiles) * BN;
+      EpiBias<BN> bias;
+      epilogue_bias<BN>(ep, n0, ewarp, lane, bias);
+      mbar_wait(&acc_full[acc], acc_phase, 4);
+      tc_fence_after();
+      uint64_t* done = &acc_empty[acc];
+      epilogue_tile<BN>(ep, &tmD, tmem_base + acc * C::kAccStride, m0, n0, ewarp, lane, my_out, buf, bias,
+                        [&]() { if (lane == 0) mbar_arrive_cluster(done, 0); });
+      next_acc();
+    }
+    if (lane == 0) tma_store_wait<0>();
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_2sm(tmem_base, C::kTmemCols);
+  }
+}
+
 int make_operand_map(CUtensorMap* m, const void* p, int64_t rows, int K, int64_t ld, int box_rows) {
   const uint64_t dims[2] = {(uint64_t)K, (uint64_t)rows};
   const uint64_t strides[2] = {2, (uint64_t)ld * 2};
@@ -865,6 +1143,39 @@ int launch2(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int K1, 
              : launch2_t<BN, false>(A1, lda1, B1, ldb1, K1, A2, lda2, B2, ldb2, K2, k2_group_n, ep, st);
 }
 
+template <int BN>
+int launch2_fused(const void* X, int64_t ldx, const void* W, int64_t ldw, int K1, const void* Ad, int64_t lda,
+                  const void* Bp, int64_t ldbp, int K2, int k2_group_n, void* U, int64_t ldu, const EpiArgs& ep,
+                  cudaStream_t st) {
+  using F = CfgF<BN>;
+  using C = typename F::C;
+  const int groups = k2_group_n > 0 ? ep.N / k2_group_n : 1;
+  CUtensorMap tX, tW, tAd, tBp, tD, tU;
+  int rc;
+  if ((rc = make_operand_map(&tX, X, ep.M, K1, ldx, BM))) return rc;
+  if ((rc = make_operand_map(&tW, W, ep.N, K1, ldw, C::kBRows))) return rc;
+  if ((rc = make_operand_map(&tAd, Ad, (int64_t)groups * K2, K1, lda, K2 / 2))) return rc;
+  if ((rc = make_operand_map(&tBp, Bp, ep.N, K2, ldbp, C::kBRows))) return rc;
+  if ((rc = make_out_map(&tD, ep))) return rc;
+  tU = tD;
+  if (U != nullptr && (rc = make_operand_map(&tU, U, ep.M, groups * K2, ldu, BM))) return rc;
+  static bool configured = false;
+  if (!configured) {
+    VST_CUDA_OK(cudaFuncSetAttribute(lora_gemm2_fused_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     F::kSmemBytes));
+    configured = true;
+  }
+  const int m_tiles = (int)((ep.M + 2 * BM - 1) / (2 * BM)), n_tiles = (ep.N + BN - 1) / BN;
+  const int64_t tiles = (int64_t)m_tiles * n_tiles;
+  VST_REQUIRE(tiles < (1ll << 31), VST_E_UNSUPPORTED, "lora_gemm_fused: too many tiles");
+  const int pairs = vst_sm_count() / 2;
+  const int grid = 2 * (int)(tiles < pairs ? tiles : pairs);
+  lora_gemm2_fused_kernel<BN><<<grid, kThreads, F::kSmemBytes, st>>>(tX, tW, tAd, tBp, tD, tU, (K1 + BK - 1) / BK, K2,
+                                                                     m_tiles, n_tiles, k2_group_n, U != nullptr, ep);
+  VST_LAUNCH_OK();
+  return VST_OK;
+}
+
 // ---- vst_lora_pack_up: B2'[n, br*r + j] = scale * m_br[n] * mask_br[n] * B_br[n, j] ------------
 template <typename T>
 __global__ void pack_up_kernel(const T* __restrict__ Bc, const T* __restrict__ mc,
@@ -885,6 +1196,18 @@ __global__ void pack_up_kernel(const T* __restrict__ Bc, const T* __restrict__ m
   if (m != nullptr) val *= (float)m[n];
   if (mk != nullptr && mk[n] == 0) val = 0.f;
   out[idx] = __float2bfloat16_rn(val);
+}
+
+// ---- vst_lora_pack_down: A'[br * rp + j, :] = A_br[j, :] (bf16), rows j >= r of each branch zero ----------
+template <typename T>
+__global__ void pack_down_kernel(const T* __restrict__ Ac, const T* __restrict__ As, __nv_bfloat16* __restrict__ out,
+                                 int r, int rp, int K, int nbr) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (int64_t)nbr * rp * K) return;
+  const int row = (int)(idx / K), k = (int)(idx % K);
+  const int br = row / rp, j = row % rp;
+  const T* src = (Ac != nullptr && br == 0) ? Ac : As;
+  out[idx] = __float2bfloat16_rn(j < r ? (float)src[(int64_t)j * K + k] : 0.f);
 }
 
 }  // namespace
@@ -1014,4 +1337,65 @@ extern "C" int vst_lora_pack_up(const void* Bc, const void* mc, const uint8_t* m
   }
   VST_LAUNCH_OK();
   return VST_OK;
+}
+
+
+extern "C" int vst_lora_pack_down(const void* Ac, const void* As, void* out, int r, int rp, int K, int param_dtype,
+                                  void* stream) {
+  VST_REQUIRE(out && (Ac || As) && r > 0 && rp >= r && K > 0, VST_E_BADARG, "lora_pack_down: bad argument");
+  const int nbr = (Ac ? 1 : 0) + (As ? 1 : 0);
+  const int64_t total = (int64_t)nbr * rp * K;
+  const unsigned grid = (unsigned)((total + 255) / 256);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (param_dtype == VST_BF16)
+    pack_down_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)Ac, (const __nv_bfloat16*)As,
+                                                          (__nv_bfloat16*)out, r, rp, K, nbr);
+  else if (param_dtype == VST_F32)
+    pack_down_kernel<float><<<grid, 256, 0, st>>>((const float*)Ac, (const float*)As, (__nv_bfloat16*)out, r, rp, K, nbr);
+  else {
+    vst_set_error("lora_pack_down: bad param dtype %d", param_dtype);
+    return VST_E_BADARG;
+  }
+  VST_LAUNCH_OK();
+  return VST_OK;
+}
+
+// != 0 (the tile width) when vst_lora_gemm_fused takes the shape: CTA-pair kernel, K2 in {64, 128}, tiles that do
+// not straddle projection groups; else 0.
+extern "C" int vst_lora_gemm_fused_supported(int64_t M, int N, int K1, int K2, int k2_group_n) {
+  if (M < 2048 || N <= 0 || K1 <= 0 || K1 % 8 || N % 8) return 0;
+  if (K2 != 64 && K2 != 128) return 0;
+  const int gn = k2_group_n;
+  if (gn < 0 || (gn > 0 && (N % gn != 0))) return 0;
+  const int unit = gn > 0 ? gn : N;
+  if (unit % 256 == 0 || (gn == 0 && N > 256)) return 256;
+  if (unit % 160 == 0) return 160;
+  if (unit % 128 == 0) return 128;
+  return 0;
+}
+
+extern "C" int vst_lora_gemm_fused(const void* X, int64_t ldx, const void* W, int64_t ldw, int K1,
+                                   const void* A_down, int64_t lda, const void* Bp, int64_t ldbp, int K2,
+                                   int k2_group_n, const void* bias, int bias_dtype, float out_scale, int act,
+                                   void* U_out, int64_t ldu, void* D, int64_t ldd, int64_t M, int N,
+                                   void* stream) {
+  VST_REQUIRE(X && W && A_down && Bp && D, VST_E_BADARG, "lora_gemm_fused: null pointer");
+  const int bn = vst_lora_gemm_fused_supported(M, N, K1, K2, k2_group_n);
+  VST_REQUIRE(bn > 0, VST_E_UNSUPPORTED,
+              "lora_gemm_fused: M=%lld N=%d K1=%d K2=%d group=%d is not a fused shape (use vst_lora_gemm)",
+              (long long)M, N, K1, K2, k2_group_n);
+  VST_REQUIRE(act == VST_ACT_NONE || act == VST_ACT_GELU, VST_E_UNSUPPORTED, "lora_gemm_fused: act none / gelu");
+  VST_REQUIRE(ldx % 8 == 0 && ldw % 8 == 0 && lda % 8 == 0 && ldbp % 8 == 0 && ldd % 8 == 0 &&
+                  (U_out == nullptr || ldu % 8 == 0),
+              VST_E_UNSUPPORTED, "lora_gemm_fused: row strides must be multiples of 8 elements");
+  VST_REQUIRE((reinterpret_cast<uintptr_t>(D) & 15) == 0 && (reinterpret_cast<uintptr_t>(bias) & 15) == 0 &&
+                  (reinterpret_cast<uintptr_t>(U_out) & 15) == 0,
+              VST_E_UNSUPPORTED, "lora_gemm_fused: D / bias / U_out must be 16-byte aligned");
+  EpiArgs ep{bias, nullptr, D, 0, ldd, M, N, out_scale, bias_dtype == VST_BF16, 0, act, 0};
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (bn) {
+    case 256: return launch2_fused<256>(X, ldx, W, ldw, K1, A_down, lda, Bp, ldbp, K2, k2_group_n, U_out, ldu, ep, st);
+    case 160: return launch2_fused<160>(X, ldx, W, ldw, K1, A_down, lda, Bp, ldbp, K2, k2_group_n, U_out, ldu, ep, st);
+    default: return launch2_fused<128>(X, ldx, W, ldw, K1, A_down, lda, Bp, ldbp, K2, k2_group_n, U_out, ldu, ep, st);
+  }
 }

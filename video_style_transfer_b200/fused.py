@@ -33,6 +33,51 @@ from ._host import bf16_cached, cached_build, fused_linear, pad8
 
 
 MERGE_LORA = os.environ.get("VST_MERGE_LORA", "1") != "0"
+# The low-rank form in ONE launch (u = x A^T computed inside the main kernel, vst_lora_gemm_fused).
+#   1 (default): projections that stand alone (to_q of a cross-attention, to_out without residual): measured
+#                103 vs 107 us (L2 to_q, M = 32768) and 135 vs 152 us (L1) against u pre-pass + extra K blocks;
+#   2:           also projections fused along N (q|k|v): measured 2-6 % SLOWER there (265 vs 251 us at L2: the
+#                u item is recomputed per (256-row tile, group) and a CTA pair's contiguous tile range cuts units);
+#   0:           never (two launches everywhere).
+FUSED_LORA = int(os.environ.get("VST_FUSED_LORA", "1"))
+
+
+def _fit_k2(a: torch.Tensor, bp: torch.Tensor, groups: int):
+    """Pad the per-group rank of (a (G*k2, in), bp (N, k2)) with zero rows / columns to the 64 or 128 the
+    single-launch kernel takes (temporal LoRA: 32 -> 64).  None when the rank does not fit."""
+    k2 = bp.shape[1]
+    if k2 in (64, 128):
+        return a, bp
+    k2p = 64 if k2 < 64 else (128 if k2 < 128 else 0)
+    if not k2p:
+        return None
+
+    def build():
+        ap = torch.nn.functional.pad(a.view(groups, k2, a.shape[1]), (0, 0, 0, k2p - k2)).reshape(groups * k2p, a.shape[1])
+        return ap.contiguous(), torch.nn.functional.pad(bp, (0, k2p - k2)).contiguous()
+
+    if torch.is_grad_enabled() and (a.requires_grad or bp.requires_grad):
+        return build()
+    return cached_build([a, bp], ("fit_k2", groups), build)
+
+
+def _fused_low_rank(x2, weight, bias, a, bp, k2_group_n: int, out_scale: float):
+    """The projection in one launch, or None when the shape is not a fused one / the form is switched off."""
+    if FUSED_LORA < (2 if k2_group_n else 1):
+        return None
+    n, groups = bp.shape[0], (bp.shape[0] // k2_group_n if k2_group_n else 1)
+    fit = _fit_k2(a, bp, groups)
+    if fit is None:
+        return None
+    a_f, bp_f = fit
+    if not ops.lora_gemm_fused_supported(x2.shape[0], n, x2.shape[1], bp_f.shape[1], k2_group_n):
+        return None
+    b = bias
+    if b is not None and not (torch.is_grad_enabled() and b.requires_grad):
+        b = b.detach()
+    if b is not None and b.dtype not in (torch.float32, torch.bfloat16):
+        b = b.float()
+    return ops.lora_gemm_fused(x2, bf16_cached(weight), a_f, bp_f, b, out_scale, k2_group_n)
 
 
 def _frozen(tensors) -> bool:
@@ -104,7 +149,12 @@ def project_one(layer, x2: torch.Tensor, scale: float = 1.0, residual=None, out_
             if MERGE_LORA and _frozen([s.site_weight(), bp] + list(downs)):
                 w_eff = merged_weight([s.site_weight()], [downs], [bp])
                 return fused_linear(x2, w_eff, s.site_bias(), None, residual, out_scale, act, out_dtype)
-            low = (ops.lora_gemm(x2, bf16_cached(*downs, pad_rows=True)), bp)
+            a = bf16_cached(*downs, pad_rows=True)
+            if residual is None and act == "none" and out_dtype == torch.bfloat16:
+                y = _fused_low_rank(x2, s.site_weight(), s.site_bias(), a, bp, 0, out_scale)
+                if y is not None:
+                    return y
+            low = (ops.lora_gemm(x2, a), bp)
     return fused_linear(x2, s.site_weight(), s.site_bias(), low, residual, out_scale, act, out_dtype)
 
 
@@ -145,7 +195,9 @@ def project_fused(layers: Sequence, x2: torch.Tensor, scale: float = 1.0, batch=
             bp = torch.cat(list(ups), dim=0)
         else:
             bp = cached_build(list(ups), "catup", lambda: torch.cat(list(ups), dim=0).contiguous())
-        u = ops.lora_gemm(x2, a_cat)                                    # (M, G*K2)
-        y = ops.lora_gemm(x2, w, u, bp, bias=bias, k2_group_n=n0)
+        y = _fused_low_rank(x2, w, bias, a_cat, bp, n0, 1.0)            # one launch (VST_FUSED_LORA=2)
+        if y is None:
+            u = ops.lora_gemm(x2, a_cat)                                # (M, G*K2)
+            y = ops.lora_gemm(x2, w, u, bp, bias=bias, k2_group_n=n0)
     from ._autograd import split_cols
     return split_cols(y, n0, len(sites), batch)

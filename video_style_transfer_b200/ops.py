@@ -321,6 +321,42 @@ def lora_gemm_raw(a1: torch.Tensor, b1: torch.Tensor, a2: Optional[torch.Tensor]
     return out
 
 
+def lora_gemm_fused_supported(m: int, n: int, k1: int, k2: int, k2_group_n: int = 0) -> bool:
+    return lib.vst_lora_gemm_fused_supported(m, n, k1, k2, k2_group_n) > 0
+
+
+def lora_gemm_fused(x: torch.Tensor, w: torch.Tensor, a_down: torch.Tensor, bp: torch.Tensor,
+                    bias: Optional[torch.Tensor] = None, out_scale: float = 1.0, k2_group_n: int = 0) -> torch.Tensor:
+    """y = (x w^T + (x a_down^T) bp^T + bias) * out_scale in ONE launch (vst_lora_gemm_fused): u = x a_down^T is
+    computed inside the kernel, per 256-row tile and projection group.  a_down (G*K2, K1), bp (N, K2), K2 in
+    {64, 128}.  Differentiable in x, w, a_down, bp, bias (the kernel then also writes u out for the backward)."""
+    if _needs_grad(x, w, a_down, bp, bias):
+        from ._autograd import FusedLoraFn
+        return FusedLoraFn.apply(x, w, a_down, bp, bias, float(out_scale), int(k2_group_n))
+    return lora_gemm_fused_raw(x, w, a_down, bp, bias, out_scale, k2_group_n, False)[0]
+
+
+def lora_gemm_fused_raw(x, w, a_down, bp, bias=None, out_scale: float = 1.0, k2_group_n: int = 0,
+                        save_u: bool = False):
+    x, w, a_down, bp = (t.detach() for t in (x, w, a_down, bp))
+    bias = None if bias is None else bias.detach()
+    _cuda(x, w, a_down, bp, bias)
+    for t, nm in ((x, "x"), (w, "w"), (a_down, "a_down"), (bp, "bp")):
+        _mat(t, nm)
+    m, k1 = x.shape
+    n, k2 = bp.shape
+    groups = (n // k2_group_n) if k2_group_n else 1
+    assert w.shape == (n, k1) and a_down.shape == (groups * k2, k1)
+    y = torch.empty((m, n), dtype=torch.bfloat16, device=x.device)
+    u = torch.empty((m, groups * k2), dtype=torch.bfloat16, device=x.device) if save_u else None
+    check(lib.vst_lora_gemm_fused(x.data_ptr(), x.stride(0), w.data_ptr(), w.stride(0), k1, a_down.data_ptr(),
+                                  a_down.stride(0), bp.data_ptr(), bp.stride(0), k2, k2_group_n, _ptr(bias),
+                                  _dt(bias) if bias is not None else VST_F32, out_scale, 0, _ptr(u),
+                                  u.stride(0) if u is not None else 0, y.data_ptr(), y.stride(0), m, n, _stream()),
+          "vst_lora_gemm_fused")
+    return y, u
+
+
 def lora_pack_up(b_c: Optional[torch.Tensor], m_c: Optional[torch.Tensor],
                  mask_c: Optional[torch.Tensor], b_s: Optional[torch.Tensor],
                  m_s: Optional[torch.Tensor], mask_s: Optional[torch.Tensor],

@@ -84,13 +84,10 @@ class LoRACompatibleLinear(nn.Linear):
                 raise TypeError("lora_layer must be a video_style_transfer_b200 LoRA layer "
                                 "(no eager fallback on the sm_100a path)")
             if x_content is None and x_style is None:
-                # single-stream inference with frozen adapters: W_eff = W + B' A, one plain GEMM
-                from .. import fused
-                downs = self.site_downs()
-                bp = self.site_up(scale) if downs else None
-                if bp is not None and fused.MERGE_LORA and fused._frozen([self.weight, bp] + list(downs)):
-                    w_eff = fused.merged_weight([self.weight], [downs], [bp])
-                    return fused_linear(x2, w_eff, self.bias, None, residual, out_scale)
+                # single stream: frozen adapters -> W_eff = W + B'A and one plain GEMM; otherwise the low-rank
+                # form, in ONE launch where the shape allows (fused.project_one)
+                from ..fused import project_one
+                return project_one(self, x2, scale, residual, out_scale)
             xc = x2 if x_content is None else x_content
             low_rank = self.lora_layer.fused_operands(xc, x_style, scale)
         return fused_linear(x2, self.weight, self.bias, low_rank, residual, out_scale)
