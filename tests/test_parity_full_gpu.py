@@ -202,18 +202,20 @@ def test_gradient_checkpointing_bit_exact(what):
             assert torch.equal(a, b)
     else:
         # the spatial attention backward adds its per-key-tile dQ contributions with fp32 atomics
-        # (csrc/attn_bwd.cu), so gradients downstream of dQ are reproducible only up to fp32
-        # summation order, with or without checkpointing: the bound asserted is that order noise
-        # (1e-5 of the tensor's max), three orders of magnitude below the bf16 tolerance.
-        assert rel(dx1, dx0) < 1e-5
+        # (csrc/attn_bwd.cu), so dQ is reproducible only up to fp32 summation order, with or without
+        # checkpointing -- and dQ is then rounded to bf16, where a different order can flip a rounding:
+        # one bf16 ulp (2^-8 of an element) on isolated elements, run to run.  The bound asserted is
+        # that ulp against the tensor's max (observed: 0 ... 6e-5); the bf16 parity tolerance is 1e-2.
+        ULP = 2.0 ** -8
+        assert rel(dx1, dx0) < ULP
         for a, b in zip(g0, g1):
-            assert rel(b, a) < 1e-5
+            assert rel(b, a) < ULP
     # reentrant flavour (what diffusers' _gradient_checkpointing_func uses on older versions)
     xi = x.detach().clone().requires_grad_(True)
     for p in params:
         p.grad = None
     checkpoint(fn, xi, use_reentrant=True).backward(dy)
-    assert torch.equal(xi.grad, dx0) if what == "motion" else rel(xi.grad, dx0) < 1e-5
+    assert torch.equal(xi.grad, dx0) if what == "motion" else rel(xi.grad, dx0) < 2.0 ** -8
 
 
 # ---- config 4: one Stage-2 optimiser step ----------------------------------------------------------------
