@@ -231,6 +231,15 @@ int vst_lora_gemm_bwd_params(const void* dY, int64_t lddy, const void* X, int64_
 int64_t vst_colsum_workspace_bytes(int64_t M, int N);
 int vst_colsum(const void* x, int64_t ld, int64_t M, int N, float alpha, float* out,
                void* workspace, int64_t workspace_bytes, void* stream);
+/* vst_colsum without a caller workspace and without any allocation (no cudaMalloc / cudaFree / allocating
+ * library call).  It has no counterpart in the reference and was added
+ * for callers that cannot allocate: code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc.  The fp32 partials live in a static device array of VST_COLSUM_NOALLOC_SCRATCH_BYTES (every GPU
+ * that loads the library holds it until exit); a shape with vst_colsum_workspace_bytes(M, N) beyond that is
+ * refused with VST_E_UNSUPPORTED and a message.  All calls share the array: nothing needs clearing between
+ * calls (every slot read is written first), but calls that overlap on the GPU (two streams or threads) race. */
+#define VST_COLSUM_NOALLOC_SCRATCH_BYTES (1 << 20)
+int vst_colsum_noalloc(const void* x, int64_t ld, int64_t M, int N, float alpha, float* out, void* stream);
 
 /* ---- §8f-1 (next): GEGLU gate of the motion feed-forward ------------------------------------
  * out[r, j] = hg[r, j] * gelu(hg[r, inner + j]); diffusers FeedForward("geglu") (un-vendored),

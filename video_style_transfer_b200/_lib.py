@@ -52,6 +52,7 @@ SIGNATURES = {
     "vst_lora_pack_up_bwd": (_i, [_p, _l, _i, _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _i, _i, _i, _p]),
     "vst_colsum_workspace_bytes": (_l, [_l, _i]),
     "vst_colsum": (_i, [_p, _l, _l, _i, _f, _p, _p, _l, _p]),
+    "vst_colsum_noalloc": (_i, [_p, _l, _l, _i, _f, _p, _p]),
     "vst_geglu": (_i, [_p, _p, _l, _i, _l, _l, _p]),
     "vst_cfg_euler_step": (_i, [_p, _p, _p, _p, _p, _l, _f, _f, _f, _i, _i, _p]),
     "vst_attn_bwd_workspace_bytes": (_l, [_i, _i, _i, _i, _i]),

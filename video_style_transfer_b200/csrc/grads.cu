@@ -143,3 +143,57 @@ extern "C" int vst_colsum(const void* x, int64_t ld, int64_t M, int N, float alp
   VST_LAUNCH_OK();
   return VST_OK;
 }
+
+
+// ---- vst_colsum_noalloc: vst_colsum for callers that cannot allocate ---------------------------------------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).  Same two
+// kernels as vst_colsum; the fp32 partials live in a file-scope device array instead of a caller workspace.
+//   * VST_COLSUM_NOALLOC_SCRATCH_BYTES (1 MiB) is the hard maximum: a shape whose partials
+//     (vst_colsum_workspace_bytes(M, N)) exceed it is refused with VST_E_UNSUPPORTED.  Every GPU that loads the
+//     library holds the array until the process exits.
+//   * The array is shared by every call and keeps the last call's contents.  Nothing has to start at zero: the first
+//     kernel writes every (chunk, column) slot the second one reads.  Calls that OVERLAP on the GPU (two streams,
+//     two host threads) race on it: serialise them.
+//   * In host code the array's NAME is a host-side stand-in, not a device address; the address is taken once per
+//     device, with that device current, by cudaGetSymbolAddress (no allocation), and passed to the kernels.
+static __device__ __align__(256) unsigned char g_colsum_noalloc_scratch[VST_COLSUM_NOALLOC_SCRATCH_BYTES];
+
+static int colsum_noalloc_scratch(float** out) {
+  constexpr int kMaxDevices = 64;
+  static float* ptrs[kMaxDevices] = {nullptr};
+  int dev = -1;
+  VST_CUDA_OK(cudaGetDevice(&dev));
+  VST_REQUIRE(dev >= 0 && dev < kMaxDevices, VST_E_UNSUPPORTED, "colsum_noalloc: device ordinal %d out of range", dev);
+  if (ptrs[dev] == nullptr) {
+    void* p = nullptr;
+    VST_CUDA_OK(cudaGetSymbolAddress(&p, g_colsum_noalloc_scratch));
+    VST_REQUIRE(p != nullptr, VST_E_CUDA, "colsum_noalloc: cudaGetSymbolAddress returned a null address");
+    ptrs[dev] = reinterpret_cast<float*>(p);
+  }
+  *out = ptrs[dev];
+  return VST_OK;
+}
+
+extern "C" int vst_colsum_noalloc(const void* x, int64_t ld, int64_t M, int N, float alpha, float* out,
+                                  void* stream) {
+  VST_REQUIRE(M > 0 && N > 0 && x && out, VST_E_BADARG, "colsum_noalloc: bad argument");
+  VST_REQUIRE(N % 2 == 0 && ld % 2 == 0, VST_E_UNSUPPORTED, "colsum_noalloc: N and ld must be even");
+  const int chunks = colsum_chunks(M, N);
+  const int64_t need = (int64_t)chunks * N * 4;
+  VST_REQUIRE(need <= (int64_t)VST_COLSUM_NOALLOC_SCRATCH_BYTES, VST_E_UNSUPPORTED,
+              "colsum_noalloc: M=%lld N=%d needs %lld bytes of scratch, the built-in array holds %lld "
+              "(use vst_colsum with a caller workspace)",
+              (long long)M, N, (long long)need, (long long)VST_COLSUM_NOALLOC_SCRATCH_BYTES);
+  float* scratch = nullptr;
+  int rc = colsum_noalloc_scratch(&scratch);
+  if (rc != VST_OK) return rc;
+  const int64_t rows_per_chunk = (M + chunks - 1) / chunks;
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 grid((N + kColsPerBlock - 1) / kColsPerBlock, chunks);
+  colsum_partial_kernel<<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, ld, M, N, rows_per_chunk, scratch);
+  VST_LAUNCH_OK();
+  colsum_final_kernel<<<(N + 255) / 256, 256, 0, st>>>(scratch, chunks, N, alpha, out);
+  VST_LAUNCH_OK();
+  return VST_OK;
+}
