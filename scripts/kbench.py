@@ -116,6 +116,16 @@ def main():
             report(f"lora_gemm {tag}", ms, b, None, 2 * m * n * (k1 + k2))
             ms, b = timeit(lambda: torch.nn.functional.linear(a1, b1, bias))
             report(f"  (cuBLAS F.linear, K1 only) {tag}", ms, b, None, 2 * m * n * k1)
+    if "dom" in which:
+        # the dominant launches of the batched-CFG step (lora_gemm2_kernel<256,0>, adapters folded): M = 2 x 16 frames
+        for tag, m, n, k in [("L2 q|k|v folded M=32768 N=3840 K=1280", 32768, 3840, 1280),
+                             ("L2 to_q / to_out folded M=32768 N=1280 K=1280", 32768, 1280, 1280),
+                             ("L1 q|k|v folded M=131072 N=1920 K=640", 131072, 1920, 640),
+                             ("L2 motion q|k|v M=32768 N=3840 K=1280 (same shape, temporal)", 32768, 3840, 1280)][:3]:
+            x = torch.randn(m, k, device="cuda").to(torch.bfloat16)
+            w = (torch.randn(n, k, device="cuda") / math.sqrt(k)).to(torch.bfloat16)
+            ms, b = timeit(lambda: ops.lora_gemm(x, w))
+            report(f"lora_gemm {tag}", ms, b, 2 * (m * k + n * k + m * n), 2 * m * n * k)
     if "fused" in which:
         # single-launch fused LoRA projection against the two-launch form (u = x A^T pre-pass + extra K blocks)
         # and against the plain GEMM with the adapters folded into W
