@@ -33,7 +33,17 @@ class PositionalEncoding(nn.Module):
         self.register_buffer("pe", pe)
 
     def table(self, device) -> torch.Tensor:
-        return self.pe.to(device=device, dtype=torch.float32).reshape(-1, self.pe.shape[-1]).contiguous()
+        """(max_len, C) fp32 view of the buffer for the kernels' fused position add; cached (the cast used to
+        be one ATen copy kernel per motion-module call once the module is bf16)."""
+        pe = self.pe
+        if pe.dtype == torch.float32 and pe.device == torch.device(device) and pe.is_contiguous():
+            return pe.reshape(-1, pe.shape[-1])
+        stamp = (pe.data_ptr(), pe._version, pe.dtype, str(device))
+        hit = getattr(self, "_table_cache", None)
+        if hit is None or hit[0] != stamp:
+            hit = (stamp, pe.to(device=device, dtype=torch.float32).reshape(-1, pe.shape[-1]).contiguous())
+            object.__setattr__(self, "_table_cache", hit)
+        return hit[1]
 
     def forward(self, x):
         """x (N, F, C) + pe[:, :F].  A (N,F,C) tensor is the planar view (B=N, C, F, HW=1), so the
