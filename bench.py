@@ -282,7 +282,9 @@ def sp_probe(args, world, rank, dev, steps):
     graphed = hpth.GraphedSPDenoiseStep(plan, xs4, xs3, texts, F, comm)
     for _ in range(3):
         graphed.replay()
-    ms_sp = timed(graphed.replay, steps)
+    with ClockSampler(dev.index) as clk_sp:               # rank 0's SM clock under the sharded step ...
+        sp_steps = max(steps, 20)                         # >= 0.7 s of timed region: enough clock samples
+        ms_sp = timed(graphed.replay, sp_steps)
 
     # ---- per-phase device time of one eager step (events on the launching stream) -----------------
     phases = {k: [] for k in ("gn_partials_share", "push", "normalize", "compute", "pull", "barrier_wait", "spatial")}
@@ -337,11 +339,12 @@ def sp_probe(args, world, rank, dev, steps):
             g1.replay()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(steps):
-            g1.replay()
-        e1.record()
-        torch.cuda.synchronize()
+        with ClockSampler(dev.index) as clk_sp1:          # ... and under the same video on this GPU alone
+            e0.record()
+            for _ in range(steps):
+                g1.replay()
+            e1.record()
+            torch.cuda.synchronize()
         ms_sp1[0] = e0.elapsed_time(e1) / steps
         del g1
     dist.all_reduce(ms_sp1, op=dist.ReduceOp.MAX)
@@ -356,9 +359,14 @@ def sp_probe(args, world, rank, dev, steps):
     del graphed
     comm.close()
     return {"workload": "cfg5-sequence-parallel: ONE 32-frame 1024^2 video, hot path, x2 CFG (batched B=2)",
-            "n_gpus": world, "frames": F, "frames_per_rank": fl_, "steps": steps,
+            "n_gpus": world, "frames": F, "frames_per_rank": fl_, "steps": sp_steps, "steps_sp1": steps,
             "ms_per_step": ms_sp, "ms_sp1": ms_sp1, "speedup": ms_sp1 / ms_sp,
             "efficiency": ms_sp1 / (world * ms_sp), "scaling": "strong",
+            "clocks": {"sp": clk_sp.summary(), "sp1": clk_sp1.summary() if rank == 0 else None,
+                       "note": "rank 0's SM clock sampled during each timed region; efficiency_iso_clock rescales "
+                               "ms_sp1 to the sharded run's median clock (compute-bound step)"},
+            "efficiency_iso_clock": (None if rank != 0 or not clk_sp.summary()["sm_mhz"] or not clk_sp1.summary()["sm_mhz"]
+                                     else (ms_sp1 * clk_sp1.summary()["sm_mhz"] / clk_sp.summary()["sm_mhz"]) / (world * ms_sp)),
             "nvlink_bytes_per_rank": egress, "parity_rel_err": perr.item(),
             "parity_note": "rank-sliced output of the sharded step vs the unsharded modules on one GPU, "
                            "max |a-b| / max |b| over the per-level outputs, max over ranks",
