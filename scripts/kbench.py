@@ -126,6 +126,18 @@ def main():
             w = (torch.randn(n, k, device="cuda") / math.sqrt(k)).to(torch.bfloat16)
             ms, b = timeit(lambda: ops.lora_gemm(x, w))
             report(f"lora_gemm {tag}", ms, b, 2 * (m * k + n * k + m * n), 2 * m * n * k)
+    if "geglu" in which:
+        # motion-module / spatial feed-forward, first GEMM with the GEGLU epilogue (batched-CFG M), per level
+        for tag, m, c in [("L0 M=524288 C=320", 524288, 320), ("L1 M=131072 C=640", 131072, 640),
+                          ("L2 M=32768 C=1280", 32768, 1280)]:
+            x = torch.randn(m, c, device="cuda").to(torch.bfloat16)
+            w = (torch.randn(8 * c, c, device="cuda") / math.sqrt(c)).to(torch.bfloat16)
+            bias = torch.randn(8 * c, device="cuda").to(torch.bfloat16)
+            ms, b = timeit(lambda: ops.lora_gemm(x, w, bias=bias, act="geglu"))
+            report(f"lora_gemm GEGLU {tag} -> 4C", ms, b, 2 * (m * c + 8 * c * c + m * 4 * c), 2 * m * c * 8 * c)
+            ms, b = timeit(lambda: ops.lora_gemm(x, w[:4 * c], bias=bias[:4 * c]))
+            report(f"  (plain GEMM, N = 4C: half the FLOPs, same output bytes) {tag}", ms, b,
+                   2 * (m * c + 4 * c * c + m * 4 * c), 2 * m * c * 4 * c)
     if "fused" in which:
         # single-launch fused LoRA projection against the two-launch form (u = x A^T pre-pass + extra K blocks)
         # and against the plain GEMM with the adapters folded into W

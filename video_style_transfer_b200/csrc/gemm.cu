@@ -361,6 +361,35 @@ __device__ __forceinline__ float gelu_as(float x) {
 // 1559 at L2 -- ~8000 clk of epilogue per 128 x 128 output tile against ~2600 clk of MMA: ~22 scalar FMA-pipe
 // instructions per element plus four bias shuffles per pair.  Packed: 10 FMA-pipe instructions per PAIR + 4 MUFU.
 __device__ __forceinline__ float2 f2(float a) { return make_float2(a, a); }
+// -DVST_GELU_ONE_MUFU=1 selects the one-MUFU form below.  Measured SLOWER (r02, kbench geglu L0: 980 vs 930 us):
+// the epilogue is bound by dependent FMA-pipe latency at two warps per scheduler, and this form is one ten-deep
+// serial chain where rcp + ex2 gives two shorter independent ones.  Kept for the record, off by default.
+#ifndef VST_GELU_ONE_MUFU
+#define VST_GELU_ONE_MUFU 0
+#endif
+#if VST_GELU_ONE_MUFU
+// Abramowitz-Stegun 7.1.28: erf(z) = 1 - (1 + a1 z + ... + a6 z^6)^-16, |err| < 3e-7.  ONE MUFU (rcp) per element
+// instead of rcp + ex2: 6 ffma2 + 4 fmul2 (squarings) per pair.  z large: the power overflows to +inf, rcp -> 0, erf -> 1.
+__device__ __forceinline__ float2 gelu2x_as(float2 x) {
+  const float2 ax = make_float2(fabsf(x.x), fabsf(x.y));
+  const float2 z = __fmul2_rn(ax, f2(0.70710678118654752f));
+  float2 d = __ffma2_rn(f2(0.0000430638f), z, f2(0.0002765672f));
+  d = __ffma2_rn(d, z, f2(0.0001520143f));
+  d = __ffma2_rn(d, z, f2(0.0092705272f));
+  d = __ffma2_rn(d, z, f2(0.0422820123f));
+  d = __ffma2_rn(d, z, f2(0.0705230784f));
+  d = __ffma2_rn(d, z, f2(1.f));
+  d = __fmul2_rn(d, d);
+  d = __fmul2_rn(d, d);
+  d = __fmul2_rn(d, d);
+  d = __fmul2_rn(d, d);
+  float2 r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r.x) : "f"(d.x));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r.y) : "f"(d.y));
+  // x + |x| erf = (x + |x|) - |x| r
+  return __ffma2_rn(make_float2(-ax.x, -ax.y), r, __fadd2_rn(x, ax));
+}
+#else
 __device__ __forceinline__ float2 gelu2x_as(float2 x) {
   const float2 ax = make_float2(fabsf(x.x), fabsf(x.y));
   const float2 den = __ffma2_rn(f2(0.3275911f * 0.70710678118654752f), ax, f2(1.f));
@@ -381,6 +410,7 @@ __device__ __forceinline__ float2 gelu2x_as(float2 x) {
   const float2 erfa = __ffma2_rn(make_float2(-pt.x, -pt.y), e, f2(1.f));
   return __ffma2_rn(ax, erfa, x);
 }
+#endif
 // eight consecutive bias values, the same address in every lane (one broadcast load per 4 / 8 values)
 __device__ __forceinline__ void bias8(const EpiArgs& ep, int col, float* b) {
   if (ep.bias_bf16) {
