@@ -116,11 +116,15 @@ struct AttnArgs {
 constexpr int NQ = 3;
 constexpr int kSmemBytesP = kTile * (NQ + 2 * KST) + 256;
 
-template <int kPoly, bool kMask>
+// BKVT: keys per block.  128 everywhere except text cross-attention (Sk = 77 <= 80: ONE block per item), which runs
+// with an 80-key block: 5 instead of 8 score / PV k-steps and 40 instead of 64 exponential pairs per row (r02: the
+// 128-wide block spent 40 % of its softmax and MMA work on masked columns; 70 launches, 5.9 ms of the step).
+template <int kPoly, bool kMask, int BKVT = BKV>
 __global__ void __launch_bounds__(kThreads, 2)
 attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                      const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
                      AttnArgs a, int n_items, int ntile) {
+  static_assert(BKVT == BKV || (!kMask && BKVT % 16 == 0 && BKVT > 64 && BKVT < BKV), "BKVT: 128, or a cross-attention block in (64, 128)");
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;                 // 128B-swizzled tiles need 1024-byte alignment (checked)
   uint8_t* sQ = smem;                       // [NQ] query tiles (each reused to stage its item's O)
@@ -142,7 +146,8 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_free + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nblk = (a.Sk + BKV - 1) / BKV;
+  const int nblk = (a.Sk + BKVT - 1) / BKVT;
+  constexpr uint32_t kKVBytes = BKVT * HD * 2;           // bytes one K / V block load brings in
 
   if (threadIdx.x == 0) {
     if (smem_u32(smem) & 1023u) {
@@ -192,11 +197,11 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
           const int st = g % KST;
           const uint32_t ph = ((g / KST) & 1) ^ 1;
           mbar_wait(&k_empty[st], ph, 10);
-          mbar_arrive_expect_tx(&k_full[st], kTile);
-          tma_load_3d(sK + st * kTile, &tmK, &k_full[st], head * HD, j * BKV, bk);
+          mbar_arrive_expect_tx(&k_full[st], kKVBytes);
+          tma_load_3d(sK + st * kTile, &tmK, &k_full[st], head * HD, j * BKVT, bk);
           mbar_wait(&v_empty[st], ph, 11);
-          mbar_arrive_expect_tx(&v_full[st], kTile);
-          tma_load_3d(sV + st * kTile, &tmV, &v_full[st], head * HD, j * BKV, bk);
+          mbar_arrive_expect_tx(&v_full[st], kKVBytes);
+          tma_load_3d(sV + st * kTile, &tmV, &v_full[st], head * HD, j * BKVT, bk);
         }
       }
     }
@@ -207,7 +212,7 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     const uint32_t tS = tmem_base;             // S (fp32) columns [0,128)
     const uint32_t tO = tS + 128;              // O accumulator (fp32), 64 columns
     const uint32_t tP = tS + 192;              // P (bf16 pairs), 64 columns
-    constexpr uint32_t idesc_s = umma_idesc_bf16(BQ, BKV, 0, 0);
+    constexpr uint32_t idesc_s = umma_idesc_bf16(BQ, BKVT, 0, 0);
     constexpr uint32_t idesc_o = umma_idesc_bf16(BQ, HD, 0, 1);  // B (= V) is MN-major
     uint32_t g = 0, blk = 0;
     int i = 0;
@@ -255,7 +260,7 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         TRACE(6, blk + j);
         if (issuer) {
 #pragma unroll
-          for (int k = 0; k < BKV / 16; ++k)
+          for (int k = 0; k < BKVT / 16; ++k)
             umma_bf16_ts(tO, tP + 8 * k, dv + uint64_t((k * 2048) >> 4), idesc_o, (j | k) != 0);
           umma_commit(&v_empty[st]);
           umma_commit(o_full);
@@ -339,14 +344,14 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       float m = -INFINITY;               // running (possibly stale) row max, log2 domain
       float2 l2 = make_float2(0.f, 0.f);
       for (int j = 0; j < nblk; ++j) {
-        const int kv0 = j * BKV;
-        const bool tail = kv0 + BKV > a.Sk;
+        const int kv0 = j * BKVT;
+        const bool tail = kv0 + BKVT > a.Sk;
         mbar_wait(s_full, (blk + j) & 1, 30);
         TRACE(0, blk + j);
         tc_fence_after();
         uint32_t r[BKV];
 #pragma unroll
-        for (int c = 0; c < BKV / 32; ++c) tmem_ld32(tS + c * 32, r + c * 32);
+        for (int c = 0; c < (BKVT + 31) / 32; ++c) tmem_ld32(tS + c * 32, r + c * 32);   // (80: 96 columns read)
         if (p_pending) {
           // the previous block's P store completes under this block's S load (traces: the
           // tcgen05.wait::st + fence + arrive chain cost ~200 clk per block when it sat behind
@@ -362,7 +367,7 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         mbar_arrive(s_free);             // the tensor pipe may overwrite S now
         if (tail) {
 #pragma unroll
-          for (int e = 0; e < BKV; ++e)
+          for (int e = 0; e < BKVT; ++e)
             if (kv0 + e >= a.Sk) r[e] = 0xff800000u;  // -inf: excluded from max, exp2 -> 0
         }
         if constexpr (kMask) {
@@ -391,7 +396,7 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         const float sl = kMask ? 1.f : a.scale_log2;
         float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-        for (int e = 0; e < BKV; e += 8) {
+        for (int e = 0; e < BKVT; e += 8) {
 #pragma unroll
           for (int c = 0; c < 4; ++c)
             mx4[c] = fmaxf(mx4[c], fmaxf(__uint_as_float(r[e + 2 * c]), __uint_as_float(r[e + 2 * c + 1])));
@@ -405,7 +410,7 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         l2 = __fmul2_rn(l2, make_float2(alpha, alpha));
         const float2 nm2 = make_float2(-m_use, -m_use);
 #pragma unroll
-        for (int e = 0; e < BKV / 2; ++e) {
+        for (int e = 0; e < BKVT / 2; ++e) {
           const float2 sv = __ffma2_rn(
               make_float2(__uint_as_float(r[2 * e]), __uint_as_float(r[2 * e + 1])), sc2, nm2);
           const bool poly = ((e * kPoly) & 7) + kPoly > 7 && kPoly > 0;
@@ -441,7 +446,7 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
           epilogue(pend_it, i - 1, pend_inv, pend_lse, blk - 1);
         }
         tmem_st32(tP, r);
-        tmem_st32(tP + 32, r + 32);
+        if (BKVT > 64) tmem_st32(tP + 32, r + 32);      // (80 keys = 40 packed words: words 40..63 are never read)
         p_pending = true;                // completion + p_full arrive: under the next S load
         TRACE(4, blk + j);
       }
@@ -468,11 +473,11 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
 }
 
 int make_qkv_map(CUtensorMap* m, const void* p, int64_t B, int64_t S, int width, int64_t ld,
-                 int rank4) {
+                 int rank4, int box_rows = 128) {
   const uint64_t dims[4] = {(uint64_t)width, (uint64_t)S, (uint64_t)B, 1};
   const uint64_t strides[4] = {2, (uint64_t)ld * 2, (uint64_t)S * ld * 2,
                                (uint64_t)B * S * ld * 2};
-  const uint32_t box[4] = {HD, 128, 1, 1};
+  const uint32_t box[4] = {HD, (uint32_t)box_rows, 1, 1};
   return vst_make_tmap(m, p, rank4 ? 4 : 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
@@ -500,8 +505,12 @@ extern "C" int vst_attn_fwd(const void* q, const void* k, const void* v, void* o
   int rc;
   const int width = heads * HD;
   if ((rc = make_qkv_map(&tQ, q, Bt, Sq, width, ldq, 0))) return rc;
-  if ((rc = make_qkv_map(&tK, k, Bt / kv_group, Sk, width, ldk, 0))) return rc;
-  if ((rc = make_qkv_map(&tV, v, Bt / kv_group, Sk, width, ldv, 0))) return rc;
+  // text cross-attention (Sk = 77): one 80-key block per item instead of a 128-key one (VST_ATTN_BKV80=0: off)
+  static int allow80 = -1;
+  if (allow80 < 0) { const char* e = getenv("VST_ATTN_BKV80"); allow80 = (e && e[0] == '0') ? 0 : 1; }
+  const bool kv80 = allow80 && mask == nullptr && Sk > 64 && Sk <= 80;
+  if ((rc = make_qkv_map(&tK, k, Bt / kv_group, Sk, width, ldk, 0, kv80 ? 80 : 128))) return rc;
+  if ((rc = make_qkv_map(&tV, v, Bt / kv_group, Sk, width, ldv, 0, kv80 ? 80 : 128))) return rc;
   if ((rc = make_qkv_map(&tO, o, Bt, Sq, width, ldo, 1))) return rc;
   // kPoly: how many of every 8 exp2 pairs run on the FMA pipe.  VST_ATTN_POLY (0..3) overrides the
   // default, VST_ATTN_CTAS_PER_SM the persistent grid (tuning only).
@@ -516,6 +525,7 @@ extern "C" int vst_attn_fwd(const void* q, const void* k, const void* v, void* o
     VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_pers_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesP));
     VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_pers_kernel<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesP));
     VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_pers_kernel<kDefaultPoly, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesP));
+    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_pers_kernel<kDefaultPoly, false, 80>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesP));
   }
   const int vec4 = mask && (reinterpret_cast<uintptr_t>(mask) & 15) == 0 && mask_sb % 4 == 0 &&
                    mask_sh % 4 == 0 && mask_sq % 4 == 0;
@@ -529,6 +539,8 @@ extern "C" int vst_attn_fwd(const void* q, const void* k, const void* v, void* o
   const int n = (int)items;
   if (mask) {
     attn_fwd_pers_kernel<kDefaultPoly, true><<<pgrid, kThreads, kSmemBytesP, st>>>(tQ, tK, tV, tO, a, n, ntile);
+  } else if (kv80) {
+    attn_fwd_pers_kernel<kDefaultPoly, false, 80><<<pgrid, kThreads, kSmemBytesP, st>>>(tQ, tK, tV, tO, a, n, ntile);
   } else {
     switch (poly) {
       case 0: attn_fwd_pers_kernel<0, false><<<pgrid, kThreads, kSmemBytesP, st>>>(tQ, tK, tV, tO, a, n, ntile); break;
