@@ -215,8 +215,11 @@ def main():
             report(f"vst_gemm TN split-K {tag}", ms, b, (a.numel() + x.numel()) * 2, 2 * m * n * k)
             ms, b = timeit(lambda: a.t() @ x)
             report(f"  (cuBLAS matmul) {tag}", ms, b, (a.numel() + x.numel()) * 2, 2 * m * n * k)
+    if "bwd" in which or "abwd" in which:
         for tag, bt, h, sq, sk in [("L1 self", 16, 10, 4096, 4096), ("L2 self", 16, 20, 1024, 1024),
                                    ("L1 cross", 16, 10, 4096, 77), ("L2 cross", 16, 20, 1024, 77)]:
+            if "bwd" not in which and "cross" in tag:
+                continue
             c = h * 64
             bk = bt if "self" in tag else 1
             q = torch.randn(bt, sq, c, device="cuda").to(bf)
@@ -227,7 +230,7 @@ def main():
             fl = 10 * bt * h * sq * sk * 64
             ms, b = timeit(lambda: ops.attn_bwd(q, k, v, o, do, lse, h))
             report(f"attn_bwd {tag} B={bt} h={h} Sq={sq} Sk={sk}", ms, b, None, fl)
-            if bk == bt:
+            if bk == bt and "bwd" in which:
                 qh, kh, vh = (t.view(bt, -1, h, 64).transpose(1, 2).detach().requires_grad_() for t in (q, k, v))
                 with torch.enable_grad():
                     oh = torch.nn.functional.scaled_dot_product_attention(qh, kh, vh)

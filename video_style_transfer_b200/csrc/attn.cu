@@ -28,6 +28,13 @@
 #include <stdlib.h>
 #include <type_traits>
 
+// Watchdog placement (r02, kbench attn on one box): with the counting watchdog in every role's waits the L1 / L2
+// self shapes ran at 855 / 718 TFLOP/s, with none at 888 / 744 (the 208-register softmax loop and the 48-register
+// auxiliary warps have no spare register for the poll counter).  The softmax and MMA warps therefore wait with
+// mbar_wait_plain; the TMA producer and the store warp keep mbar_wait -- every deadlock of this protocol ends with
+// the store warp waiting for an o_staged that never comes (or the producer for a k_empty), so the launch still
+// fails loudly instead of hanging.
+#define VST_MBAR_QUIET 1
 #include "common.cuh"
 
 namespace {
@@ -218,7 +225,7 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     int i = 0;
     auto issue_s = [&](uint64_t dq, uint32_t gg, uint32_t tr) {
       const int st = gg % KST;
-      mbar_wait(&k_full[st], (gg / KST) & 1, 21);
+      mbar_wait_plain(&k_full[st], (gg / KST) & 1);
       tc_fence_after();
       const uint64_t dk = umma_desc_sw128(smem_u32(sK + st * kTile), 1024);
       TRACE(5, tr);
@@ -234,7 +241,7 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       const int buf = i % NQ;
       const uint64_t dq = umma_desc_sw128(smem_u32(sQ + buf * kTile), 1024);
       if (i == 0) {
-        mbar_wait(&q_full[0], 0, 20);
+        mbar_wait_plain(&q_full[0], 0);
         issue_s(dq, 0, 0);
       }
       const bool has_next = it + (int)gridDim.x < n_items;
@@ -243,18 +250,18 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         // item, or the FIRST block of the next item (its Q sits in the next ring buffer) -- is
         // issued as soon as S_j is in registers, so it overlaps softmax j also across items.
         if (j + 1 < nblk) {
-          mbar_wait(s_free, (blk + j) & 1, 24);
+          mbar_wait_plain(s_free, (blk + j) & 1);
           issue_s(dq, g + j + 1, blk + j + 1);
         } else if (has_next) {
           const int nb = (i + 1) % NQ;
-          mbar_wait(&q_full[nb], ((i + 1) / NQ) & 1, 20);
-          mbar_wait(s_free, (blk + j) & 1, 25);
+          mbar_wait_plain(&q_full[nb], ((i + 1) / NQ) & 1);
+          mbar_wait_plain(s_free, (blk + j) & 1);
           issue_s(umma_desc_sw128(smem_u32(sQ + nb * kTile), 1024), g + nblk, blk + nblk);
         }
         const int st = (g + j) % KST;
-        mbar_wait(p_full, (blk + j) & 1, 22);
-        if (j == 0) mbar_wait(o_free, (i & 1) ^ 1, 26);    // the previous item's O has left TMEM
-        mbar_wait(&v_full[st], ((g + j) / KST) & 1, 23);
+        mbar_wait_plain(p_full, (blk + j) & 1);
+        if (j == 0) mbar_wait_plain(o_free, (i & 1) ^ 1);    // the previous item's O has left TMEM
+        mbar_wait_plain(&v_full[st], ((g + j) / KST) & 1);
         tc_fence_after();
         const uint64_t dv = umma_desc_sw128(smem_u32(sV + st * kTile), 1024, 8192);
         TRACE(6, blk + j);
@@ -305,7 +312,7 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     bool p_pending = false;              // a P store is in flight, p_full not yet signalled
     auto epilogue = [&](int pit, int pi, float inv, float lse, uint32_t last_blk) {
       // O of item pit (ring slot pi % NQ): TMEM -> normalise -> its dead Q buffer -> store warp
-      mbar_wait(o_full, last_blk & 1, 32);
+      mbar_wait_plain(o_full, last_blk & 1);
       TRACE(7, pi);
       tc_fence_after();
       uint8_t* orow = sQ + (pi % NQ) * kTile + row * 128;
@@ -346,7 +353,7 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       for (int j = 0; j < nblk; ++j) {
         const int kv0 = j * BKVT;
         const bool tail = kv0 + BKVT > a.Sk;
-        mbar_wait(s_full, (blk + j) & 1, 30);
+        mbar_wait_plain(s_full, (blk + j) & 1);
         TRACE(0, blk + j);
         tc_fence_after();
         uint32_t r[BKV];
@@ -420,7 +427,7 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         }
         TRACE(2, blk + j);
         if (j > 0) {
-          mbar_wait(o_full, (blk + j - 1) & 1, 31);   // P V of the previous block is done with P and O
+          mbar_wait_plain(o_full, (blk + j - 1) & 1);   // P V of the previous block is done with P and O
           TRACE(3, blk + j);
           tc_fence_after();
           if (__any_sync(0xffffffffu, grow)) {

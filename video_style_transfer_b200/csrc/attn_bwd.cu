@@ -24,7 +24,29 @@
 // Roofline: tensor pipe; FLOPs = 2.5 x forward = 10 * Bt*h*Sq*Sk*d.
 #include "common.cuh"
 
+// -DVST_BWD_ABLATE=<bits>: timing-only builds that drop one stage (WRONG results; never shipped):
+// 1 = no dQ atomics, 2 = no exponential / dS arithmetic, 8 = no dV / dK / dQ MMAs, 16 = no P / dS stores.
+#ifndef VST_BWD_ABLATE
+#define VST_BWD_ABLATE 0
+#endif
+
+// VST_BWD_WARP_ARRIVE: one elected mbarrier arrival per warp (after __syncwarp) instead of one per thread
+#ifndef VST_BWD_WARP_ARRIVE
+#define VST_BWD_WARP_ARRIVE 1
+#endif
+
 namespace {
+
+#if VST_BWD_WARP_ARRIVE
+constexpr int kArrivePerWarp = 1;
+__device__ __forceinline__ void warp_arrive(uint64_t* bar) {
+  __syncwarp();
+  if ((threadIdx.x & 31) == 0) mbar_arrive(bar);
+}
+#else
+constexpr int kArrivePerWarp = 32;
+__device__ __forceinline__ void warp_arrive(uint64_t* bar) { mbar_arrive(bar); }
+#endif
 
 constexpr int BQ = 128, BKV = 128, HD = 64;
 constexpr int kTile = 128 * HD * 2;     // 16 KB: one [128 x 64] bf16 tile
@@ -151,11 +173,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       mbar_init(&q_empty[i], 1);
     }
     mbar_init(sdp_full, 1);
-    mbar_init(sdp_free, 32 * kSoftmaxWarps);
-    mbar_init(pds_full, 32 * kSoftmaxWarps);
+    mbar_init(sdp_free, kArrivePerWarp * kSoftmaxWarps);
+    mbar_init(pds_full, kArrivePerWarp * kSoftmaxWarps);
     mbar_init(pds_free, 1);
     mbar_init(dq_full, 1);
-    mbar_init(dq_free, 128);
+    mbar_init(dq_free, kArrivePerWarp * 4);
     fence_mbar_init();
   }
   if (warp == kMmaWarp) tmem_alloc(tmem_slot, 512);
@@ -225,6 +247,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       const uint64_t ddO_mn = umma_desc_sw128(smem_u32(sdO + st * kTile), 1024, 8192);
       const uint64_t dQ_mn = umma_desc_sw128(smem_u32(sQ + st * kTile), 1024, 8192);
       if (issuer) {
+#if VST_BWD_ABLATE & 8
+        if (i < 0)
+#endif
+        {
 #pragma unroll
         for (int k = 0; k < BQ / 16; ++k)     // dV += P^T dO : contraction over the 128 query rows
           umma_bf16_ss(tdV, dP_mn + kRow16 * k, ddO_mn + kRow16 * k, idesc_t, (i | k) != 0);
@@ -235,6 +261,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         for (int k = 0; k < BKV / 16; ++k) {  // dQ = dS K : contraction over the 128 keys
           const uint64_t dS_k = umma_desc_sw128(smem_u32(sdS + (k >> 2) * 16384), 1024);
           umma_bf16_ss(tdQ, dS_k + 2 * (k & 3), dK_mn + kRow16 * k, idesc_q, k != 0);
+        }
         }
         umma_commit(&q_empty[st]);
         umma_commit(pds_free);
@@ -271,7 +298,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         tmem_ld_wait();
         if (c == 1) {
           tc_fence_before();
-          mbar_arrive(sdp_free);       // S / dP may be overwritten by the next pair
+          warp_arrive(sdp_free);       // S / dP may be overwritten by the next pair
         }
         const int key0 = kv0 + half * 64 + c * 32;
 #pragma unroll
@@ -281,6 +308,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             if (key0 + 2 * e < a.Sk) b0 = fmaf(__ldg(mrow + key0 + 2 * e), 1.4426950408889634f, -lse2);
             if (key0 + 2 * e + 1 < a.Sk) b1 = fmaf(__ldg(mrow + key0 + 2 * e + 1), 1.4426950408889634f, -lse2);
           }
+#if VST_BWD_ABLATE & 2
+          pw[c * 16 + e] = s[2 * e] ^ __float_as_uint(b0);
+          dsw[c * 16 + e] = dp[2 * e + 1] ^ __float_as_uint(b1);
+          continue;
+#endif
           float p0 = ex2f(fmaf(__uint_as_float(s[2 * e]), a.scale_log2, b0));
           float p1 = ex2f(fmaf(__uint_as_float(s[2 * e + 1]), a.scale_log2, b1));
           if (key0 + 2 * e >= a.Sk) p0 = 0.f;
@@ -293,13 +325,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
       if (i > 0) mbar_wait(pds_free, (i - 1) & 1, 31);   // previous pair's MMAs are done with sP / sdS
 #pragma unroll
-      for (int cc = 0; cc < 8; ++cc) {
+      for (int cc = 0; cc < ((VST_BWD_ABLATE & 16) ? 0 : 8); ++cc) {
         const int off = (cc ^ rx) * 16;
         *reinterpret_cast<uint4*>(prow + off) = make_uint4(pw[4 * cc], pw[4 * cc + 1], pw[4 * cc + 2], pw[4 * cc + 3]);
         *reinterpret_cast<uint4*>(dsrow + off) = make_uint4(dsw[4 * cc], dsw[4 * cc + 1], dsw[4 * cc + 2], dsw[4 * cc + 3]);
       }
       fence_proxy_async_smem();
-      mbar_arrive(pds_full);
+      warp_arrive(pds_full);
     }
     // ---- dV (half 0) / dK (half 1): TMEM lane = key row ----
     mbar_wait(pds_free, (nq - 1) & 1, 32);
@@ -351,9 +383,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       tmem_ld32(tdQ + lane_off + 32, o + 32);
       tmem_ld_wait();
       tc_fence_before();
-      mbar_arrive(dq_free);
+      warp_arrive(dq_free);
       const int q = i * BQ + row;
-      if (q < a.Sq) {
+      if (q < a.Sq && !(VST_BWD_ABLATE & 1)) {
         float* dst = a.dq_acc + (((int64_t)b * a.heads + head) * a.Sq + q) * HD;
 #pragma unroll
         for (int v = 0; v < 16; ++v)

@@ -124,10 +124,31 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t by
 }
 
 // Watchdog: a protocol bug in a warp-specialised kernel would otherwise spin forever and hang
-// the box.  After ~4 s without progress the waiter records where it was and traps, which
-// fails the launch loudly instead.
+// the box.  A waiter that has polled VST_WATCHDOG_SPINS times without progress traps, which fails
+// the launch loudly instead.  The bound is a poll COUNT: one unsuccessful mbarrier.try_wait
+// suspends the thread for ~4 us whatever the hint (scripts/ubench/trywait_limit.cu: 7845 clk), so
+// 2^20 polls are ~4 s -- never a legitimate wait in these kernels.
+// VST_MBAR_QUIET (defined by a .cu before this header): trap without the printf that names the
+// barrier.  The printf call in the wait loop costs the register-tight attention kernels 6-12 %
+// (r02, kbench attn, same box: L1 self 824-845 -> 891 TFLOP/s, L2 self 694-717 -> 743, text cross
+// 49.2 -> 45.1 us) while the GEMM kernels measure 6 % FASTER with it (1673 vs 1572 TFLOP/s at the
+// L2 q|k|v shape), so each file chooses; -DVST_WATCHDOG_VERBOSE brings the message back everywhere.
 #ifndef VST_WATCHDOG_NS
 #define VST_WATCHDOG_NS 4000000000ull
+#endif
+#ifndef VST_WATCHDOG_SPINS
+#define VST_WATCHDOG_SPINS (1u << 20)
+#endif
+#if defined(VST_MBAR_QUIET) && !defined(VST_WATCHDOG_VERBOSE)
+#define mbar_timeout(tag) __trap()
+#else
+// (inlined: a __noinline__ helper makes ptxas give up on the setmaxnreg kernels)
+#define mbar_timeout(tag)                                                                            \
+  do {                                                                                               \
+    printf("vst watchdog: mbarrier wait timed out (tag %d, block %d,%d,%d thread %d)\n", (tag),      \
+           blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x);                                         \
+    __trap();                                                                                        \
+  } while (0)
 #endif
 __device__ __forceinline__ uint64_t globaltimer_ns() {
   uint64_t t;
@@ -159,8 +180,26 @@ __device__ __forceinline__ uint32_t mbar_test(uint64_t* bar, uint32_t parity) {
       : "memory");
   return done;
 }
+// -DVST_MBAR_MODE (tuning builds): 1 = try_wait loop without the watchdog, 2 = test_wait spin (no suspend),
+// 3 = the r01 clock-bounded watchdog
+#ifndef VST_MBAR_MODE
+#define VST_MBAR_MODE 0
+#endif
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int tag = 0) {
   const uint32_t addr = smem_u32(bar);
+#if VST_MBAR_MODE == 1
+  while (!mbar_try_wait(addr, parity)) {}
+  return;
+#elif VST_MBAR_MODE == 2
+  while (!mbar_test(bar, parity)) {}
+  return;
+#elif VST_MBAR_MODE == 0
+  uint32_t spins = 0;
+  while (!mbar_try_wait(addr, parity))
+    if (++spins > VST_WATCHDOG_SPINS) mbar_timeout(tag);
+  return;
+#endif
+  // VST_MBAR_MODE == 3: the r01 form (clock-bounded), kept for A/B timing
   if (mbar_try_wait(addr, parity)) return;
   const uint64_t t0 = globaltimer_ns();
   while (!mbar_try_wait(addr, parity)) {
@@ -172,12 +211,18 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int ta
   }
 }
 
+// wait without the watchdog counter, for roles whose register budget is full.  Only valid in a kernel where some
+// OTHER role that every deadlock also blocks (a producer or a store warp) waits with mbar_wait.
+__device__ __forceinline__ void mbar_wait_plain(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  while (!mbar_try_wait(addr, parity)) {}
+}
+
 // wait whose acquire is cluster-scoped: pairs with a peer CTA's mbarrier.arrive.release.cluster when DATA
 // (shared-memory writes of the peer, read next by this CTA's tcgen05 ops) rides on the barrier
 __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity, int tag = 0) {
   const uint32_t addr = smem_u32(bar);
-  const uint64_t t0 = globaltimer_ns();
-  uint32_t done = 0;
+  uint32_t done = 0, spins = 0;
   while (!done) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
@@ -186,11 +231,7 @@ __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity
         : "=r"(done)
         : "r"(addr), "r"(parity), "r"(1000000u)
         : "memory");
-    if (!done && globaltimer_ns() - t0 > VST_WATCHDOG_NS) {
-      printf("vst watchdog: cluster mbarrier wait timed out (tag %d, block %d thread %d)\n", tag, blockIdx.x,
-             threadIdx.x);
-      __trap();
-    }
+    if (!done && ++spins > VST_WATCHDOG_SPINS) mbar_timeout(tag);
   }
 }
 
