@@ -30,10 +30,10 @@
 
 // Watchdog placement (r02, kbench attn on one box): with the counting watchdog in every role's waits the L1 / L2
 // self shapes ran at 855 / 718 TFLOP/s, with none at 888 / 744 (the 208-register softmax loop and the 48-register
-// auxiliary warps have no spare register for the poll counter).  The softmax and MMA warps therefore wait with
-// mbar_wait_plain; the TMA producer and the store warp keep mbar_wait -- every deadlock of this protocol ends with
-// the store warp waiting for an o_staged that never comes (or the producer for a k_empty), so the launch still
-// fails loudly instead of hanging.
+// auxiliary warps have no spare register for the poll counter; the producer's waits are on the critical path of
+// the one-block text cross-attention items, 48 -> 45 us).  Every role but one therefore waits with mbar_wait_plain;
+// the store warp keeps mbar_wait -- every deadlock of this protocol ends with the store warp waiting for an
+// o_staged that never comes, so the launch still fails loudly instead of hanging.
 #define VST_MBAR_QUIET 1
 #include "common.cuh"
 
@@ -43,8 +43,12 @@ constexpr int BQ = 128;   // query rows per CTA
 constexpr int BKV = 128;  // keys per block
 constexpr int HD = 64;    // head dim
 constexpr int kThreads = 256;          // warpgroup 0: softmax; warpgroup 1: TMA, MMA, store, idle
-constexpr int kRegsSoftmax = 208;      // setmaxnreg: 128 * 208 + 128 * 48 = half the register file,
-constexpr int kRegsAux = 48;           // so two CTAs stay resident and the softmax loop does not spill
+#ifndef VST_ATTN_REGS_SM
+#define VST_ATTN_REGS_SM 208
+#define VST_ATTN_REGS_AUX 48
+#endif
+constexpr int kRegsSoftmax = VST_ATTN_REGS_SM;      // setmaxnreg: 128 * 208 + 128 * 48 = half the register file,
+constexpr int kRegsAux = VST_ATTN_REGS_AUX;           // so two CTAs stay resident and the softmax loop does not spill
 constexpr int KST = 2;    // K and V stages
 constexpr int kTile = 128 * HD * 2;  // 16 KB
 constexpr int kDefaultPoly = 2;
@@ -197,16 +201,16 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++i) {
         const int qtile = it % ntile, head = (it / ntile) % a.heads, b = it / (ntile * a.heads);
         const int bk = b / a.kv_group, buf = i % NQ;
-        mbar_wait(&q_empty[buf], ((i / NQ) & 1) ^ 1, 40);
+        mbar_wait_plain(&q_empty[buf], ((i / NQ) & 1) ^ 1);
         mbar_arrive_expect_tx(&q_full[buf], kTile);
         tma_load_3d(sQ + buf * kTile, &tmQ, &q_full[buf], head * HD, qtile * BQ, b);
         for (int j = 0; j < nblk; ++j, ++g) {
           const int st = g % KST;
           const uint32_t ph = ((g / KST) & 1) ^ 1;
-          mbar_wait(&k_empty[st], ph, 10);
+          mbar_wait_plain(&k_empty[st], ph);
           mbar_arrive_expect_tx(&k_full[st], kKVBytes);
           tma_load_3d(sK + st * kTile, &tmK, &k_full[st], head * HD, j * BKVT, bk);
-          mbar_wait(&v_empty[st], ph, 11);
+          mbar_wait_plain(&v_empty[st], ph);
           mbar_arrive_expect_tx(&v_full[st], kKVBytes);
           tma_load_3d(sV + st * kTile, &tmV, &v_full[st], head * HD, j * BKVT, bk);
         }
