@@ -283,7 +283,8 @@ def sp_probe(args, world, rank, dev, steps):
     for _ in range(3):
         graphed.replay()
     with ClockSampler(dev.index) as clk_sp:               # rank 0's SM clock under the sharded step ...
-        sp_steps = max(steps, 20)                         # >= 0.7 s of timed region: enough clock samples
+        sp_steps = max(steps, 20 * world)                 # ~5 s of timed region at every N: nvidia-smi answers in
+                                                          # 0.3-1 s with N ranks polling, 20 steps at N = 8 gave ONE sample
         ms_sp = timed(graphed.replay, sp_steps)
 
     # ---- per-phase device time of one eager step (events on the launching stream) -----------------
