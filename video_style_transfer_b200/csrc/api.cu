@@ -229,6 +229,12 @@ static EncodeTiledFn get_encode() {
 int vst_make_tmap(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
                   const uint64_t* strides_bytes, const uint32_t* box, CUtensorMapSwizzle swz,
                   CUtensorMapL2promotion l2) {
+  return vst_make_tmap_dt(out, base, rank, dims, strides_bytes, box, swz, l2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16);
+}
+
+int vst_make_tmap_dt(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
+                     const uint64_t* strides_bytes, const uint32_t* box, CUtensorMapSwizzle swz,
+                     CUtensorMapL2promotion l2, CUtensorMapDataType dt) {
   EncodeTiledFn enc = get_encode();
   VST_REQUIRE(enc != nullptr, VST_E_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
   VST_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, VST_E_BADARG,
@@ -246,14 +252,14 @@ int vst_make_tmap(CUtensorMap* out, const void* base, int rank, const uint64_t* 
                   (unsigned long long)s[i - 1], i);
     }
   }
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base),
+  CUresult r = enc(out, dt, (cuuint32_t)rank, const_cast<void*>(base),
                    d, s, b, es, CU_TENSOR_MAP_INTERLEAVE_NONE, swz, l2,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r == CUDA_ERROR_INVALID_CONTEXT) {
     // a thread that has made no runtime call yet (torch's autograd worker entering a backward whose first
     // device action is this driver call) has no current context: bind the primary one and retry
     cudaFree(0);
-    r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), d, s, b, es,
+    r = enc(out, dt, (cuuint32_t)rank, const_cast<void*>(base), d, s, b, es,
             CU_TENSOR_MAP_INTERLEAVE_NONE, swz, l2, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   }
   VST_REQUIRE(r == CUDA_SUCCESS, VST_E_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d",

@@ -31,8 +31,23 @@
 #endif
 
 // VST_BWD_WARP_ARRIVE: one elected mbarrier arrival per warp (after __syncwarp) instead of one per thread
+#ifndef VST_BWD_COMMIT_ORDER
+#define VST_BWD_COMMIT_ORDER 0
+#endif
+#ifndef VST_BWD_ELECT_WAIT
+#define VST_BWD_ELECT_WAIT 0
+#endif
 #ifndef VST_BWD_WARP_ARRIVE
 #define VST_BWD_WARP_ARRIVE 1
+#endif
+
+// -DVST_BWD_TRACE: CTA (0,0,0) records clock64() stamps of its pipeline events (scripts/attn_bwd_trace.py)
+#ifdef VST_BWD_TRACE
+__device__ long long g_bwd_trace[12 * 64];   // [slot][pair index]
+#define BTRACE(slot, idx) do { if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (idx) < 64 && \
+    (threadIdx.x & 31) == 0) g_bwd_trace[(slot) * 64 + (idx)] = clock64(); } while (0)
+#else
+#define BTRACE(slot, idx) do { } while (0)
 #endif
 
 namespace {
@@ -54,13 +69,52 @@ constexpr int kPBytes = 128 * 128 * 2;  // 32 KB: P or dS, two 64-key blocks of 
 constexpr int kSoftmaxWarps = 8;
 constexpr int kTmaWarp = 8, kMmaWarp = 9;   // warps 10..13: dQ drain
 constexpr int kThreads = 32 * 14;
-constexpr int kSmemBytes = 2 * kTile /*K,V*/ + 4 * kTile /*Q,dO x2*/ + 2 * kPBytes + 1024 + 256;
+// Q / dO stages (three were measured: the S / dP issue moves 1200 clk earlier, the pair period does not change).
+#ifndef VST_BWD_QSTAGES
+#define VST_BWD_QSTAGES 2
+#endif
+constexpr int kQS = VST_BWD_QSTAGES;
+// VST_BWD_DQ_TMA: the dQ tile of a pair leaves through a swizzled fp32 staging buffer and ONE bulk tensor reduction
+// (cp.reduce.async.bulk.tensor ... .add, done by the TMA unit in L2) per 32-column half instead of 2048 RED.128
+// instructions per pair from the drain warps: the r02 trace showed the softmax warps' shared-memory / barrier
+// instructions queueing behind those atomics in the SM's memory pipe for ~2000 clk per pair.
+#ifndef VST_BWD_DQ_TMA
+#define VST_BWD_DQ_TMA 1
+#endif
+constexpr int kDQStage = VST_BWD_DQ_TMA ? 128 * HD * 4 : 0;   // 32 KB: two [128 rows x 128 B] swizzled boxes
+constexpr int kSmemBytes = 2 * kTile /*K,V*/ + 2 * kQS * kTile /*Q,dO*/ + 2 * kPBytes + kDQStage + 1024 + 256;
 
 __device__ __forceinline__ float ex2f(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+
+// exp2 on the FMA pipe for a share of the pairs (same polynomial as csrc/attn.cu: Cody-Waite split + degree-3
+// minimax, |rel err| < 7.6e-5, far below the bf16 rounding of P): the 16384 exponentials of a pair are 1024 clk of
+// MUFU.EX2 at 16/clk/SM.  x <= ~0 here (P = exp(s - lse) <= 1); x is clamped to >= -126.
+__device__ __forceinline__ float2 ex2_poly2(float2 x) {
+  const float2 magic = make_float2(12582912.f, 12582912.f);      // 1.5 * 2^23
+  const float2 nmagic = make_float2(-12582912.f, -12582912.f);
+  x.x = fmaxf(x.x, -126.f);
+  x.y = fmaxf(x.y, -126.f);
+  const float2 xf = __fadd2_rn(x, magic);
+  const float2 xi = __fadd2_rn(xf, nmagic);
+  const float2 f = __fadd2_rn(x, make_float2(-xi.x, -xi.y));
+  const float2 c3 = make_float2(0.05520550534129143f, 0.05520550534129143f);
+  const float2 c2 = make_float2(0.24261397123336792f, 0.24261397123336792f);
+  const float2 c1 = make_float2(0.6932547688484192f, 0.6932547688484192f);
+  const float2 c0 = make_float2(0.9999276995658875f, 0.9999276995658875f);
+  float2 p = __ffma2_rn(c3, f, c2);
+  p = __ffma2_rn(p, f, c1);
+  p = __ffma2_rn(p, f, c0);
+  p.x = __int_as_float(__float_as_int(p.x) + (__float_as_int(xf.x) << 23));
+  p.y = __int_as_float(__float_as_int(p.y) + (__float_as_int(xf.y) << 23));
+  return p;
+}
+#ifndef VST_BWD_POLY
+#define VST_BWD_POLY 2          // of every 8 pairs
+#endif
 
 struct BwdArgs {
   const float* lse;   // [Bt, heads, Sq] natural log
@@ -139,21 +193,22 @@ __global__ void attn_bwd_rows_convert_kernel(const float* __restrict__ acc, __nv
 __global__ void __launch_bounds__(kThreads, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
-                BwdArgs a) {
+                const __grid_constant__ CUtensorMap tmdQ, BwdArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
   uint8_t* sK = smem;
   uint8_t* sV = sK + kTile;
-  uint8_t* sQ = sV + kTile;          // [2]
-  uint8_t* sdO = sQ + 2 * kTile;     // [2]
-  uint8_t* sP = sdO + 2 * kTile;     // [2 key blocks][128 q][128 B]
+  uint8_t* sQ = sV + kTile;          // [kQS]
+  uint8_t* sdO = sQ + kQS * kTile;   // [kQS]
+  uint8_t* sP = sdO + kQS * kTile;     // [2 key blocks][128 q][128 B]
   uint8_t* sdS = sP + kPBytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sdS + kPBytes);
+  uint8_t* sDQ = sdS + kPBytes;      // [2 column halves][128 q][128 B] fp32 dQ staging (VST_BWD_DQ_TMA)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sDQ + kDQStage);
   uint64_t* kv_full = bars;
-  uint64_t* q_full = bars + 1;       // [2]
-  uint64_t* q_empty = q_full + 2;    // [2]
-  uint64_t* sdp_full = q_empty + 2;  // S_i, dP_i complete in TMEM
+  uint64_t* q_full = bars + 1;       // [kQS]
+  uint64_t* q_empty = q_full + kQS;  // [kQS]
+  uint64_t* sdp_full = q_empty + kQS;  // S_i, dP_i complete in TMEM
   uint64_t* sdp_free = sdp_full + 1; // ... and copied to registers by the 256 softmax threads
   uint64_t* pds_full = sdp_free + 1; // P_i, dS_i in shared memory
   uint64_t* pds_free = pds_full + 1; // dV / dK / dQ MMAs of pair i have read them
@@ -168,7 +223,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 
   if (threadIdx.x == 0) {
     mbar_init(kv_full, 1);
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < kQS; ++i) {
       mbar_init(&q_full[i], 1);
       mbar_init(&q_empty[i], 1);
     }
@@ -199,8 +254,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       tma_load_3d(sK, &tmK, kv_full, head * HD, kv0, bk);
       tma_load_3d(sV, &tmV, kv_full, head * HD, kv0, bk);
       for (int i = 0; i < nq; ++i) {
-        const int st = i & 1;
-        mbar_wait(&q_empty[st], ((i >> 1) & 1) ^ 1, 10);
+        const int st = i % kQS;
+        mbar_wait(&q_empty[st], ((i / kQS) & 1) ^ 1, 10);
+        BTRACE(9, i);
         mbar_arrive_expect_tx(&q_full[st], 2 * kTile);
         tma_load_3d(sQ + st * kTile, &tmQ, &q_full[st], head * HD, i * BQ, b);
         tma_load_3d(sdO + st * kTile, &tmdO, &q_full[st], head * HD, i * BQ, b);
@@ -220,11 +276,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const uint64_t dS_mn = umma_desc_sw128(smem_u32(sdS), 1024, 16384);
     mbar_wait(kv_full, 0, 20);
     auto issue_sdp = [&](int i) {
-      const int st = i & 1;
-      mbar_wait(&q_full[st], (i >> 1) & 1, 21);
+      const int st = i % kQS;
+      BTRACE(11, i);
+      mbar_wait(&q_full[st], (i / kQS) & 1, 21);
       tc_fence_after();
       const uint64_t dQ_k = umma_desc_sw128(smem_u32(sQ + st * kTile), 1024);
       const uint64_t ddO_k = umma_desc_sw128(smem_u32(sdO + st * kTile), 1024);
+      BTRACE(5, i);
       if (issuer) {
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k) umma_bf16_ss(tS, dQ_k + 2 * k, dK_k + 2 * k, idesc_s, k != 0);
@@ -236,16 +294,18 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     };
     issue_sdp(0);
     for (int i = 0; i < nq; ++i) {
-      const int st = i & 1;
+      const int st = i % kQS;
       if (i + 1 < nq) {
         mbar_wait(sdp_free, i & 1, 22);
         issue_sdp(i + 1);
       }
       mbar_wait(pds_full, i & 1, 23);
+      BTRACE(10, i);
       if (i > 0) mbar_wait(dq_free, (i - 1) & 1, 24);
       tc_fence_after();
       const uint64_t ddO_mn = umma_desc_sw128(smem_u32(sdO + st * kTile), 1024, 8192);
       const uint64_t dQ_mn = umma_desc_sw128(smem_u32(sQ + st * kTile), 1024, 8192);
+      BTRACE(6, i);
       if (issuer) {
 #if VST_BWD_ABLATE & 8
         if (i < 0)
@@ -263,9 +323,15 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           umma_bf16_ss(tdQ, dS_k + 2 * (k & 3), dK_mn + kRow16 * k, idesc_q, k != 0);
         }
         }
+#if VST_BWD_COMMIT_ORDER == 1
+        umma_commit(pds_free);
+        umma_commit(dq_full);
+        umma_commit(&q_empty[st]);
+#else
         umma_commit(&q_empty[st]);
         umma_commit(pds_free);
         umma_commit(dq_full);
+#endif
       }
       __syncwarp();
     }
@@ -278,52 +344,93 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     uint8_t* prow = sP + half * 16384 + row * 128;
     uint8_t* dsrow = sdS + half * 16384 + row * 128;
     const int rx = row & 7;
+    // The arithmetic is the longest stage of a pair (r02 clock64 trace, scripts/attn_bwd_trace.py: ~3000 of 5550 clk
+    // with scalar math and per-element bounds / mask predicates), so the common case -- no additive mask, key tile
+    // inside Sk (CTA-uniform) -- runs on packed f32x2 math without predicates, VST_BWD_POLY of every 8 exponential
+    // pairs on the FMA pipe, and the per-row LSE / D of the NEXT pair are fetched under this pair's arithmetic (their
+    // L2 latency was a 730 clk stall at the top of every pair).
+    const bool fast = a.mask == nullptr && kv0 + BKV <= a.Sk;
+    auto row_stats = [&](int i, float& lse2, float& dv) {
+      const int q = i * BQ + row;
+      // rows past Sq: LSE = +inf makes P = 0 (their Q / dO rows are zero-filled by TMA)
+      lse2 = q < a.Sq ? a.lse[vec_base + q] * 1.4426950408889634f : INFINITY;
+      dv = q < a.Sq ? a.dvec[vec_base + q] : 0.f;
+    };
+    float lse2, dv;
+    row_stats(0, lse2, dv);
     for (int i = 0; i < nq; ++i) {
       const int q = i * BQ + row;
-      const bool valid = q < a.Sq;
-      // rows past Sq: LSE = +inf makes P = 0 (their Q / dO rows are zero-filled by TMA)
-      const float lse2 = valid ? a.lse[vec_base + q] * 1.4426950408889634f : INFINITY;
-      const float dv = valid ? a.dvec[vec_base + q] : 0.f;
       const float* mrow = a.mask == nullptr ? nullptr
                               : a.mask + (int64_t)b * a.mask_sb + (int64_t)head * a.mask_sh +
                                     (int64_t)min(q, a.Sq - 1) * a.mask_sq;
       uint32_t pw[32], dsw[32];
       mbar_wait(sdp_full, i & 1, 30);
+      if (warp == 0) BTRACE(0, i);
       tc_fence_after();
+      float lse2_n = INFINITY, dv_n = 0.f;
+      const float2 sc2 = make_float2(a.scale_log2, a.scale_log2), nl2 = make_float2(-lse2, -lse2);
+      const float2 s2 = make_float2(a.scale, a.scale), nd2 = make_float2(-dv * a.scale, -dv * a.scale);
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         uint32_t s[32], dp[32];
         tmem_ld32(tS + lane_off + half * 64 + c * 32, s);
         tmem_ld32(tdP + lane_off + half * 64 + c * 32, dp);
+        if (c == 0 && i + 1 < nq) row_stats(i + 1, lse2_n, dv_n);     // in flight under the arithmetic
         tmem_ld_wait();
         if (c == 1) {
           tc_fence_before();
           warp_arrive(sdp_free);       // S / dP may be overwritten by the next pair
+          if (warp == 0) BTRACE(1, i);
         }
         const int key0 = kv0 + half * 64 + c * 32;
+        if (fast) {
 #pragma unroll
-        for (int e = 0; e < 16; ++e) {
-          float b0 = -lse2, b1 = -lse2;
-          if (mrow != nullptr) {       // warp-uniform branch; P = exp(s * scale + mask - lse)
-            if (key0 + 2 * e < a.Sk) b0 = fmaf(__ldg(mrow + key0 + 2 * e), 1.4426950408889634f, -lse2);
-            if (key0 + 2 * e + 1 < a.Sk) b1 = fmaf(__ldg(mrow + key0 + 2 * e + 1), 1.4426950408889634f, -lse2);
-          }
+          for (int e = 0; e < 16; ++e) {
 #if VST_BWD_ABLATE & 2
-          pw[c * 16 + e] = s[2 * e] ^ __float_as_uint(b0);
-          dsw[c * 16 + e] = dp[2 * e + 1] ^ __float_as_uint(b1);
-          continue;
+            pw[c * 16 + e] = s[2 * e] ^ __float_as_uint(nl2.x);
+            dsw[c * 16 + e] = dp[2 * e + 1] ^ __float_as_uint(nd2.x);
+            continue;
 #endif
-          float p0 = ex2f(fmaf(__uint_as_float(s[2 * e]), a.scale_log2, b0));
-          float p1 = ex2f(fmaf(__uint_as_float(s[2 * e + 1]), a.scale_log2, b1));
-          if (key0 + 2 * e >= a.Sk) p0 = 0.f;
-          if (key0 + 2 * e + 1 >= a.Sk) p1 = 0.f;
-          const float d0 = p0 * (__uint_as_float(dp[2 * e]) - dv) * a.scale;
-          const float d1 = p1 * (__uint_as_float(dp[2 * e + 1]) - dv) * a.scale;
-          pw[c * 16 + e] = pack_bf16(p0, p1);
-          dsw[c * 16 + e] = pack_bf16(d0, d1);
+            const float2 x = __ffma2_rn(make_float2(__uint_as_float(s[2 * e]), __uint_as_float(s[2 * e + 1])), sc2, nl2);
+            const bool poly = ((e * VST_BWD_POLY) & 7) + VST_BWD_POLY > 7 && VST_BWD_POLY > 0;
+            const float2 pv = poly ? ex2_poly2(x) : make_float2(ex2f(x.x), ex2f(x.y));
+            // dS = P (dP - D) scale
+            const float2 t = __ffma2_rn(make_float2(__uint_as_float(dp[2 * e]), __uint_as_float(dp[2 * e + 1])), s2, nd2);
+            const float2 d = __fmul2_rn(pv, t);
+            pw[c * 16 + e] = pack_bf16(pv.x, pv.y);
+            dsw[c * 16 + e] = pack_bf16(d.x, d.y);
+          }
+        } else {
+#pragma unroll
+          for (int e = 0; e < 16; ++e) {
+            float b0 = -lse2, b1 = -lse2;
+            if (mrow != nullptr) {       // warp-uniform branch; P = exp(s * scale + mask - lse)
+              if (key0 + 2 * e < a.Sk) b0 = fmaf(__ldg(mrow + key0 + 2 * e), 1.4426950408889634f, -lse2);
+              if (key0 + 2 * e + 1 < a.Sk) b1 = fmaf(__ldg(mrow + key0 + 2 * e + 1), 1.4426950408889634f, -lse2);
+            }
+            float p0 = ex2f(fmaf(__uint_as_float(s[2 * e]), a.scale_log2, b0));
+            float p1 = ex2f(fmaf(__uint_as_float(s[2 * e + 1]), a.scale_log2, b1));
+            if (key0 + 2 * e >= a.Sk) p0 = 0.f;
+            if (key0 + 2 * e + 1 >= a.Sk) p1 = 0.f;
+            const float d0 = p0 * (__uint_as_float(dp[2 * e]) - dv) * a.scale;
+            const float d1 = p1 * (__uint_as_float(dp[2 * e + 1]) - dv) * a.scale;
+            pw[c * 16 + e] = pack_bf16(p0, p1);
+            dsw[c * 16 + e] = pack_bf16(d0, d1);
+          }
         }
       }
+      lse2 = lse2_n;
+      dv = dv_n;
+      if (warp == 0) BTRACE(2, i);
+#if VST_BWD_ELECT_WAIT
+      if (i > 0) {
+        if (lane == 0) mbar_wait(pds_free, (i - 1) & 1, 31);
+        __syncwarp();
+      }
+#else
       if (i > 0) mbar_wait(pds_free, (i - 1) & 1, 31);   // previous pair's MMAs are done with sP / sdS
+#endif
+      if (warp == 0) BTRACE(3, i);
 #pragma unroll
       for (int cc = 0; cc < ((VST_BWD_ABLATE & 16) ? 0 : 8); ++cc) {
         const int off = (cc ^ rx) * 16;
@@ -332,6 +439,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
       fence_proxy_async_smem();
       warp_arrive(pds_full);
+      if (warp == 0) BTRACE(4, i);
     }
     // ---- dV (half 0) / dK (half 1): TMEM lane = key row ----
     mbar_wait(pds_free, (nq - 1) & 1, 32);
@@ -375,8 +483,15 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
     const uint32_t lane_off = uint32_t(quarter * 32) << 16;
+#if VST_BWD_DQ_TMA
+    const bool leader = warp == 10 && lane == 0;
+    const int bh = b * a.heads + head;
+    const int rx = row & 7;
+    if (leader) tma_prefetch_desc(&tmdQ);
+#endif
     for (int i = 0; i < nq; ++i) {
       mbar_wait(dq_full, i & 1, 40);
+      if (warp == 10) BTRACE(7, i);
       tc_fence_after();
       uint32_t o[64];
       tmem_ld32(tdQ + lane_off, o);
@@ -384,6 +499,32 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       tmem_ld_wait();
       tc_fence_before();
       warp_arrive(dq_free);
+#if VST_BWD_DQ_TMA
+      if (i > 0) {
+        if (leader) tma_store_wait_read<0>();          // the previous pair's reduction has read the staging tile
+        asm volatile("bar.sync 2, 128;" ::: "memory");
+      }
+#if !(VST_BWD_ABLATE & 1)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        uint8_t* drow = sDQ + h * 16384 + row * 128;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<uint4*>(drow + ((j ^ rx) * 16)) =
+              make_uint4(o[h * 32 + 4 * j], o[h * 32 + 4 * j + 1], o[h * 32 + 4 * j + 2], o[h * 32 + 4 * j + 3]);
+      }
+#endif
+      fence_proxy_async_smem();
+      asm volatile("bar.sync 2, 128;" ::: "memory");
+      if (leader) {
+#if !(VST_BWD_ABLATE & 1)
+        // rows past Sq are clipped by the tensor map (dims {64, Sq, Bt * heads})
+        tma_reduce_add_3d(&tmdQ, sDQ, 0, i * BQ, bh);
+        tma_reduce_add_3d(&tmdQ, sDQ + 16384, 32, i * BQ, bh);
+#endif
+        tma_store_commit();
+      }
+#else
       const int q = i * BQ + row;
       if (q < a.Sq && !(VST_BWD_ABLATE & 1)) {
         float* dst = a.dq_acc + (((int64_t)b * a.heads + head) * a.Sq + q) * HD;
@@ -393,7 +534,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                     make_float4(__uint_as_float(o[4 * v]), __uint_as_float(o[4 * v + 1]),
                                 __uint_as_float(o[4 * v + 2]), __uint_as_float(o[4 * v + 3])));
       }
+#endif
+      if (warp == 10) BTRACE(8, i);
     }
+#if VST_BWD_DQ_TMA
+    if (leader) tma_store_wait<0>();
+#endif
   }
 
   tc_fence_before();
@@ -414,6 +560,12 @@ int make_map3(CUtensorMap* m, const void* p, int64_t B, int64_t S, int width, in
 int64_t align256(int64_t x) { return (x + 255) / 256 * 256; }
 
 }  // namespace
+
+#ifdef VST_BWD_TRACE
+extern "C" int vst_attn_bwd_debug_trace(long long* host_dst) {
+  return (int)cudaMemcpyFromSymbol(host_dst, g_bwd_trace, sizeof(long long) * 12 * 64);
+}
+#endif
 
 extern "C" int64_t vst_attn_bwd_workspace_bytes(int Bt, int heads, int Sq, int Sk, int kv_group) {
   if (Bt <= 0 || heads <= 0 || Sq <= 0 || Sk <= 0 || kv_group <= 0) return 0;
@@ -474,6 +626,16 @@ extern "C" int vst_attn_bwd(const void* q, const void* k, const void* v, const v
   if ((rc = make_map3(&tK, k, Bk, Sk, C, ldk))) return rc;
   if ((rc = make_map3(&tV, v, Bk, Sk, C, ldv))) return rc;
   if ((rc = make_map3(&tdO, d_o, Bt, Sq, C, lddo))) return rc;
+  CUtensorMap tdQ;
+  {
+    // fp32 accumulator [Bt * heads][Sq][64]: boxes of 32 columns (128 B, 128-byte swizzle) x 128 rows
+    const uint64_t dims[3] = {(uint64_t)HD, (uint64_t)Sq, (uint64_t)Bt * heads};
+    const uint64_t strides[3] = {4, (uint64_t)HD * 4, (uint64_t)Sq * HD * 4};
+    const uint32_t box[3] = {32, 128, 1};
+    if ((rc = vst_make_tmap_dt(&tdQ, dq_acc, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B,
+                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_DATA_TYPE_FLOAT32)))
+      return rc;
+  }
   static bool configured = false;
   if (!configured) {
     VST_CUDA_OK(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
@@ -498,7 +660,7 @@ extern "C" int vst_attn_bwd(const void* q, const void* k, const void* v, const v
   a.mask_sh = mask_sh;
   a.mask_sq = mask_sq;
   dim3 grid((Sk + BKV - 1) / BKV, heads, Bt);
-  attn_bwd_kernel<<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tdO, a);
+  attn_bwd_kernel<<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tdO, tdQ, a);
   VST_LAUNCH_OK();
   {
     const int64_t threads = rows * heads * 8;
