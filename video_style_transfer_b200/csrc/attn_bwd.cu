@@ -22,6 +22,8 @@
 // 448 threads: warps 0..7 softmax (warp w: TMEM lane quarter w%4, key half w/4), warp 8 TMA,
 // warp 9 MMA issue (elected lane), warps 10..13 dQ drain.
 // Roofline: tensor pipe; FLOPs = 2.5 x forward = 10 * Bt*h*Sq*Sk*d.
+#include <type_traits>
+
 #include "common.cuh"
 
 // -DVST_BWD_ABLATE=<bits>: timing-only builds that drop one stage (WRONG results; never shipped):
@@ -69,9 +71,10 @@ constexpr int kPBytes = 128 * 128 * 2;  // 32 KB: P or dS, two 64-key blocks of 
 constexpr int kSoftmaxWarps = 8;
 constexpr int kTmaWarp = 8, kMmaWarp = 9;   // warps 10..13: dQ drain
 constexpr int kThreads = 32 * 14;
-// Q / dO stages (three were measured: the S / dP issue moves 1200 clk earlier, the pair period does not change).
+// Q / dO stages: with two, the load of pair i+1 can only start when the gradient MMAs of pair i-1 release their
+// stage and its ~1300 clk of TMA latency sits in front of the S / dP issue (three: L1 self 2411 -> 2361 us).
 #ifndef VST_BWD_QSTAGES
-#define VST_BWD_QSTAGES 2
+#define VST_BWD_QSTAGES 3
 #endif
 constexpr int kQS = VST_BWD_QSTAGES;
 // VST_BWD_DQ_TMA: the dQ tile of a pair leaves through a swizzled fp32 staging buffer and ONE bulk tensor reduction
@@ -124,6 +127,7 @@ struct BwdArgs {
   void* dv;
   int64_t ldk, ldv;   // row strides (elements) of dk / dv
   int Sq, Sk, heads, kv_group;
+  int qsplit;         // CTAs per key tile, each walking 1/qsplit of the query tiles (only with fp32 dK / dV accumulators)
   float scale, scale_log2;
   const float* mask;                  // optional additive mask of the forward (natural-log domain)
   int64_t mask_sb, mask_sh, mask_sq;  // element strides over (batch, head, query); 0 = broadcast
@@ -217,9 +221,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(dq_free + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int kv0 = blockIdx.x * BKV, head = blockIdx.y, b = blockIdx.z;
+  const int kv0 = (blockIdx.x / a.qsplit) * BKV, head = blockIdx.y, b = blockIdx.z;
   const int bk = b / a.kv_group;
-  const int nq = (a.Sq + BQ - 1) / BQ;
+  // this CTA's query tiles: [qt0, qt0 + nq) -- all of them unless the launch splits the walk (a.qsplit > 1)
+  const int nq_all = (a.Sq + BQ - 1) / BQ;
+  const int q_per = (nq_all + a.qsplit - 1) / a.qsplit;
+  const int qt0 = (blockIdx.x % a.qsplit) * q_per;
+  const int nq = min(q_per, nq_all - qt0);      // >= 1 by the host's choice of qsplit
 
   if (threadIdx.x == 0) {
     mbar_init(kv_full, 1);
@@ -258,8 +266,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         mbar_wait(&q_empty[st], ((i / kQS) & 1) ^ 1, 10);
         BTRACE(9, i);
         mbar_arrive_expect_tx(&q_full[st], 2 * kTile);
-        tma_load_3d(sQ + st * kTile, &tmQ, &q_full[st], head * HD, i * BQ, b);
-        tma_load_3d(sdO + st * kTile, &tmdO, &q_full[st], head * HD, i * BQ, b);
+        tma_load_3d(sQ + st * kTile, &tmQ, &q_full[st], head * HD, (qt0 + i) * BQ, b);
+        tma_load_3d(sdO + st * kTile, &tmdO, &q_full[st], head * HD, (qt0 + i) * BQ, b);
       }
     }
   } else if (warp == kMmaWarp) {
@@ -349,9 +357,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     // inside Sk (CTA-uniform) -- runs on packed f32x2 math without predicates, VST_BWD_POLY of every 8 exponential
     // pairs on the FMA pipe, and the per-row LSE / D of the NEXT pair are fetched under this pair's arithmetic (their
     // L2 latency was a 730 clk stall at the top of every pair).
-    const bool fast = a.mask == nullptr && kv0 + BKV <= a.Sk;
+    const bool fast = a.mask == nullptr;
+    const bool tail = kv0 + BKV > a.Sk;       // CTA-uniform: keys past Sk get P = 0 (their K / V rows are zero-filled)
     auto row_stats = [&](int i, float& lse2, float& dv) {
-      const int q = i * BQ + row;
+      const int q = (qt0 + i) * BQ + row;
       // rows past Sq: LSE = +inf makes P = 0 (their Q / dO rows are zero-filled by TMA)
       lse2 = q < a.Sq ? a.lse[vec_base + q] * 1.4426950408889634f : INFINITY;
       dv = q < a.Sq ? a.dvec[vec_base + q] : 0.f;
@@ -359,7 +368,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     float lse2, dv;
     row_stats(0, lse2, dv);
     for (int i = 0; i < nq; ++i) {
-      const int q = i * BQ + row;
+      const int q = (qt0 + i) * BQ + row;
       const float* mrow = a.mask == nullptr ? nullptr
                               : a.mask + (int64_t)b * a.mask_sb + (int64_t)head * a.mask_sh +
                                     (int64_t)min(q, a.Sq - 1) * a.mask_sq;
@@ -384,22 +393,29 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         }
         const int key0 = kv0 + half * 64 + c * 32;
         if (fast) {
+          auto chunk = [&](auto tail_c) {
 #pragma unroll
-          for (int e = 0; e < 16; ++e) {
+            for (int e = 0; e < 16; ++e) {
 #if VST_BWD_ABLATE & 2
-            pw[c * 16 + e] = s[2 * e] ^ __float_as_uint(nl2.x);
-            dsw[c * 16 + e] = dp[2 * e + 1] ^ __float_as_uint(nd2.x);
-            continue;
+              pw[c * 16 + e] = s[2 * e] ^ __float_as_uint(nl2.x);
+              dsw[c * 16 + e] = dp[2 * e + 1] ^ __float_as_uint(nd2.x);
+              continue;
 #endif
-            const float2 x = __ffma2_rn(make_float2(__uint_as_float(s[2 * e]), __uint_as_float(s[2 * e + 1])), sc2, nl2);
-            const bool poly = ((e * VST_BWD_POLY) & 7) + VST_BWD_POLY > 7 && VST_BWD_POLY > 0;
-            const float2 pv = poly ? ex2_poly2(x) : make_float2(ex2f(x.x), ex2f(x.y));
-            // dS = P (dP - D) scale
-            const float2 t = __ffma2_rn(make_float2(__uint_as_float(dp[2 * e]), __uint_as_float(dp[2 * e + 1])), s2, nd2);
-            const float2 d = __fmul2_rn(pv, t);
-            pw[c * 16 + e] = pack_bf16(pv.x, pv.y);
-            dsw[c * 16 + e] = pack_bf16(d.x, d.y);
-          }
+              const float2 x = __ffma2_rn(make_float2(__uint_as_float(s[2 * e]), __uint_as_float(s[2 * e + 1])), sc2, nl2);
+              const bool poly = ((e * VST_BWD_POLY) & 7) + VST_BWD_POLY > 7 && VST_BWD_POLY > 0;
+              float2 pv = poly ? ex2_poly2(x) : make_float2(ex2f(x.x), ex2f(x.y));
+              if (decltype(tail_c)::value) {
+                if (key0 + 2 * e >= a.Sk) pv.x = 0.f;
+                if (key0 + 2 * e + 1 >= a.Sk) pv.y = 0.f;
+              }
+              // dS = P (dP - D) scale
+              const float2 t = __ffma2_rn(make_float2(__uint_as_float(dp[2 * e]), __uint_as_float(dp[2 * e + 1])), s2, nd2);
+              const float2 d = __fmul2_rn(pv, t);
+              pw[c * 16 + e] = pack_bf16(pv.x, pv.y);
+              dsw[c * 16 + e] = pack_bf16(d.x, d.y);
+            }
+          };
+          if (tail) chunk(std::true_type{}); else chunk(std::false_type{});
         } else {
 #pragma unroll
           for (int e = 0; e < 16; ++e) {
@@ -519,13 +535,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       if (leader) {
 #if !(VST_BWD_ABLATE & 1)
         // rows past Sq are clipped by the tensor map (dims {64, Sq, Bt * heads})
-        tma_reduce_add_3d(&tmdQ, sDQ, 0, i * BQ, bh);
-        tma_reduce_add_3d(&tmdQ, sDQ + 16384, 32, i * BQ, bh);
+        tma_reduce_add_3d(&tmdQ, sDQ, 0, (qt0 + i) * BQ, bh);
+        tma_reduce_add_3d(&tmdQ, sDQ + 16384, 32, (qt0 + i) * BQ, bh);
 #endif
         tma_store_commit();
       }
 #else
-      const int q = i * BQ + row;
+      const int q = (qt0 + i) * BQ + row;
       if (q < a.Sq && !(VST_BWD_ABLATE & 1)) {
         float* dst = a.dq_acc + (((int64_t)b * a.heads + head) * a.Sq + q) * HD;
 #pragma unroll
@@ -659,7 +675,18 @@ extern "C" int vst_attn_bwd(const void* q, const void* k, const void* v, const v
   a.mask_sb = mask_sb;
   a.mask_sh = mask_sh;
   a.mask_sq = mask_sq;
-  dim3 grid((Sk + BKV - 1) / BKV, heads, Bt);
+  // Text cross-attention has ONE key tile per (batch, head): 160-320 CTAs of 8-32 pairs each, under two waves of
+  // 148.  Its dK / dV already accumulate in fp32 with atomics (kv_group > 1), so the query walk can be split over
+  // several CTAs per key tile until the grid is a few waves deep.
+  const int kt = (Sk + BKV - 1) / BKV, nq_all = (Sq + BQ - 1) / BQ;
+  int qsplit = 1;
+  if (kv_group > 1) {
+    const int64_t ctas = (int64_t)kt * heads * Bt;
+    while (qsplit < 8 && ctas * qsplit < 4 * vst_sm_count() && (nq_all + 2 * qsplit - 1) / (2 * qsplit) >= 2) qsplit *= 2;
+    while (qsplit > 1 && ((nq_all + qsplit - 1) / qsplit) * (qsplit - 1) >= nq_all) --qsplit;   // no empty CTA
+  }
+  a.qsplit = qsplit;
+  dim3 grid(kt * qsplit, heads, Bt);
   attn_bwd_kernel<<<grid, kThreads, kSmemBytes, st>>>(tQ, tK, tV, tdO, tdQ, a);
   VST_LAUNCH_OK();
   {
