@@ -33,9 +33,9 @@ def run(sq=4096, heads=10, bt=16):
         ops.attn_bwd(q, k, v, o, do, lse, heads)
         torch.cuda.synchronize()
     raw = ctypes.CDLL(LIB)
-    buf = np.zeros(12 * 64, dtype=np.int64)
+    buf = np.zeros(16 * 64, dtype=np.int64)
     assert raw.vst_attn_bwd_debug_trace(buf.ctypes.data_as(ctypes.c_void_p)) == 0
-    t = buf.reshape(12, 64)
+    t = buf.reshape(16, 64)
     n = min(sq // 128, 64)
     t0 = t[5, 0]
     names = ["sdp_full", "in_regs", "math_done", "pds_free", "stored", "SdP_issue", "grad_issue", "dq_full", "dq_added",
@@ -51,7 +51,11 @@ def run(sq=4096, heads=10, bt=16):
     print("steady state (pairs %d..%d), clk:" % (lo, hi - 1))
     print("  period                         %8.0f" % float(np.mean([t[4, i + 1] - t[4, i] for i in range(lo, hi)])))
     print("  sdp_full -> S/dP in registers  %8.0f" % mean(0, 1))
-    print("  arithmetic                     %8.0f" % mean(1, 2))
+    print("    sdp_full -> chunk 0 loaded   %8.0f" % mean(0, 12))
+    print("    chunk 0 arithmetic           %8.0f" % mean(12, 13))
+    print("    chunk 1 load                 %8.0f" % mean(13, 14))
+    print("    fence + arrive sdp_free      %8.0f" % mean(14, 1))
+    print("  arithmetic (chunk 1)           %8.0f" % mean(1, 2))
     print("  wait pds_free                  %8.0f" % mean(2, 3))
     print("  P/dS stores + fence + arrive   %8.0f" % mean(3, 4))
     print("  stored(i) -> sdp_full(i+1)     %8.0f" % float(np.mean([t[0, i + 1] - t[4, i] for i in range(lo, hi)])))

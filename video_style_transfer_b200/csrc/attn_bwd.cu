@@ -33,8 +33,8 @@
 #endif
 
 // VST_BWD_WARP_ARRIVE: one elected mbarrier arrival per warp (after __syncwarp) instead of one per thread
-#ifndef VST_BWD_COMMIT_ORDER
-#define VST_BWD_COMMIT_ORDER 0
+#ifndef VST_BWD_ORDER
+#define VST_BWD_ORDER 0
 #endif
 #ifndef VST_BWD_ELECT_WAIT
 #define VST_BWD_ELECT_WAIT 0
@@ -45,7 +45,7 @@
 
 // -DVST_BWD_TRACE: CTA (0,0,0) records clock64() stamps of its pipeline events (scripts/attn_bwd_trace.py)
 #ifdef VST_BWD_TRACE
-__device__ long long g_bwd_trace[12 * 64];   // [slot][pair index]
+__device__ long long g_bwd_trace[16 * 64];   // [slot][pair index]
 #define BTRACE(slot, idx) do { if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (idx) < 64 && \
     (threadIdx.x & 31) == 0) g_bwd_trace[(slot) * 64 + (idx)] = clock64(); } while (0)
 #else
@@ -300,13 +300,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
       __syncwarp();
     };
-    issue_sdp(0);
-    for (int i = 0; i < nq; ++i) {
+    // gradient MMAs of pair i: dV, dK (accumulated over the walk) and dQ (fresh), then the three releases
+    auto issue_grads = [&](int i) {
       const int st = i % kQS;
-      if (i + 1 < nq) {
-        mbar_wait(sdp_free, i & 1, 22);
-        issue_sdp(i + 1);
-      }
       mbar_wait(pds_full, i & 1, 23);
       BTRACE(10, i);
       if (i > 0) mbar_wait(dq_free, (i - 1) & 1, 24);
@@ -331,18 +327,30 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           umma_bf16_ss(tdQ, dS_k + 2 * (k & 3), dK_mn + kRow16 * k, idesc_q, k != 0);
         }
         }
-#if VST_BWD_COMMIT_ORDER == 1
-        umma_commit(pds_free);
-        umma_commit(dq_full);
-        umma_commit(&q_empty[st]);
-#else
         umma_commit(&q_empty[st]);
         umma_commit(pds_free);
         umma_commit(dq_full);
-#endif
       }
       __syncwarp();
+    };
+    issue_sdp(0);
+#if VST_BWD_ORDER == 1
+    // (measured, slower: 5080 against 3860 clk per pair) gradient MMAs of pair i-1 issued only once S / dP of pair i
+    // are in registers, then S / dP of pair i+1 -- the P / dS buffers are then held through the next pair's loads.
+    for (int i = 0; i <= nq; ++i) {
+      if (i < nq) mbar_wait(sdp_free, i & 1, 22);
+      if (i >= 1) issue_grads(i - 1);
+      if (i + 1 < nq) issue_sdp(i + 1);
     }
+#else
+    for (int i = 0; i < nq; ++i) {
+      if (i + 1 < nq) {
+        mbar_wait(sdp_free, i & 1, 22);
+        issue_sdp(i + 1);
+      }
+      issue_grads(i);
+    }
+#endif
   } else if (warp < kSoftmaxWarps) {
     // ================= softmax warps: P and dS of this warp's 32 rows x 64 keys =================
     const int quarter = warp & 3, half = warp >> 2;
@@ -376,7 +384,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       mbar_wait(sdp_full, i & 1, 30);
       if (warp == 0) BTRACE(0, i);
       tc_fence_after();
-      float lse2_n = INFINITY, dv_n = 0.f;
+      float lse_raw_n = 0.f, dv_n = 0.f;      // next pair's row statistics: RAW loads only, no arithmetic on them
+      bool valid_n = false;                   // before the end of this pair (an FMUL here would stall on L2 latency)
       const float2 sc2 = make_float2(a.scale_log2, a.scale_log2), nl2 = make_float2(-lse2, -lse2);
       const float2 s2 = make_float2(a.scale, a.scale), nd2 = make_float2(-dv * a.scale, -dv * a.scale);
 #pragma unroll
@@ -384,14 +393,27 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         uint32_t s[32], dp[32];
         tmem_ld32(tS + lane_off + half * 64 + c * 32, s);
         tmem_ld32(tdP + lane_off + half * 64 + c * 32, dp);
-        if (c == 0 && i + 1 < nq) row_stats(i + 1, lse2_n, dv_n);     // in flight under the arithmetic
         tmem_ld_wait();
+        if (c == 1 && i + 1 < nq) {
+          // In flight under the chunk-1 arithmetic and the stores.  AFTER the pair's last tcgen05.wait::ld: with the
+          // loads issued before it, that wait also sat out their L2 latency (r02 trace: 997 clk for the first
+          // chunk's TMEM load against 99 for the second).
+          const int qn = (qt0 + i + 1) * BQ + row;
+          valid_n = qn < a.Sq;
+          if (valid_n) {
+            lse_raw_n = __ldg(a.lse + vec_base + qn);
+            dv_n = __ldg(a.dvec + vec_base + qn);
+          }
+        }
+        if (c == 0 && warp == 0) BTRACE(12, i);
+        if (c == 1 && warp == 0) BTRACE(14, i);
         if (c == 1) {
           tc_fence_before();
           warp_arrive(sdp_free);       // S / dP may be overwritten by the next pair
           if (warp == 0) BTRACE(1, i);
         }
         const int key0 = kv0 + half * 64 + c * 32;
+        if (c == 1 && warp == 0) BTRACE(15, i);
         if (fast) {
           auto chunk = [&](auto tail_c) {
 #pragma unroll
@@ -416,6 +438,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             }
           };
           if (tail) chunk(std::true_type{}); else chunk(std::false_type{});
+          if (c == 0 && warp == 0) BTRACE(13, i);
         } else {
 #pragma unroll
           for (int e = 0; e < 16; ++e) {
@@ -435,7 +458,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           }
         }
       }
-      lse2 = lse2_n;
+      lse2 = valid_n ? lse_raw_n * 1.4426950408889634f : INFINITY;
       dv = dv_n;
       if (warp == 0) BTRACE(2, i);
 #if VST_BWD_ELECT_WAIT
@@ -579,7 +602,7 @@ int64_t align256(int64_t x) { return (x + 255) / 256 * 256; }
 
 #ifdef VST_BWD_TRACE
 extern "C" int vst_attn_bwd_debug_trace(long long* host_dst) {
-  return (int)cudaMemcpyFromSymbol(host_dst, g_bwd_trace, sizeof(long long) * 12 * 64);
+  return (int)cudaMemcpyFromSymbol(host_dst, g_bwd_trace, sizeof(long long) * 16 * 64);
 }
 #endif
 
