@@ -202,7 +202,13 @@ def _sdpa_ref(q, k, v, heads, d_o):
 
 
 @pytest.mark.parametrize("bt,bk,heads,sq,sk", [(2, 2, 2, 128, 128), (2, 2, 3, 256, 384), (3, 3, 2, 200, 136),
-                                               (4, 1, 2, 256, 77), (2, 2, 1, 64, 520), (6, 2, 2, 130, 77)])
+                                               (4, 1, 2, 256, 77), (2, 2, 1, 64, 520), (6, 2, 2, 130, 77),
+                                               # shared K / V with a long ragged query walk: the launch splits the walk
+                                               # over three CTAs per key tile (9 query tiles, the last one 76 rows)
+                                               (4, 1, 2, 1100, 77),
+                                               # 11 query tiles against 3 key tiles: the three-stage Q / dO ring wraps,
+                                               # dQ tiles leave by bulk tensor reduction with a clipped last tile
+                                               (1, 1, 1, 1300, 300)])
 def test_attn_bwd_vs_autograd(ops, bt, bk, heads, sq, sk):
     torch.manual_seed(bt * 1000 + sq + sk)
     c = heads * 64
