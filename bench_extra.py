@@ -211,6 +211,22 @@ def run_cfg4(args, common):
     else:
         step = step_eager
     torch.cuda.synchronize()
+    prof_out = os.environ.get("VST_KERNEL_TABLE")
+    if prof_out:
+        # per-kernel device time of ONE step (CUPTI through torch.profiler: kernels of a graph replay are recorded
+        # like any others; far cheaper than an ncu pass over ~4000 launches) -> tab-separated file
+        from torch.profiler import ProfilerActivity, profile
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            step()
+            torch.cuda.synchronize()
+        rows = sorted(((e.key, e.count, e.device_time_total) for e in prof.key_averages() if e.device_time_total > 0),
+                      key=lambda r: -r[2])
+        tot = sum(r[2] for r in rows)
+        with open(prof_out, "w") as f:
+            f.write(f"# one cfg4 training step, kernel device time (us), total {tot:.1f} us over {sum(r[1] for r in rows)} launches\n")
+            f.write("kernel\tlaunches\ttotal_us\tshare\n")
+            for k, n, t in rows:
+                f.write(f"{k[:120]}\t{n}\t{t:.1f}\t{t / tot:.4f}\n")
     l0 = _lib.launch_count
     with common["ClockSampler"](0) as clk:
         ms = _timed(step, args.steps, 1, dev)

@@ -45,17 +45,16 @@ def run(sq=4096, heads=10, bt=16):
         row = [int(t[s, i] - t0) for s in range(12)]
         per = int(t[4, i] - t[4, i - 1]) if i else 0
         print(f"{i:4d} " + " ".join(f"{x:10d}" for x in row) + f" {per:10d}")
-    lo, hi = 4, n - 2
+    life = t[12]
+    print("CTA lifetime (clk from entry): set-up done %d, K/V landed %d, first S/dP issue %d, last P/dS stored %d, "
+          "dV/dK stored %d, exit %d" % tuple(int(x - life[0]) for x in (life[1], life[2], t[5, 0], t[4, n - 1], life[3], life[4])))
+    lo, hi = min(4, n // 2), n - 2
     def mean(a, b):
         return float(np.mean([t[b, i] - t[a, i] for i in range(lo, hi)]))
     print("steady state (pairs %d..%d), clk:" % (lo, hi - 1))
     print("  period                         %8.0f" % float(np.mean([t[4, i + 1] - t[4, i] for i in range(lo, hi)])))
     print("  sdp_full -> S/dP in registers  %8.0f" % mean(0, 1))
-    print("    sdp_full -> chunk 0 loaded   %8.0f" % mean(0, 12))
-    print("    chunk 0 arithmetic           %8.0f" % mean(12, 13))
-    print("    chunk 1 load                 %8.0f" % mean(13, 14))
-    print("    fence + arrive sdp_free      %8.0f" % mean(14, 1))
-    print("  arithmetic (chunk 1)           %8.0f" % mean(1, 2))
+    print("  arithmetic (second chunk)      %8.0f" % mean(1, 2))
     print("  wait pds_free                  %8.0f" % mean(2, 3))
     print("  P/dS stores + fence + arrive   %8.0f" % mean(3, 4))
     print("  stored(i) -> sdp_full(i+1)     %8.0f" % float(np.mean([t[0, i + 1] - t[4, i] for i in range(lo, hi)])))

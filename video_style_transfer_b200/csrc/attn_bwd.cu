@@ -221,6 +221,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(dq_free + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 0) BTRACE(12, 0);          // CTA lifetime stamps: entry, set-up done, K/V landed, dV/dK stored, exit
   const int kv0 = (blockIdx.x / a.qsplit) * BKV, head = blockIdx.y, b = blockIdx.z;
   const int bk = b / a.kv_group;
   // this CTA's query tiles: [qt0, qt0 + nq) -- all of them unless the launch splits the walk (a.qsplit > 1)
@@ -229,7 +230,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   const int qt0 = (blockIdx.x % a.qsplit) * q_per;
   const int nq = min(q_per, nq_all - qt0);      // >= 1 by the host's choice of qsplit
 
-  if (threadIdx.x == 0) {
+  // Set-up and the first loads by ONE thread (lane 0 of the TMA warp), before the CTA-wide barrier: the K / V tiles
+  // take ~4300 clk to land (cold) and a CTA of the S = 1024 shape lives only ~41000 clk (r02 trace), so they must
+  // not wait for the TMEM allocation and the __syncthreads as well.
+  if (threadIdx.x == kTmaWarp * 32) {
     mbar_init(kv_full, 1);
     for (int i = 0; i < kQS; ++i) {
       mbar_init(&q_full[i], 1);
@@ -242,26 +246,32 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     mbar_init(dq_full, 1);
     mbar_init(dq_free, kArrivePerWarp * 4);
     fence_mbar_init();
+    tma_prefetch_desc(&tmK);
+    tma_prefetch_desc(&tmV);
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmdO);
+    mbar_arrive_expect_tx(kv_full, 2 * kTile);
+    tma_load_3d(sK, &tmK, kv_full, head * HD, kv0, bk);
+    tma_load_3d(sV, &tmV, kv_full, head * HD, kv0, bk);
+    for (int i = 0; i < kQS && i < nq; ++i) {          // first fill of the Q / dO ring: every stage is free
+      mbar_arrive_expect_tx(&q_full[i], 2 * kTile);
+      tma_load_3d(sQ + i * kTile, &tmQ, &q_full[i], head * HD, (qt0 + i) * BQ, b);
+      tma_load_3d(sdO + i * kTile, &tmdO, &q_full[i], head * HD, (qt0 + i) * BQ, b);
+    }
   }
   if (warp == kMmaWarp) tmem_alloc(tmem_slot, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (warp == 0) BTRACE(12, 1);
   const uint32_t tS = tmem_base, tdP = tmem_base + 128, tdV = tmem_base + 256,
                  tdK = tmem_base + 320, tdQ = tmem_base + 384;
 
   if (warp == kTmaWarp) {
     // ================= TMA producer =================
     if (lane == 0) {
-      tma_prefetch_desc(&tmQ);
-      tma_prefetch_desc(&tmK);
-      tma_prefetch_desc(&tmV);
-      tma_prefetch_desc(&tmdO);
-      mbar_arrive_expect_tx(kv_full, 2 * kTile);
-      tma_load_3d(sK, &tmK, kv_full, head * HD, kv0, bk);
-      tma_load_3d(sV, &tmV, kv_full, head * HD, kv0, bk);
-      for (int i = 0; i < nq; ++i) {
+      for (int i = kQS; i < nq; ++i) {           // (K / V and the first kQS pairs were issued during set-up)
         const int st = i % kQS;
         mbar_wait(&q_empty[st], ((i / kQS) & 1) ^ 1, 10);
         BTRACE(9, i);
@@ -283,6 +293,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const uint64_t dP_mn = umma_desc_sw128(smem_u32(sP), 1024, 16384);  // P^T: MN blocks 16 KB apart
     const uint64_t dS_mn = umma_desc_sw128(smem_u32(sdS), 1024, 16384);
     mbar_wait(kv_full, 0, 20);
+    BTRACE(12, 2);
     auto issue_sdp = [&](int i) {
       const int st = i % kQS;
       BTRACE(11, i);
@@ -405,15 +416,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             dv_n = __ldg(a.dvec + vec_base + qn);
           }
         }
-        if (c == 0 && warp == 0) BTRACE(12, i);
-        if (c == 1 && warp == 0) BTRACE(14, i);
         if (c == 1) {
           tc_fence_before();
           warp_arrive(sdp_free);       // S / dP may be overwritten by the next pair
           if (warp == 0) BTRACE(1, i);
         }
         const int key0 = kv0 + half * 64 + c * 32;
-        if (c == 1 && warp == 0) BTRACE(15, i);
         if (fast) {
           auto chunk = [&](auto tail_c) {
 #pragma unroll
@@ -438,7 +446,6 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             }
           };
           if (tail) chunk(std::true_type{}); else chunk(std::false_type{});
-          if (c == 0 && warp == 0) BTRACE(13, i);
         } else {
 #pragma unroll
           for (int e = 0; e < 16; ++e) {
@@ -577,12 +584,14 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       if (warp == 10) BTRACE(8, i);
     }
 #if VST_BWD_DQ_TMA
-    if (leader) tma_store_wait<0>();
+    if (leader) tma_store_wait_read<0>();      // shared memory read out; the reductions complete with the kernel
 #endif
   }
 
+  if (warp == 0) BTRACE(12, 3);
   tc_fence_before();
   __syncthreads();
+  if (warp == 0) BTRACE(12, 4);
   if (warp == kMmaWarp) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
