@@ -19,8 +19,8 @@
 // TMEM over the whole walk; dQ of each pair is added to an fp32 accumulator in global memory
 // (vector atomics, [Bt, heads, Sq, 64] so a warp adds whole 128-byte lines) and converted to bf16
 // afterwards.  TMEM: S [0,128) dP [128,256) dV [256,320) dK [320,384) dQ [384,448).
-// 448 threads: warps 0..7 softmax (warp w: TMEM lane quarter w%4, key half w/4), warp 8 TMA,
-// warp 9 MMA issue (elected lane), warps 10..13 dQ drain.
+// (kSoftmaxWarps + 6) warps: softmax warps (warp w: TMEM lane quarter w%4, key slice w/4), then one TMA warp,
+// one MMA-issue warp (elected lane), four dQ drain warps.
 // Roofline: tensor pipe; FLOPs = 2.5 x forward = 10 * Bt*h*Sq*Sk*d.
 #include <type_traits>
 
@@ -68,9 +68,19 @@ __device__ __forceinline__ void warp_arrive(uint64_t* bar) { mbar_arrive(bar); }
 constexpr int BQ = 128, BKV = 128, HD = 64;
 constexpr int kTile = 128 * HD * 2;     // 16 KB: one [128 x 64] bf16 tile
 constexpr int kPBytes = 128 * 128 * 2;  // 32 KB: P or dS, two 64-key blocks of [128 q x 128 B]
-constexpr int kSoftmaxWarps = 8;
-constexpr int kTmaWarp = 8, kMmaWarp = 9;   // warps 10..13: dQ drain
-constexpr int kThreads = 32 * 14;
+// Softmax warps: 4 TMEM lane quarters x (kSoftmaxWarps / 4) key slices.  Eight: each thread handles 64 keys in two
+// 32-key rounds, and the second round's TMEM load waits out the previous pair's gradient MMAs (r02 trace).  Sixteen
+// (32 keys per thread, one load round; 704 threads at 80 registers) was measured: every stage slows down with 22
+// warps on the SM (pair period 3990 against 3560 clk, S = 1024 shape 494 against 449 us), also with the gradient
+// MMAs held back until the loads are done (VST_BWD_ORDER=1: 5070 clk).
+#ifndef VST_BWD_SOFTMAX_WARPS
+#define VST_BWD_SOFTMAX_WARPS 8
+#endif
+constexpr int kSoftmaxWarps = VST_BWD_SOFTMAX_WARPS;
+constexpr int kKeysPerThread = BKV / (kSoftmaxWarps / 4);       // 64 or 32
+constexpr int kChunks = kKeysPerThread / 32;                    // TMEM load rounds per pair and thread
+constexpr int kTmaWarp = kSoftmaxWarps, kMmaWarp = kSoftmaxWarps + 1, kDrainWarp0 = kSoftmaxWarps + 2;   // + 4 dQ drain warps
+constexpr int kThreads = 32 * (kSoftmaxWarps + 6);
 // Q / dO stages: with two, the load of pair i+1 can only start when the gradient MMAs of pair i-1 release their
 // stage and its ~1300 clk of TMA latency sits in front of the S / dP issue (three: L1 self 2411 -> 2361 us).
 #ifndef VST_BWD_QSTAGES
@@ -364,12 +374,14 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #endif
   } else if (warp < kSoftmaxWarps) {
     // ================= softmax warps: P and dS of this warp's 32 rows x 64 keys =================
-    const int quarter = warp & 3, half = warp >> 2;
+    const int quarter = warp & 3, ks = warp >> 2;       // key slice: columns [ks * kKeysPerThread, + kKeysPerThread)
+    const int col0 = ks * kKeysPerThread;
     const int row = quarter * 32 + lane;
     const uint32_t lane_off = uint32_t(quarter * 32) << 16;
     const int64_t vec_base = ((int64_t)b * a.heads + head) * a.Sq;
-    uint8_t* prow = sP + half * 16384 + row * 128;
-    uint8_t* dsrow = sdS + half * 16384 + row * 128;
+    uint8_t* prow = sP + (col0 >> 6) * 16384 + row * 128;      // [64-key block][row][128 B]
+    uint8_t* dsrow = sdS + (col0 >> 6) * 16384 + row * 128;
+    const int cb = (col0 & 63) >> 3;                           // first 16-byte chunk of this thread in the row
     const int rx = row & 7;
     // The arithmetic is the longest stage of a pair (r02 clock64 trace, scripts/attn_bwd_trace.py: ~3000 of 5550 clk
     // with scalar math and per-element bounds / mask predicates), so the common case -- no additive mask, key tile
@@ -391,7 +403,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       const float* mrow = a.mask == nullptr ? nullptr
                               : a.mask + (int64_t)b * a.mask_sb + (int64_t)head * a.mask_sh +
                                     (int64_t)min(q, a.Sq - 1) * a.mask_sq;
-      uint32_t pw[32], dsw[32];
+      uint32_t pw[16 * kChunks], dsw[16 * kChunks];
       mbar_wait(sdp_full, i & 1, 30);
       if (warp == 0) BTRACE(0, i);
       tc_fence_after();
@@ -400,12 +412,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       const float2 sc2 = make_float2(a.scale_log2, a.scale_log2), nl2 = make_float2(-lse2, -lse2);
       const float2 s2 = make_float2(a.scale, a.scale), nd2 = make_float2(-dv * a.scale, -dv * a.scale);
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
+      for (int c = 0; c < kChunks; ++c) {
         uint32_t s[32], dp[32];
-        tmem_ld32(tS + lane_off + half * 64 + c * 32, s);
-        tmem_ld32(tdP + lane_off + half * 64 + c * 32, dp);
+        tmem_ld32(tS + lane_off + col0 + c * 32, s);
+        tmem_ld32(tdP + lane_off + col0 + c * 32, dp);
         tmem_ld_wait();
-        if (c == 1 && i + 1 < nq) {
+        if (c == kChunks - 1 && i + 1 < nq) {
           // In flight under the chunk-1 arithmetic and the stores.  AFTER the pair's last tcgen05.wait::ld: with the
           // loads issued before it, that wait also sat out their L2 latency (r02 trace: 997 clk for the first
           // chunk's TMEM load against 99 for the second).
@@ -416,12 +428,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             dv_n = __ldg(a.dvec + vec_base + qn);
           }
         }
-        if (c == 1) {
+        if (c == kChunks - 1) {
           tc_fence_before();
           warp_arrive(sdp_free);       // S / dP may be overwritten by the next pair
           if (warp == 0) BTRACE(1, i);
         }
-        const int key0 = kv0 + half * 64 + c * 32;
+        const int key0 = kv0 + col0 + c * 32;
         if (fast) {
           auto chunk = [&](auto tail_c) {
 #pragma unroll
@@ -478,8 +490,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #endif
       if (warp == 0) BTRACE(3, i);
 #pragma unroll
-      for (int cc = 0; cc < ((VST_BWD_ABLATE & 16) ? 0 : 8); ++cc) {
-        const int off = (cc ^ rx) * 16;
+      for (int cc = 0; cc < ((VST_BWD_ABLATE & 16) ? 0 : 4 * kChunks); ++cc) {
+        const int off = ((cb + cc) ^ rx) * 16;
         *reinterpret_cast<uint4*>(prow + off) = make_uint4(pw[4 * cc], pw[4 * cc + 1], pw[4 * cc + 2], pw[4 * cc + 3]);
         *reinterpret_cast<uint4*>(dsrow + off) = make_uint4(dsw[4 * cc], dsw[4 * cc + 1], dsw[4 * cc + 2], dsw[4 * cc + 3]);
       }
@@ -487,7 +499,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       warp_arrive(pds_full);
       if (warp == 0) BTRACE(4, i);
     }
-    // ---- dV (half 0) / dK (half 1): TMEM lane = key row ----
+    // ---- dV (warps 0..3) / dK (warps 4..7): TMEM lane = key row ----
+    if (warp < 8) {
+    const int half = warp >> 2;
     mbar_wait(pds_free, (nq - 1) & 1, 32);
     tc_fence_after();
     const int key = kv0 + row;
@@ -524,20 +538,21 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         }
       }
     }
+    }
   } else {
     // ================= dQ drain (warps 10..13): add each pair's dQ tile to the fp32 accumulator ===
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
     const uint32_t lane_off = uint32_t(quarter * 32) << 16;
 #if VST_BWD_DQ_TMA
-    const bool leader = warp == 10 && lane == 0;
+    const bool leader = warp == kDrainWarp0 && lane == 0;
     const int bh = b * a.heads + head;
     const int rx = row & 7;
     if (leader) tma_prefetch_desc(&tmdQ);
 #endif
     for (int i = 0; i < nq; ++i) {
       mbar_wait(dq_full, i & 1, 40);
-      if (warp == 10) BTRACE(7, i);
+      if (warp == kDrainWarp0) BTRACE(7, i);
       tc_fence_after();
       uint32_t o[64];
       tmem_ld32(tdQ + lane_off, o);
@@ -581,7 +596,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                                 __uint_as_float(o[4 * v + 2]), __uint_as_float(o[4 * v + 3])));
       }
 #endif
-      if (warp == 10) BTRACE(8, i);
+      if (warp == kDrainWarp0) BTRACE(8, i);
     }
 #if VST_BWD_DQ_TMA
     if (leader) tma_store_wait_read<0>();      // shared memory read out; the reductions complete with the kernel
