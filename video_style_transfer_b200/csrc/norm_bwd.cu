@@ -26,6 +26,31 @@ __device__ __forceinline__ void store8bf(__nv_bfloat16* p, const float* v) {
 }
 template <typename TP>
 __device__ __forceinline__ float ldparam(const TP* p, int i) { return p ? (float)p[i] : 1.f; }
+// eight consecutive parameters (16-byte aligned offset) in one or two 16-byte loads
+__device__ __forceinline__ void ldparam8(const float* p, int off, float* o) {
+  if (p == nullptr) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = 1.f;
+    return;
+  }
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p + off)), b = __ldg(reinterpret_cast<const float4*>(p + off) + 1);
+  o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
+}
+__device__ __forceinline__ void ldparam8(const __nv_bfloat16* p, int off, float* o) {
+  if (p == nullptr) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = 1.f;
+    return;
+  }
+  const uint4 u = __ldg(reinterpret_cast<const uint4*>(p + off));
+  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 e = unpack_bf16(w[i]);
+    o[2 * i] = e.x;
+    o[2 * i + 1] = e.y;
+  }
+}
 
 // ---- LayerNorm backward -----------------------------------------------------------------------
 // y = xhat * gamma + beta (+ pe: additive, no gradient).  Per row, with g = dy * gamma:
@@ -48,19 +73,45 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restri
 #pragma unroll
     for (int j = 0; j < 8; ++j) dgam[i][j] = dbet[i][j] = 0.f;
   const float invC = 1.f / (float)C;
-  for (int64_t row = (int64_t)blockIdx.x * kLnWarps + warp; row < rows; row += (int64_t)gridDim.x * kLnWarps) {
+  // the NEXT row's 16-byte loads are in flight (raw, in registers) while this row goes through its three warp
+  // reductions: one resident block of 8 warps per SM has nothing else to hide the load latency with
+  const int64_t rstep = (int64_t)gridDim.x * kLnWarps;
+  int64_t row = (int64_t)blockIdx.x * kLnWarps + warp;
+  uint4 nx[MAXV], ng[MAXV];
+  auto fetch = [&](int64_t r) {
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int vi = lane + 32 * i;
+      if (vi < nvec) {
+        nx[i] = ld_stream16(x + r * C + vi * 8);
+        ng[i] = ld_stream16(dy + r * C + vi * 8);
+      }
+    }
+  };
+  auto unpack = [](const uint4& u, float* o) {
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float2 e = unpack_bf16(w[q]);
+      o[2 * q] = e.x;
+      o[2 * q + 1] = e.y;
+    }
+  };
+  if (row < rows) fetch(row);
+  for (; row < rows; row += rstep) {
     float v[MAXV][8], g[MAXV][8];
     float sum = 0.f;
 #pragma unroll
     for (int i = 0; i < MAXV; ++i) {
       const int vi = lane + 32 * i;
       if (vi < nvec) {
-        load8bf(x + row * C + vi * 8, v[i]);
-        load8bf(dy + row * C + vi * 8, g[i]);
+        unpack(nx[i], v[i]);
+        unpack(ng[i], g[i]);
 #pragma unroll
         for (int j = 0; j < 8; ++j) sum += v[i][j];
       }
     }
+    if (row + rstep < rows) fetch(row + rstep);
     const float mean = warp_sum(sum) * invC;
     float m2 = 0.f;
 #pragma unroll
@@ -78,13 +129,15 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restri
     for (int i = 0; i < MAXV; ++i) {
       const int vi = lane + 32 * i;
       if (vi < nvec) {
+        float gam8[8];
+        ldparam8(gamma, vi * 8, gam8);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const float xh = (v[i][j] - mean) * rstd;
           const float d = g[i][j];
           dgam[i][j] = fmaf(d, xh, dgam[i][j]);
           dbet[i][j] += d;
-          const float gg = d * ldparam(gamma, vi * 8 + j);
+          const float gg = d * gam8[j];
           v[i][j] = xh;
           g[i][j] = gg;
           s1 += gg;
@@ -136,9 +189,13 @@ __global__ void ln_bwd_reduce_kernel(const float* __restrict__ partial, int bloc
   float* out = which == 0 ? dgamma : dbeta;
   if (out) out[col] = s;
 }
-int ln_bwd_blocks(int64_t rows) {
+// Blocks = what is resident at once: the C > 512 instantiation holds 160 accumulators + 80 row values per lane
+// (191 registers) and 8 x 2 x C floats of shared memory, ONE block per SM; four waves of such blocks (r01: a cap of
+// 4 x SMs) left each block 28 rows to amortise its 80 KB cross-warp reduction over (S = 1024 level: 126 us, 0.15 of
+// HBM).
+int ln_bwd_blocks(int64_t rows, int C) {
   int64_t b = (rows + kLnWarps - 1) / kLnWarps;
-  const int64_t cap = 4 * (int64_t)vst_sm_count();
+  const int64_t cap = (C <= 512 ? 2 : 1) * (int64_t)vst_sm_count();
   return (int)(b < cap ? b : cap);
 }
 
@@ -296,7 +353,7 @@ __global__ void gn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ x, const _
 
 extern "C" int64_t vst_layernorm_bwd_workspace_bytes(int64_t rows, int C) {
   if (rows <= 0 || C <= 0) return 0;
-  return (int64_t)ln_bwd_blocks(rows) * 2 * C * 4;
+  return (int64_t)ln_bwd_blocks(rows, C) * 2 * C * 4;
 }
 
 extern "C" int vst_layernorm_bwd(const void* x, const void* dy, const void* gamma, void* dx,
@@ -308,7 +365,7 @@ extern "C" int vst_layernorm_bwd(const void* x, const void* dy, const void* gamm
   VST_REQUIRE(x && dy && dx, VST_E_BADARG, "layernorm_bwd: null pointer");
   VST_REQUIRE(C % 8 == 0 && C <= 1280, VST_E_UNSUPPORTED,
               "layernorm_bwd: C must be a multiple of 8, <= 1280 (motion-module widths)");
-  const int blocks = ln_bwd_blocks(rows);
+  const int blocks = ln_bwd_blocks(rows, C);
   VST_REQUIRE(workspace && workspace_bytes >= (int64_t)blocks * 2 * C * 4, VST_E_BADARG,
               "layernorm_bwd: workspace of vst_layernorm_bwd_workspace_bytes() bytes required");
   cudaStream_t st = (cudaStream_t)stream;
@@ -323,9 +380,9 @@ extern "C" int vst_layernorm_bwd(const void* x, const void* dy, const void* gamm
                                               (float*)workspace, rows, C, eps);                     \
   } while (0)
   if (param_dtype == VST_BF16) {
-    if (nvec <= 64) LN_BWD(__nv_bfloat16, 2); else LN_BWD(__nv_bfloat16, 5);
+    if (nvec <= 64) LN_BWD(__nv_bfloat16, 2); else if (nvec <= 96) LN_BWD(__nv_bfloat16, 3); else LN_BWD(__nv_bfloat16, 5);
   } else if (param_dtype == VST_F32) {
-    if (nvec <= 64) LN_BWD(float, 2); else LN_BWD(float, 5);
+    if (nvec <= 64) LN_BWD(float, 2); else if (nvec <= 96) LN_BWD(float, 3); else LN_BWD(float, 5);
   } else {
     vst_set_error("layernorm_bwd: bad param dtype %d", param_dtype);
     return VST_E_BADARG;
