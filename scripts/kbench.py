@@ -215,6 +215,12 @@ def main():
             report(f"vst_gemm TN split-K {tag}", ms, b, (a.numel() + x.numel()) * 2, 2 * m * n * k)
             ms, b = timeit(lambda: a.t() @ x)
             report(f"  (cuBLAS matmul) {tag}", ms, b, (a.numel() + x.numel()) * 2, 2 * m * n * k)
+    if "bwd" in which or "colsum" in which:
+        for tag, m, n in [("L0 FF bias grad M=262144 N=2560", 262144, 2560), ("L0 proj bias grad M=262144 N=320", 262144, 320),
+                          ("L2 FF bias grad M=16384 N=10240", 16384, 10240)]:
+            dy = torch.randn(m, n, device="cuda").to(bf)
+            ms, b = timeit(lambda: ops.colsum(dy))
+            report(f"colsum {tag}", ms, b, m * n * 2)
     if "bwd" in which or "abwd" in which:
         for tag, bt, h, sq, sk in [("L1 self", 16, 10, 4096, 4096), ("L2 self", 16, 20, 1024, 1024),
                                    ("L1 cross", 16, 10, 4096, 77), ("L2 cross", 16, 20, 1024, 77)]:

@@ -75,6 +75,50 @@ __global__ void colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, int64
     *reinterpret_cast<float2*>(partial + (int64_t)blockIdx.y * N + c0) = t;
   }
 }
+// Same sums with 16-byte loads (N, ld multiples of 8 elements, 16-byte aligned base): block = 128 columns x one row
+// chunk, 256 threads = 16 row lanes x 16 column octets, four rows in flight per thread.  The 4-byte form above
+// measured 0.34 of HBM over the 60 bias-gradient launches of a config-4 step (r02, profiles/cfg4_kernels_r02.tsv).
+constexpr int kVecCols = 128;
+__global__ void __launch_bounds__(256)
+colsum_partial_vec_kernel(const __nv_bfloat16* __restrict__ x, int64_t ld, int64_t M, int N,
+                          int64_t rows_per_chunk, float* __restrict__ partial) {
+  const int cg = threadIdx.x & 15, rl = threadIdx.x >> 4;   // column octet, row lane 0..15
+  const int c0 = blockIdx.x * kVecCols + cg * 8;
+  const int64_t r0 = (int64_t)blockIdx.y * rows_per_chunk;
+  const int64_t r1 = min(M, r0 + rows_per_chunk);
+  float s[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = 0.f;
+  auto add = [&](const uint4& u) {
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float2 e = unpack_bf16(w[q]);
+      s[2 * q] += e.x;
+      s[2 * q + 1] += e.y;
+    }
+  };
+  if (c0 < N) {
+    const __nv_bfloat16* p = x + c0;
+    int64_t r = r0 + rl;
+    for (; r + 48 < r1; r += 64) {
+      const uint4 a = ld_stream16(p + r * ld), b = ld_stream16(p + (r + 16) * ld);
+      const uint4 c = ld_stream16(p + (r + 32) * ld), d = ld_stream16(p + (r + 48) * ld);
+      add(a); add(b); add(c); add(d);
+    }
+    for (; r < r1; r += 16) add(ld_stream16(p + r * ld));
+  }
+  __shared__ float sm[16][kVecCols + 4];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) sm[rl][cg * 8 + j] = s[j];
+  __syncthreads();
+  if (threadIdx.x < kVecCols && blockIdx.x * kVecCols + threadIdx.x < N) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) t += sm[i][threadIdx.x];
+    partial[(int64_t)blockIdx.y * N + blockIdx.x * kVecCols + threadIdx.x] = t;
+  }
+}
 __global__ void colsum_final_kernel(const float* __restrict__ partial, int chunks, int N,
                                     float alpha, float* __restrict__ out) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
@@ -84,9 +128,22 @@ __global__ void colsum_final_kernel(const float* __restrict__ partial, int chunk
   out[n] = alpha * s;
 }
 
+void colsum_launch_partial(const void* x, int64_t ld, int64_t M, int N, int chunks, float* partial,
+                           cudaStream_t st) {
+  const int64_t rows_per_chunk = (M + chunks - 1) / chunks;
+  if (N % 8 == 0 && ld % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0) {
+    dim3 grid((N + kVecCols - 1) / kVecCols, chunks);
+    colsum_partial_vec_kernel<<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, ld, M, N, rows_per_chunk, partial);
+  } else {
+    dim3 grid((N + kColsPerBlock - 1) / kColsPerBlock, chunks);
+    colsum_partial_kernel<<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, ld, M, N, rows_per_chunk, partial);
+  }
+}
+
 int colsum_chunks(int64_t M, int N) {
-  const int col_blocks = (N + kColsPerBlock - 1) / kColsPerBlock;
-  int64_t chunks = (4 * vst_sm_count() + col_blocks - 1) / col_blocks;
+  // enough (column block, row chunk) blocks for ~8 resident blocks of 256 threads per SM
+  const int col_blocks = (N + kVecCols - 1) / kVecCols;
+  int64_t chunks = (8 * vst_sm_count() + col_blocks - 1) / col_blocks;
   const int64_t max_chunks = (M + 63) / 64;
   if (chunks > max_chunks) chunks = max_chunks;
   if (chunks < 1) chunks = 1;
@@ -133,11 +190,8 @@ extern "C" int vst_colsum(const void* x, int64_t ld, int64_t M, int N, float alp
   const int chunks = colsum_chunks(M, N);
   VST_REQUIRE(workspace && workspace_bytes >= (int64_t)chunks * N * 4, VST_E_BADARG,
               "colsum: workspace of vst_colsum_workspace_bytes(M, N) bytes required");
-  const int64_t rows_per_chunk = (M + chunks - 1) / chunks;
   cudaStream_t st = (cudaStream_t)stream;
-  dim3 grid((N + kColsPerBlock - 1) / kColsPerBlock, chunks);
-  colsum_partial_kernel<<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, ld, M, N, rows_per_chunk,
-                                              (float*)workspace);
+  colsum_launch_partial(x, ld, M, N, chunks, (float*)workspace, st);
   VST_LAUNCH_OK();
   colsum_final_kernel<<<(N + 255) / 256, 256, 0, st>>>((const float*)workspace, chunks, N, alpha, out);
   VST_LAUNCH_OK();
@@ -188,10 +242,8 @@ extern "C" int vst_colsum_noalloc(const void* x, int64_t ld, int64_t M, int N, f
   float* scratch = nullptr;
   int rc = colsum_noalloc_scratch(&scratch);
   if (rc != VST_OK) return rc;
-  const int64_t rows_per_chunk = (M + chunks - 1) / chunks;
   cudaStream_t st = (cudaStream_t)stream;
-  dim3 grid((N + kColsPerBlock - 1) / kColsPerBlock, chunks);
-  colsum_partial_kernel<<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, ld, M, N, rows_per_chunk, scratch);
+  colsum_launch_partial(x, ld, M, N, chunks, scratch, st);      // the same kernels as vst_colsum
   VST_LAUNCH_OK();
   colsum_final_kernel<<<(N + 255) / 256, 256, 0, st>>>(scratch, chunks, N, alpha, out);
   VST_LAUNCH_OK();
