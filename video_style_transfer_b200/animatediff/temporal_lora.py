@@ -124,27 +124,33 @@ def compute_orth_loss(unet, spatial_index: Dict, lambda_orth: float) -> torch.Te
     instead of the reference's two dense in x in products."""
     if lambda_orth == 0.0 or not spatial_index:
         return torch.tensor(0.0)
-    total: Optional[torch.Tensor] = None
-    count = 0
+    # Layers of equal shape are stacked and go through batched matmuls: per layer the terms are five r x r products
+    # (plus their backward), ~7 us of latency each on the GPU -- 1050 fp32 SGEMM launches, 7.5 ms of a 259 ms
+    # config-4 step (profiles/cfg4_kernels_r02.tsv) -- and the SDXL stack has only a handful of distinct shapes.
+    groups: Dict[tuple, list] = {}
     for name, module in unet.named_modules():
         if name not in spatial_index or not isinstance(module, TemporalLoRALinear):
             continue
         d = spatial_index[name].lora_matrix_dic
-        a_t, b_t = module.lora_A.float(), module.lora_B.float() * module.scale
-        gram_t = a_t @ a_t.T
-        term = None
+        key = (tuple(module.lora_A.shape), tuple(module.lora_B.shape)) + tuple(
+            tuple(d[f"{k}_{w}"].weight.shape) for k in ("content", "style") for w in ("down", "up"))
+        groups.setdefault(key, []).append((module, d))
+    count = sum(len(v) for v in groups.values())
+    if count == 0:
+        return torch.tensor(0.0)
+    total: Optional[torch.Tensor] = None
+    for items in groups.values():
+        a_t = torch.stack([m.lora_A.float() for m, _ in items])                  # (n, r_t, in)
+        b_t = torch.stack([m.lora_B.float() * m.scale for m, _ in items])        # (n, out, r_t)
+        gram_t = a_t @ a_t.transpose(1, 2)
         for key in ("content", "style"):
             with torch.no_grad():
-                b_x = d[f"{key}_up"].weight.float()
-                a_x = d[f"{key}_down"].weight.float()
-                gram_x = a_x @ a_x.T
-            core = b_t.T @ b_x                                         # (r_t, r_x)
+                b_x = torch.stack([d[f"{key}_up"].weight.float() for _, d in items])
+                a_x = torch.stack([d[f"{key}_down"].weight.float() for _, d in items])
+                gram_x = a_x @ a_x.transpose(1, 2)
+            core = b_t.transpose(1, 2) @ b_x                                     # (n, r_t, r_x)
             val = torch.sum((gram_t @ core) * (core @ gram_x))
-            term = val if term is None else term + val
-        total = term if total is None else total + term
-        count += 1
-    if total is None:
-        return torch.tensor(0.0)
+            total = val if total is None else total + val
     return lambda_orth * total / count
 
 
