@@ -471,6 +471,21 @@ def run_ours(args):
 
     for _ in range(max(args.warmup, 3)):
         step_device()
+    if os.environ.get("VST_KERNEL_TABLE"):
+        # per-kernel device time of ONE step through torch.profiler (CUPTI): cheap next to an ncu pass; tab-separated
+        from torch.profiler import ProfilerActivity, profile
+        torch.cuda.synchronize()
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            step_device()
+            torch.cuda.synchronize()
+        rows = sorted(((e.key, e.count, e.device_time_total) for e in prof.key_averages() if e.device_time_total > 0),
+                      key=lambda r: -r[2])
+        tot = sum(r[2] for r in rows)
+        with open(os.environ["VST_KERNEL_TABLE"], "w") as f:
+            f.write(f"# one hot-path denoise step, kernel device time (us), total {tot:.1f} us over {sum(r[1] for r in rows)} launches\n")
+            f.write("kernel\tlaunches\ttotal_us\tshare\n")
+            for k, n, t in rows:
+                f.write(f"{k[:120]}\t{n}\t{t:.1f}\t{t / tot:.4f}\n")
     if args.ncu_step:
         torch.cuda.synchronize()
         torch.cuda.profiler.start()
