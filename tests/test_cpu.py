@@ -613,3 +613,82 @@ def test_cpu_arm_uses_reference_modules_when_placed():
         close(op.motion_module(xm, w, 8, 8, 32, {"scale": 1.0 / 32}), mm(xm, 8), 2e-5)
     arm = ref_cpu.CpuArm(8, 32)
     assert arm.kind == "reference" and set(arm.units) == set(arm.CALLS)
+
+
+# ---- on-disk formats against files the REFERENCE's own helpers wrote / read (formats were only
+# ---- checked against this repository's own loader) ------------------------------------------------------------
+def test_formats_match_reference_written_files(tmp_path):
+    """tests/golden/formats.npz holds what the reference's insert_unziplora_to_unet / freeze_spatial_layers /
+    save_checkpoint / unet_inverse_ziplora_state_dict produced on the toy UNet of oracle/toy_unet.py
+    (oracle/make_golden_formats.py; reference unziplora_unet/utils.py:289-310,388-483,
+    animatediff/utils.py:66-163, temporal_lora.py:86-192).  The drop-in helpers must read the same input
+    files into the same state dict and write files with the same keys and tensors."""
+    from safetensors.torch import save_file
+    from oracle.toy_unet import ToyUNet
+    from video_style_transfer_b200.unziplora_unet import utils as U
+    from video_style_transfer_b200.animatediff import utils as AU
+    from video_style_transfer_b200.animatediff.temporal_lora import inject_temporal_lora, TemporalLoRALinear
+    from video_style_transfer_b200.unziplora_unet.unziplora_linear_layer import UnZipLoRALinearLayer
+    g = np.load(os.path.join(GOLD, "formats.npz"))
+    sub = lambda prefix: {k[len(prefix):]: torch.from_numpy(g[k]) for k in g.files if k.startswith(prefix)}
+    assert str(g["lora_file_name"]) == U.LORA_WEIGHT_NAME_SAFE
+    unet = ToyUNet()
+    unet.load_state_dict(sub("toy/"))
+    for b in ("content", "style"):
+        (tmp_path / b).mkdir()
+        save_file(sub(f"in/lora_{b}/"), str(tmp_path / b / U.LORA_WEIGHT_NAME_SAFE))
+        torch.save(sub(f"in/merger_{b}/"), str(tmp_path / f"merger_{b}.pth"))
+    U.insert_unziplora_to_unet(unet, str(tmp_path / "content"), str(tmp_path / "style"),
+                               str(tmp_path / "merger_content.pth"), str(tmp_path / "merger_style.pth"), rank=4)
+    want, got = sub("inserted/"), unet.state_dict()
+    assert set(got) == set(want)
+    assert all(torch.equal(got[k], want[k]) for k in want)
+    # Stage 2: temporal LoRA injection count, the same parameter updates, the freeze map, the checkpoint files
+    assert inject_temporal_lora(unet, rank=2, alpha=1.0) == int(g["n_wrapped"])
+    with torch.no_grad():
+        for n, m in unet.named_modules():
+            if isinstance(m, TemporalLoRALinear):
+                m.lora_A.copy_(torch.from_numpy(g[f"lora_A/{n}"]))
+                m.lora_B.copy_(torch.from_numpy(g[f"lora_B/{n}"]))
+        for _, ll in U._lora_sites(unet):
+            ll.merge_content.mul_(0.5)
+            ll.merge_style.add_(0.25)
+    AU.freeze_spatial_layers(unet, unfreeze_mergers=True)
+    rg = {k[len("requires_grad/"):]: bool(g[k]) for k in g.files if k.startswith("requires_grad/")}
+    assert {n: p.requires_grad for n, p in unet.named_parameters()} == rg
+    path = AU.save_checkpoint(unet, str(tmp_path), 7, save_mergers=True)
+    assert sorted(os.listdir(path)) == [str(s) for s in g["checkpoint_files"]]
+    for fn in os.listdir(path):
+        want, got = sub(f"ckpt/{fn}/"), torch.load(os.path.join(path, fn))
+        assert set(got) == set(want), fn
+        for k in want:
+            assert got[k].dtype == want[k].dtype and got[k].shape == want[k].shape, (fn, k)
+            assert torch.allclose(got[k], want[k], rtol=0, atol=1e-6), (fn, k)    # merged W + scale*B A: fp32 order
+    # the reference-written Stage-2 merger files load straight back through the drop-in's inference wiring
+    unet2 = ToyUNet()
+    for fn in ("merger_content_stage2.pth", "merger_style_stage2.pth"):
+        torch.save(sub(f"ckpt/{fn}/"), str(tmp_path / fn))
+    U.insert_unziplora_to_unet(unet2, sub("in/lora_content/"), sub("in/lora_style/"),
+                               str(tmp_path / "merger_content_stage2.pth"), str(tmp_path / "merger_style_stage2.pth"), rank=4)
+    for name, ll in U._lora_sites(unet2):
+        assert torch.equal(ll.merge_content, torch.from_numpy(g[f"ckpt/merger_content_stage2.pth/unet.{name}.lora.merge_content"]))
+        assert torch.equal(ll.merge_style, torch.from_numpy(g[f"ckpt/merger_style_stage2.pth/unet.{name}.lora.merge_style"]))
+    # Stage-1 export of trained layers
+    unet1 = ToyUNet()
+    unet1.load_state_dict(sub("toy/"))
+    for n in U.spatial_attention_names(unet1):
+        attn = unet1.get_submodule(n)
+        for parent, leaf, part in ((attn, "to_q", "to_q"), (attn, "to_k", "to_k"), (attn, "to_v", "to_v"),
+                                   (attn.to_out, "0", "to_out.0")):
+            U._make_lora_compatible(parent, leaf)
+            lin = getattr(parent, leaf)
+            lay = UnZipLoRALinearLayer(lin.in_features, lin.out_features, 4, ["content", "style"], lora_matrix_num=2)
+            missing = lay.load_state_dict(sub(f"stage1/layer/{n}.{part}/"), strict=True)
+            assert not missing.missing_keys and not missing.unexpected_keys
+            lin.set_lora_layer(lay)
+    for key in ("content", "style"):
+        lora_sd, mask_sd = U.unet_inverse_ziplora_state_dict(unet1, key)
+        for kind, got in (("lora", lora_sd), ("mask", mask_sd)):
+            want = sub(f"stage1/export_{key}/{kind}/")
+            assert set(got) == set(want)
+            assert all(torch.allclose(got[k].detach(), want[k], rtol=0, atol=1e-7) for k in want), (key, kind)
