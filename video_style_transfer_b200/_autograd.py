@@ -104,42 +104,81 @@ class FusedLoraFn(torch.autograd.Function):
     def backward(ctx, dy):
         x, w, a, bp, u = ctx.saved_tensors
         out_scale, gn, bias_dtype = ctx.cfg
+        return _low_rank_backward(ctx.needs_input_grad, x, w, a, bp, u, _rows_bf16(dy), out_scale, gn,
+                                  bias_dtype) + (None, None)
+
+
+def _low_rank_backward(need, x, w, a, bp, u, g, out_scale, gn, bias_dtype):
+    """(dx, dw, da, dbp, dbias) of y = (x w^T + u bp^T [grouped] + bias) * out_scale with u = x a^T, from
+    g = dy (2-D bf16 rows); need = needs_input_grad in the order (x, w, a, bp, bias, ...)."""
+    m, n = g.shape
+    k2 = bp.shape[1]
+    groups = (n // gn) if gn else 1
+    dx = dw = da = dbp = dbias = None
+    du = None
+    if need[0] or need[2]:                       # du = dy bp   (per projection group)
+        if groups == 1:
+            du = ops.gemm(g, bp, trans_b=True, alpha=out_scale)
+        else:
+            du = torch.empty((m, groups * k2), dtype=torch.bfloat16, device=g.device)
+            for i in range(groups):
+                ops.gemm(g[:, i * gn:(i + 1) * gn], bp[i * gn:(i + 1) * gn], trans_b=True, alpha=out_scale,
+                         out=du[:, i * k2:(i + 1) * k2])
+    if need[0]:                                  # dx = dy w + du a   (two operand pairs, one GEMM)
+        if (out_scale == 1.0 and m >= 256 and n % 8 == 0 and w.shape[1] % 8 == 0 and du.shape[1] % 8 == 0
+                and not need[1]):
+            # frozen W (every LoRA site of Stage 1 / Stage 2): W is transposed once (memoised; the rank-sized A
+            # again whenever it changed), so the two-pair product runs on the K-major CTA-pair GEMM like
+            # LoraGemmFn's dx, not on vst_gemm's single-CTA MN-major path
+            dx = ops.lora_gemm_raw(g, _transposed(w), du, _transposed(a))
+        elif out_scale == 1.0:
+            dx = ops.gemm(g, w, du, a, trans_b=True)
+        else:
+            dx = ops.gemm(g, w, trans_b=True, alpha=out_scale)
+            ops.gemm(du, a, trans_b=True, out=dx, accumulate=True)
+    if need[1]:
+        dw = ops.gemm(g, x, trans_a=True, trans_b=True, alpha=out_scale)
+    if need[2]:
+        da = ops.gemm(du, x, trans_a=True, trans_b=True)
+    if need[3]:
+        if groups == 1:
+            dbp = ops.gemm(g, u, trans_a=True, trans_b=True, alpha=out_scale)
+        else:
+            dbp = torch.empty((n, k2), dtype=torch.bfloat16, device=g.device)
+            for i in range(groups):
+                ops.gemm(g[:, i * gn:(i + 1) * gn], u[:, i * k2:(i + 1) * k2], trans_a=True, trans_b=True,
+                         alpha=out_scale, out=dbp[i * gn:(i + 1) * gn])
+    if need[4]:
+        dbias = ops.colsum(g, out_scale).to(bias_dtype)
+    return dx, dw, da, dbp, dbias
+
+
+class TwoLaunchLoraFn(torch.autograd.Function):
+    """y = (x w^T + (x a^T) bp^T [grouped] + bias + residual) * out_scale as u = x a^T followed by the GEMM with
+    extra K blocks -- the form grouped q|k|v and residual-carrying projections take -- recorded as ONE node.
+    As two LoraGemmFn nodes (u, then y) autograd summed the two contributions to dx with an elementwise
+    kernel, three passes over an (M, in) tensor per projection; here dx = dy w + du a is one GEMM with two
+    operand pairs, exactly as in FusedLoraFn."""
+
+    @staticmethod
+    def forward(ctx, x, w, a, bp, bias, residual, out_scale, k2_group_n):
+        u = ops.lora_gemm_raw(x, a)
+        y = ops.lora_gemm_raw(x, w, u, bp, bias, residual, out_scale, "none", k2_group_n)
+        ctx.save_for_backward(x, w, a, bp, u)
+        ctx.cfg = (out_scale, k2_group_n, None if bias is None else bias.dtype,
+                   None if residual is None else residual.dtype)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w, a, bp, u = ctx.saved_tensors
+        out_scale, gn, bias_dtype, res_dtype = ctx.cfg
         need = ctx.needs_input_grad
         g = _rows_bf16(dy)
-        m, n = g.shape
-        k2 = bp.shape[1]
-        groups = (n // gn) if gn else 1
-        dx = dw = da = dbp = dbias = None
-        du = None
-        if need[0] or need[2]:                       # du = dy bp   (per projection group)
-            if groups == 1:
-                du = ops.gemm(g, bp, trans_b=True, alpha=out_scale)
-            else:
-                du = torch.empty((m, groups * k2), dtype=torch.bfloat16, device=g.device)
-                for i in range(groups):
-                    ops.gemm(g[:, i * gn:(i + 1) * gn], bp[i * gn:(i + 1) * gn], trans_b=True, alpha=out_scale,
-                             out=du[:, i * k2:(i + 1) * k2])
-        if need[0]:                                  # dx = dy w + du a   (two operand pairs, one GEMM)
-            if out_scale == 1.0:
-                dx = ops.gemm(g, w, du, a, trans_b=True)
-            else:
-                dx = ops.gemm(g, w, trans_b=True, alpha=out_scale)
-                ops.gemm(du, a, trans_b=True, out=dx, accumulate=True)
-        if need[1]:
-            dw = ops.gemm(g, x, trans_a=True, trans_b=True, alpha=out_scale)
-        if need[2]:
-            da = ops.gemm(du, x, trans_a=True, trans_b=True)
-        if need[3]:
-            if groups == 1:
-                dbp = ops.gemm(g, u, trans_a=True, trans_b=True, alpha=out_scale)
-            else:
-                dbp = torch.empty((n, k2), dtype=torch.bfloat16, device=g.device)
-                for i in range(groups):
-                    ops.gemm(g[:, i * gn:(i + 1) * gn], u[:, i * k2:(i + 1) * k2], trans_a=True, trans_b=True,
-                             alpha=out_scale, out=dbp[i * gn:(i + 1) * gn])
-        if need[4]:
-            dbias = ops.colsum(g, out_scale).to(bias_dtype)
-        return dx, dw, da, dbp, dbias, None, None
+        dres = None
+        if need[5]:
+            dres = (g if out_scale == 1.0 else g * out_scale).to(res_dtype).reshape(dy.shape)
+        return _low_rank_backward(need, x, w, a, bp, u, g, out_scale, gn, bias_dtype) + (dres, None, None)
 
 
 class CastCatFn(torch.autograd.Function):

@@ -72,7 +72,10 @@ def bf16_cached(*tensors: torch.Tensor, pad_rows: bool = False) -> torch.Tensor:
     if len(tensors) == 1 and not pad_rows:
         t = tensors[0]
         if t.dtype == torch.bfloat16 and t.is_contiguous():
-            return t if track else t.detach()
+            # the parameter itself, never a fresh `.detach()` alias: caches of operands derived from it
+            # (transposes, folded weights) key on the tensor object's identity, and a new alias per call
+            # made them miss every time (nothing is recorded for a frozen tensor or under no_grad anyway)
+            return t
     if track:
         from ._autograd import CastCatFn
         with torch.no_grad():

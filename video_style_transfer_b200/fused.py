@@ -80,6 +80,14 @@ def _fused_low_rank(x2, weight, bias, a, bp, k2_group_n: int, out_scale: float):
     return ops.lora_gemm_fused(x2, bf16_cached(weight), a_f, bp_f, b, out_scale, k2_group_n)
 
 
+def _gemm_bias(b):
+    if b is not None and not (torch.is_grad_enabled() and b.requires_grad):
+        b = b.detach()
+    if b is not None and b.dtype not in (torch.float32, torch.bfloat16):
+        b = b.float()
+    return b
+
+
 def _frozen(tensors) -> bool:
     return not (torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in tensors))
 
@@ -154,6 +162,9 @@ def project_one(layer, x2: torch.Tensor, scale: float = 1.0, residual=None, out_
                 y = _fused_low_rank(x2, s.site_weight(), s.site_bias(), a, bp, 0, out_scale)
                 if y is not None:
                     return y
+            if act == "none" and out_dtype == torch.bfloat16:
+                return ops.lora_linear_two_launch(x2, bf16_cached(s.site_weight()), a, bp, _gemm_bias(s.site_bias()),
+                                                  residual, out_scale, 0)
             low = (ops.lora_gemm(x2, a), bp)
     return fused_linear(x2, s.site_weight(), s.site_bias(), low, residual, out_scale, act, out_dtype)
 
@@ -196,8 +207,7 @@ def project_fused(layers: Sequence, x2: torch.Tensor, scale: float = 1.0, batch=
         else:
             bp = cached_build(list(ups), "catup", lambda: torch.cat(list(ups), dim=0).contiguous())
         y = _fused_low_rank(x2, w, bias, a_cat, bp, n0, 1.0)            # one launch (VST_FUSED_LORA=2)
-        if y is None:
-            u = ops.lora_gemm(x2, a_cat)                                # (M, G*K2)
-            y = ops.lora_gemm(x2, w, u, bp, bias=bias, k2_group_n=n0)
+        if y is None:                                                   # u = x a_cat^T (M, G*K2), then the GEMM
+            y = ops.lora_linear_two_launch(x2, w, a_cat, bp, bias, None, 1.0, n0)
     from ._autograd import split_cols
     return split_cols(y, n0, len(sites), batch)

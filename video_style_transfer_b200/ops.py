@@ -321,6 +321,19 @@ def lora_gemm_raw(a1: torch.Tensor, b1: torch.Tensor, a2: Optional[torch.Tensor]
     return out
 
 
+def lora_linear_two_launch(x: torch.Tensor, w: torch.Tensor, a_down: torch.Tensor, bp: torch.Tensor,
+                           bias: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,
+                           out_scale: float = 1.0, k2_group_n: int = 0) -> torch.Tensor:
+    """y = (x w^T + (x a_down^T) bp^T [grouped] + bias + residual) * out_scale: the u = x a_down^T pre-pass and
+    the GEMM with extra K blocks (two launches).  Under autograd it is ONE node (TwoLaunchLoraFn), so dx is a
+    single two-pair GEMM instead of two GEMMs and an elementwise sum."""
+    if _needs_grad(x, w, a_down, bp, bias, residual):
+        from ._autograd import TwoLaunchLoraFn
+        return TwoLaunchLoraFn.apply(x, w, a_down, bp, bias, residual, float(out_scale), int(k2_group_n))
+    u = lora_gemm_raw(x, a_down)
+    return lora_gemm_raw(x, w, u, bp, bias, residual, out_scale, "none", k2_group_n)
+
+
 def lora_gemm_fused_supported(m: int, n: int, k1: int, k2: int, k2_group_n: int = 0) -> bool:
     return lib.vst_lora_gemm_fused_supported(m, n, k1, k2, k2_group_n) > 0
 
