@@ -620,6 +620,165 @@ layernorm_flat_pers_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* _
   }
 }
 
+// ---- lane-owned LayerNorm (bf16 activations, C = 64 * KS) ----------------------------------------------------
+// The flat kernels above are bound by instruction ISSUE, not by memory: per 16-byte vector they unpack the
+// activations three times, fetch and unpack gamma / beta / the position row and run scalar fp32 math -- ~130
+// thread instructions per vector, i.e. > 5 warp instructions per clock and SM at the HBM rate against 4 issue
+// slots (measured: 0.58-0.66 of HBM with gamma + beta + positions, 0.81-0.86 with none, profiles/ln_probe_r02.log).
+// Here a lane owns the SAME channel pairs {64 k + 2 lane, +1} of every row it touches and a warp only visits rows
+// of ONE frame (row = position * F + frame), so gamma, beta and the position row are loaded once per kernel and
+// stay in registers: nothing but activations moves in the loop.  A row is KS coalesced 128-byte warp loads of one
+// packed bf16 pair per lane; the arithmetic runs on packed f32x2 instructions (FADD2 / FMUL2 / FFMA2).  R rows are
+// processed per trip with the rows of the next TWO trips in flight (register ring, loop unrolled by three so the
+// ring never moves).  Numerics as the flat kernels: fp32 two-pass statistics, ((x - mean) * rstd) * gamma + beta
+// rounded to bf16, then + position row in fp32 and rounded again (the two roundings of the torch module).
+__device__ __forceinline__ uint32_t ld_stream4(const void* p) {
+  uint32_t r;
+  asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void st_stream4(void* p, uint32_t v) {
+  asm volatile("st.global.L1::no_allocate.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+template <typename TP>
+__device__ __forceinline__ float2 ldparam2(const TP* p);
+template <>
+__device__ __forceinline__ float2 ldparam2<__nv_bfloat16>(const __nv_bfloat16* p) {
+  return unpack_bf16(__ldg(reinterpret_cast<const uint32_t*>(p)));
+}
+template <>
+__device__ __forceinline__ float2 ldparam2<float>(const float* p) {
+  return __ldg(reinterpret_cast<const float2*>(p));
+}
+
+template <typename TP, int KS, int R>
+__global__ void __launch_bounds__(256, 2)
+layernorm_lane_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
+                      const TP* __restrict__ gamma, const TP* __restrict__ beta,
+                      const float* __restrict__ pe, int rows, int Fq, float eps) {
+  // 32-bit indices throughout (the host takes this kernel only when rows * C < 2^31)
+  constexpr int C = 64 * KS;
+  constexpr float kInvC = 1.f / (float)C;
+  const int lane = threadIdx.x & 31;
+  const int wg = blockIdx.x * 8 + (threadIdx.x >> 5), W = gridDim.x * 8;
+  const int f = wg % Fq;                                  // the one frame this warp visits
+  const int q = wg / Fq, Q = W / Fq;                      // position block of this warp, position blocks in flight
+  const int npos = (rows + Fq - 1) / Fq;
+  const int n_trips = (npos + Q * R - 1) / (Q * R);
+  const int c0 = 2 * lane;
+
+  float2 gm[KS], bt[KS], pp[KS];
+#pragma unroll
+  for (int k = 0; k < KS; ++k) {
+    gm[k] = gamma ? ldparam2<TP>(gamma + 64 * k + c0) : make_float2(1.f, 1.f);
+    bt[k] = beta ? ldparam2<TP>(beta + 64 * k + c0) : make_float2(0.f, 0.f);
+    pp[k] = pe ? __ldg(reinterpret_cast<const float2*>(pe + (int64_t)f * C + 64 * k + c0)) : make_float2(0.f, 0.f);
+  }
+
+  auto row_of = [&](int t, int j) -> int {                // -1: no such row
+    const int pos = (t * Q + q) * R + j;
+    const int row = pos * Fq + f;
+    return (pos < npos && row < rows) ? row : -1;
+  };
+  auto load = [&](uint32_t (&buf)[R][KS], int t) {
+#pragma unroll
+    for (int j = 0; j < R; ++j) {
+      const int row = row_of(t, j);
+#pragma unroll
+      for (int k = 0; k < KS; ++k) buf[j][k] = row >= 0 ? ld_stream4(x + row * C + 64 * k + c0) : 0u;
+    }
+  };
+  auto process = [&](uint32_t (&buf)[R][KS], int t) {
+    float mean[R], rstd[R];
+    {
+      float part[R];
+#pragma unroll
+      for (int j = 0; j < R; ++j) {
+        float2 s2 = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int k = 0; k < KS; ++k) s2 = __fadd2_rn(s2, unpack_bf16(buf[j][k]));
+        part[j] = s2.x + s2.y;
+      }
+#pragma unroll
+      for (int j = 0; j < R; ++j) mean[j] = warp_sum(part[j]) * kInvC;
+#pragma unroll
+      for (int j = 0; j < R; ++j) {
+        const float2 nm = make_float2(-mean[j], -mean[j]);
+        float2 m2 = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int k = 0; k < KS; ++k) {
+          const float2 d = __fadd2_rn(unpack_bf16(buf[j][k]), nm);
+          m2 = __ffma2_rn(d, d, m2);
+        }
+        part[j] = m2.x + m2.y;
+      }
+#pragma unroll
+      for (int j = 0; j < R; ++j) rstd[j] = rsqrtf(warp_sum(part[j]) * kInvC + eps);
+    }
+#pragma unroll
+    for (int j = 0; j < R; ++j) {
+      const int row = row_of(t, j);
+      if (row < 0) continue;
+      const float2 nm = make_float2(-mean[j], -mean[j]), rs = make_float2(rstd[j], rstd[j]);
+      __nv_bfloat16* yr = y + row * C + c0;
+#pragma unroll
+      for (int k = 0; k < KS; ++k) {
+        const float2 d = __fmul2_rn(__fadd2_rn(unpack_bf16(buf[j][k]), nm), rs);
+        const float2 o = __ffma2_rn(d, gm[k], bt[k]);
+        uint32_t w = pack_bf16(o.x, o.y);
+        if (pe) {
+          const float2 e = __fadd2_rn(unpack_bf16(w), pp[k]);
+          w = pack_bf16(e.x, e.y);
+        }
+        st_stream4(yr + 64 * k, w);
+      }
+    }
+  };
+
+  uint32_t b0[R][KS], b1[R][KS], b2[R][KS];
+  if (n_trips > 0) load(b0, 0);
+  if (n_trips > 1) load(b1, 1);
+  for (int t = 0; t < n_trips; t += 3) {
+    if (t + 2 < n_trips) load(b2, t + 2);
+    process(b0, t);
+    if (t + 1 >= n_trips) break;
+    if (t + 3 < n_trips) load(b0, t + 3);
+    process(b1, t + 1);
+    if (t + 2 >= n_trips) break;
+    if (t + 4 < n_trips) load(b1, t + 4);
+    process(b2, t + 2);
+  }
+}
+
+inline int ln_lane_mode() {
+  static const int mode = [] {
+    const char* e = getenv("VST_LN_LANE");
+    return e ? atoi(e) : 1;
+  }();
+  return mode;
+}
+
+// The lane-owned kernel when the shape is one of its instantiations and there is work for two trips of every
+// resident warp; otherwise the caller goes on to the flat kernels (kLnNotTaken).
+constexpr int kLnNotTaken = 1;
+template <typename TP, int KS, int R>
+int try_launch_ln_lane(const void* x, void* y, const void* g, const void* b, const float* pe, int64_t rows,
+                       int F, float eps, cudaStream_t st) {
+  if (!ln_lane_mode()) return kLnNotTaken;
+  const int Fq = pe ? F : 1;
+  if (Fq <= 0) return kLnNotTaken;
+  int a = Fq, c = 8;
+  while (c) { const int t = a % c; a = c; c = t; }
+  const int mult = Fq / a;                              // blocks * 8 warps must be a multiple of Fq
+  int64_t blocks = (int64_t)vst_sm_count() * 2;
+  blocks -= blocks % mult;
+  if (blocks < mult || rows < blocks * 8 * R * 2 || (rows + 2 * Fq) * (64 * KS) >= (1ll << 31)) return kLnNotTaken;
+  layernorm_lane_kernel<TP, KS, R><<<(unsigned)blocks, 256, 0, st>>>(
+      (const __nv_bfloat16*)x, (__nv_bfloat16*)y, (const TP*)g, (const TP*)b, pe, (int)rows, Fq, eps);
+  VST_LAUNCH_OK();
+  return VST_OK;
+}
+
 inline int ln_pers_mode() {
   static const int mode = [] {
     const char* e = getenv("VST_LN_PERS");
@@ -633,6 +792,23 @@ int launch_ln_flat(const void* x, void* y, const void* g, const void* b, const f
                    int F, float eps, cudaStream_t st) {
   constexpr int ROWS = 160 / NVEC;
   if constexpr (sizeof(TI) == 2 && sizeof(TO) == 2) {
+    // VST_LN_LANE: 0 = flat kernels only; 1 (default) = 3 rows per trip at C = 320 (no spills at 128 registers;
+    // L0 with gamma + beta + positions: 124 us = 0.83 of HBM against 162 us flat); 2 / 4 = 2 / 4 rows per trip
+    // (tuning builds: 136 us, and 158 us with 92 bytes of spills)
+    if constexpr (NVEC == 40) {
+      const int mode = ln_lane_mode();
+      const int rc = mode == 2 ? try_launch_ln_lane<TP, 5, 2>(x, y, g, b, pe, rows, F, eps, st)
+                   : mode == 4 ? try_launch_ln_lane<TP, 5, 4>(x, y, g, b, pe, rows, F, eps, st)
+                               : try_launch_ln_lane<TP, 5, 3>(x, y, g, b, pe, rows, F, eps, st);
+      if (rc != kLnNotTaken) return rc;
+    }
+    if constexpr (NVEC == 80 && sizeof(TP) == 2) {
+      // C = 640: the parameters fill 60 registers, one row per trip (two rows spill and measured 80 vs 67 us at
+      // L1; gamma / beta packed and unpacked per use likewise); without a position table the flat kernel is the
+      // faster one at this width (61 vs 65 us)
+      const int rc = pe == nullptr ? kLnNotTaken : try_launch_ln_lane<TP, 10, 1>(x, y, g, b, pe, rows, F, eps, st);
+      if (rc != kLnNotTaken) return rc;
+    }
     const int64_t groups = (rows + ROWS - 1) / ROWS;
     // blocks of 8 warps; the warp count must be a multiple of F / gcd(F, ROWS) groups (see the kernel)
     int per = 1;
