@@ -30,7 +30,8 @@ def _bf(t):
 # ---- vst_gemm: every transpose combination, ragged edges, split-K, two operand pairs -------------
 @pytest.mark.parametrize("ta,tb", [(0, 0), (0, 1), (1, 0), (1, 1)])
 @pytest.mark.parametrize("m,n,k", [(128, 64, 64), (200, 136, 328), (1000, 264, 72), (136, 128, 16384),
-                                   (64, 1288, 4104)])
+                                   (64, 1288, 4104),
+                                   (392, 320, 200), (256, 640, 2056)])      # tile widths 160 and 224 (N = 320, 640)
 def test_gemm_transposes(ops, ta, tb, m, n, k):
     if ta and m % 8:
         pytest.skip("MN-major A needs M % 8 == 0")
