@@ -166,6 +166,10 @@ def main():
         with open(os.path.join(PROF, "ncu_traffic.json"), "w") as f:
             json.dump(traffic, f, indent=1)
             f.write("\n")
+    for name in ("ln", "gn"):                  # memory-bound kernels: summaries only (scripts/gpu_round4.sh)
+        summarise_raw(name, tag)
+    if os.path.exists(os.path.join(OUT, "cfg4_kernels.tsv")):
+        shutil.copy(os.path.join(OUT, "cfg4_kernels.tsv"), os.path.join(PROF, f"cfg4_kernels_{tag}.tsv"))
     for name in ("attn", "attn_bwd"):
         p = os.path.join(OUT, f"prof_{name}_source.csv.gz")
         if os.path.exists(p) and os.path.getsize(p) < 1_000_000:
