@@ -12,7 +12,7 @@ FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-li
 
 def build():
     obj = "/tmp/attn_trace.o"
-    subprocess.check_call(["nvcc"] + FLAGS + ["-DVST_ATTN_TRACE", "-c", os.path.join(CSRC, "attn.cu"), "-o", obj])
+    subprocess.check_call(["nvcc"] + FLAGS + os.environ.get("TRACE_FLAGS", "").split() + ["-DVST_ATTN_TRACE", "-c", os.path.join(CSRC, "attn.cu"), "-o", obj])
     others = [o for o in glob.glob(os.path.join(CSRC, "*.o")) if not o.endswith("/attn.o")]
     subprocess.check_call(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB, obj] + others)
 

@@ -17,6 +17,10 @@
 //         (8 x 128x64x16, A = P from TMEM, B = V MN-major straight from its row-major tile),
 //         so P never touches shared memory.
 //   6     store warp: staged O tiles leave by TMA.   7: idle (warpgroup 1 runs on 48 registers).
+// Text cross-attention (64 < Sk <= 80, one 80-key block per item) is its own instantiation: an HBM-bound stream of
+// Q tiles in and O tiles out, shaped by scripts/attn_trace_cross.py -- four Q buffers (the 80-key K / V slots are
+// 10 KB), only the last 16 keys are tested for masking, and P's completion is signalled at once so the MMA warp
+// runs an item ahead (r02: 46.1 / 29.5 -> 39.7 / 24.6 us at the L1 / L2 shapes before the last of these).
 // What bounds it (r01 measurements: scripts/ubench/*.cu, scripts/attn_trace.py,
 // profiles/attn_r01_notes.md): at head dim 64 a 128x128 score block is ~530 clk of tensor work but
 // 1024 clk of MUFU.EX2 (16/clk/SM; ex2.f16x2 is two MUFU ops, no packed rate) plus ~500 issue
@@ -124,8 +128,30 @@ struct AttnArgs {
 //   * a dedicated store warp (warp 6) sends the staged tile by TMA and recycles the buffer, so the
 //     softmax warps never wait for a bulk store to read shared memory.
 // All barrier phases run on global counters (g: K/V blocks loaded, blk: score blocks, i: items).
-constexpr int NQ = 3;
-constexpr int kSmemBytesP = kTile * (NQ + 2 * KST) + 256;
+// cross-attention (80-key block) ring shape; -D overrides for tuning builds.  Measured (L1 / L2 text cross, us):
+// 3 Q buffers 46.1 / 29.5 (round-2 start), 4 Q buffers + masking only the last 16 keys 39.9 / 25.5, 5 Q buffers with
+// single-staged K / V 50.1 / 29.7 (the K load lands on the MMA warp's critical path: k_full wait 1400 clk), a separate
+// Q producer warp 39.8 / 25.6 (no gain: the chain PV(i-1) issue -> S(i+1) issue -> s_full is what is left)
+#ifndef VST_ATTN_X_NQ
+#define VST_ATTN_X_NQ 4
+#define VST_ATTN_X_KST 2
+#endif
+#ifndef VST_ATTN_X_EAGER_P
+#define VST_ATTN_X_EAGER_P 1
+#endif
+#ifndef VST_ATTN_X_SPLITQ
+#define VST_ATTN_X_SPLITQ 1
+#endif
+template <int BKVT_>
+struct AttnSmem {
+  static constexpr int kNQ = BKVT_ == BKV ? 3 : VST_ATTN_X_NQ;                      // Q ring depth
+  static constexpr int kKST = BKVT_ == BKV ? KST : VST_ATTN_X_KST;                  // K and V stages
+  static constexpr int kKVSlot = BKVT_ == BKV ? kTile : (BKVT_ * HD * 2 + 1023) / 1024 * 1024;   // bytes per K / V stage
+  static constexpr int kBytes = kTile * kNQ + 2 * kKST * kKVSlot + 256;
+};
+constexpr int kSmemBytesP = AttnSmem<BKV>::kBytes;
+constexpr int kSmemBytes80 = AttnSmem<80>::kBytes;
+static_assert(kSmemBytes80 <= kSmemBytesP, "the cross-attention instantiation must keep two CTAs per SM");
 
 // BKVT: keys per block.  128 everywhere except text cross-attention (Sk = 77 <= 80: ONE block per item), which runs
 // with an 80-key block: 5 instead of 8 score / PV k-steps and 40 instead of 64 exponential pairs per row (r02: the
@@ -136,20 +162,27 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
                      const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
                      AttnArgs a, int n_items, int ntile) {
   static_assert(BKVT == BKV || (!kMask && BKVT % 16 == 0 && BKVT > 64 && BKVT < BKV), "BKVT: 128, or a cross-attention block in (64, 128)");
+  // Text cross-attention (BKVT = 80) is ONE block per item, i.e. an HBM-bound stream of Q tiles in and O tiles out:
+  // the clock64 trace (scripts/attn_trace_cross.py) showed the MMA warp waiting ~2800 clk per item for the next Q
+  // tile -- its ring buffer doubles as the O staging buffer of the item three back, so with three buffers a Q load
+  // could only be issued ~1.3 item periods ahead of its use, less than the loaded DRAM latency.  The 80-key K / V
+  // slots are 10 KB instead of 16 KB, which pays for a fourth Q buffer inside the same 2-CTA-per-SM budget.
+  constexpr int NQT = AttnSmem<BKVT>::kNQ, KSTT = AttnSmem<BKVT>::kKST, kKVSlot = AttnSmem<BKVT>::kKVSlot;
+  constexpr bool kSplitQ = BKVT < BKV && VST_ATTN_X_SPLITQ;      // Q loads from their own warp (see warp 7)
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;                 // 128B-swizzled tiles need 1024-byte alignment (checked)
-  uint8_t* sQ = smem;                       // [NQ] query tiles (each reused to stage its item's O)
-  uint8_t* sK = sQ + NQ * kTile;            // [KST]
-  uint8_t* sV = sK + KST * kTile;           // [KST]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + KST * kTile);
-  uint64_t* q_full = bars;                  // [NQ]
-  uint64_t* q_empty = q_full + NQ;          // [NQ]  the O store staged in this buffer has been read
-  uint64_t* o_staged = q_empty + NQ;        // [NQ]  the item's O is normalised and staged (128 rows)
-  uint64_t* k_full = o_staged + NQ;         // [KST]
-  uint64_t* k_empty = k_full + KST;         // [KST]
-  uint64_t* v_full = k_empty + KST;         // [KST]
-  uint64_t* v_empty = v_full + KST;         // [KST]
-  uint64_t* s_full = v_empty + KST;         // S_j complete in TMEM
+  uint8_t* sQ = smem;                       // [NQT] query tiles (each reused to stage its item's O)
+  uint8_t* sK = sQ + NQT * kTile;            // [KSTT]
+  uint8_t* sV = sK + KSTT * kKVSlot;         // [KSTT]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + KSTT * kKVSlot);
+  uint64_t* q_full = bars;                  // [NQT]
+  uint64_t* q_empty = q_full + NQT;          // [NQT]  the O store staged in this buffer has been read
+  uint64_t* o_staged = q_empty + NQT;        // [NQT]  the item's O is normalised and staged (128 rows)
+  uint64_t* k_full = o_staged + NQT;         // [KSTT]
+  uint64_t* k_empty = k_full + KSTT;         // [KSTT]
+  uint64_t* v_full = k_empty + KSTT;         // [KSTT]
+  uint64_t* v_empty = v_full + KSTT;         // [KSTT]
+  uint64_t* s_full = v_empty + KSTT;         // S_j complete in TMEM
   uint64_t* s_free = s_full + 1;            // S_j copied to registers by all 128 rows
   uint64_t* p_full = s_free + 1;            // P_j in TMEM (and O rescaled if needed)
   uint64_t* o_full = p_full + 1;            // O += P_j V_j complete
@@ -165,12 +198,12 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       printf("vst attn_fwd: dynamic shared memory is not 1024-byte aligned\n");
       __trap();
     }
-    for (int i = 0; i < NQ; ++i) {
+    for (int i = 0; i < NQT; ++i) {
       mbar_init(&q_full[i], 1);
       mbar_init(&q_empty[i], 1);
       mbar_init(&o_staged[i], 128);
     }
-    for (int i = 0; i < KST; ++i) {
+    for (int i = 0; i < KSTT; ++i) {
       mbar_init(&k_full[i], 1);
       mbar_init(&k_empty[i], 1);
       mbar_init(&v_full[i], 1);
@@ -200,19 +233,21 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       int i = 0;
       for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++i) {
         const int qtile = it % ntile, head = (it / ntile) % a.heads, b = it / (ntile * a.heads);
-        const int bk = b / a.kv_group, buf = i % NQ;
-        mbar_wait_plain(&q_empty[buf], ((i / NQ) & 1) ^ 1);
-        mbar_arrive_expect_tx(&q_full[buf], kTile);
-        tma_load_3d(sQ + buf * kTile, &tmQ, &q_full[buf], head * HD, qtile * BQ, b);
+        const int bk = b / a.kv_group, buf = i % NQT;
+        if constexpr (!kSplitQ) {
+          mbar_wait_plain(&q_empty[buf], ((i / NQT) & 1) ^ 1);
+          mbar_arrive_expect_tx(&q_full[buf], kTile);
+          tma_load_3d(sQ + buf * kTile, &tmQ, &q_full[buf], head * HD, qtile * BQ, b);
+        }
         for (int j = 0; j < nblk; ++j, ++g) {
-          const int st = g % KST;
-          const uint32_t ph = ((g / KST) & 1) ^ 1;
+          const int st = g % KSTT;
+          const uint32_t ph = ((g / KSTT) & 1) ^ 1;
           mbar_wait_plain(&k_empty[st], ph);
           mbar_arrive_expect_tx(&k_full[st], kKVBytes);
-          tma_load_3d(sK + st * kTile, &tmK, &k_full[st], head * HD, j * BKVT, bk);
+          tma_load_3d(sK + st * kKVSlot, &tmK, &k_full[st], head * HD, j * BKVT, bk);
           mbar_wait_plain(&v_empty[st], ph);
           mbar_arrive_expect_tx(&v_full[st], kKVBytes);
-          tma_load_3d(sV + st * kTile, &tmV, &v_full[st], head * HD, j * BKVT, bk);
+          tma_load_3d(sV + st * kKVSlot, &tmV, &v_full[st], head * HD, j * BKVT, bk);
         }
       }
     }
@@ -228,10 +263,10 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     uint32_t g = 0, blk = 0;
     int i = 0;
     auto issue_s = [&](uint64_t dq, uint32_t gg, uint32_t tr) {
-      const int st = gg % KST;
-      mbar_wait_plain(&k_full[st], (gg / KST) & 1);
+      const int st = gg % KSTT;
+      mbar_wait_plain(&k_full[st], (gg / KSTT) & 1);
       tc_fence_after();
-      const uint64_t dk = umma_desc_sw128(smem_u32(sK + st * kTile), 1024);
+      const uint64_t dk = umma_desc_sw128(smem_u32(sK + st * kKVSlot), 1024);
       TRACE(5, tr);
       if (issuer) {
 #pragma unroll
@@ -242,7 +277,7 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       __syncwarp();
     };
     for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++i) {
-      const int buf = i % NQ;
+      const int buf = i % NQT;
       const uint64_t dq = umma_desc_sw128(smem_u32(sQ + buf * kTile), 1024);
       if (i == 0) {
         mbar_wait_plain(&q_full[0], 0);
@@ -257,17 +292,20 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
           mbar_wait_plain(s_free, (blk + j) & 1);
           issue_s(dq, g + j + 1, blk + j + 1);
         } else if (has_next) {
-          const int nb = (i + 1) % NQ;
-          mbar_wait_plain(&q_full[nb], ((i + 1) / NQ) & 1);
+          const int nb = (i + 1) % NQT;
+          TRACE(9, blk + nblk);
+          mbar_wait_plain(&q_full[nb], ((i + 1) / NQT) & 1);
+          TRACE(10, blk + nblk);
           mbar_wait_plain(s_free, (blk + j) & 1);
+          TRACE(11, blk + nblk);
           issue_s(umma_desc_sw128(smem_u32(sQ + nb * kTile), 1024), g + nblk, blk + nblk);
         }
-        const int st = (g + j) % KST;
+        const int st = (g + j) % KSTT;
         mbar_wait_plain(p_full, (blk + j) & 1);
         if (j == 0) mbar_wait_plain(o_free, (i & 1) ^ 1);    // the previous item's O has left TMEM
-        mbar_wait_plain(&v_full[st], ((g + j) / KST) & 1);
+        mbar_wait_plain(&v_full[st], ((g + j) / KSTT) & 1);
         tc_fence_after();
-        const uint64_t dv = umma_desc_sw128(smem_u32(sV + st * kTile), 1024, 8192);
+        const uint64_t dv = umma_desc_sw128(smem_u32(sV + st * kKVSlot), 1024, 8192);
         TRACE(6, blk + j);
         if (issuer) {
 #pragma unroll
@@ -288,17 +326,34 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       int i = 0;
       for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++i) {
         const int qtile = it % ntile, head = (it / ntile) % a.heads, b = it / (ntile * a.heads);
-        const int buf = i % NQ;
-        mbar_wait(&o_staged[buf], (i / NQ) & 1, 41);
+        const int buf = i % NQT;
+        mbar_wait(&o_staged[buf], (i / NQT) & 1, 41);
         tma_store_4d(&tmO, sQ + buf * kTile, head * HD, qtile * BQ, b, 0);
         tma_store_commit();
-        tma_store_wait_read<0>();          // smem read out: the buffer may take the Q of item i + NQ
+        tma_store_wait_read<0>();          // smem read out: the buffer may take the Q of item i + NQT
         mbar_arrive(&q_empty[buf]);
       }
       tma_store_wait<0>();
     }
   } else if (warp > 6) {
-    setmaxnreg_dec<kRegsAux>();          // idle warp of the auxiliary warpgroup
+    setmaxnreg_dec<kRegsAux>();          // idle warp of the auxiliary warpgroup, except:
+    if constexpr (kSplitQ) {
+      // one-block items: the Q ring is fed by this warp.  One producer thread issuing Q, K, V in item order
+      // stalls on the K / V stages of item i + 2 (free only once P V of item i has retired) before it can ask
+      // for the Q of item i + 3, which held the Q lead at about one item period whatever the ring depth
+      // (q_full wait of the MMA warp: 1380 clk per item, scripts/attn_trace_cross.py).
+      if (lane == 0) {
+        tma_prefetch_desc(&tmQ);
+        int i = 0;
+        for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++i) {
+          const int qtile = it % ntile, head = (it / ntile) % a.heads, b = it / (ntile * a.heads);
+          const int buf = i % NQT;
+          mbar_wait_plain(&q_empty[buf], ((i / NQT) & 1) ^ 1);
+          mbar_arrive_expect_tx(&q_full[buf], kTile);
+          tma_load_3d(sQ + buf * kTile, &tmQ, &q_full[buf], head * HD, qtile * BQ, b);
+        }
+      }
+    }
   } else {
     // ================= softmax + output (warps 0..3) =================
     setmaxnreg_inc<kRegsSoftmax>();
@@ -315,11 +370,11 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     float pend_inv = 0.f, pend_lse = 0.f;
     bool p_pending = false;              // a P store is in flight, p_full not yet signalled
     auto epilogue = [&](int pit, int pi, float inv, float lse, uint32_t last_blk) {
-      // O of item pit (ring slot pi % NQ): TMEM -> normalise -> its dead Q buffer -> store warp
+      // O of item pit (ring slot pi % NQT): TMEM -> normalise -> its dead Q buffer -> store warp
       mbar_wait_plain(o_full, last_blk & 1);
       TRACE(7, pi);
       tc_fence_after();
-      uint8_t* orow = sQ + (pi % NQ) * kTile + row * 128;
+      uint8_t* orow = sQ + (pi % NQT) * kTile + row * 128;
       const int rx = row & 7;
 #pragma unroll
       for (int c = 0; c < HD / 32; ++c) {
@@ -341,7 +396,7 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         }
       }
       fence_proxy_async_smem();
-      mbar_arrive(&o_staged[pi % NQ]);
+      mbar_arrive(&o_staged[pi % NQT]);
       TRACE(8, pi);
       if (a.lse != nullptr) {
         const int qt = (pit % ntile) * BQ;
@@ -377,8 +432,9 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         tc_fence_before();
         mbar_arrive(s_free);             // the tensor pipe may overwrite S now
         if (tail) {
+          // (an 80-key block is only launched for 64 < Sk <= 80: its masked keys are among the last 16)
 #pragma unroll
-          for (int e = 0; e < BKVT; ++e)
+          for (int e = (BKVT < BKV ? 64 : 0); e < BKVT; ++e)
             if (kv0 + e >= a.Sk) r[e] = 0xff800000u;  // -inf: excluded from max, exp2 -> 0
         }
         if constexpr (kMask) {
@@ -458,7 +514,18 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         }
         tmem_st32(tP, r);
         if (BKVT > 64) tmem_st32(tP + 32, r + 32);      // (80 keys = 40 packed words: words 40..63 are never read)
-        p_pending = true;                // completion + p_full arrive: under the next S load
+        if constexpr (BKVT < BKV && VST_ATTN_X_EAGER_P) {
+          // one-block items (text cross-attention): the deferred arrive reaches the MMA warp only when the NEXT
+          // item's S is already being loaded, and that warp issues in program order -- P V of this item, then
+          // the S of the item after next -- so every item's S was issued ~1600 clk after the previous S left
+          // TMEM and the softmax warps idled 600-1000 clk per item (scripts/attn_trace_cross.py).  Paying the
+          // store's completion here (~200 clk) lets the MMA warp run a whole item ahead.
+          tmem_st_wait();
+          tc_fence_before();
+          mbar_arrive(p_full);
+        } else {
+          p_pending = true;              // completion + p_full arrive: under the next S load
+        }
         TRACE(4, blk + j);
       }
       const float l = l2.x + l2.y;
@@ -536,7 +603,7 @@ extern "C" int vst_attn_fwd(const void* q, const void* k, const void* v, void* o
     VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_pers_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesP));
     VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_pers_kernel<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesP));
     VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_pers_kernel<kDefaultPoly, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesP));
-    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_pers_kernel<kDefaultPoly, false, 80>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesP));
+    VST_CUDA_OK(cudaFuncSetAttribute(attn_fwd_pers_kernel<kDefaultPoly, false, 80>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes80));
   }
   const int vec4 = mask && (reinterpret_cast<uintptr_t>(mask) & 15) == 0 && mask_sb % 4 == 0 &&
                    mask_sh % 4 == 0 && mask_sq % 4 == 0;
@@ -551,7 +618,7 @@ extern "C" int vst_attn_fwd(const void* q, const void* k, const void* v, void* o
   if (mask) {
     attn_fwd_pers_kernel<kDefaultPoly, true><<<pgrid, kThreads, kSmemBytesP, st>>>(tQ, tK, tV, tO, a, n, ntile);
   } else if (kv80) {
-    attn_fwd_pers_kernel<kDefaultPoly, false, 80><<<pgrid, kThreads, kSmemBytesP, st>>>(tQ, tK, tV, tO, a, n, ntile);
+    attn_fwd_pers_kernel<kDefaultPoly, false, 80><<<pgrid, kThreads, kSmemBytes80, st>>>(tQ, tK, tV, tO, a, n, ntile);
   } else {
     switch (poly) {
       case 0: attn_fwd_pers_kernel<0, false><<<pgrid, kThreads, kSmemBytesP, st>>>(tQ, tK, tV, tO, a, n, ntile); break;
