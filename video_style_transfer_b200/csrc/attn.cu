@@ -19,8 +19,9 @@
 //   6     store warp: staged O tiles leave by TMA.   7: idle (warpgroup 1 runs on 48 registers).
 // Text cross-attention (64 < Sk <= 80, one 80-key block per item) is its own instantiation: an HBM-bound stream of
 // Q tiles in and O tiles out, shaped by scripts/attn_trace_cross.py -- four Q buffers (the 80-key K / V slots are
-// 10 KB), only the last 16 keys are tested for masking, and P's completion is signalled at once so the MMA warp
-// runs an item ahead (r02: 46.1 / 29.5 -> 39.7 / 24.6 us at the L1 / L2 shapes before the last of these).
+// 10 KB and O has a staging buffer of its own, so a Q buffer returns to the ring when its S MMA retires), only the
+// last 16 keys are tested for masking, P's completion is signalled at once and the Q ring has its own producer warp,
+// so the MMA warp runs an item ahead (r02: 46.1 / 29.5 -> 38.9 / 24.6 us at the L1 / L2 shapes).
 // What bounds it (r01 measurements: scripts/ubench/*.cu, scripts/attn_trace.py,
 // profiles/attn_r01_notes.md): at head dim 64 a 128x128 score block is ~530 clk of tensor work but
 // 1024 clk of MUFU.EX2 (16/clk/SM; ex2.f16x2 is two MUFU ops, no packed rate) plus ~500 issue
@@ -128,26 +129,36 @@ struct AttnArgs {
 //   * a dedicated store warp (warp 6) sends the staged tile by TMA and recycles the buffer, so the
 //     softmax warps never wait for a bulk store to read shared memory.
 // All barrier phases run on global counters (g: K/V blocks loaded, blk: score blocks, i: items).
-// cross-attention (80-key block) ring shape; -D overrides for tuning builds.  Measured (L1 / L2 text cross, us):
-// 3 Q buffers 46.1 / 29.5 (round-2 start), 4 Q buffers + masking only the last 16 keys 39.9 / 25.5, 5 Q buffers with
-// single-staged K / V 50.1 / 29.7 (the K load lands on the MMA warp's critical path: k_full wait 1400 clk), a separate
-// Q producer warp 39.8 / 25.6 (no gain: the chain PV(i-1) issue -> S(i+1) issue -> s_full is what is left)
-#ifndef VST_ATTN_X_NQ
-#define VST_ATTN_X_NQ 4
-#define VST_ATTN_X_KST 2
-#endif
+// Cross-attention (80-key block) instantiation; -D overrides for tuning builds.  Measured, L1 / L2 text cross in us
+// (kbench attn, B = 16): 3 Q buffers doubling as O stages 46.1 / 29.5 (round-2 start); + masking test on the last 16
+// keys only, 4 Q buffers 39.9 / 25.5; 5 Q buffers with single-staged K / V 50.1 / 29.7 (k_full wait 1400 clk on the
+// MMA warp's critical path); + P completion signalled at once 38.9 / 24.6; + Q ring fed by its own warp 37.9 / 25.6;
+// rows stored straight from registers 49.1 / 28.7; shipped: 3 Q buffers released by the S MMA's commit + one
+// dedicated O staging buffer + the three changes above, 38.9 / 24.6.  In that form the MMA warp no longer waits
+// (q_full 130, s_free 84, k_full 180 clk per item) and CTA 0's steady state is 2700 clk per item, i.e. two resident
+// CTAs move 64 KB per 2700 clk and SM = the HBM rate: what keeps the launch at 0.52-0.66 of HBM is the ramp
+// (9-17 items per CTA at these sizes), not the pipeline.
 #ifndef VST_ATTN_X_EAGER_P
 #define VST_ATTN_X_EAGER_P 1
 #endif
 #ifndef VST_ATTN_X_SPLITQ
 #define VST_ATTN_X_SPLITQ 1
 #endif
+#ifndef VST_ATTN_X_OWNO
+#define VST_ATTN_X_OWNO 1
+#endif
+#ifndef VST_ATTN_X_NQ
+#define VST_ATTN_X_NQ 3
+#define VST_ATTN_X_KST 2
+#endif
+
 template <int BKVT_>
 struct AttnSmem {
   static constexpr int kNQ = BKVT_ == BKV ? 3 : VST_ATTN_X_NQ;                      // Q ring depth
   static constexpr int kKST = BKVT_ == BKV ? KST : VST_ATTN_X_KST;                  // K and V stages
   static constexpr int kKVSlot = BKVT_ == BKV ? kTile : (BKVT_ * HD * 2 + 1023) / 1024 * 1024;   // bytes per K / V stage
-  static constexpr int kBytes = kTile * kNQ + 2 * kKST * kKVSlot + 256;
+  static constexpr int kOStage = BKVT_ == BKV ? 0 : VST_ATTN_X_OWNO;                // dedicated O staging buffers
+  static constexpr int kBytes = kTile * (kNQ + kOStage) + 2 * kKST * kKVSlot + 256;
 };
 constexpr int kSmemBytesP = AttnSmem<BKV>::kBytes;
 constexpr int kSmemBytes80 = AttnSmem<80>::kBytes;
@@ -166,13 +177,22 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
   // the clock64 trace (scripts/attn_trace_cross.py) showed the MMA warp waiting ~2800 clk per item for the next Q
   // tile -- its ring buffer doubles as the O staging buffer of the item three back, so with three buffers a Q load
   // could only be issued ~1.3 item periods ahead of its use, less than the loaded DRAM latency.  The 80-key K / V
-  // slots are 10 KB instead of 16 KB, which pays for a fourth Q buffer inside the same 2-CTA-per-SM budget.
+  // slots are 10 KB instead of 16 KB, which pays for a fourth 16 KB buffer inside the same 2-CTA-per-SM budget
+  // (a dedicated O stage, see kOwnO).
   constexpr int NQT = AttnSmem<BKVT>::kNQ, KSTT = AttnSmem<BKVT>::kKST, kKVSlot = AttnSmem<BKVT>::kKVSlot;
   constexpr bool kSplitQ = BKVT < BKV && VST_ATTN_X_SPLITQ;      // Q loads from their own warp (see warp 7)
+  // one-block items: O is staged in a buffer of its own and the Q buffer goes back to the ring as soon as its S MMA
+  // has read it.  Staged in its dead Q buffer (as the other instantiations do), an item's O held that buffer until
+  // the TMA store had READ it, behind the loads queued on the same unit: the MMA warp still waited ~1200 clk per
+  // item for q_full with four buffers and a dedicated Q producer (scripts/attn_trace_cross.py).  Storing the rows
+  // straight from registers instead measured slower (49 vs 38 us at L1: 8 x 32-line stores per warp and item, the
+  // softmax warps drift 2000 clk apart).
+  constexpr bool kOwnO = BKVT < BKV && VST_ATTN_X_OWNO;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;                 // 128B-swizzled tiles need 1024-byte alignment (checked)
   uint8_t* sQ = smem;                       // [NQT] query tiles (each reused to stage its item's O)
-  uint8_t* sK = sQ + NQT * kTile;            // [KSTT]
+  uint8_t* sO = sQ + NQT * kTile;            // (kOwnO) the O staging buffer
+  uint8_t* sK = sO + (kOwnO ? kTile : 0);   // [KSTT]
   uint8_t* sV = sK + KSTT * kKVSlot;         // [KSTT]
   uint64_t* bars = reinterpret_cast<uint64_t*>(sV + KSTT * kKVSlot);
   uint64_t* q_full = bars;                  // [NQT]
@@ -187,7 +207,8 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
   uint64_t* p_full = s_free + 1;            // P_j in TMEM (and O rescaled if needed)
   uint64_t* o_full = p_full + 1;            // O += P_j V_j complete
   uint64_t* o_free = o_full + 1;            // the item's O has been read out of TMEM
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_free + 1);
+  uint64_t* so_empty = o_free + 1;          // (kOwnO) the TMA store has read the O staging buffer
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(so_empty + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nblk = (a.Sk + BKVT - 1) / BKVT;
@@ -214,6 +235,7 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     mbar_init(p_full, 128);
     mbar_init(o_full, 1);
     mbar_init(o_free, 128);
+    mbar_init(so_empty, 1);
     fence_mbar_init();
   }
   if (warp == 4) tmem_alloc(tmem_slot, 256);
@@ -272,6 +294,7 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k) umma_bf16_ss(tS, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
         umma_commit(&k_empty[st]);
+        if (kOwnO) umma_commit(&q_empty[gg % NQT]);      // (one block per item: block index == item index)
         umma_commit(s_full);
       }
       __syncwarp();
@@ -328,10 +351,10 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         const int qtile = it % ntile, head = (it / ntile) % a.heads, b = it / (ntile * a.heads);
         const int buf = i % NQT;
         mbar_wait(&o_staged[buf], (i / NQT) & 1, 41);
-        tma_store_4d(&tmO, sQ + buf * kTile, head * HD, qtile * BQ, b, 0);
+        tma_store_4d(&tmO, kOwnO ? sO : sQ + buf * kTile, head * HD, qtile * BQ, b, 0);
         tma_store_commit();
-        tma_store_wait_read<0>();          // smem read out: the buffer may take the Q of item i + NQT
-        mbar_arrive(&q_empty[buf]);
+        tma_store_wait_read<0>();          // smem read out: the buffer may take the Q of item i + NQT (or the next O)
+        mbar_arrive(kOwnO ? so_empty : &q_empty[buf]);
       }
       tma_store_wait<0>();
     }
@@ -374,8 +397,9 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       mbar_wait_plain(o_full, last_blk & 1);
       TRACE(7, pi);
       tc_fence_after();
-      uint8_t* orow = sQ + (pi % NQT) * kTile + row * 128;
+      uint8_t* orow = (kOwnO ? sO : sQ + (pi % NQT) * kTile) + row * 128;
       const int rx = row & 7;
+      if constexpr (kOwnO) mbar_wait_plain(so_empty, (pi & 1) ^ 1);    // the previous item's store has read the buffer
 #pragma unroll
       for (int c = 0; c < HD / 32; ++c) {
         uint32_t o[32];
