@@ -147,6 +147,9 @@ struct AttnArgs {
 #ifndef VST_ATTN_X_OWNO
 #define VST_ATTN_X_OWNO 1
 #endif
+#ifndef VST_ATTN_LAG_PV
+#define VST_ATTN_LAG_PV 0        // measured slower (see the MMA warp): tuning builds only
+#endif
 #ifndef VST_ATTN_X_NQ
 #define VST_ATTN_X_NQ 3
 #define VST_ATTN_X_KST 2
@@ -188,6 +191,7 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
   // straight from registers instead measured slower (49 vs 38 us at L1: 8 x 32-line stores per warp and item, the
   // softmax warps drift 2000 clk apart).
   constexpr bool kOwnO = BKVT < BKV && VST_ATTN_X_OWNO;
+  constexpr bool kLagPV = BKVT == BKV && VST_ATTN_LAG_PV;          // P V issued one block late (see the MMA warp)
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;                 // 128B-swizzled tiles need 1024-byte alignment (checked)
   uint8_t* sQ = smem;                       // [NQT] query tiles (each reused to stage its item's O)
@@ -299,6 +303,26 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       }
       __syncwarp();
     };
+    auto issue_pv = [&](int pj, uint32_t pg, uint32_t pblk, int pi) {
+      const int st = pg % KSTT;
+      mbar_wait_plain(p_full, pblk & 1);
+      if (pj == 0) mbar_wait_plain(o_free, (pi & 1) ^ 1);    // the previous item's O has left TMEM
+      mbar_wait_plain(&v_full[st], (pg / KSTT) & 1);
+      tc_fence_after();
+      const uint64_t dv = umma_desc_sw128(smem_u32(sV + st * kKVSlot), 1024, 8192);
+      TRACE(6, pblk);
+      if (issuer) {
+#pragma unroll
+        for (int k = 0; k < BKVT / 16; ++k)
+          umma_bf16_ts(tO, tP + 8 * k, dv + uint64_t((k * 2048) >> 4), idesc_o, (pj | k) != 0);
+        umma_commit(&v_empty[st]);
+        umma_commit(o_full);
+      }
+      __syncwarp();
+    };
+    bool pv_pending = false;
+    int pv_j = 0, pv_i = 0;
+    uint32_t pv_g = 0, pv_blk = 0;
     for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++i) {
       const int buf = i % NQT;
       const uint64_t dq = umma_desc_sw128(smem_u32(sQ + buf * kTile), 1024);
@@ -323,25 +347,23 @@ attn_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
           TRACE(11, blk + nblk);
           issue_s(umma_desc_sw128(smem_u32(sQ + nb * kTile), 1024), g + nblk, blk + nblk);
         }
-        const int st = (g + j) % KSTT;
-        mbar_wait_plain(p_full, (blk + j) & 1);
-        if (j == 0) mbar_wait_plain(o_free, (i & 1) ^ 1);    // the previous item's O has left TMEM
-        mbar_wait_plain(&v_full[st], ((g + j) / KSTT) & 1);
-        tc_fence_after();
-        const uint64_t dv = umma_desc_sw128(smem_u32(sV + st * kKVSlot), 1024, 8192);
-        TRACE(6, blk + j);
-        if (issuer) {
-#pragma unroll
-          for (int k = 0; k < BKVT / 16; ++k)
-            umma_bf16_ts(tO, tP + 8 * k, dv + uint64_t((k * 2048) >> 4), idesc_o, (j | k) != 0);
-          umma_commit(&v_empty[st]);
-          umma_commit(o_full);
+        // P V of block j -- or, in a kLagPV build, of the block before.  The trace (scripts/attn_trace.py, S = 1024)
+        // shows S(j+1) leaving ~880 clk after S(j) is in warp 0's registers and reaching the softmax warps ~220 clk
+        // late; p_full(j-1) is signalled ~140 clk before s_free(j), so P V(j-1) (8 MMAs) is issued just ahead of
+        // S(j+1).  Issuing P V one block late (S first) did NOT move the S issue (still +780 clk: it follows the
+        // slowest of the four softmax warps' s_free arrivals, not the P V) and made o_full late (wait 105 -> 455
+        // clk): 743 -> 683 TFLOP/s at the L2 shape.  Kept off.
+        if constexpr (kLagPV) {
+          if (pv_pending) issue_pv(pv_j, pv_g, pv_blk, pv_i);
+          pv_pending = true; pv_j = j; pv_g = g + j; pv_blk = blk + j; pv_i = i;
+        } else {
+          issue_pv(j, g + j, blk + j, i);
         }
-        __syncwarp();
       }
       g += nblk;
       blk += nblk;
     }
+    if (pv_pending) issue_pv(pv_j, pv_g, pv_blk, pv_i);
   } else if (warp == 6) {
     // ================= store warp: staged O tiles leave by TMA, buffers go back to the ring ======
     setmaxnreg_dec<kRegsAux>();
