@@ -95,6 +95,31 @@ def test_groupnorm5d_rearrange(ops, hp, shape, dtype):
     assert rel_err(y, want) < tol
 
 
+@pytest.mark.parametrize("layout", ["frames", "channels"])
+@pytest.mark.parametrize("shape", [(2, 320, 5, 32, 32),     # HW a power of two, 2 slabs per (group, frame), ragged last
+                                   (1, 64, 3, 6, 4),        # HW = 24: 16-byte friendly but not a power of two
+                                   (3, 96, 2, 16, 24),      # HW = 384, three batches
+                                   (1, 32, 4, 5, 3)])       # HW = 15: the scalar kernel
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_groupnorm5d_stats_addressing(ops, shape, dtype, layout):
+    """Every addressing branch of the statistics kernel (csrc/norm.cu: channels of a group contiguous /
+    shift-and-mask / division / scalar) against fp64 statistics, on frames-major (B*F, C, H, W) activations --
+    the path's layout -- and on a contiguous (B, C, F, H, W) tensor (the reference's view, attention_processor.py
+    :33-36 / GroupNorm over the 5-D view)."""
+    torch.manual_seed(5)
+    b, c, f, h, w = shape
+    if layout == "frames":
+        x = (torch.randn(b, f, c, h, w) * 1.7 - 0.4).to(dtype).cuda().permute(0, 2, 1, 3, 4)
+    else:
+        x = (torch.randn(b, c, f, h, w) * 1.7 - 0.4).to(dtype).cuda()
+    groups = 32 if c % 32 == 0 and c >= 64 else 8
+    mean, rstd = ops.groupnorm5d_stats(x, groups, 1e-6)
+    xr = x.double().cpu().reshape(b, groups, -1)
+    assert torch.allclose(mean.cpu().double(), xr.mean(-1).reshape(-1), atol=2e-6, rtol=1e-5)
+    want_rstd = (xr.var(-1, unbiased=False) + 1e-6).rsqrt().reshape(-1)
+    assert torch.allclose(rstd.cpu().double(), want_rstd, atol=0, rtol=2e-5)
+
+
 @pytest.mark.parametrize("c", [320, 640, 1280, 64])
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
 def test_layernorm(ops, hp, c, dtype):
