@@ -137,16 +137,18 @@ def test_layernorm(ops, hp, c, dtype):
     assert rel_err(y2, want2.reshape(-1, c)) < tol
 
 
+@pytest.mark.parametrize("pdtype", [torch.bfloat16, torch.float32])
 @pytest.mark.parametrize("c,f,extra", [(320, 16, 0), (320, 5, 3), (320, 7, 1), (640, 16, 1), (640, 3, 0),
                                        (1280, 16, 0), (1280, 6, 5), (320, 32, 2)])
-def test_layernorm_persistent_path(ops, hp, c, f, extra):
+def test_layernorm_persistent_path(ops, hp, c, f, extra, pdtype):
     """Row counts large enough for the persistent flat kernel (>= 2 groups per resident warp), ragged last
     group, frame counts that do not divide the rows a warp holds (the grid is then trimmed so that a warp's
     position-table rows stay fixed): bit-exact against the torch restatement with the same two roundings."""
     torch.manual_seed(12)
     rows = 6000 * (160 // (c // 8)) + extra          # > 2 * 8 warps * 2 blocks * 148 SMs groups of 160 vectors
     x = (torch.randn(rows, c) * 1.5 + 0.3).to(torch.bfloat16).cuda()
-    g, b = torch.randn(c).to(torch.bfloat16).cuda(), torch.randn(c).to(torch.bfloat16).cuda()
+    # (bf16 parameters: the inference stack; fp32 parameters: the training stack's master weights)
+    g, b = torch.randn(c).to(pdtype).cuda(), torch.randn(c).to(pdtype).cuda()
     pe = hp.positional_table(c).cuda()
     got = ops.layernorm(x, g, b, 1e-5, pe=pe, frames=f)
     xf = x.float()
@@ -161,6 +163,8 @@ def test_layernorm_persistent_path(ops, hp, c, f, extra):
     assert float((diff > 0).float().mean()) < 0.02
     plain = ops.layernorm(x, g, b, 1e-5)
     assert rel_err(plain, ln) < 1e-2
+    bare = ops.layernorm(x, None, None, 1e-5)                # no parameters at all
+    assert rel_err(bare, (xf - mu) * torch.rsqrt(var + 1e-5)) < 1e-2
     # the last (ragged) rows and the first rows of the second sweep of the grid
     assert torch.isfinite(got.float()).all()
 
