@@ -333,7 +333,11 @@ def test_lora_pack_up(ops):
                                                (3, 1, 1, 100, 300), (1, 1, 2, 64, 1),
                                                # persistent form, more items than resident CTAs:
                                                # several items per CTA, one / two key blocks each
-                                               (16, 1, 4, 1024, 77), (16, 16, 5, 512, 200)])
+                                               (16, 1, 4, 1024, 77), (16, 16, 5, 512, 200),
+                                               # the 80-key cross-attention instantiation at its key-count
+                                               # limits (65, 80), 5+ items per CTA (Q ring and O stage wrap),
+                                               # ragged last query tile
+                                               (40, 2, 8, 640, 65), (24, 3, 12, 520, 80)])
 def test_attn_fwd(ops, hp, bt, bk, heads, sq, sk):
     torch.manual_seed(7)
     c = heads * 64
