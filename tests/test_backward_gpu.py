@@ -31,7 +31,8 @@ def _bf(t):
 @pytest.mark.parametrize("ta,tb", [(0, 0), (0, 1), (1, 0), (1, 1)])
 @pytest.mark.parametrize("m,n,k", [(128, 64, 64), (200, 136, 328), (1000, 264, 72), (136, 128, 16384),
                                    (64, 1288, 4104),
-                                   (392, 320, 200), (256, 640, 2056)])      # tile widths 160 and 224 (N = 320, 640)
+                                   (392, 320, 200), (256, 640, 2056),       # tile widths 160 and 224 (N = 320, 640)
+                                   (5000, 1000, 136)])     # 80 pair tiles: more than one per SM pair (persistent walk)
 def test_gemm_transposes(ops, ta, tb, m, n, k):
     if ta and m % 8:
         pytest.skip("MN-major A needs M % 8 == 0")
