@@ -42,7 +42,14 @@ constexpr int kResBufs = VST_RES_BUFS, kResAhead = VST_RES_AHEAD;
 constexpr int kSmemTotal = 227 * 1024;       // per-CTA limit; 1024 alignment slack + 512 B of barriers
 constexpr int kBarBytes = 512;
 
-constexpr int out_bytes(bool res) { return kEpiWarps * (res ? kResBufs : 2) * kStageOutBytes; }
+// staging buffers per epilogue warp of the kernels without a residual (tuning: -DVST_OUT_BUFS=n; four instead of two
+// measured within 2 % either way on the K = 320 shapes and 2-4 % slower on the others -- fewer operand stages --, so
+// the store read-back is not what bounds the short-K epilogue)
+#ifndef VST_OUT_BUFS
+#define VST_OUT_BUFS 2
+#endif
+constexpr int kOutBufs = VST_OUT_BUFS;
+constexpr int out_bytes(bool res) { return kEpiWarps * (res ? kResBufs : kOutBufs) * kStageOutBytes; }
 constexpr int ring_budget(bool res) { return kSmemTotal - 1024 - kBarBytes - out_bytes(res); }
 
 template <int BN, bool RES = false>
@@ -221,7 +228,7 @@ __device__ __forceinline__ void epilogue_tile(const EpiArgs& ep, const CUtensorM
       uint32_t w[16];
       epilogue_pack(ep, rc, bias.v[i], nullptr, w);
       uint8_t* sbuf = stage_out + buf * kStageOutBytes;
-      if (lane == 0) tma_store_wait_read<1>();      // the store that last used this buffer is done
+      if (lane == 0) tma_store_wait_read<kOutBufs - 1>();   // the store that last used this buffer is done
       __syncwarp();
       uint8_t* srow = sbuf + lane * 64;
       const int sx = (lane >> 1) & 3;                // SWIZZLE_64B: 16-B chunk ^= (row >> 1) & 3
@@ -235,7 +242,7 @@ __device__ __forceinline__ void epilogue_tile(const EpiArgs& ep, const CUtensorM
         tma_store_2d(tmD, sbuf, n0 + c0, m0 + quarter * 32);
         tma_store_commit();
       }
-      buf ^= 1;
+      buf = buf + 1 == kOutBufs ? 0 : buf + 1;
     } else {
       epilogue_chunk(ep, rc, row, row_ok, n0, c0, bias.v[i]);
     }
@@ -475,7 +482,7 @@ __device__ __forceinline__ void epilogue_tile_geglu(const EpiArgs& ep, const CUt
       }
     }
     uint8_t* sbuf = stage_out + buf * kStageOutBytes;
-    if (lane == 0) tma_store_wait_read<1>();
+    if (lane == 0) tma_store_wait_read<kOutBufs - 1>();
     __syncwarp();
     uint8_t* srow = sbuf + lane * 64;
     const int sx = (lane >> 1) & 3;
@@ -489,7 +496,7 @@ __device__ __forceinline__ void epilogue_tile_geglu(const EpiArgs& ep, const CUt
       tma_store_2d(tmD, sbuf, n0 + c0, m0 + quarter * 32);
       tma_store_commit();
     }
-    buf ^= 1;
+    buf = buf + 1 == kOutBufs ? 0 : buf + 1;
   }
 }
 
@@ -605,7 +612,7 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
           [&](int tile, int& m0, int& n0) { m0 = (tile / n_tiles) * BM; n0 = (tile % n_tiles) * BN; },
           [&](int acc) { if (lane == 0) mbar_arrive(&acc_empty[acc]); });
     } else {
-      uint8_t* my_out = stage_out + ewarp * 2 * kStageOutBytes;
+      uint8_t* my_out = stage_out + ewarp * kOutBufs * kStageOutBytes;
       int buf = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
@@ -780,7 +787,7 @@ lora_gemm2_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constan
           [&](int tile, int& m0, int& n0) { m0 = (tile / n_tiles) * (2 * BM) + rank * BM; n0 = (tile % n_tiles) * BN; },
           [&](int acc) { if (lane == 0) mbar_arrive_cluster(&acc_empty[acc], 0); });
     } else {
-      uint8_t* my_out = stage_out + ewarp * 2 * kStageOutBytes;
+      uint8_t* my_out = stage_out + ewarp * kOutBufs * kStageOutBytes;
       int buf = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
@@ -1023,7 +1030,7 @@ lora_gemm2_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_co
     // ================= epilogue (warps 2..9 of both CTAs; own 128 rows) =================
     const int ewarp = warp - 2;
     const int quarter = (ewarp + 2) & 3, half = ewarp >> 2;
-    uint8_t* my_out = stage_out + ewarp * 2 * kStageOutBytes;
+    uint8_t* my_out = stage_out + ewarp * kOutBufs * kStageOutBytes;
     int buf = 0;
     int acc = 0;
     uint32_t acc_phase = 0, unit_phase = 0;
